@@ -35,6 +35,7 @@ ENUMS: Dict[str, Dict[str, int]] = {
     "PoolMethod": {"MAX": 0, "AVE": 1, "STOCHASTIC": 2},                # :775
     "NormRegion": {"ACROSS_CHANNELS": 0, "WITHIN_CHANNEL": 1},          # :742
     "EltwiseOp": {"PROD": 0, "SUM": 1, "MAX": 2},                       # :603
+    "DB": {"LEVELDB": 0, "LMDB": 1},                                    # DataParameter.DB
 }
 
 SCHEMA: Dict[str, Dict[str, Tuple[int, str, int]]] = {
@@ -110,7 +111,7 @@ SCHEMA: Dict[str, Dict[str, Tuple[int, str, int]]] = {
     },
     "DataParameter": {
         "source": (1, "string", OPT), "batch_size": (4, "uint32", OPT), "rand_skip": (7, "uint32", OPT),
-        "backend": (8, "int32", OPT), "scale": (2, "float", OPT), "mean_file": (3, "string", OPT),
+        "backend": (8, "enum:DB", OPT), "scale": (2, "float", OPT), "mean_file": (3, "string", OPT),
         "crop_size": (5, "uint32", OPT), "mirror": (6, "bool", OPT),
         "force_encoded_color": (9, "bool", OPT), "prefetch": (10, "uint32", OPT),
     },
