@@ -1,0 +1,130 @@
+/* ccaffe.h — C ABI of the B200-native libccaffe.so.
+ *
+ * The first block is the reference's own boundary, symbol for symbol: libccaffe/ccaffe.h:5-77
+ * (implemented by the reference in libccaffe/ccaffe.cpp:22-304 and bound from the JVM by
+ * src/main/java/libs/CaffeLibrary.java:8-76 through JNA).  Names, argument order and types are
+ * unchanged so Net.scala / ProtoLoader.scala keep working without modification.
+ *
+ * The second block ("extensions") is an ABI superset used by the in-box multi-GPU driver, the
+ * tests and bench.py.  Nothing in the first block depends on it.
+ *
+ * Conventions kept from the reference: opaque state handle owned by the library; blob handles are
+ * valid for the life of the state; get_data/get_diff return a host pointer that shows the current
+ * values and becomes the authoritative copy (the caller may write through it; the next device use
+ * re-uploads); errors abort the process after printing to stderr (the reference's glog CHECK).
+ * There is no CPU compute path: set_mode_cpu() is accepted and ignored.
+ */
+#ifndef SPARKNET_B200_CCAFFE_H_
+#define SPARKNET_B200_CCAFFE_H_
+
+#include <stdbool.h>
+
+#define DTYPE float
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void (*error_callback_t)(const char* msg);                                /* ccaffe.h:6 */
+/* caffe/include/caffe/data_layers.hpp:23-25; num_dims/shape exclude the batch dimension */
+typedef void (*java_callback_t)(void* data, int batch_size, int num_dims, int* shape);
+
+struct caffenet_state;                                                            /* ccaffe.h:10 */
+typedef struct caffenet_state caffenet_state;
+
+/* ---- reference ABI ------------------------------------------------------------------------ */
+void init_logging(const char* log_filename, int log_verbosity);                   /* ccaffe.h:13, ccaffe.cpp:33-37 */
+void set_basepath(const char* path);                                              /* :15, cpp:39-41 */
+int get_int_size(void);                                                           /* :17, cpp:43-45 */
+int get_dtype_size(void);                                                         /* :18, cpp:47-49 */
+
+/* LevelDB/LMDB writers: out of the hot path; exported, abort with a message */
+void create_db(caffenet_state* state, char* db_name, int name_len, char* db_type, int db_type_len);      /* :20 */
+void write_to_db(caffenet_state* state, char* image, int label, int channels, int height, int width, char* key_str); /* :21 */
+void commit_db_txn(caffenet_state* state);                                        /* :22 */
+void close_db(caffenet_state* state);                                             /* :23 */
+void save_mean_image(caffenet_state* state, float* mean_image, int channels, int height, int width,
+                     char* filename, int filename_len);                           /* :25, cpp:83-97 */
+
+caffenet_state* create_state(void);                                               /* :27, cpp:99-110 */
+void destroy_state(caffenet_state* state);                                        /* :28, cpp:112-126 */
+
+void load_solver_from_protobuf(caffenet_state* state, const char* solver_param, int solver_param_len); /* :30, cpp:128-134 */
+void load_net_from_protobuf(caffenet_state* state, const char* net_param, int net_param_len);          /* :31, cpp:136-140 */
+
+/* 0 = ok, -1 = layer_idx invalid, -2 = layer is not a JavaData layer */
+int set_train_data_callback(caffenet_state* state, int layer_idx, java_callback_t callback);           /* :35, cpp:197-212 */
+int set_test_data_callback(caffenet_state* state, int layer_idx, java_callback_t callback);            /* :36, cpp:214-216 */
+
+void forward(caffenet_state* state);                                              /* :38, cpp:218-222 */
+void backward(caffenet_state* state);                                             /* :39, cpp:224-228 */
+
+int solver_step(caffenet_state* state, int step);                                 /* :41, cpp:230-233 */
+void solver_test(caffenet_state* state, int num_steps);                           /* :42, cpp:235-238 */
+int num_test_scores(caffenet_state* state);                                       /* :44, cpp:174-177 */
+DTYPE get_test_score(caffenet_state* state, int test_score_layer_idx);            /* :45, cpp:240-243 */
+
+int num_layers(caffenet_state* state);                                            /* :47, cpp:142-144 */
+const char* layer_name(caffenet_state* state, int layer_idx);                     /* :48, cpp:146-148 */
+int num_layer_weights(caffenet_state* state, int layer_idx);                      /* :49, cpp:150-152 */
+
+int num_data_blobs(caffenet_state* state);                                        /* :51, cpp:166-168 */
+void* get_data_blob(caffenet_state* state, int blob_idx);                         /* :52, cpp:154-156 */
+const char* get_data_blob_name(caffenet_state* state, int blob_idx);              /* :53, cpp:158-160 */
+void* get_weight_blob(caffenet_state* state, int layer_idx, int weight_idx);      /* :54, cpp:162-164 */
+
+DTYPE* get_data(void* blob);                                                      /* :56, cpp:181-183 */
+DTYPE* get_diff(void* blob);                                                      /* :57, cpp:185-187 */
+int get_num_axes(void* blob);                                                     /* :59, cpp:189-191 */
+int get_axis_shape(void* blob, int axis);                                         /* :60, cpp:193-195 */
+
+void set_global_error_callback(error_callback_t c);                               /* :62, cpp:245-247 */
+
+void set_mode_cpu(void);                                                          /* :64, cpp:253-255 — accepted, ignored */
+void set_mode_gpu(void);                                                          /* :65, cpp:249-251 */
+void set_device(int gpu_id);                                                      /* :66, cpp:257-259 */
+
+void load_weights_from_file(caffenet_state* state, const char* filename);         /* :68, cpp:261-263 */
+void save_weights_to_file(caffenet_state* state, const char* filename);           /* :69, cpp:265-269 */
+void restore_solver_from_file(caffenet_state* state, const char* filename);       /* :70, cpp:271-273 */
+
+bool parse_net_prototxt(caffenet_state* state, const char* filename);             /* :72, cpp:290-292 */
+bool parse_solver_prototxt(caffenet_state* state, const char* filename);          /* :73, cpp:294-296 */
+int get_prototxt_len(caffenet_state* state);                                      /* :75, cpp:298-300 */
+char* get_prototxt_data(caffenet_state* state);                                   /* :76, cpp:302-304 */
+
+/* ---- extensions (no counterpart in libccaffe/ccaffe.h) --------------------------------------- */
+const char* sparknet_version(void);
+/* 0 = fp32 FFMA validation kernels, 1 = TF32 tcgen05/TMEM kernels.  Returns the mode in effect. */
+int sparknet_set_precision(caffenet_state* state, int mode);
+int sparknet_get_iter(caffenet_state* state);
+/* Loss of the most recent forward pass (reads one float back; synchronises the stream). */
+float sparknet_last_loss(caffenet_state* state);
+/* Copies the losses of the last n solver iterations (oldest first) kept on the device; returns count. */
+int sparknet_get_loss_history(caffenet_state* state, float* out, int n);
+/* Make Dropout layer `layer_idx` of the train net use `mask` (count values, 0 = drop, non-zero = keep)
+ * instead of drawing one; NULL restores drawing.  0 ok, -1 bad index, -2 not Dropout, -3 bad count. */
+int sparknet_inject_dropout_mask(caffenet_state* state, int layer_idx, const unsigned* mask, int count);
+/* Blocks until all queued device work of this process is done. */
+void sparknet_sync(caffenet_state* state);
+/* Learnable parameters: count, and bulk copies in (layer, blob) order, tightly packed. */
+long sparknet_num_params(caffenet_state* state);
+int sparknet_get_weights_flat(caffenet_state* state, float* out, long count);
+int sparknet_set_weights_flat(caffenet_state* state, const float* in, long count);
+/* Momentum history of learnable blob `param_idx` (testing aid). */
+int sparknet_get_history(caffenet_state* state, int param_idx, float* out, long count);
+/* int32 argmax mask of MAX-pooling layer `layer_idx` (testing aid). */
+int sparknet_get_pool_mask(caffenet_state* state, int layer_idx, int* out, long count);
+/* Pull n minibatches through the train callbacks now and keep them resident in HBM; later passes
+ * cycle through them without calling back or copying.  n = 0 restores callback mode. */
+int sparknet_set_resident_inputs(caffenet_state* state, int n);
+/* Number of kernels launched by this process so far. */
+long sparknet_kernel_launches(caffenet_state* state);
+/* out[i] = (((r0[i] + r1[i]) + ...) / n in IEEE fp32, replica order; all pointers are device pointers
+ * on the current device (single-GPU emulation of the cross-GPU exchange; the arithmetic is the same). */
+int sparknet_average_replicas_device(const void* const* replicas, int n, long count, void* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPARKNET_B200_CCAFFE_H_ */

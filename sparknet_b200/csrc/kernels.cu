@@ -1,0 +1,620 @@
+// kernels.cu — the bandwidth-bound kernels of the hot path (sm_100a).
+//
+// Each kernel replaces a group of reference kernels / cuBLAS level-1 calls
+// and is bounded by HBM bandwidth; DESIGN.md lists the algorithmic bytes per element used for the
+// roofline.  Common rules: 128-bit accesses where the layout allows, grid = multiple of the SM
+// count with grid-stride loops, warp-shuffle reductions, no atomics on floating point (fixed
+// reduction order => run-to-run deterministic), IEEE arithmetic (no -use_fast_math).
+#include <cfloat>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+
+#include "kernels.hpp"
+
+namespace sn {
+
+static constexpr int kSMs = 148;
+
+static inline int grid_for(size_t work_items, int block, int max_waves = 8) {
+  size_t b = (work_items + block - 1) / block;
+  size_t cap = (size_t)kSMs * max_waves;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------
+// fill / axpy / split_add
+// ------------------------------------------------------------------------------------------
+__global__ void fill_kernel(size_t n4, size_t n, float4* __restrict__ p4, float* __restrict__ p, float v) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const float4 v4 = make_float4(v, v, v, v);
+  for (size_t j = i; j < n4; j += stride) p4[j] = v4;
+  for (size_t j = n4 * 4 + i; j < n; j += stride) p[j] = v;
+}
+void fill(cudaStream_t s, size_t n, float* p, float v) {
+  if (!n) return;
+  const size_t n4 = (((uintptr_t)p & 15) == 0) ? n / 4 : 0;
+  fill_kernel<<<grid_for(n4 ? n4 : n, 256), 256, 0, s>>>(n4, n, (float4*)p, p, v);
+  count_launch();
+}
+__global__ void split_add_kernel(size_t n, const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ o) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    o[i] = a[i] + b[i];
+}
+void split_add(cudaStream_t s, size_t n, const float* a, const float* b, float* out) {
+  split_add_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, a, b, out);
+  count_launch();
+}
+__global__ void axpy_kernel(size_t n, float a, const float* __restrict__ x, float* __restrict__ y) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    y[i] = __fadd_rn(y[i], __fmul_rn(a, x[i]));
+}
+void axpy(cudaStream_t s, size_t n, float a, const float* x, float* y) {
+  axpy_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, a, x, y);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// ReLU — reference ReLUForward/ReLUBackward caffe/src/caffe/layers/relu_layer.cu:9-14,35-41
+// (CPU form relu_layer.cpp:16-17,32-33).  fwd 8 B/elt, bwd 12 B/elt.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float relu1(float x, float slope) { return fmaxf(x, 0.f) + slope * fminf(x, 0.f); }
+__global__ void relu_fwd_kernel(size_t n4, size_t n, const float4* __restrict__ x4, float4* __restrict__ y4,
+                                const float* __restrict__ x, float* __restrict__ y, float slope) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x, i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (size_t j = i; j < n4; j += stride) {
+    float4 v = x4[j];
+    v.x = relu1(v.x, slope); v.y = relu1(v.y, slope); v.z = relu1(v.z, slope); v.w = relu1(v.w, slope);
+    y4[j] = v;
+  }
+  for (size_t j = n4 * 4 + i; j < n; j += stride) y[j] = relu1(x[j], slope);
+}
+void relu_fwd(cudaStream_t s, size_t n, const float* x, float* y, float slope) {
+  const size_t n4 = n / 4;
+  relu_fwd_kernel<<<grid_for(n4 + 1, 256), 256, 0, s>>>(n4, n, (const float4*)x, (float4*)y, x, y, slope);
+  count_launch();
+}
+__device__ __forceinline__ float relu_g(float dy, float x, float slope) {
+  return dy * ((x > 0.f ? 1.f : 0.f) + slope * (x <= 0.f ? 1.f : 0.f));
+}
+__global__ void relu_bwd_kernel(size_t n4, size_t n, const float4* __restrict__ dy4, const float4* __restrict__ x4,
+                                float4* __restrict__ dx4, const float* __restrict__ dy, const float* __restrict__ x,
+                                float* __restrict__ dx, float slope) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x, i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  for (size_t j = i; j < n4; j += stride) {
+    const float4 g = dy4[j], v = x4[j];
+    dx4[j] = make_float4(relu_g(g.x, v.x, slope), relu_g(g.y, v.y, slope), relu_g(g.z, v.z, slope), relu_g(g.w, v.w, slope));
+  }
+  for (size_t j = n4 * 4 + i; j < n; j += stride) dx[j] = relu_g(dy[j], x[j], slope);
+}
+void relu_bwd(cudaStream_t s, size_t n, const float* dy, const float* x, float* dx, float slope) {
+  const size_t n4 = n / 4;
+  relu_bwd_kernel<<<grid_for(n4 + 1, 256), 256, 0, s>>>(n4, n, (const float4*)dy, (const float4*)x, (float4*)dx, dy, x, dx, slope);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// Dropout — reference DropoutForward/Backward caffe/src/caffe/layers/dropout_layer.cu:10-16,39-45
+// with curandGenerate replaced by in-kernel Philox4x32-10 (counter = element/4 + offset, key = seed).
+// mask = (u32 > ratio*UINT_MAX) as in dropout_layer.cu:14,27; y = x * mask * 1/(1-ratio).
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
+  const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(M0, c.x), lo0 = M0 * c.x;
+    const uint32_t hi1 = __umulhi(M1, c.z), lo1 = M1 * c.z;
+    c = make_uint4(hi1 ^ c.y ^ k.x, lo1, hi0 ^ c.w ^ k.y, lo0);
+    k.x += W0;
+    k.y += W1;
+  }
+  return c;
+}
+__global__ void dropout_fwd_kernel(size_t n, const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ mask,
+                                   uint32_t thres, float scale, bool draw, uint64_t seed, uint64_t offset) {
+  const size_t n4 = (n + 3) / 4;
+  for (size_t q = blockIdx.x * (size_t)blockDim.x + threadIdx.x; q < n4; q += (size_t)gridDim.x * blockDim.x) {
+    uint32_t r[4];
+    if (draw) {
+      const uint64_t ctr = q + offset;
+      const uint4 v = philox4x32_10(make_uint4((uint32_t)ctr, (uint32_t)(ctr >> 32), 0u, 0u),
+                                    make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)));
+      r[0] = v.x; r[1] = v.y; r[2] = v.z; r[3] = v.w;
+    }
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const size_t i = q * 4 + e;
+      if (i < n) {
+        uint8_t m;
+        if (draw) { m = r[e] > thres ? 1 : 0; mask[i] = m; } else { m = mask[i]; }
+        y[i] = x[i] * (float)m * scale;
+      }
+    }
+  }
+}
+void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* mask, float ratio, float scale, bool draw,
+                 uint64_t seed, uint64_t offset) {
+  const uint32_t thres = (uint32_t)((double)0xFFFFFFFFu * ratio);   // dropout_layer.cpp:18 uint_thres_
+  dropout_fwd_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, s>>>(n, x, y, mask, thres, scale, draw, seed, offset);
+  count_launch();
+}
+__global__ void dropout_bwd_kernel(size_t n, const float* __restrict__ dy, const uint8_t* __restrict__ mask,
+                                   float* __restrict__ dx, float scale) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    dx[i] = dy[i] * (float)mask[i] * scale;
+}
+void dropout_bwd(cudaStream_t s, size_t n, const float* dy, const uint8_t* mask, float* dx, float scale) {
+  dropout_bwd_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, dy, mask, dx, scale);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// Pooling — reference MaxPoolForward/MaxPoolBackward/AvePoolForward/AvePoolBackward
+// caffe/src/caffe/layers/pooling_layer.cu:11-47,50-80,217-260,263-296 (CPU: pooling_layer.cpp:136-292).
+// Tie rule: strict '>' scanning h then w (first maximum wins), start value -FLT_MAX, mask = h*W+w.
+// AVE divisor = window area clipped to H+pad / W+pad (counts the padding), true division.
+// ------------------------------------------------------------------------------------------
+__global__ void pool_max_fwd_kernel(PoolGeom g, size_t total, const float* __restrict__ x, float* __restrict__ y,
+                                    int* __restrict__ mask) {
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int pw = (int)(idx % g.PW), ph = (int)((idx / g.PW) % g.PH);
+    const size_t plane = idx / ((size_t)g.PW * g.PH);
+    int hs = ph * g.sh - g.ph, ws = pw * g.sw - g.pw;
+    const int he = min(hs + g.kh, g.H), we = min(ws + g.kw, g.W);
+    hs = max(hs, 0); ws = max(ws, 0);
+    const float* xp = x + plane * (size_t)(g.H * g.W);
+    float best = -FLT_MAX;
+    int bi = -1;
+    for (int h = hs; h < he; ++h)
+      for (int w = ws; w < we; ++w) {
+        const float v = __ldg(xp + h * g.W + w);
+        if (v > best) { best = v; bi = h * g.W + w; }
+      }
+    y[idx] = best;
+    mask[idx] = bi;
+  }
+}
+void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask) {
+  const size_t total = (size_t)g.N * g.C * g.PH * g.PW;
+  pool_max_fwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, x, y, mask);
+  count_launch();
+}
+// gather form: every input element sums the top diffs of the windows whose argmax it is
+__global__ void pool_max_bwd_kernel(PoolGeom g, size_t total, const float* __restrict__ dy, const int* __restrict__ mask,
+                                    float* __restrict__ dx) {
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int w = (int)(idx % g.W), h = (int)((idx / g.W) % g.H);
+    const size_t plane = idx / ((size_t)g.W * g.H);
+    const int phs = (h + g.ph < g.kh) ? 0 : (h + g.ph - g.kh) / g.sh + 1;
+    const int phe = min((h + g.ph) / g.sh + 1, g.PH);
+    const int pws = (w + g.pw < g.kw) ? 0 : (w + g.pw - g.kw) / g.sw + 1;
+    const int pwe = min((w + g.pw) / g.sw + 1, g.PW);
+    const size_t off = plane * (size_t)(g.PH * g.PW);
+    const int me = h * g.W + w;
+    float acc = 0.f;
+    for (int ph = phs; ph < phe; ++ph)
+      for (int pw = pws; pw < pwe; ++pw)
+        if (__ldg(mask + off + ph * g.PW + pw) == me) acc += __ldg(dy + off + ph * g.PW + pw);
+    dx[idx] = acc;
+  }
+}
+void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx) {
+  const size_t total = (size_t)g.N * g.C * g.H * g.W;
+  pool_max_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, mask, dx);
+  count_launch();
+}
+__global__ void pool_ave_fwd_kernel(PoolGeom g, size_t total, const float* __restrict__ x, float* __restrict__ y) {
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int pw = (int)(idx % g.PW), ph = (int)((idx / g.PW) % g.PH);
+    const size_t plane = idx / ((size_t)g.PW * g.PH);
+    int hs = ph * g.sh - g.ph, ws = pw * g.sw - g.pw;
+    int he = min(hs + g.kh, g.H + g.ph), we = min(ws + g.kw, g.W + g.pw);
+    const int pool_size = (he - hs) * (we - ws);
+    hs = max(hs, 0); ws = max(ws, 0); he = min(he, g.H); we = min(we, g.W);
+    const float* xp = x + plane * (size_t)(g.H * g.W);
+    float acc = 0.f;
+    for (int h = hs; h < he; ++h)
+      for (int w = ws; w < we; ++w) acc += __ldg(xp + h * g.W + w);
+    y[idx] = __fdiv_rn(acc, (float)pool_size);
+  }
+}
+void pool_ave_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y) {
+  const size_t total = (size_t)g.N * g.C * g.PH * g.PW;
+  pool_ave_fwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, x, y);
+  count_launch();
+}
+__global__ void pool_ave_bwd_kernel(PoolGeom g, size_t total, const float* __restrict__ dy, float* __restrict__ dx) {
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int w = (int)(idx % g.W) + g.pw, h = (int)((idx / g.W) % g.H) + g.ph;
+    const size_t plane = idx / ((size_t)g.W * g.H);
+    const int phs = (h < g.kh) ? 0 : (h - g.kh) / g.sh + 1, phe = min(h / g.sh + 1, g.PH);
+    const int pws = (w < g.kw) ? 0 : (w - g.kw) / g.sw + 1, pwe = min(w / g.sw + 1, g.PW);
+    const size_t off = plane * (size_t)(g.PH * g.PW);
+    float acc = 0.f;
+    for (int ph = phs; ph < phe; ++ph)
+      for (int pw = pws; pw < pwe; ++pw) {
+        const int hs = ph * g.sh - g.ph, ws = pw * g.sw - g.pw;
+        const int he = min(hs + g.kh, g.H + g.ph), we = min(ws + g.kw, g.W + g.pw);
+        acc += __fdiv_rn(__ldg(dy + off + ph * g.PW + pw), (float)((he - hs) * (we - ws)));
+      }
+    dx[idx] = acc;
+  }
+}
+void pool_ave_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, float* dx) {
+  const size_t total = (size_t)g.N * g.C * g.H * g.W;
+  pool_ave_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, dx);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// LRN across channels — reference LRNFillScale / LRNComputeOutput / LRNComputeDiff
+// caffe/src/caffe/layers/lrn_layer.cu:9-52,72-77,122-177 (CPU: lrn_layer.cpp:108-152,180-232).
+// One thread per (n,h,w) walks the channels with a running window; consecutive threads are
+// consecutive w, so every step is a coalesced row access.  fwd 12 B/elt (x, scale, y), bwd 20 B/elt.
+// ------------------------------------------------------------------------------------------
+__global__ void lrn_across_fwd_kernel(LrnGeom g, int nthreads, const float* __restrict__ x, float* __restrict__ y,
+                                      float* __restrict__ scale) {
+  const int HW = g.H * g.W;
+  const int pre = (g.size - 1) / 2, post = g.size - pre - 1;
+  const float aos = g.alpha / g.size;
+  const float nbeta = -g.beta;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nthreads; idx += gridDim.x * blockDim.x) {
+    const int pix = idx % HW, n = idx / HW;
+    const size_t off = (size_t)n * g.C * HW + pix;
+    const float* xi = x + off;
+    float* yi = y + off;
+    float* si = scale + off;
+    int head = 0;
+    float accum = 0.f;
+    while (head < post && head < g.C) {
+      const float v = xi[(size_t)head * HW];
+      accum += v * v;
+      ++head;
+    }
+    while (head < g.C) {
+      const float v = xi[(size_t)head * HW];
+      accum += v * v;
+      if (head - g.size >= 0) {
+        const float t = xi[(size_t)(head - g.size) * HW];
+        accum -= t * t;
+      }
+      const int c = head - post;
+      const float sc = g.k + accum * aos;
+      si[(size_t)c * HW] = sc;
+      yi[(size_t)c * HW] = xi[(size_t)c * HW] * powf(sc, nbeta);
+      ++head;
+    }
+    while (head < g.C + post) {
+      if (head - g.size >= 0) {
+        const float t = xi[(size_t)(head - g.size) * HW];
+        accum -= t * t;
+      }
+      const int c = head - post;
+      if (c >= 0 && c < g.C) {
+        const float sc = g.k + accum * aos;
+        si[(size_t)c * HW] = sc;
+        yi[(size_t)c * HW] = xi[(size_t)c * HW] * powf(sc, nbeta);
+      }
+      ++head;
+    }
+  }
+}
+void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, float* scale) {
+  const int nthreads = g.N * g.H * g.W;
+  lrn_across_fwd_kernel<<<grid_for(nthreads, 128, 16), 128, 0, s>>>(g, nthreads, x, y, scale);
+  count_launch();
+}
+__global__ void lrn_across_bwd_kernel(LrnGeom g, int nthreads, const float* __restrict__ x, const float* __restrict__ y,
+                                      const float* __restrict__ scale, const float* __restrict__ dy,
+                                      float* __restrict__ dx) {
+  const int HW = g.H * g.W;
+  const int pre = g.size - (g.size + 1) / 2, post = g.size - pre - 1;
+  const float cache_ratio = 2.f * g.alpha * g.beta / g.size;
+  const float nbeta = -g.beta;
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nthreads; idx += gridDim.x * blockDim.x) {
+    const int pix = idx % HW, n = idx / HW;
+    const size_t off = (size_t)n * g.C * HW + pix;
+    const float *xi = x + off, *yi = y + off, *si = scale + off, *gi = dy + off;
+    float* di = dx + off;
+    int head = 0;
+    float accum = 0.f;
+    while (head < post && head < g.C) {
+      accum += gi[(size_t)head * HW] * yi[(size_t)head * HW] / si[(size_t)head * HW];
+      ++head;
+    }
+    while (head < g.C + post) {
+      if (head < g.C) accum += gi[(size_t)head * HW] * yi[(size_t)head * HW] / si[(size_t)head * HW];
+      if (head - g.size >= 0)
+        accum -= gi[(size_t)(head - g.size) * HW] * yi[(size_t)(head - g.size) * HW] / si[(size_t)(head - g.size) * HW];
+      const int c = head - post;
+      if (c >= 0 && c < g.C)
+        di[(size_t)c * HW] = gi[(size_t)c * HW] * powf(si[(size_t)c * HW], nbeta) - cache_ratio * xi[(size_t)c * HW] * accum;
+      ++head;
+    }
+  }
+}
+void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* y, const float* scale,
+                    const float* dy, float* dx) {
+  const int nthreads = g.N * g.H * g.W;
+  lrn_across_bwd_kernel<<<grid_for(nthreads, 128, 16), 128, 0, s>>>(g, nthreads, x, y, scale, dy, dx);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// LRN within channel — the reference composes Split + Power(x^2) + AVE pool (k=size, pad=(size-1)/2,
+// stride 1) + Power((1+alpha*x)^-beta) + Eltwise PROD (caffe/src/caffe/layers/lrn_layer.cpp:17-65,
+// 155-162,235-247; power_layer.cpp:20-93; eltwise_layer.cpp:53-58,111-123; split_layer.cpp:26-49):
+// ~12 launches and 4 scratch blobs.  Here: one fused stencil kernel each way, one CTA per (n,c)
+// plane staged in shared memory.  fwd 8 B/elt, bwd 12 B/elt, no intermediates kept.
+// ------------------------------------------------------------------------------------------
+constexpr int kLrnWithinMaxPlane = 1024;
+__global__ void lrn_within_fwd_kernel(LrnGeom g, const float* __restrict__ x, float* __restrict__ y) {
+  __shared__ float xs[kLrnWithinMaxPlane];
+  const int HW = g.H * g.W, pre = (g.size - 1) / 2;
+  const size_t off = (size_t)blockIdx.x * HW;
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) xs[i] = x[off + i];
+  __syncthreads();
+  const float area = (float)(g.size * g.size);    // clipped-to-(H+pad) area is size^2 everywhere for stride 1
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+    const int h = i / g.W, w = i % g.W;
+    const int hs = max(h - pre, 0), he = min(h - pre + g.size, g.H), ws = max(w - pre, 0), we = min(w - pre + g.size, g.W);
+    float acc = 0.f;
+    for (int a = hs; a < he; ++a)
+      for (int b = ws; b < we; ++b) { const float v = xs[a * g.W + b]; acc += powf(v, 2.f); }
+    const float avg = __fdiv_rn(acc, area);
+    y[off + i] = xs[i] * powf(__fadd_rn(__fmul_rn(avg, g.alpha), 1.f), -g.beta);
+  }
+}
+void lrn_within_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y) {
+  if (g.H * g.W > kLrnWithinMaxPlane) fatal("lrn_within: plane %dx%d exceeds the %d-element shared-memory tile", g.H, g.W, kLrnWithinMaxPlane);
+  const int threads = g.H * g.W >= 256 ? 256 : (g.H * g.W >= 128 ? 128 : 64);
+  lrn_within_fwd_kernel<<<g.N * g.C, threads, 0, s>>>(g, x, y);
+  count_launch();
+}
+__global__ void lrn_within_bwd_kernel(LrnGeom g, const float* __restrict__ x, const float* __restrict__ dy,
+                                      float* __restrict__ dx) {
+  __shared__ float xs[kLrnWithinMaxPlane], ps[kLrnWithinMaxPlane], qs[kLrnWithinMaxPlane];
+  const int HW = g.H * g.W, pre = (g.size - 1) / 2;
+  const size_t off = (size_t)blockIdx.x * HW;
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) xs[i] = x[off + i];
+  __syncthreads();
+  const float area = (float)(g.size * g.size);
+  const float diff_scale = (-g.beta) * g.alpha;
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+    const int h = i / g.W, w = i % g.W;
+    const int hs = max(h - pre, 0), he = min(h - pre + g.size, g.H), ws = max(w - pre, 0), we = min(w - pre + g.size, g.W);
+    float acc = 0.f;
+    for (int a = hs; a < he; ++a)
+      for (int b = ws; b < we; ++b) { const float v = xs[a * g.W + b]; acc += powf(v, 2.f); }
+    const float base = __fadd_rn(__fmul_rn(__fdiv_rn(acc, area), g.alpha), 1.f);
+    const float p = powf(base, -g.beta);
+    const float gy = dy[off + i];
+    ps[i] = p * gy;                                            // d(product input) = power_out * dy
+    qs[i] = (xs[i] * gy) * (__fdiv_rn(p, base) * diff_scale);  // d(pool out) = (x*dy) * diff_scale * y_pow / base
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < HW; i += blockDim.x) {
+    const int h = i / g.W, w = i % g.W;
+    // windows j=(a,b) that contain pixel i: a in [h+pre-size+1, h+pre] intersect [0,H)
+    const int as = max(h + pre - g.size + 1, 0), ae = min(h + pre + 1, g.H);
+    const int bs = max(w + pre - g.size + 1, 0), be = min(w + pre + 1, g.W);
+    float acc = 0.f;
+    for (int a = as; a < ae; ++a)
+      for (int b = bs; b < be; ++b) acc += __fdiv_rn(qs[a * g.W + b], area);
+    dx[off + i] = __fadd_rn(ps[i], __fmul_rn(acc, __fmul_rn(2.f, xs[i])));
+  }
+}
+void lrn_within_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx) {
+  if (g.H * g.W > kLrnWithinMaxPlane) fatal("lrn_within: plane %dx%d exceeds the %d-element shared-memory tile", g.H, g.W, kLrnWithinMaxPlane);
+  const int threads = g.H * g.W >= 256 ? 256 : (g.H * g.W >= 128 ? 128 : 64);
+  lrn_within_bwd_kernel<<<g.N * g.C, threads, 0, s>>>(g, x, dy, dx);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// SoftmaxWithLoss — reference: kernel_channel_max/subtract/exp/sum/div + SoftmaxLossForwardGPU +
+// 2x cublasSasum (+ cublasSdot in Layer::Forward) = ~7 launches and 3 host syncs per iteration
+// (caffe/src/caffe/layers/softmax_layer.cu:13-120, softmax_loss_layer.cu:11-120, layer.hpp:468-480).
+// Here: one warp per row with shuffle reductions, the loss reduced on the device in a fixed order,
+// nothing read back unless the host asks for the loss blob.
+// ------------------------------------------------------------------------------------------
+__global__ void softmax_rows_kernel(int rows, int classes, const float* __restrict__ x, const float* __restrict__ label,
+                                    float* __restrict__ prob, float* __restrict__ row_loss) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float* xr = x + (size_t)warp * classes;
+  float* pr = prob + (size_t)warp * classes;
+  float m = -FLT_MAX;
+  for (int c = lane; c < classes; c += 32) m = fmaxf(m, xr[c]);
+  m = warp_max(m);
+  float sum = 0.f;
+  for (int c = lane; c < classes; c += 32) {
+    const float e = expf(xr[c] - m);
+    pr[c] = e;
+    sum += e;
+  }
+  sum = warp_sum(sum);
+  for (int c = lane; c < classes; c += 32) pr[c] = __fdiv_rn(pr[c], sum);
+  __syncwarp();
+  if (lane == 0) {
+    const int lv = (int)label[warp];
+    const float p = (lv >= 0 && lv < classes) ? pr[lv] : 1.f;
+    row_loss[warp] = -logf(fmaxf(p, FLT_MIN));
+  }
+}
+// out[0] = (sum_i v[i]) / denom with a fixed-shape tree (deterministic)
+__global__ void reduce_rows_kernel(int n, const float* __restrict__ v, float denom, float* __restrict__ out,
+                                   float* __restrict__ out2) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) acc += v[i];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) {
+      const float r = __fdiv_rn(t, denom);
+      out[0] = r;
+      if (out2) out2[0] = r;
+    }
+  }
+}
+void softmax_loss_fwd(cudaStream_t s, int rows, int classes, const float* x, const float* label, float* prob,
+                      float* loss_out, float* row_scratch, float* loss_log) {
+  const int wpb = 4;
+  softmax_rows_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, s>>>(rows, classes, x, label, prob, row_scratch);
+  reduce_rows_kernel<<<1, 256, 0, s>>>(rows, row_scratch, (float)rows, loss_out, loss_log);
+  count_launch(2);
+}
+__global__ void softmax_loss_bwd_kernel(int rows, int classes, const float* __restrict__ prob, const float* __restrict__ label,
+                                        const float* __restrict__ lw, float* __restrict__ dx) {
+  const float scale = __fdiv_rn(lw[0], (float)rows);     // loss_weight / count   (softmax_loss_layer.cpp:110-116)
+  const size_t total = (size_t)rows * classes;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(i / classes), c = (int)(i % classes);
+    float v = prob[i];
+    if (c == (int)label[r]) v -= 1.f;
+    dx[i] = v * scale;
+  }
+}
+void softmax_loss_bwd(cudaStream_t s, int rows, int classes, const float* prob, const float* label,
+                      const float* loss_weight_dev, float* dx) {
+  softmax_loss_bwd_kernel<<<grid_for((size_t)rows * classes, 256), 256, 0, s>>>(rows, classes, prob, label, loss_weight_dev, dx);
+  count_launch();
+}
+// Accuracy top-1 (caffe/src/caffe/layers/accuracy_layer.cpp:48-103): the reference sorts
+// (value, index) pairs with std::greater, i.e. among equal values the larger index ranks first.
+__global__ void accuracy_rows_kernel(int rows, int classes, const float* __restrict__ x, const float* __restrict__ label,
+                                     float* __restrict__ hit) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= rows) return;
+  const float* xr = x + (size_t)warp * classes;
+  float bv = -FLT_MAX;
+  int bi = -1;
+  for (int c = lane; c < classes; c += 32) {
+    const float v = xr[c];
+    if (v > bv || (v == bv && c > bi)) { bv = v; bi = c; }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+    const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+    if (ov > bv || (ov == bv && oi > bi)) { bv = ov; bi = oi; }
+  }
+  if (lane == 0) hit[warp] = (bi == (int)label[warp]) ? 1.f : 0.f;
+}
+void accuracy_top1(cudaStream_t s, int rows, int classes, const float* x, const float* label, float* acc_out,
+                   float* row_scratch) {
+  const int wpb = 4;
+  accuracy_rows_kernel<<<(rows + wpb - 1) / wpb, wpb * 32, 0, s>>>(rows, classes, x, label, row_scratch);
+  reduce_rows_kernel<<<1, 256, 0, s>>>(rows, row_scratch, (float)rows, acc_out, nullptr);
+  count_launch(2);
+}
+
+// ------------------------------------------------------------------------------------------
+// bias gradients
+// ------------------------------------------------------------------------------------------
+// one CTA per channel: db[c] (+)= sum_n sum_pix dy[n][c][pix]
+__global__ void conv_bias_grad_kernel(int N, int C, int HW, const float* __restrict__ dy, float* __restrict__ db, int accumulate) {
+  __shared__ float sh[32];
+  const int c = blockIdx.x;
+  float acc = 0.f;
+  for (int n = 0; n < N; ++n) {
+    const float* p = dy + ((size_t)n * C + c) * HW;
+    for (int i = threadIdx.x; i < HW; i += blockDim.x) acc += p[i];
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) db[c] = accumulate ? db[c] + t : t;
+  }
+}
+void conv_bias_grad(cudaStream_t s, int N, int C, int HW, const float* dy, float* db, bool accumulate) {
+  conv_bias_grad_kernel<<<C, 256, 0, s>>>(N, C, HW, dy, db, accumulate ? 1 : 0);
+  count_launch();
+}
+__global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict__ dy, float* __restrict__ db, int accumulate) {
+  const int j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= cols) return;
+  float acc = 0.f;
+  for (int i = 0; i < rows; ++i) acc += dy[(size_t)i * cols + j];
+  db[j] = accumulate ? db[j] + acc : acc;
+}
+void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db, bool accumulate) {
+  ip_bias_grad_kernel<<<(cols + 127) / 128, 128, 0, s>>>(rows, cols, dy, db, accumulate ? 1 : 0);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// Fused SGD update — reference: per learnable blob cublasSaxpy (L2) + cublasSscal + cublasSaxpy
+// (axpby) + cudaMemcpy (history -> diff) + cublasSaxpy (w -= diff): 6 passes, ~96 launches/iter for
+// CaffeNet (caffe/src/caffe/solvers/sgd_solver.cpp:145-239, caffe/src/caffe/blob.cpp:154-177,
+// caffe/src/caffe/util/math_functions.cu:94-98).  Here: one launch over the whole parameter arena,
+// 3 reads + 3 writes per parameter (24 B), rounding order of the CPU path kept:
+//   g <- g + decay*w ; h <- (mu*h) + (rate*g) ; g <- h ; w <- w - h     (mul and add rounded separately)
+// Blobs start on 1024-element boundaries in the arena, so chunk_table[i/1024] gives the blob's
+// (lr_mult, local_decay); local_rate = rate * lr_mult is formed in fp32 as in the reference.
+// ------------------------------------------------------------------------------------------
+__global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ h,
+                                  const SgdChunk* __restrict__ table, float rate, float mu) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    const SgdChunk ck = table[i >> 8];           // 1024 floats = 256 float4
+    const float local_rate = __fmul_rn(rate, ck.lr_mult);   // sgd_solver.cpp:210-211
+    float4 wv = w[i], gv = g[i], hv = h[i];
+#define SN_SGD1(F)                                                        \
+    {                                                                     \
+      float gg = gv.F;                                                    \
+      if (ck.decay != 0.f) gg = __fadd_rn(gg, __fmul_rn(ck.decay, wv.F)); \
+      const float hh = __fadd_rn(__fmul_rn(mu, hv.F), __fmul_rn(local_rate, gg)); \
+      hv.F = hh; gv.F = hh; wv.F = __fsub_rn(wv.F, hh);                   \
+    }
+    SN_SGD1(x) SN_SGD1(y) SN_SGD1(z) SN_SGD1(w)
+#undef SN_SGD1
+    w[i] = wv; g[i] = gv; h[i] = hv;
+  }
+}
+void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, const SgdChunk* chunk_table, float rate,
+                float momentum) {
+  if (n % 1024) fatal("sgd_update: arena length %zu is not a multiple of 1024", n);
+  sgd_update_kernel<<<grid_for(n / 4, 256), 256, 0, s>>>(n / 4, (float4*)w, (float4*)g, (float4*)h, chunk_table, rate, momentum);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
+// Weight averaging over N replicas resident on this device (used for the emulated multi-rank test
+// and as the reduce stage of the multi-GPU exchange): sequential fp32 sum in replica order, then
+// one IEEE division by (float)N.
+// ------------------------------------------------------------------------------------------
+__global__ void average_replicas_kernel(const float* const* __restrict__ reps, int nrep, size_t n, float* __restrict__ out) {
+  const float denom = (float)nrep;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    float acc = reps[0][i];
+    for (int r = 1; r < nrep; ++r) acc = __fadd_rn(acc, reps[r][i]);
+    out[i] = __fdiv_rn(acc, denom);
+  }
+}
+void average_replicas(cudaStream_t s, const float* const* replicas_dev, int nrep, size_t n, float* out) {
+  average_replicas_kernel<<<grid_for(n, 256), 256, 0, s>>>(replicas_dev, nrep, n, out);
+  count_launch();
+}
+
+}  // namespace sn

@@ -1,0 +1,92 @@
+// kernels.hpp — host-callable launchers of every device kernel on the hot path.
+// All launch on the given stream, never synchronise, never allocate (scratch comes from
+// get_workspace, owned by the runtime).  Reference anchors are given per kernel in kernels.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+#include "gemm_ops.cuh"
+
+namespace sn {
+
+// ---- runtime services implemented in runtime.cpp -------------------------------------------------
+void fatal(const char* fmt, ...) __attribute__((noreturn, format(printf, 1, 2)));
+float* get_workspace(size_t nfloats);           // per-device scratch, grown on demand (never shrinks)
+void count_launch(int n = 1);                   // bookkeeping for bench.py's gpu_launches
+#define SN_CUDA(expr)                                                                        \
+  do {                                                                                       \
+    cudaError_t e_ = (expr);                                                                 \
+    if (e_ != cudaSuccess) sn::fatal("CUDA error %s at %s:%d: %s", cudaGetErrorName(e_), __FILE__, __LINE__, \
+                                     cudaGetErrorString(e_));                                \
+  } while (0)
+
+// ---- FFMA validation contractions (gemm_ffma.cu) ---------------------------------------------
+void ffma_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float* w, const float* bias, float* y, bool relu);
+void ffma_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx);
+void ffma_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate);
+void ffma_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w, const float* bias, float* y, bool relu);
+void ffma_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w, float* dx);
+void ffma_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);
+int splitk_slices(int tiles, int R);
+
+// ---- TF32 tcgen05 contractions (gemm_tc.cu) --------------------------------------------------
+bool tc_available();                           // false until the tcgen05 path is compiled in
+void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float* w, const float* bias, float* y, bool relu);
+void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx);
+void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate);
+void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w, const float* bias, float* y, bool relu);
+void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w, float* dx);
+void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);
+
+// ---- bandwidth-bound kernels (kernels.cu) ----------------------------------------------------
+struct PoolGeom { int N, C, H, W, kh, kw, sh, sw, ph, pw, PH, PW; };
+void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask);
+void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx);
+void pool_ave_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y);
+void pool_ave_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, float* dx);
+
+void relu_fwd(cudaStream_t s, size_t n, const float* x, float* y, float slope);
+void relu_bwd(cudaStream_t s, size_t n, const float* dy, const float* x_or_y, float* dx, float slope);
+
+// mask: one byte per element (1 = keep).  If `draw` the kernel draws it (Philox4x32-10 keyed by
+// seed/offset); otherwise it uses the mask as given (injected by tests).
+void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* mask, float ratio, float scale,
+                 bool draw, uint64_t seed, uint64_t offset);
+void dropout_bwd(cudaStream_t s, size_t n, const float* dy, const uint8_t* mask, float* dx, float scale);
+
+struct LrnGeom { int N, C, H, W, size; float alpha, beta, k; };
+void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, float* scale);
+void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* y, const float* scale,
+                    const float* dy, float* dx);
+void lrn_within_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y);
+void lrn_within_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx);
+
+// prob[rows][classes]; loss_out[0] = -(1/rows) sum log max(p[label], FLT_MIN)   (normalize = true)
+// loss_log (nullable): second destination for the scalar (per-iteration loss history kept on the device)
+void softmax_loss_fwd(cudaStream_t s, int rows, int classes, const float* x, const float* label, float* prob,
+                      float* loss_out, float* row_scratch, float* loss_log);
+void softmax_loss_bwd(cudaStream_t s, int rows, int classes, const float* prob, const float* label,
+                      const float* loss_weight_dev, float* dx);
+void accuracy_top1(cudaStream_t s, int rows, int classes, const float* x, const float* label, float* acc_out,
+                   float* row_scratch);
+
+// bias gradients: db[c] (+)= sum over (n, pix) dY[n][c][pix]   (base_conv_layer.cpp:303-307)
+void conv_bias_grad(cudaStream_t s, int N, int C, int HW, const float* dy, float* db, bool accumulate);
+// db[j] (+)= sum_i dY[i][j]                                   (inner_product_layer.cpp:104-109)
+void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db, bool accumulate);
+
+// fused SGD step over the whole parameter arena (sgd_solver.cpp:145-239 + blob.cpp:154-162):
+//   g += decay*w ; h = momentum*h + rate*g ; g = h ; w -= h       per 1024-element chunk table
+struct SgdChunk { float lr_mult, decay; };     // per-chunk lr_mult and local_decay (= weight_decay * decay_mult)
+void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, const SgdChunk* chunk_table, float rate,
+                float momentum);
+
+void fill(cudaStream_t s, size_t n, float* p, float v);
+void split_add(cudaStream_t s, size_t n, const float* a, const float* b, float* out);
+void axpy(cudaStream_t s, size_t n, float a, const float* x, float* y);
+
+// averaging: out[i] = (((r0[i] + r1[i]) + r2[i]) + ...) / (float)nrep, IEEE fp32, rank order
+// (src/main/java/libs/JavaNDArray.java:84-117, src/main/scala/apps/CifarApp.scala:133-134)
+void average_replicas(cudaStream_t s, const float* const* replicas_dev, int nrep, size_t n, float* out);
+
+}  // namespace sn

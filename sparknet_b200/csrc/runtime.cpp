@@ -1,0 +1,997 @@
+// runtime.cpp — see runtime.hpp.  Host logic only; all arithmetic is in the CUDA kernels.
+#include "runtime.hpp"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <random>
+#include <sstream>
+
+namespace sn {
+
+error_callback_t g_error_callback = nullptr;
+
+void fatal(const char* fmt, ...) {
+  char buf[2048];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  fprintf(stderr, "libccaffe(b200): FATAL: %s\n", buf);
+  fflush(stderr);
+  if (g_error_callback) g_error_callback(buf);
+  abort();   // reference behaviour: glog CHECK / LOG(FATAL) aborts the process (SURVEY §8b "Errors")
+}
+
+#define SN_CHECK(cond, ...)            \
+  do {                                 \
+    if (!(cond)) sn::fatal(__VA_ARGS__); \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------
+// Context
+// ------------------------------------------------------------------------------------------
+Context& raw_ctx() {
+  static Context c;
+  return c;
+}
+Context& ctx() {
+  Context& c = raw_ctx();
+  if (!c.initialised) c.init();
+  return c;
+}
+void Context::init() {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    fatal("no CUDA device available (%s). This library has no CPU path.", cudaGetErrorString(e));
+  SN_CUDA(cudaSetDevice(device));
+  SN_CUDA(cudaStreamCreateWithFlags(&compute, cudaStreamNonBlocking));
+  SN_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
+  initialised = true;
+}
+float* get_workspace(size_t nfloats) {
+  Context& c = ctx();
+  if (nfloats > c.workspace_floats) {
+    SN_CUDA(cudaStreamSynchronize(c.compute));
+    if (c.workspace) SN_CUDA(cudaFree(c.workspace));
+    size_t want = std::max(nfloats, c.workspace_floats * 2);
+    SN_CUDA(cudaMalloc(&c.workspace, want * sizeof(float)));
+    c.workspace_floats = want;
+  }
+  return c.workspace;
+}
+void count_launch(int n) { ctx().launches += n; }
+
+// ------------------------------------------------------------------------------------------
+// Storage / Blob
+// ------------------------------------------------------------------------------------------
+Storage::~Storage() {
+  if (dev && owns_dev) cudaFree(dev);
+  if (host) cudaFreeHost(host);
+}
+void Storage::ensure_dev() {
+  if (!dev) {
+    SN_CUDA(cudaMalloc(&dev, std::max<size_t>(count, 1) * sizeof(float)));
+    owns_dev = true;
+  }
+}
+void Storage::ensure_host() {
+  if (!host) SN_CUDA(cudaMallocHost(&host, std::max<size_t>(count, 1) * sizeof(float)));
+}
+const float* Storage::gpu() {
+  Context& c = ctx();
+  switch (head) {
+    case UNINIT:
+      ensure_dev();
+      SN_CUDA(cudaMemsetAsync(dev, 0, count * sizeof(float), c.compute));
+      head = AT_DEVICE;
+      break;
+    case AT_HOST:
+      ensure_dev();
+      SN_CUDA(cudaMemcpyAsync(dev, host, count * sizeof(float), cudaMemcpyHostToDevice, c.compute));
+      head = SYNCED;
+      break;
+    default: break;
+  }
+  return dev;
+}
+float* Storage::mutable_gpu() {
+  gpu();
+  head = AT_DEVICE;
+  return dev;
+}
+float* Storage::mutable_cpu() {
+  Context& c = ctx();
+  ensure_host();
+  switch (head) {
+    case UNINIT:
+      memset(host, 0, count * sizeof(float));
+      break;
+    case AT_DEVICE:
+      SN_CUDA(cudaMemcpyAsync(host, dev, count * sizeof(float), cudaMemcpyDeviceToHost, c.compute));
+      SN_CUDA(cudaStreamSynchronize(c.compute));
+      break;
+    case SYNCED:
+      // a previous upload from this host buffer may still be in flight; the caller may write next
+      SN_CUDA(cudaStreamSynchronize(c.compute));
+      break;
+    default: break;
+  }
+  head = AT_HOST;
+  return host;
+}
+void Blob::reshape(const std::vector<int>& s) {
+  shape = s;
+  const size_t c = count();
+  if (!data || data->count != c) {
+    data = std::make_shared<Storage>(c);
+    diff = std::make_shared<Storage>(c);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// Fillers (caffe/include/caffe/filler.hpp:31-46,48-63,65-95,144-166) — host side, one-time.
+// The RNG stream differs from boost's (unpinned in the reference); tests copy weights instead.
+// ------------------------------------------------------------------------------------------
+static std::mt19937& host_rng() {
+  static std::mt19937 g(std::random_device{}());
+  return g;
+}
+static void fill_blob(const cp::FillerParameter& f, Blob* b) {
+  const size_t n = b->count();
+  SN_CHECK(n > 0, "filler: empty blob");
+  float* d = b->data->mutable_cpu();
+  if (f.type == "constant") {
+    for (size_t i = 0; i < n; ++i) d[i] = f.value;
+  } else if (f.type == "gaussian") {
+    SN_CHECK(f.sparse == -1, "sparse gaussian filler is not on the supported path");
+    std::normal_distribution<float> dist(f.mean, f.std);
+    for (size_t i = 0; i < n; ++i) d[i] = dist(host_rng());
+  } else if (f.type == "xavier") {
+    const int fan_in = (int)(n / (size_t)b->num()), fan_out = (int)(n / (size_t)b->channels());
+    float nn = (float)fan_in;
+    if (f.variance_norm == 2) nn = (fan_in + fan_out) / 2.f;
+    else if (f.variance_norm == 1) nn = (float)fan_out;
+    const float scale = std::sqrt(3.f / nn);
+    std::uniform_real_distribution<float> dist(-scale, scale);
+    for (size_t i = 0; i < n; ++i) d[i] = dist(host_rng());
+  } else if (f.type == "uniform") {
+    std::uniform_real_distribution<float> dist(f.min, f.max);
+    for (size_t i = 0; i < n; ++i) d[i] = dist(host_rng());
+  } else {
+    fatal("filler type '%s' is not on the supported path", f.type.c_str());
+  }
+}
+
+void Layer::set_loss_weights(const std::vector<Blob*>& top) {   // layer.hpp:405-427
+  loss.assign(top.size(), 0.f);
+  for (size_t i = 0; i < lp.loss_weight.size() && i < top.size(); ++i) {
+    const float w = lp.loss_weight[i];
+    if (w == 0.f) continue;
+    loss[i] = w;
+    float* d = top[i]->diff->mutable_cpu();
+    for (size_t k = 0; k < top[i]->count(); ++k) d[k] = w;
+  }
+}
+
+using std::string;
+using std::vector;
+static cudaStream_t S() { return ctx().compute; }
+
+// ------------------------------------------------------------------------------------------
+// JavaDataLayer — reference caffe/src/caffe/layers/java_data_layer.cpp:10-44: callback into a
+// malloc'ed buffer, then a blocking pageable H2D on the next gpu_data() (syncedmem.cpp:61-69).
+// Here: the callback fills PINNED memory, the upload runs on a side stream into one of two
+// device buffers, and the compute stream only waits on an event; the upload of iteration i+1
+// overlaps the compute of iteration i.  Callback order and count are exactly the reference's
+// (one call per JavaData layer per forward pass, data before label).
+// ------------------------------------------------------------------------------------------
+struct JavaDataLayer : Layer {
+  java_callback_t cb = nullptr;
+  vector<int> shape, java_shape;
+  size_t count = 0;
+  float* pinned[2] = {nullptr, nullptr};
+  float* devbuf[2] = {nullptr, nullptr};
+  cudaEvent_t h2d_done[2], consumed[2];
+  bool consumed_valid[2] = {false, false};
+  int parity = 0;
+  // resident mode (sparknet_set_resident_inputs): a pool of minibatches already in HBM
+  float* pool = nullptr;
+  int pool_n = 0, pool_i = 0;
+  using Layer::Layer;
+  ~JavaDataLayer() override {
+    for (int i = 0; i < 2; ++i) {
+      if (pinned[i]) cudaFreeHost(pinned[i]);
+      if (devbuf[i]) cudaFree(devbuf[i]);
+      if (count) { cudaEventDestroy(h2d_done[i]); cudaEventDestroy(consumed[i]); }
+    }
+    if (pool) cudaFree(pool);
+  }
+  const char* type() const override { return "JavaData"; }
+  void setup(const vector<Blob*>&, const vector<Blob*>& top) override {
+    SN_CHECK(lp.has_java_data_param, "JavaData layer %s needs java_data_param", lp.name.c_str());
+    for (int64_t d : lp.java_data_shape.dim) shape.push_back((int)d);
+    SN_CHECK(!shape.empty(), "JavaData shape needs a batch dimension");
+    java_shape.assign(shape.begin() + 1, shape.end());
+    top[0]->reshape(shape);
+    count = top[0]->count();
+    SN_CHECK(count > 0, "batch_size, channels, height, and width must be specified and positive in java_data_param");
+    for (int i = 0; i < 2; ++i) {
+      SN_CUDA(cudaMallocHost(&pinned[i], count * sizeof(float)));
+      memset(pinned[i], 0, count * sizeof(float));
+      SN_CUDA(cudaMalloc(&devbuf[i], count * sizeof(float)));
+      SN_CUDA(cudaEventCreateWithFlags(&h2d_done[i], cudaEventDisableTiming));
+      SN_CUDA(cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming));
+    }
+    // the top blob's device pointer is swapped between devbuf[0/1] (or pool slots)
+    top[0]->data = std::make_shared<Storage>(count, devbuf[0]);
+    SN_CUDA(cudaMemset(devbuf[0], 0, count * sizeof(float)));
+    top[0]->data->head = Storage::AT_DEVICE;
+  }
+  void forward(const vector<Blob*>&, const vector<Blob*>& top) override {
+    Context& c = ctx();
+    Storage* st = top[0]->data.get();
+    if (pool) {                                   // resident inputs: no callback, no copy
+      st->dev = pool + (size_t)(pool_i % pool_n) * count;
+      st->head = Storage::AT_DEVICE;
+      ++pool_i;
+      return;
+    }
+    SN_CHECK(cb, "JavaDataLayer needs to be initalized by calling SetCallback");
+    const int p = parity, q = parity ^ 1;
+    // everything enqueued so far on the compute stream is the last reader of buffer q
+    SN_CUDA(cudaEventRecord(consumed[q], c.compute));
+    consumed_valid[q] = true;
+    SN_CUDA(cudaEventSynchronize(h2d_done[p]));   // pinned[p] free again (no-op the first time)
+    cb((void*)pinned[p], shape[0], (int)shape.size() - 1, java_shape.data());
+    if (consumed_valid[p]) SN_CUDA(cudaStreamWaitEvent(c.copy, consumed[p], 0));
+    SN_CUDA(cudaMemcpyAsync(devbuf[p], pinned[p], count * sizeof(float), cudaMemcpyHostToDevice, c.copy));
+    SN_CUDA(cudaEventRecord(h2d_done[p], c.copy));
+    SN_CUDA(cudaStreamWaitEvent(c.compute, h2d_done[p], 0));
+    st->dev = devbuf[p];
+    st->head = Storage::AT_DEVICE;
+    parity = q;
+  }
+  void backward(const vector<Blob*>&, const vector<bool>&, const vector<Blob*>&) override {}
+  // Pull `n` minibatches through the callback now and keep them in HBM.
+  void make_resident(int n) {
+    if (pool) { cudaFree(pool); pool = nullptr; }
+    pool_n = n; pool_i = 0;
+    if (n <= 0) return;
+    SN_CHECK(cb, "set the data callback before sparknet_set_resident_inputs");
+    SN_CUDA(cudaMalloc(&pool, (size_t)n * count * sizeof(float)));
+  }
+  void fill_resident_slot(int i) {
+    cb((void*)pinned[0], shape[0], (int)shape.size() - 1, java_shape.data());
+    SN_CUDA(cudaMemcpy(pool + (size_t)i * count, pinned[0], count * sizeof(float), cudaMemcpyHostToDevice));
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// Convolution — reference conv_layer.{cpp:8-71,cu:7-56} + base_conv_layer.cpp:12-376 (N x im2col +
+// group x sgemm + bias gemm forward; gemv + im2col + 2 sgemm + col2im backward).  Here: one
+// implicit GEMM per group and direction, bias (+ in-place ReLU) in the epilogue.
+// ------------------------------------------------------------------------------------------
+struct ConvolutionLayer : Layer {
+  ConvGeom g;
+  bool bias_term = true, fuse_relu = false;
+  using Layer::Layer;
+  const char* type() const override { return "Convolution"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const cp::ConvolutionParameter& c = lp.convolution_param;
+    SN_CHECK(bottom[0]->shape.size() == 4, "Convolution %s: input must be 4-D (N,C,H,W)", lp.name.c_str());
+    SN_CHECK(c.axis == 1, "Convolution %s: only channel axis 1 is supported", lp.name.c_str());
+    if (c.has_kernel_h || c.has_kernel_w) {
+      SN_CHECK(c.kernel_size.empty(), "Either kernel_size or kernel_h/w should be specified; not both.");
+      g.kh = (int)c.kernel_h; g.kw = (int)c.kernel_w;
+    } else {
+      SN_CHECK(!c.kernel_size.empty(), "Convolution %s: kernel_size must be specified", lp.name.c_str());
+      g.kh = (int)c.kernel_size[0];
+      g.kw = (int)(c.kernel_size.size() > 1 ? c.kernel_size[1] : c.kernel_size[0]);
+    }
+    SN_CHECK(g.kh > 0 && g.kw > 0, "Filter dimensions must be nonzero.");
+    if (c.has_stride_h || c.has_stride_w) { g.sh = (int)c.stride_h; g.sw = (int)c.stride_w; }
+    else if (c.stride.empty()) { g.sh = g.sw = 1; }
+    else { g.sh = (int)c.stride[0]; g.sw = (int)(c.stride.size() > 1 ? c.stride[1] : c.stride[0]); }
+    if (c.has_pad_h || c.has_pad_w) { g.ph = (int)c.pad_h; g.pw = (int)c.pad_w; }
+    else if (c.pad.empty()) { g.ph = g.pw = 0; }
+    else { g.ph = (int)c.pad[0]; g.pw = (int)(c.pad.size() > 1 ? c.pad[1] : c.pad[0]); }
+    SN_CHECK(g.sh > 0 && g.sw > 0, "stride must be positive");
+    g.N = bottom[0]->num(); g.C = bottom[0]->channels(); g.H = bottom[0]->height(); g.W = bottom[0]->width();
+    g.Cout = (int)c.num_output;
+    g.group = (int)c.group;
+    SN_CHECK(g.Cout > 0, "num_output must be positive");
+    SN_CHECK(g.C % g.group == 0 && g.Cout % g.group == 0, "channels and num_output must be multiples of group");
+    bias_term = c.bias_term;
+    g.Ho = (g.H + 2 * g.ph - g.kh) / g.sh + 1;
+    g.Wo = (g.W + 2 * g.pw - g.kw) / g.sw + 1;
+    if (blobs.empty()) {
+      blobs.push_back(std::make_shared<Blob>());
+      blobs[0]->reshape({g.Cout, g.C / g.group, g.kh, g.kw});
+      fill_blob(c.weight_filler, blobs[0].get());
+      if (bias_term) {
+        blobs.push_back(std::make_shared<Blob>());
+        blobs[1]->reshape({g.Cout});
+        fill_blob(c.bias_filler, blobs[1].get());
+      }
+    }
+    param_propagate_down.assign(blobs.size(), true);
+    top[0]->reshape({g.N, g.Cout, g.Ho, g.Wo});
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const float* x = bottom[0]->data->gpu();
+    const float* w = blobs[0]->data->gpu();
+    const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
+    float* y = top[0]->data->mutable_gpu();
+    if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, w, b, y, fuse_relu);
+    else ffma_conv_fwd(S(), g, x, w, b, y, fuse_relu);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    const float* dy = top[0]->diff->gpu();
+    const bool acc = !net->overwrite_param_diffs;
+    if (bias_term && param_propagate_down[1])
+      conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
+    if (param_propagate_down[0]) {
+      const float* x = bottom[0]->data->gpu();
+      float* dw = blobs[0]->diff->mutable_gpu();
+      if (net->precision == PREC_TF32) tc_conv_wgrad(S(), g, x, dy, dw, acc);
+      else ffma_conv_wgrad(S(), g, x, dy, dw, acc);
+    }
+    if (pd[0]) {
+      const float* w = blobs[0]->data->gpu();
+      float* dx = bottom[0]->diff->mutable_gpu();
+      if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
+      else ffma_conv_dgrad(S(), g, dy, w, dx);
+    }
+  }
+};
+
+// InnerProduct — reference inner_product_layer.{cpp:10-117,cu:10-56}
+struct InnerProductLayer : Layer {
+  int M = 0, N = 0, K = 0;
+  bool bias_term = true, fuse_relu = false;
+  using Layer::Layer;
+  const char* type() const override { return "InnerProduct"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const cp::InnerProductParameter& p = lp.inner_product_param;
+    N = (int)p.num_output;
+    SN_CHECK(N > 0, "InnerProduct %s: num_output must be positive", lp.name.c_str());
+    bias_term = p.bias_term;
+    const int axis = p.axis < 0 ? p.axis + (int)bottom[0]->shape.size() : p.axis;
+    K = (int)bottom[0]->count(axis, (int)bottom[0]->shape.size());
+    M = (int)bottom[0]->count(0, axis);
+    if (blobs.empty()) {
+      blobs.push_back(std::make_shared<Blob>());
+      blobs[0]->reshape({N, K});
+      fill_blob(p.weight_filler, blobs[0].get());
+      if (bias_term) {
+        blobs.push_back(std::make_shared<Blob>());
+        blobs[1]->reshape({N});
+        fill_blob(p.bias_filler, blobs[1].get());
+      }
+    }
+    param_propagate_down.assign(blobs.size(), true);
+    vector<int> ts(bottom[0]->shape.begin(), bottom[0]->shape.begin() + axis);
+    ts.push_back(N);
+    top[0]->reshape(ts);
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const float* x = bottom[0]->data->gpu();
+    const float* w = blobs[0]->data->gpu();
+    const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
+    float* y = top[0]->data->mutable_gpu();
+    if (net->precision == PREC_TF32) tc_ip_fwd(S(), M, N, K, x, w, b, y, fuse_relu);
+    else ffma_ip_fwd(S(), M, N, K, x, w, b, y, fuse_relu);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    const float* dy = top[0]->diff->gpu();
+    const bool acc = !net->overwrite_param_diffs;
+    if (param_propagate_down[0]) {
+      const float* x = bottom[0]->data->gpu();
+      float* dw = blobs[0]->diff->mutable_gpu();
+      if (net->precision == PREC_TF32) tc_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
+      else ffma_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
+    }
+    if (bias_term && param_propagate_down[1]) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
+    if (pd[0]) {
+      const float* w = blobs[0]->data->gpu();
+      float* dx = bottom[0]->diff->mutable_gpu();
+      if (net->precision == PREC_TF32) tc_ip_dgrad(S(), M, N, K, dy, w, dx);
+      else ffma_ip_dgrad(S(), M, N, K, dy, w, dx);
+    }
+  }
+};
+
+// Pooling — reference pooling_layer.{cpp:17-307,cu:11-380}
+struct PoolingLayer : Layer {
+  PoolGeom g;
+  int method = 0;
+  int* mask = nullptr;
+  using Layer::Layer;
+  ~PoolingLayer() override { if (mask) cudaFree(mask); }
+  const char* type() const override { return "Pooling"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const cp::PoolingParameter& p = lp.pooling_param;
+    method = p.pool;
+    SN_CHECK(method == 0 || method == 1, "Pooling %s: only MAX and AVE are on the supported path", lp.name.c_str());
+    SN_CHECK(bottom[0]->shape.size() == 4, "Pooling %s: input must have 4 axes", lp.name.c_str());
+    g.N = bottom[0]->num(); g.C = bottom[0]->channels(); g.H = bottom[0]->height(); g.W = bottom[0]->width();
+    if (p.global_pooling) { g.kh = g.H; g.kw = g.W; }
+    else if (p.has_kernel_size) { g.kh = g.kw = (int)p.kernel_size; }
+    else {
+      SN_CHECK(p.has_kernel_h && p.has_kernel_w, "For non-square filters both kernel_h and kernel_w are required.");
+      g.kh = (int)p.kernel_h; g.kw = (int)p.kernel_w;
+    }
+    SN_CHECK(g.kh > 0 && g.kw > 0, "Filter dimensions cannot be zero.");
+    if (p.has_pad_h || p.has_pad_w) { g.ph = (int)p.pad_h; g.pw = (int)p.pad_w; } else { g.ph = g.pw = (int)p.pad; }
+    if (p.has_stride_h || p.has_stride_w) { g.sh = (int)p.stride_h; g.sw = (int)p.stride_w; } else { g.sh = g.sw = (int)p.stride; }
+    if (g.ph || g.pw) SN_CHECK(g.ph < g.kh && g.pw < g.kw, "pad must be smaller than the kernel");
+    g.PH = (int)std::ceil((float)(g.H + 2 * g.ph - g.kh) / g.sh) + 1;   // pooling_layer.cpp:90-93 (ceil)
+    g.PW = (int)std::ceil((float)(g.W + 2 * g.pw - g.kw) / g.sw) + 1;
+    if (g.ph || g.pw) {                                                 // :94-105
+      if ((g.PH - 1) * g.sh >= g.H + g.ph) --g.PH;
+      if ((g.PW - 1) * g.sw >= g.W + g.pw) --g.PW;
+    }
+    top[0]->reshape({g.N, g.C, g.PH, g.PW});
+    if (method == 0 && !mask) SN_CUDA(cudaMalloc(&mask, top[0]->count() * sizeof(int)));
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const float* x = bottom[0]->data->gpu();
+    float* y = top[0]->data->mutable_gpu();
+    if (method == 0) pool_max_fwd(S(), g, x, y, mask); else pool_ave_fwd(S(), g, x, y);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    if (!pd[0]) return;
+    const float* dy = top[0]->diff->gpu();
+    float* dx = bottom[0]->diff->mutable_gpu();
+    if (method == 0) pool_max_bwd(S(), g, dy, mask, dx); else pool_ave_bwd(S(), g, dy, dx);
+  }
+};
+
+// ReLU — reference relu_layer.{cpp:9-36,cu:9-58}.  When the producer's epilogue already applied it
+// (fused_by_producer), forward is a no-op; backward is unchanged (tests y > 0, same predicate in place).
+struct ReLULayer : Layer {
+  bool fused_by_producer = false;
+  using Layer::Layer;
+  const char* type() const override { return "ReLU"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    if (top[0] != bottom[0]) top[0]->reshape(bottom[0]->shape);
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    if (fused_by_producer) return;
+    const float* x = bottom[0]->data->gpu();
+    relu_fwd(S(), bottom[0]->count(), x, top[0]->data->mutable_gpu(), lp.relu_negative_slope);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    if (!pd[0]) return;
+    const float* dy = top[0]->diff->gpu();
+    const float* x = bottom[0]->data->gpu();
+    relu_bwd(S(), bottom[0]->count(), dy, x, bottom[0]->diff->mutable_gpu(), lp.relu_negative_slope);
+  }
+};
+
+// Dropout — reference dropout_layer.{cpp:11-65,cu:10-67}
+struct DropoutLayer : Layer {
+  float ratio = 0.5f, scale = 2.f;
+  uint8_t* mask = nullptr;
+  size_t n = 0;
+  bool injected = false;
+  uint64_t seed = 0, offset = 0;
+  using Layer::Layer;
+  ~DropoutLayer() override { if (mask) cudaFree(mask); }
+  const char* type() const override { return "Dropout"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    ratio = lp.dropout_ratio;
+    SN_CHECK(ratio > 0.f && ratio < 1.f, "dropout_ratio must be in (0,1)");
+    scale = (float)(1. / (1. - ratio));
+    if (top[0] != bottom[0]) top[0]->reshape(bottom[0]->shape);
+    n = bottom[0]->count();
+    if (!mask) SN_CUDA(cudaMalloc(&mask, n));
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const float* x = bottom[0]->data->gpu();
+    float* y = top[0]->data->mutable_gpu();
+    if (phase == cp::TRAIN) {
+      dropout_fwd(S(), n, x, y, mask, ratio, scale, !injected, seed, offset);
+      offset += (n + 3) / 4;
+    } else if (x != y) {
+      SN_CUDA(cudaMemcpyAsync(y, x, n * sizeof(float), cudaMemcpyDeviceToDevice, S()));
+    }
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    if (!pd[0]) return;
+    const float* dy = top[0]->diff->gpu();
+    float* dx = bottom[0]->diff->mutable_gpu();
+    if (phase == cp::TRAIN) dropout_bwd(S(), n, dy, mask, dx, scale);
+    else if (dx != dy) SN_CUDA(cudaMemcpyAsync(dx, dy, n * sizeof(float), cudaMemcpyDeviceToDevice, S()));
+  }
+};
+
+// LRN — reference lrn_layer.{cpp:9-247,cu:9-190}
+struct LRNLayer : Layer {
+  LrnGeom g;
+  int region = 0;
+  float* scale = nullptr;
+  using Layer::Layer;
+  ~LRNLayer() override { if (scale) cudaFree(scale); }
+  const char* type() const override { return "LRN"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const cp::LRNParameter& p = lp.lrn_param;
+    g.size = (int)p.local_size;
+    SN_CHECK(g.size % 2 == 1, "LRN only supports odd values for local_size");
+    g.alpha = p.alpha; g.beta = p.beta; g.k = p.k; region = p.norm_region;
+    SN_CHECK(bottom[0]->shape.size() == 4, "LRN %s: input must have 4 axes", lp.name.c_str());
+    g.N = bottom[0]->num(); g.C = bottom[0]->channels(); g.H = bottom[0]->height(); g.W = bottom[0]->width();
+    top[0]->reshape(bottom[0]->shape);
+    if (region == 0 && !scale) SN_CUDA(cudaMalloc(&scale, bottom[0]->count() * sizeof(float)));
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    const float* x = bottom[0]->data->gpu();
+    float* y = top[0]->data->mutable_gpu();
+    if (region == 0) lrn_across_fwd(S(), g, x, y, scale); else lrn_within_fwd(S(), g, x, y);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    if (!pd[0]) return;
+    const float* dy = top[0]->diff->gpu();
+    const float* x = bottom[0]->data->gpu();
+    float* dx = bottom[0]->diff->mutable_gpu();
+    if (region == 0) lrn_across_bwd(S(), g, x, top[0]->data->gpu(), scale, dy, dx);
+    else lrn_within_bwd(S(), g, x, dy, dx);
+  }
+};
+
+// SoftmaxWithLoss — reference softmax_loss_layer.{cpp:11-119,cu:11-120}, softmax_layer.{cpp,cu}, loss_layer.cpp:8-23
+struct SoftmaxWithLossLayer : Layer {
+  int rows = 0, classes = 0;
+  float* prob = nullptr;
+  float* row_scratch = nullptr;
+  using Layer::Layer;
+  ~SoftmaxWithLossLayer() override { if (prob) cudaFree(prob); if (row_scratch) cudaFree(row_scratch); }
+  const char* type() const override { return "SoftmaxWithLoss"; }
+  bool is_loss() const override { return true; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    if (lp.loss_weight.empty()) lp.loss_weight.push_back(1.f);
+    SN_CHECK(bottom.size() == 2, "SoftmaxWithLoss needs (prediction, label) bottoms");
+    const int axis = lp.softmax_axis < 0 ? lp.softmax_axis + (int)bottom[0]->shape.size() : lp.softmax_axis;
+    rows = (int)bottom[0]->count(0, axis);
+    classes = bottom[0]->shape[(size_t)axis];
+    const size_t inner = bottom[0]->count(axis + 1, (int)bottom[0]->shape.size());
+    SN_CHECK(inner == 1, "SoftmaxWithLoss %s: spatial softmax (inner_num > 1) is not on the supported path", lp.name.c_str());
+    SN_CHECK((size_t)rows == bottom[1]->count(), "Number of labels must match number of predictions");
+    SN_CHECK(!lp.loss_param.has_ignore_label && lp.loss_param.normalize, "ignore_label / normalize=false are not on the supported path");
+    if (!prob) {
+      SN_CUDA(cudaMalloc(&prob, (size_t)rows * classes * sizeof(float)));
+      SN_CUDA(cudaMalloc(&row_scratch, (size_t)rows * sizeof(float)));
+    }
+    top[0]->reshape({});
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    softmax_loss_fwd(S(), rows, classes, bottom[0]->data->gpu(), bottom[1]->data->gpu(), prob,
+                     top[0]->data->mutable_gpu(), row_scratch, net->loss_log);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    SN_CHECK(pd.size() < 2 || !pd[1], "SoftmaxWithLoss Layer cannot backpropagate to label inputs.");
+    if (!pd[0]) return;
+    softmax_loss_bwd(S(), rows, classes, prob, bottom[1]->data->gpu(), top[0]->diff->gpu(), bottom[0]->diff->mutable_gpu());
+  }
+};
+
+// Accuracy (top-1) — reference accuracy_layer.cpp:13-103 (CPU only there; on the device here)
+struct AccuracyLayer : Layer {
+  int rows = 0, classes = 0;
+  float* row_scratch = nullptr;
+  using Layer::Layer;
+  ~AccuracyLayer() override { if (row_scratch) cudaFree(row_scratch); }
+  const char* type() const override { return "Accuracy"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    SN_CHECK(lp.accuracy_param.top_k == 1, "Accuracy %s: only top_k = 1 is on the supported path", lp.name.c_str());
+    SN_CHECK(!lp.accuracy_param.has_ignore_label, "Accuracy ignore_label is not on the supported path");
+    const int axis = lp.accuracy_param.axis < 0 ? lp.accuracy_param.axis + (int)bottom[0]->shape.size() : lp.accuracy_param.axis;
+    rows = (int)bottom[0]->count(0, axis);
+    classes = bottom[0]->shape[(size_t)axis];
+    SN_CHECK(bottom[0]->count(axis + 1, (int)bottom[0]->shape.size()) == 1, "Accuracy: inner_num > 1 not supported");
+    SN_CHECK((size_t)rows == bottom[1]->count(), "Number of labels must match number of predictions");
+    if (!row_scratch) SN_CUDA(cudaMalloc(&row_scratch, (size_t)rows * sizeof(float)));
+    top[0]->reshape({});
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    accuracy_top1(S(), rows, classes, bottom[0]->data->gpu(), bottom[1]->data->gpu(), top[0]->data->mutable_gpu(), row_scratch);
+  }
+  void backward(const vector<Blob*>&, const vector<bool>&, const vector<Blob*>&) override {}
+};
+
+// Split — reference split_layer.cpp:10-49: tops alias the bottom's data; backward sums the diffs.
+struct SplitLayer : Layer {
+  using Layer::Layer;
+  const char* type() const override { return "Split"; }
+  void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    for (Blob* t : top) { t->reshape(bottom[0]->shape); t->share_data(*bottom[0]); }
+  }
+  void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
+    for (Blob* t : top) t->share_data(*bottom[0]);
+  }
+  void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
+    if (!pd[0]) return;
+    const size_t n = bottom[0]->count();
+    float* bd = bottom[0]->diff->mutable_gpu();
+    if (top.size() == 1) {
+      SN_CUDA(cudaMemcpyAsync(bd, top[0]->diff->gpu(), n * sizeof(float), cudaMemcpyDeviceToDevice, S()));
+      return;
+    }
+    split_add(S(), n, top[0]->diff->gpu(), top[1]->diff->gpu(), bd);
+    for (size_t k = 2; k < top.size(); ++k) axpy(S(), n, 1.f, top[k]->diff->gpu(), bd);
+  }
+};
+
+static std::shared_ptr<Layer> create_layer(const cp::LayerParameter& lp) {
+  const string& t = lp.type;
+  if (t == "JavaData") return std::make_shared<JavaDataLayer>(lp);
+  if (t == "Convolution") return std::make_shared<ConvolutionLayer>(lp);
+  if (t == "InnerProduct") return std::make_shared<InnerProductLayer>(lp);
+  if (t == "Pooling") return std::make_shared<PoolingLayer>(lp);
+  if (t == "ReLU") return std::make_shared<ReLULayer>(lp);
+  if (t == "Dropout") return std::make_shared<DropoutLayer>(lp);
+  if (t == "LRN") return std::make_shared<LRNLayer>(lp);
+  if (t == "SoftmaxWithLoss") return std::make_shared<SoftmaxWithLossLayer>(lp);
+  if (t == "Accuracy") return std::make_shared<AccuracyLayer>(lp);
+  if (t == "Split") return std::make_shared<SplitLayer>(lp);
+  fatal("layer type '%s' (layer '%s') is outside the supported hot path", t.c_str(), lp.name.c_str());
+}
+
+// ------------------------------------------------------------------------------------------
+// InsertSplits — reference caffe/src/caffe/util/insert_splits.cpp:12-137
+// ------------------------------------------------------------------------------------------
+static string split_layer_name(const string& layer, const string& blob, int idx) {
+  std::ostringstream s;
+  s << blob << "_" << layer << "_" << idx << "_split";
+  return s.str();
+}
+static string split_blob_name(const string& layer, const string& blob, int idx, int split) {
+  std::ostringstream s;
+  s << blob << "_" << layer << "_" << idx << "_split_" << split;
+  return s.str();
+}
+static vector<cp::LayerParameter> insert_splits(const vector<cp::LayerParameter>& layers) {
+  typedef std::pair<int, int> PI;
+  std::map<string, PI> last_top;
+  std::map<PI, PI> bottom_src;
+  std::map<PI, int> top_count, split_idx;
+  std::map<PI, float> top_lw;
+  for (int i = 0; i < (int)layers.size(); ++i) {
+    const cp::LayerParameter& lp = layers[(size_t)i];
+    for (int j = 0; j < (int)lp.bottom.size(); ++j) {
+      auto it = last_top.find(lp.bottom[(size_t)j]);
+      SN_CHECK(it != last_top.end(), "Unknown bottom blob '%s' (layer '%s', bottom index %d)", lp.bottom[(size_t)j].c_str(), lp.name.c_str(), j);
+      bottom_src[{i, j}] = it->second;
+      ++top_count[it->second];
+    }
+    for (int j = 0; j < (int)lp.top.size(); ++j) last_top[lp.top[(size_t)j]] = {i, j};
+    const int last_loss = std::min((int)lp.loss_weight.size(), (int)lp.top.size());
+    for (int j = 0; j < last_loss; ++j) {
+      const PI t = last_top[lp.top[(size_t)j]];
+      top_lw[t] = lp.loss_weight[(size_t)j];
+      if (top_lw[t]) ++top_count[t];
+    }
+  }
+  vector<cp::LayerParameter> out;
+  for (int i = 0; i < (int)layers.size(); ++i) {
+    cp::LayerParameter lp = layers[(size_t)i];
+    for (int j = 0; j < (int)lp.bottom.size(); ++j) {
+      const PI t = bottom_src[{i, j}];
+      if (top_count[t] > 1)
+        lp.bottom[(size_t)j] = split_blob_name(layers[(size_t)t.first].name, lp.bottom[(size_t)j], t.second, split_idx[t]++);
+    }
+    vector<cp::LayerParameter> splits;
+    for (int j = 0; j < (int)lp.top.size(); ++j) {
+      const PI t{i, j};
+      const int sc = top_count[t];
+      if (sc > 1) {
+        cp::LayerParameter sp;
+        sp.bottom.push_back(lp.top[(size_t)j]);
+        sp.name = split_layer_name(lp.name, lp.top[(size_t)j], j);
+        sp.type = "Split";
+        const float lw = top_lw[t];
+        for (int k = 0; k < sc; ++k) {
+          sp.top.push_back(split_blob_name(lp.name, lp.top[(size_t)j], j, k));
+          if (lw) sp.loss_weight.push_back(k == 0 ? lw : 0.f);
+        }
+        if (lw) { lp.loss_weight.clear(); split_idx[t]++; }
+        splits.push_back(sp);
+      }
+    }
+    out.push_back(lp);
+    for (auto& s : splits) out.push_back(s);
+  }
+  return out;
+}
+
+// ------------------------------------------------------------------------------------------
+// Net — reference caffe/src/caffe/net.cpp:40-284 (Init), 385-562 (Append*), 565-581, 635-645,
+// 737-766 (ShareTrainedLayersWith)
+// ------------------------------------------------------------------------------------------
+Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_), rng_seed(seed) {
+  cp::NetState st = in.state;
+  st.phase = phase_;
+  vector<cp::LayerParameter> param = insert_splits(cp::filter_net(in, st));
+  name = in.name;
+  SN_CHECK(in.input.empty(), "net-level `input` blobs are not on the supported path (use JavaData layers)");
+  std::map<string, int> name_to_idx;
+  std::set<string> available;
+  const int L = (int)param.size();
+  bottom_vecs.resize((size_t)L); top_vecs.resize((size_t)L); bottom_ids.resize((size_t)L); top_ids.resize((size_t)L);
+  bottom_need_backward.resize((size_t)L);
+  for (int li = 0; li < L; ++li) {
+    cp::LayerParameter lp = param[(size_t)li];
+    if (!lp.has_phase) { lp.phase = phase; lp.has_phase = true; }
+    std::shared_ptr<Layer> layer = create_layer(lp);
+    layer->phase = lp.phase;
+    layer->net = this;
+    layers.push_back(layer);
+    layer_names.push_back(lp.name);
+    bool need_backward = false;
+    for (int b = 0; b < (int)lp.bottom.size(); ++b) {
+      const string& bn = lp.bottom[(size_t)b];
+      SN_CHECK(available.count(bn), "Unknown bottom blob '%s' (layer '%s', bottom index %d)", bn.c_str(), lp.name.c_str(), b);
+      const int id = name_to_idx[bn];
+      bottom_vecs[(size_t)li].push_back(blobs[(size_t)id].get());
+      bottom_ids[(size_t)li].push_back(id);
+      available.erase(bn);
+      const bool pd = lp.propagate_down.empty() ? true : (bool)lp.propagate_down[(size_t)b];
+      bottom_need_backward[(size_t)li].push_back(blob_need_backward[(size_t)id] && pd);
+      need_backward |= blob_need_backward[(size_t)id];
+    }
+    for (int t = 0; t < (int)lp.top.size(); ++t) {
+      const string& tn = lp.top[(size_t)t];
+      if (t < (int)lp.bottom.size() && lp.bottom[(size_t)t] == tn) {   // in-place computation
+        const int id = name_to_idx[tn];
+        top_vecs[(size_t)li].push_back(blobs[(size_t)id].get());
+        top_ids[(size_t)li].push_back(id);
+      } else {
+        SN_CHECK(!name_to_idx.count(tn), "Top blob '%s' produced by multiple sources.", tn.c_str());
+        blobs.push_back(std::make_shared<Blob>());
+        const int id = (int)blobs.size() - 1;
+        blob_names.push_back(tn);
+        blob_need_backward.push_back(false);
+        name_to_idx[tn] = id;
+        top_vecs[(size_t)li].push_back(blobs[(size_t)id].get());
+        top_ids[(size_t)li].push_back(id);
+      }
+      available.insert(tn);
+    }
+    layer->setup(bottom_vecs[(size_t)li], top_vecs[(size_t)li]);
+    layer->set_loss_weights(top_vecs[(size_t)li]);
+    const int nparam = (int)layer->blobs.size();
+    SN_CHECK((int)lp.param.size() <= nparam, "Too many params specified for layer %s", lp.name.c_str());
+    for (int p = 0; p < nparam; ++p) {
+      cp::ParamSpec spec;
+      if (p < (int)lp.param.size()) spec = lp.param[(size_t)p];
+      SN_CHECK(spec.name.empty(), "named (shared) params are not on the supported path");
+      const bool pnb = spec.lr_mult != 0.f;
+      need_backward |= pnb;
+      layer->param_propagate_down[(size_t)p] = pnb;
+      learnable_params.push_back(layer->blobs[(size_t)p].get());
+      params_lr.push_back(spec.lr_mult);
+      params_decay.push_back(spec.decay_mult);
+    }
+    layer_need_backward.push_back(need_backward);
+    if (need_backward)
+      for (int id : top_ids[(size_t)li]) blob_need_backward[(size_t)id] = true;
+    if (DropoutLayer* d = dynamic_cast<DropoutLayer*>(layer.get())) d->seed = rng_seed * 0x9E3779B97F4A7C15ull + (uint64_t)li;
+  }
+  // which blobs contribute to the loss (net.cpp:191-247)
+  std::set<string> under_loss, skip_bp;
+  for (int li = L - 1; li >= 0; --li) {
+    bool contributes = false, skip_pd = true;
+    for (int t = 0; t < (int)top_vecs[(size_t)li].size(); ++t) {
+      const string& bn = blob_names[(size_t)top_ids[(size_t)li][(size_t)t]];
+      if ((t < (int)layers[(size_t)li]->loss.size() && layers[(size_t)li]->loss[(size_t)t]) || under_loss.count(bn)) contributes = true;
+      if (!skip_bp.count(bn)) skip_pd = false;
+      if (contributes && !skip_pd) break;
+    }
+    if (layer_need_backward[(size_t)li] && skip_pd) {
+      layer_need_backward[(size_t)li] = false;
+      for (size_t b = 0; b < bottom_need_backward[(size_t)li].size(); ++b) bottom_need_backward[(size_t)li][b] = false;
+    }
+    if (!contributes) layer_need_backward[(size_t)li] = false;
+    for (int b = 0; b < (int)bottom_vecs[(size_t)li].size(); ++b) {
+      const string& bn = blob_names[(size_t)bottom_ids[(size_t)li][(size_t)b]];
+      if (contributes) under_loss.insert(bn); else bottom_need_backward[(size_t)li][(size_t)b] = false;
+      if (!bottom_need_backward[(size_t)li][(size_t)b]) skip_bp.insert(bn);
+    }
+  }
+  if (in.force_backward) {   // net.cpp:248-265
+    for (int li = 0; li < L; ++li) {
+      layer_need_backward[(size_t)li] = true;
+      for (size_t b = 0; b < bottom_need_backward[(size_t)li].size(); ++b) {
+        const bool allow = !(layers[(size_t)li]->is_loss() && b == 1) && string(layers[(size_t)li]->type()) != "Accuracy";
+        bottom_need_backward[(size_t)li][b] = bottom_need_backward[(size_t)li][b] || allow;
+        const int id = bottom_ids[(size_t)li][b];
+        blob_need_backward[(size_t)id] = blob_need_backward[(size_t)id] || bottom_need_backward[(size_t)li][b];
+      }
+      for (size_t p = 0; p < layers[(size_t)li]->param_propagate_down.size(); ++p) layers[(size_t)li]->param_propagate_down[p] = true;
+    }
+  }
+  for (const string& bn : available) {   // std::set => name order (net.cpp:266-274)
+    output_blobs.push_back(blobs[(size_t)name_to_idx[bn]].get());
+    output_blob_indices.push_back(name_to_idx[bn]);
+  }
+  // Producer/ReLU fusion: Convolution or InnerProduct immediately followed by an in-place ReLU
+  // (negative_slope 0) on its top applies the ReLU in its epilogue.
+  for (int li = 0; li + 1 < L; ++li) {
+    ReLULayer* r = dynamic_cast<ReLULayer*>(layers[(size_t)li + 1].get());
+    if (!r || r->lp.relu_negative_slope != 0.f) continue;
+    if (bottom_vecs[(size_t)li + 1][0] != top_vecs[(size_t)li + 1][0] || bottom_vecs[(size_t)li + 1][0] != top_vecs[(size_t)li][0]) continue;
+    if (ConvolutionLayer* c = dynamic_cast<ConvolutionLayer*>(layers[(size_t)li].get())) { c->fuse_relu = true; r->fused_by_producer = true; }
+    else if (InnerProductLayer* ip = dynamic_cast<InnerProductLayer*>(layers[(size_t)li].get())) { ip->fuse_relu = true; r->fused_by_producer = true; }
+  }
+  // Parameter arena: one contiguous device allocation for all weights and one for all gradients;
+  // every blob starts on a 1024-float boundary (lets one SGD launch and one all-reduce cover the net).
+  size_t off = 0;
+  for (Blob* b : learnable_params) {
+    param_offsets.push_back(off);
+    off += (b->count() + 1023) / 1024 * 1024;
+  }
+  arena_floats = off;
+  if (arena_floats) {
+    SN_CUDA(cudaMalloc(&arena_w, arena_floats * sizeof(float)));
+    SN_CUDA(cudaMalloc(&arena_g, arena_floats * sizeof(float)));
+    SN_CUDA(cudaMemset(arena_w, 0, arena_floats * sizeof(float)));
+    SN_CUDA(cudaMemset(arena_g, 0, arena_floats * sizeof(float)));
+    owns_arena = true;
+    for (size_t i = 0; i < learnable_params.size(); ++i) {
+      Blob* b = learnable_params[i];
+      SN_CHECK(b->data->dev == nullptr && b->diff->dev == nullptr, "param blob touched before arena placement");
+      b->data->dev = arena_w + param_offsets[i];
+      b->data->owns_dev = false;
+      b->diff->dev = arena_g + param_offsets[i];
+      b->diff->owns_dev = false;
+      b->diff->head = Storage::AT_DEVICE;   // zeroed above
+    }
+  }
+}
+Net::~Net() {
+  layers.clear();
+  blobs.clear();
+  if (owns_arena) {
+    cudaFree(arena_w);
+    cudaFree(arena_g);
+  }
+}
+void Net::forward_from_to(int start, int end) {
+  for (int i = start; i <= end; ++i) layers[(size_t)i]->forward(bottom_vecs[(size_t)i], top_vecs[(size_t)i]);
+}
+void Net::backward_from_to(int start, int end) {
+  for (int i = start; i >= end; --i)
+    if (layer_need_backward[(size_t)i]) layers[(size_t)i]->backward(top_vecs[(size_t)i], bottom_need_backward[(size_t)i], bottom_vecs[(size_t)i]);
+}
+void Net::share_trained_layers_with(const Net& other) {
+  for (size_t i = 0; i < other.layers.size(); ++i) {
+    const string& src = other.layer_names[i];
+    size_t t = 0;
+    while (t != layer_names.size() && layer_names[t] != src) ++t;
+    if (t == layer_names.size()) continue;
+    SN_CHECK(layers[t]->blobs.size() == other.layers[i]->blobs.size(), "Incompatible number of blobs for layer %s", src.c_str());
+    for (size_t j = 0; j < layers[t]->blobs.size(); ++j) {
+      SN_CHECK(layers[t]->blobs[j]->shape == other.layers[i]->blobs[j]->shape, "Cannot share param %zu weights from layer '%s'", j, src.c_str());
+      layers[t]->blobs[j] = other.layers[i]->blobs[j];
+    }
+  }
+}
+float Net::total_loss() {
+  float l = 0.f;
+  for (size_t li = 0; li < layers.size(); ++li)
+    for (size_t t = 0; t < top_vecs[li].size() && t < layers[li]->loss.size(); ++t) {
+      if (layers[li]->loss[t] == 0.f) continue;
+      Blob* b = top_vecs[li][t];
+      // read back without disturbing the head state of the blob
+      std::vector<float> d(b->count()), w(b->count());
+      SN_CUDA(cudaMemcpyAsync(d.data(), b->data->gpu(), d.size() * sizeof(float), cudaMemcpyDeviceToHost, S()));
+      SN_CUDA(cudaMemcpyAsync(w.data(), b->diff->gpu(), w.size() * sizeof(float), cudaMemcpyDeviceToHost, S()));
+      SN_CUDA(cudaStreamSynchronize(S()));
+      for (size_t k = 0; k < d.size(); ++k) l += d[k] * w[k];
+    }
+  return l;
+}
+
+// ------------------------------------------------------------------------------------------
+// Solver — reference caffe/src/caffe/solver.cpp:44-190,193-282,413-444 and
+// caffe/src/caffe/solvers/sgd_solver.cpp:27-63,66-78,102-116,145-239
+// ------------------------------------------------------------------------------------------
+Solver::Solver(const cp::SolverParameter& p) : param(p) {
+  SN_CHECK(param.type == "SGD", "only the SGD solver is on the path (libccaffe/ccaffe.cpp:131 hard-codes SGDSolver)");
+  SN_CHECK(param.has_net_param || param.has_train_net_param, "SolverParameter must embed the net (net_param); file paths are not supported");
+  SN_CHECK(param.regularization_type == "L2", "only L2 regularization is on the supported path");
+  SN_CHECK(param.clip_gradients < 0, "clip_gradients is not on the supported path");
+  SN_CHECK(param.iter_size == 1, "iter_size != 1 is not on the supported path");
+  uint64_t seed = param.random_seed >= 0 ? (uint64_t)param.random_seed : (uint64_t)std::random_device{}();
+  if (param.random_seed >= 0) host_rng().seed((uint32_t)param.random_seed);   // solver.cpp:52-54
+  const cp::NetParameter& np = param.has_train_net_param ? param.train_net_param : param.net_param;
+  net.reset(new Net(np, cp::TRAIN, seed));
+  if (param.has_net_param) test_net.reset(new Net(param.net_param, cp::TEST, seed + 1));
+  else if (!param.test_net_param.empty()) test_net.reset(new Net(param.test_net_param[0], cp::TEST, seed + 1));
+  if (test_net) test_net->share_trained_layers_with(*net);
+  const size_t n = net->arena_floats;
+  if (n) {
+    SN_CUDA(cudaMalloc(&arena_h, n * sizeof(float)));
+    SN_CUDA(cudaMemset(arena_h, 0, n * sizeof(float)));
+    std::vector<SgdChunk> table(n / 1024);
+    for (size_t i = 0; i < net->learnable_params.size(); ++i) {
+      const size_t c0 = net->param_offsets[i] / 1024, c1 = c0 + (net->learnable_params[i]->count() + 1023) / 1024;
+      for (size_t c = c0; c < c1; ++c) table[c] = SgdChunk{net->params_lr[i], param.weight_decay * net->params_decay[i]};
+    }
+    SN_CUDA(cudaMalloc(&chunk_table, table.size() * sizeof(SgdChunk)));
+    SN_CUDA(cudaMemcpy(chunk_table, table.data(), table.size() * sizeof(SgdChunk), cudaMemcpyHostToDevice));
+  }
+  SN_CUDA(cudaMalloc(&loss_hist, kLossHist * sizeof(float)));
+  SN_CUDA(cudaMemset(loss_hist, 0, kLossHist * sizeof(float)));
+}
+Solver::~Solver() {
+  test_net.reset();
+  net.reset();
+  if (arena_h) cudaFree(arena_h);
+  if (chunk_table) cudaFree(chunk_table);
+  if (loss_hist) cudaFree(loss_hist);
+}
+float Solver::get_learning_rate() {   // sgd_solver.cpp:27-63, same expression types
+  const string& pol = param.lr_policy;
+  float rate = 0.f;
+  if (pol == "fixed") rate = param.base_lr;
+  else if (pol == "step") { current_step = iter / param.stepsize; rate = (float)(param.base_lr * std::pow(param.gamma, current_step)); }
+  else if (pol == "exp") rate = (float)(param.base_lr * std::pow(param.gamma, iter));
+  else if (pol == "inv") rate = param.base_lr * std::pow(1.f + param.gamma * iter, -param.power);
+  else if (pol == "multistep") {
+    if (current_step < (int)param.stepvalue.size() && iter >= param.stepvalue[(size_t)current_step]) current_step++;
+    rate = (float)(param.base_lr * std::pow(param.gamma, current_step));
+  } else if (pol == "poly") rate = param.base_lr * std::pow(1.f - ((float)iter / (float)param.max_iter), param.power);
+  else if (pol == "sigmoid") rate = param.base_lr * (1.f / (1.f + std::exp(-param.gamma * ((float)iter - (float)param.stepsize))));
+  else fatal("Unknown learning rate policy: %s", pol.c_str());
+  return rate;
+}
+void Solver::step(int iters) {
+  const int stop_iter = iter + iters;
+  const int L = (int)net->layers.size();
+  // every learnable blob's device copy must be current before the fused update touches the arena
+  for (Blob* b : net->learnable_params) { b->data->mutable_gpu(); b->diff->mutable_gpu(); }
+  net->overwrite_param_diffs = true;     // Net::ClearParamDiffs (net.cpp:990-1008) folded into the wgrad epilogues
+  while (iter < stop_iter) {
+    net->loss_log = loss_hist + (iter % kLossHist);
+    net->forward_from_to(0, L - 1);
+    net->backward_from_to(L - 1, 0);
+    if (param.display && iter % param.display == 0) {
+      const float loss = net->total_loss();
+      fprintf(stderr, "Iteration %d, loss = %g, lr = %g\n", iter, loss, get_learning_rate());
+    }
+    const float rate = get_learning_rate();
+    if (net->arena_floats) sgd_update(ctx().compute, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
+    ++iter;
+  }
+  net->overwrite_param_diffs = false;
+  net->loss_log = nullptr;
+}
+void Solver::test_and_store(int num_steps, std::vector<float>* score) {   // solver.cpp:413-444
+  SN_CHECK(test_net != nullptr, "solver_test: the solver has no test net");
+  test_net->precision = net->precision;
+  test_net->share_trained_layers_with(*net);
+  const int L = (int)test_net->layers.size();
+  size_t total = 0;
+  for (Blob* r : test_net->output_blobs) total += r->count();
+  std::vector<float> sums(total, 0.f), tmp;
+  for (int i = 0; i < num_steps; ++i) {
+    test_net->forward_from_to(0, L - 1);
+    size_t idx = 0;
+    for (Blob* r : test_net->output_blobs) {
+      tmp.resize(r->count());
+      SN_CUDA(cudaMemcpyAsync(tmp.data(), r->data->gpu(), tmp.size() * sizeof(float), cudaMemcpyDeviceToHost, S()));
+      SN_CUDA(cudaStreamSynchronize(S()));
+      for (float v : tmp) sums[idx++] += v;
+    }
+  }
+  score->assign(sums.begin(), sums.end());
+}
+
+}  // namespace sn
+#include "ccaffe_abi.inc"

@@ -1,0 +1,157 @@
+// runtime.hpp — host runtime of the B200 libccaffe: blobs with Caffe's host/device mirror
+// semantics, layers, the net graph builder and the SGD solver.  C++ only; every compute step is a
+// launch from kernels.hpp.  There is no CPU compute path: set_mode_cpu() is accepted and ignored.
+//
+// Reference counterparts (what this replaces): caffe/src/caffe/{blob,syncedmem,net,solver}.cpp,
+// caffe/src/caffe/solvers/sgd_solver.cpp, caffe/src/caffe/layers/*.{cpp,cu} (on-path subset),
+// caffe/src/caffe/util/insert_splits.cpp.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <map>
+#include <memory>
+#include <set>
+#include <string>
+#include <vector>
+
+#include "caffe_proto.hpp"
+#include "kernels.hpp"
+
+extern "C" {
+typedef void (*java_callback_t)(void* data, int batch_size, int num_dims, int* shape);
+typedef void (*error_callback_t)(const char* msg);
+}
+
+namespace sn {
+namespace cp = caffe_proto;
+
+// Per-process device context (one GPU per process is the deployment model; set_device() picks it).
+struct Context {
+  int device = 0;
+  bool initialised = false;
+  cudaStream_t compute = nullptr;   // all kernels
+  cudaStream_t copy = nullptr;      // JavaData H2D staging
+  float* workspace = nullptr;
+  size_t workspace_floats = 0;
+  long launches = 0;
+  void init();
+};
+Context& ctx();       // initialises the device context on first use
+Context& raw_ctx();   // the same object, without initialising it
+
+// ------------------------------------------------------------------------------------------
+// Storage: one buffer with a device copy and a lazily created pinned host mirror.  State machine
+// of caffe/src/caffe/syncedmem.cpp:25-153 (UNINITIALIZED / HEAD_AT_CPU / HEAD_AT_GPU / SYNCED).
+// ------------------------------------------------------------------------------------------
+struct Storage {
+  enum Head { UNINIT, AT_HOST, AT_DEVICE, SYNCED };
+  size_t count = 0;
+  float* dev = nullptr;
+  float* host = nullptr;
+  bool owns_dev = true;
+  Head head = UNINIT;
+  explicit Storage(size_t n) : count(n) {}
+  Storage(size_t n, float* arena_ptr) : count(n), dev(arena_ptr), owns_dev(false) {}
+  ~Storage();
+  const float* gpu();            // device copy current (uploads if the host copy is newer)
+  float* mutable_gpu();          // + device copy becomes authoritative
+  float* mutable_cpu();          // host copy current and authoritative (ccaffe.cpp:181-187 get_data/get_diff)
+  void ensure_dev();
+  void ensure_host();
+};
+
+struct Blob {
+  std::vector<int> shape;
+  std::shared_ptr<Storage> data, diff;
+  size_t count() const {
+    size_t c = 1;
+    for (int d : shape) c *= (size_t)d;
+    return c;
+  }
+  size_t count(int from, int to) const {
+    size_t c = 1;
+    for (int i = from; i < to; ++i) c *= (size_t)shape[(size_t)i];
+    return c;
+  }
+  int dim(int i) const { return shape[(size_t)(i < 0 ? i + (int)shape.size() : i)]; }
+  int num() const { return shape.size() > 0 ? shape[0] : 1; }
+  int channels() const { return shape.size() > 1 ? shape[1] : 1; }
+  int height() const { return shape.size() > 2 ? shape[2] : 1; }
+  int width() const { return shape.size() > 3 ? shape[3] : 1; }
+  void reshape(const std::vector<int>& s);
+  void share_data(const Blob& o) { data = o.data; }
+};
+typedef std::shared_ptr<Blob> BlobP;
+
+enum Precision { PREC_FFMA = 0, PREC_TF32 = 1 };
+
+struct Net;
+struct Layer {
+  cp::LayerParameter lp;
+  int phase = cp::TRAIN;
+  Net* net = nullptr;
+  std::vector<BlobP> blobs;
+  std::vector<bool> param_propagate_down;
+  std::vector<float> loss;
+  explicit Layer(const cp::LayerParameter& p) : lp(p) {}
+  virtual ~Layer() {}
+  virtual const char* type() const = 0;
+  virtual void setup(const std::vector<Blob*>& bottom, const std::vector<Blob*>& top) = 0;
+  virtual void forward(const std::vector<Blob*>& bottom, const std::vector<Blob*>& top) = 0;
+  virtual void backward(const std::vector<Blob*>& top, const std::vector<bool>& pd, const std::vector<Blob*>& bottom) = 0;
+  virtual bool is_loss() const { return false; }
+  void set_loss_weights(const std::vector<Blob*>& top);
+};
+
+struct Net {
+  std::string name;
+  int phase;
+  int precision = PREC_FFMA;
+  bool overwrite_param_diffs = false;   // true inside solver_step: weight gradients overwrite (ClearParamDiffs folded away)
+  float* loss_log = nullptr;            // device slot for this iteration's loss (solver-owned), or null
+  uint64_t rng_seed = 0;
+  std::vector<std::shared_ptr<Layer>> layers;
+  std::vector<std::string> layer_names;
+  std::vector<BlobP> blobs;
+  std::vector<std::string> blob_names;
+  std::vector<bool> blob_need_backward;
+  std::vector<std::vector<Blob*>> bottom_vecs, top_vecs;
+  std::vector<std::vector<int>> bottom_ids, top_ids;
+  std::vector<std::vector<bool>> bottom_need_backward;
+  std::vector<bool> layer_need_backward;
+  std::vector<Blob*> learnable_params;
+  std::vector<float> params_lr, params_decay;
+  std::vector<Blob*> output_blobs;
+  std::vector<int> output_blob_indices;
+  // parameter arena (weights | gradients), blobs start on 1024-float boundaries
+  float* arena_w = nullptr;
+  float* arena_g = nullptr;
+  size_t arena_floats = 0;
+  std::vector<size_t> param_offsets;
+  bool owns_arena = false;
+
+  Net(const cp::NetParameter& param, int phase, uint64_t seed);
+  ~Net();
+  void forward_from_to(int start, int end);
+  void backward_from_to(int start, int end);
+  void share_trained_layers_with(const Net& other);
+  float total_loss();                   // sum over loss tops of dot(data, loss weights) — reads back (syncs)
+};
+
+struct Solver {
+  cp::SolverParameter param;
+  std::unique_ptr<Net> net, test_net;
+  int iter = 0, current_step = 0;
+  float* arena_h = nullptr;             // momentum history, same layout as the net's arena
+  SgdChunk* chunk_table = nullptr;      // device, one entry per 1024 floats
+  float* loss_hist = nullptr;           // device ring of per-iteration losses
+  static constexpr int kLossHist = 4096;
+  float smoothed_loss = 0.f;
+  explicit Solver(const cp::SolverParameter& p);
+  ~Solver();
+  float get_learning_rate();
+  void step(int iters);
+  void test_and_store(int num_steps, std::vector<float>* score);
+};
+
+}  // namespace sn
