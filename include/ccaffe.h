@@ -97,6 +97,13 @@ char* get_prototxt_data(caffenet_state* state);                                 
 const char* sparknet_version(void);
 /* 0 = fp32 FFMA validation kernels, 1 = TF32 tcgen05/TMEM kernels.  Returns the mode in effect. */
 int sparknet_set_precision(caffenet_state* state, int mode);
+int sparknet_get_precision(caffenet_state* state);
+int sparknet_tc_available(void);
+/* cudaStream_t all kernels of this library are launched on. */
+void* sparknet_compute_stream(caffenet_state* state);
+/* Device address / length in floats of the contiguous weight arena (all learnable blobs in layer
+ * order, each starting on a 1024-float boundary, padding zero).  The device copy becomes authoritative. */
+int sparknet_param_arena(caffenet_state* state, void** ptr, long* count);
 int sparknet_get_iter(caffenet_state* state);
 /* Loss of the most recent forward pass (reads one float back; synchronises the stream). */
 float sparknet_last_loss(caffenet_state* state);
@@ -120,9 +127,18 @@ int sparknet_get_pool_mask(caffenet_state* state, int layer_idx, int* out, long 
 int sparknet_set_resident_inputs(caffenet_state* state, int n);
 /* Number of kernels launched by this process so far. */
 long sparknet_kernel_launches(caffenet_state* state);
+/* CUDA-event stopwatch on the library's compute stream (bench.py times the hot path with it). */
+void sparknet_timer_start(caffenet_state* state);
+float sparknet_timer_stop_ms(caffenet_state* state);
+/* Run ONE training iteration with events around every layer (consumes one callback pair).  Fills
+ * per-layer forward/backward milliseconds (n = capacity) and the update time; returns the layer count. */
+int sparknet_profile_step(caffenet_state* state, float* fwd_ms, float* bwd_ms, float* update_ms, int n);
 /* out[i] = (((r0[i] + r1[i]) + ...) / n in IEEE fp32, replica order; all pointers are device pointers
  * on the current device (single-GPU emulation of the cross-GPU exchange; the arithmetic is the same). */
 int sparknet_average_replicas_device(const void* const* replicas, int n, long count, void* out);
+/* Same, enqueued on the compute stream and not synchronised (the multi-GPU driver gathers the
+ * replicas with NCCL on that stream first). */
+int sparknet_average_replicas_async(const void* const* replicas, int n, long count, void* out);
 
 #ifdef __cplusplus
 }

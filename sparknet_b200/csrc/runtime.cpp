@@ -972,6 +972,43 @@ void Solver::step(int iters) {
   net->overwrite_param_diffs = false;
   net->loss_log = nullptr;
 }
+// One training iteration with CUDA events around every layer's forward and backward and around the
+// update (the per-layer timing of `caffe time`, caffe/tools/caffe.cpp:290-375, on the device).
+void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_ms, float* update_ms) {
+  const int L = (int)net->layers.size();
+  std::vector<cudaEvent_t> ev((size_t)(2 * L + 3));
+  for (auto& e : ev) SN_CUDA(cudaEventCreate(&e));
+  cudaStream_t s = ctx().compute;
+  for (Blob* b : net->learnable_params) { b->data->mutable_gpu(); b->diff->mutable_gpu(); }
+  net->overwrite_param_diffs = true;
+  net->loss_log = loss_hist + (iter % kLossHist);
+  for (int i = 0; i < L; ++i) {
+    SN_CUDA(cudaEventRecord(ev[(size_t)i], s));
+    net->layers[(size_t)i]->forward(net->bottom_vecs[(size_t)i], net->top_vecs[(size_t)i]);
+  }
+  for (int i = L - 1; i >= 0; --i) {
+    SN_CUDA(cudaEventRecord(ev[(size_t)(L + (L - 1 - i))], s));
+    if (net->layer_need_backward[(size_t)i])
+      net->layers[(size_t)i]->backward(net->top_vecs[(size_t)i], net->bottom_need_backward[(size_t)i], net->bottom_vecs[(size_t)i]);
+  }
+  SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L)], s));
+  const float rate = get_learning_rate();
+  if (net->arena_floats) sgd_update(s, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
+  SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L + 1)], s));
+  SN_CUDA(cudaStreamSynchronize(s));
+  ++iter;
+  net->overwrite_param_diffs = false;
+  net->loss_log = nullptr;
+  fwd_ms->assign((size_t)L, 0.f);
+  bwd_ms->assign((size_t)L, 0.f);
+  for (int i = 0; i < L; ++i) SN_CUDA(cudaEventElapsedTime(&(*fwd_ms)[(size_t)i], ev[(size_t)i], ev[(size_t)i + 1]));
+  for (int i = L - 1; i >= 0; --i) {
+    const size_t k = (size_t)(L + (L - 1 - i));
+    SN_CUDA(cudaEventElapsedTime(&(*bwd_ms)[(size_t)i], ev[k], ev[k + 1]));
+  }
+  SN_CUDA(cudaEventElapsedTime(update_ms, ev[(size_t)(2 * L)], ev[(size_t)(2 * L + 1)]));
+  for (auto& e : ev) cudaEventDestroy(e);
+}
 void Solver::test_and_store(int num_steps, std::vector<float>* score) {   // solver.cpp:413-444
   SN_CHECK(test_net != nullptr, "solver_test: the solver has no test net");
   test_net->precision = net->precision;

@@ -151,6 +151,7 @@ struct Solver {
   ~Solver();
   float get_learning_rate();
   void step(int iters);
+  void step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_ms, float* update_ms);
   void test_and_store(int num_steps, std::vector<float>* score);
 };
 

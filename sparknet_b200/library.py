@@ -66,6 +66,10 @@ _EXTENSIONS = {
     "sparknet_inject_dropout_mask": (c_int, [c_void_p, c_int, POINTER(ctypes.c_uint), c_int]),
     "sparknet_set_precision": (c_int, [c_void_p, c_int]),
     "sparknet_version": (c_char_p, []),
+    "sparknet_get_precision": (c_int, [c_void_p]),
+    "sparknet_tc_available": (c_int, []),
+    "sparknet_compute_stream": (c_void_p, [c_void_p]),
+    "sparknet_param_arena": (c_int, [c_void_p, POINTER(c_void_p), POINTER(ctypes.c_long)]),
     "sparknet_sync": (None, [c_void_p]),
     "sparknet_num_params": (ctypes.c_long, [c_void_p]),
     "sparknet_get_weights_flat": (c_int, [c_void_p, POINTER(c_float), ctypes.c_long]),
@@ -77,7 +81,13 @@ _EXTENSIONS = {
     "sparknet_average_weights": (c_int, [c_void_p]),
     "sparknet_last_average_ms": (c_float, [c_void_p]),
     "sparknet_average_replicas_device": (c_int, [POINTER(c_void_p), c_int, ctypes.c_long, c_void_p]),
-    "sparknet_step_timing": (c_int, [c_void_p, POINTER(c_float), c_int]),
+    "sparknet_average_replicas_async": (c_int, [POINTER(c_void_p), c_int, ctypes.c_long, c_void_p]),
+    "sparknet_timer_start": (None, [c_void_p]),
+    "sparknet_timer_stop_ms": (c_float, [c_void_p]),
+    "sparknet_profile_step": (c_int, [c_void_p, POINTER(c_float), POINTER(c_float), POINTER(c_float), c_int]),
+    "sparknet_get_loss_history": (c_int, [c_void_p, POINTER(c_float), c_int]),
+    "sparknet_get_history": (c_int, [c_void_p, c_int, POINTER(c_float), ctypes.c_long]),
+    "sparknet_get_pool_mask": (c_int, [c_void_p, c_int, POINTER(c_int), ctypes.c_long]),
     # oracle-only helpers
     "oracle_pool_mask": (POINTER(c_int), [c_void_p, c_int]),
     "oracle_history": (POINTER(c_float), [c_void_p, c_int]),

@@ -1,0 +1,88 @@
+"""Weight averaging across the replicas of one box — the replacement of SparkNet's
+collect / reduce(WeightCollection.add) / scalarDivide / broadcast / setWeights round
+(src/main/scala/apps/CifarApp.scala:92-99,133-134; src/main/scala/libs/Net.scala:14-47,132-172).
+
+One process per GPU.  Every rank contributes its whole weight arena; the result on every rank is
+    (((w_0 + w_1) + w_2) + ... + w_{N-1}) / (float)N
+in IEEE fp32, summed in RANK ORDER — bit-exact against the reference's sequential JVM sum.  NCCL is
+only the transport (all-gather over NVLink/NVSwitch); the arithmetic is this library's own kernel
+(csrc/kernels.cu average_replicas), which reads the gathered replicas in rank order.  NCCL's own
+all-reduce is not used because its ring/tree order is not the reference's order.
+
+torch / torch.distributed are plumbing here (process group, device buffer for the gather)."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import numpy as np
+
+
+class _DevArray:
+    """Minimal __cuda_array_interface__ carrier so torch can wrap the library's weight arena."""
+
+    def __init__(self, ptr: int, n: int):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": "<f4", "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+class Averager:
+    def __init__(self, lib, net, rank: int, world: int):
+        self.lib, self.net, self.rank, self.world = lib, net, rank, world
+        self.method = "identity (1 replica)" if world == 1 else \
+            "NCCL all-gather over NVLink + rank-ordered fp32 reduce kernel on the weight arena"
+        if world == 1:
+            return
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        ptr, cnt = ctypes.c_void_p(), ctypes.c_long()
+        assert lib.sparknet_param_arena(net.state, ctypes.byref(ptr), ctypes.byref(cnt)) == 0
+        self.n = int(cnt.value)
+        self.arena = torch.as_tensor(_DevArray(ptr.value, self.n), device="cuda")
+        assert self.arena.data_ptr() == ptr.value
+        self.gathered = torch.empty((world, self.n), dtype=torch.float32, device="cuda")
+        self.stream = torch.cuda.ExternalStream(lib.sparknet_compute_stream(net.state))
+        self.ptrs = (ctypes.c_void_p * world)(*[self.gathered[r].data_ptr() for r in range(world)])
+        self.ev0 = torch.cuda.Event(enable_timing=True)
+        self.ev1 = torch.cuda.Event(enable_timing=True)
+
+    def _touch(self):
+        ptr, cnt = ctypes.c_void_p(), ctypes.c_long()
+        self.lib.sparknet_param_arena(self.net.state, ctypes.byref(ptr), ctypes.byref(cnt))   # heads -> device
+
+    def broadcast_from_rank0(self) -> None:
+        """All replicas start from rank 0's weights (the driver's first broadcast, CifarApp.scala:92-99)."""
+        if self.world == 1:
+            return
+        self._touch()
+        with self.torch.cuda.stream(self.stream):
+            self.dist.broadcast(self.arena, src=0)
+        self.stream.synchronize()
+
+    def average(self) -> float:
+        """Average the weights of all replicas in place; returns the device time in ms."""
+        if self.world == 1:
+            return 0.0
+        self._touch()
+        with self.torch.cuda.stream(self.stream):
+            self.ev0.record(self.stream)
+            self.dist.all_gather_into_tensor(self.gathered.view(-1), self.arena)
+        # same stream: the reduce kernel runs after the gather without a host sync
+        assert self.lib.sparknet_average_replicas_async(self.ptrs, self.world, self.n,
+                                                        ctypes.c_void_p(self.arena.data_ptr())) == 0
+        self.ev1.record(self.stream)
+        self.ev1.synchronize()
+        return float(self.ev0.elapsed_time(self.ev1))
+
+
+def sequential_average(weight_lists):
+    """Host restatement of the same arithmetic for N lists of numpy arrays (used by the gloo tests)."""
+    n = len(weight_lists)
+    out = []
+    for parts in zip(*weight_lists):
+        acc = parts[0].astype(np.float32, copy=True)
+        for p in parts[1:]:
+            acc = (acc + p).astype(np.float32)
+        out.append((acc / np.float32(n)).astype(np.float32))
+    return out

