@@ -1,12 +1,722 @@
-// gemm_tc.cu — TF32 tcgen05/TMEM contractions (placeholder until the tensor-core path lands).
+// gemm_tc.cu — TF32 tensor-core contractions for sm_100a: tcgen05.mma with the accumulator in TMEM,
+// operands staged in 128-byte-swizzled shared memory by TMA (weights) and by gather warps (the
+// implicit-GEMM views of NCHW activations), mbarrier producer/consumer pipeline, epilogue straight
+// from TMEM (bias + ReLU fused).  Replaces the reference's im2col + cublasSgemm loops
+// (caffe/src/caffe/layers/base_conv_layer.cpp:243-376, caffe/src/caffe/util/im2col.cu:9-58,
+// caffe/src/caffe/layers/inner_product_layer.cu:10-56).
+//
+// Every contraction is  D[m][n] = sum_r A(m,r) * B(n,r)  with a 128 x BN accumulator tile per CTA:
+//   warps 0-3  gather/convert the operands that cannot come through TMA (fp32 -> tf32 with
+//              round-to-nearest; TMA-fed weights come from a pre-rounded shadow copy), then run the
+//              epilogue (tcgen05.ld: warp w owns TMEM lanes 32w..32w+31 = tile rows);
+//   warp 4     allocates TMEM and issues tcgen05.mma (one thread), 4 x (128 x n_mma x 8) per 32-deep chunk;
+//   warp 5     issues the TMA loads.
+// Reductions that leave too few tiles for 148 SMs are split along r; the slices are summed in a
+// fixed order by splitk_reduce (deterministic, no atomics).
+#include <cuda.h>
+
+#include <cstring>
+#include <mutex>
+#include <type_traits>
+
+#include "gemm_ops.cuh"
 #include "kernels.hpp"
+#include "tc_prims.cuh"
+
 namespace sn {
-bool tc_available() { return false; }
-#define SN_TC_STUB fatal("TF32 tcgen05 kernels are not built into this library yet")
-void tc_conv_fwd(cudaStream_t, const ConvGeom&, const float*, const float*, const float*, float*, bool) { SN_TC_STUB; }
-void tc_conv_dgrad(cudaStream_t, const ConvGeom&, const float*, const float*, float*) { SN_TC_STUB; }
-void tc_conv_wgrad(cudaStream_t, const ConvGeom&, const float*, const float*, float*, bool) { SN_TC_STUB; }
-void tc_ip_fwd(cudaStream_t, int, int, int, const float*, const float*, const float*, float*, bool) { SN_TC_STUB; }
-void tc_ip_dgrad(cudaStream_t, int, int, int, const float*, const float*, float*) { SN_TC_STUB; }
-void tc_ip_wgrad(cudaStream_t, int, int, int, const float*, const float*, float*, bool) { SN_TC_STUB; }
+using namespace tc;
+
+constexpr int TBM = 128, TBK = 32, TSTAGES = 4;
+constexpr int kATileBytes = TBM * TBK * 4;            // 16 KB
+
+// ------------------------------------------------------------------------------------------
+// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by the 128 gather threads.
+// kMN: MN-major tile (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows
+// actually needed (128 for A, n_mma for B); rows beyond the operand's extent are zero-filled.
+// ------------------------------------------------------------------------------------------
+struct NoState {};
+
+// weights through TMA, K-major: tensor {K (contiguous), rows}; box {32, rows_box}
+struct LoadTmaK {
+  static constexpr bool kTMA = true, kMN = false;
+  typedef NoState State;
+  int rows_box;
+  __device__ uint32_t bytes() const { return (uint32_t)rows_box * 128u; }
+  __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
+    tma_load_2d(tile, tm, bar, r0, row0);
+  }
+};
+// weights through TMA, MN-major: tensor {MN (contiguous), R rows}; box {32, 32}; one box per 32 rows
+struct LoadTmaMN {
+  static constexpr bool kTMA = true, kMN = true;
+  typedef NoState State;
+  int rows;                                       // multiple of 32
+  __device__ uint32_t bytes() const { return (uint32_t)(rows / 32) * 4096u; }
+  __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
+    for (int i = 0; i < rows / 32; ++i) tma_load_2d(tile + i * 4096, tm, bar, row0 + 32 * i, r0);
+  }
+};
+
+// dense [row][r] (r contiguous), K-major tile.  128-bit path when the pitch allows it.
+struct LoadDenseK {
+  static constexpr bool kTMA = false, kMN = false;
+  typedef NoState State;
+  const float* p; int ld, nrows, nred, rows; int vec;
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    if (vec) {
+      const int c = t & 7;                         // 16-byte chunk within the 128-byte row
+      const int r = r0 + 4 * c;
+      for (int row = t >> 3; row < rows; row += 16) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int gr = row0 + row;
+        if (gr < nrows && r < r_end) {
+          const float* q = p + (size_t)gr * ld + r;
+          if (r + 3 < r_end) v = __ldg((const float4*)q);
+          else { v.x = __ldg(q); if (r + 1 < r_end) v.y = __ldg(q + 1); if (r + 2 < r_end) v.z = __ldg(q + 2); }
+        }
+        v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
+        *(float4*)(tile + off_kmajor(row, 4 * c)) = v;
+      }
+    } else {
+      const int k = t & 31, r = r0 + k;
+      for (int row = t >> 5; row < rows; row += 4) {
+        const int gr = row0 + row;
+        const float v = (gr < nrows && r < r_end) ? __ldg(p + (size_t)gr * ld + r) : 0.f;
+        *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+      }
+    }
+  }
+};
+// dense [r][mn] (mn contiguous), MN-major tile
+struct LoadDenseMN {
+  static constexpr bool kTMA = false, kMN = true;
+  typedef NoState State;
+  const float* p; int ld, nrows, nred, rows; int vec;
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    if (vec) {
+      const int ch = rows >> 2;                    // 16-byte chunks per r
+      for (int j = t; j < ch * TBK; j += 128) {
+        const int c = j % ch, k = j / ch;
+        const int mn = row0 + 4 * c, r = r0 + k;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < r_end && mn < nrows) {
+          const float* q = p + (size_t)r * ld + mn;
+          if (mn + 3 < nrows) v = __ldg((const float4*)q);
+          else { v.x = __ldg(q); if (mn + 1 < nrows) v.y = __ldg(q + 1); if (mn + 2 < nrows) v.z = __ldg(q + 2); }
+        }
+        v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
+        *(float4*)(tile + off_mnmajor(4 * c, k)) = v;
+      }
+    } else {
+      for (int j = t; j < rows * TBK; j += 128) {
+        const int m = j % rows, k = j / rows;
+        const int mn = row0 + m, r = r0 + k;
+        const float v = (r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
+        *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
+      }
+    }
+  }
+};
+
+// Any accessor of gemm_ops.cuh as a K-major tile (lane = r, warp = rows): generic, index math per element.
+template <class Acc>
+struct LoadAccK {
+  static constexpr bool kTMA = false, kMN = false;
+  typedef NoState State;
+  Acc acc; int rows;
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int k = t & 31, r = r0 + k;
+    for (int row = t >> 5; row < rows; row += 4) {
+      const float v = r < r_end ? acc(row0 + row, r) : 0.f;
+      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    }
+  }
+};
+// Any accessor as an MN-major tile (thread = row, loop over k): generic.
+template <class Acc>
+struct LoadAccMN {
+  static constexpr bool kTMA = false, kMN = true;
+  typedef NoState State;
+  Acc acc; int rows;
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    for (int m = t; m < rows; m += 128)
+      for (int k = 0; k < TBK; ++k) {
+        const int r = r0 + k;
+        const float v = r < r_end ? acc(row0 + m, r) : 0.f;
+        *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
+      }
+  }
+};
+
+// Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t owns
+// pixel row0+t for the whole reduction: its (n,ho,wo) is decomposed once, the (c,kh,kw) counter runs
+// incrementally (warp-uniform), padding is a per-thread bit test.  Lanes = consecutive pixels, so the
+// global reads are coalesced along W and the swizzled 128-byte rows are written conflict-free.
+struct LoadIm2colRowsMN {
+  static constexpr bool kTMA = false, kMN = true;
+  const float* x; ConvGeom g; int grp;
+  FastDiv dHoWo, dWo, dKhKw, dKw;
+  struct State { int base; uint32_t hmask, wmask; int c, ky, kx, delta; bool live; };
+  __device__ void init(State& s, int row0, int r_begin, int t) const {
+    const int row = row0 + t;
+    s.live = row < g.N * g.Ho * g.Wo;
+    uint32_t n = 0, pix = 0, ho = 0, wo = 0;
+    if (s.live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
+    const int hi0 = (int)ho * g.sh - g.ph, wi0 = (int)wo * g.sw - g.pw;
+    s.base = ((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0;
+    s.hmask = 0; s.wmask = 0;
+    for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) s.hmask |= 1u << k;
+    for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) s.wmask |= 1u << k;
+    if (!s.live) s.hmask = 0;
+    uint32_t c, tt, ky, kx;
+    dKhKw.divmod(r_begin, c, tt);
+    dKw.divmod(tt, ky, kx);
+    s.c = c; s.ky = ky; s.kx = kx;
+    s.delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
+  }
+  __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int K = g.Kdim();
+#pragma unroll 4
+    for (int k = 0; k < TBK; ++k) {
+      float v = 0.f;
+      if (r0 + k < r_end && r0 + k < K && ((s.hmask >> s.ky) & (s.wmask >> s.kx) & 1u)) v = __ldg(x + s.base + s.delta);
+      *(float*)(tile + off_mnmajor(t, k)) = to_tf32(v);
+      // advance (c, ky, kx) — identical in every thread
+      ++s.kx; ++s.delta;
+      if (s.kx == g.kw) {
+        s.kx = 0; ++s.ky; s.delta += g.W - g.kw;
+        if (s.ky == g.kh) { s.ky = 0; ++s.c; s.delta += (g.H - g.kh) * g.W; }
+      }
+    }
+  }
+};
+
+// Convolution backward-data A operand (stride 1): rows = input pixels, r = (co,kh,kw), MN-major.
+// value = dY[n][co][h+ph-kh][w+pw-kw] when that output position exists.
+struct LoadDgradRowsMN {
+  static constexpr bool kTMA = false, kMN = true;
+  const float* dy; ConvGeom g; int grp;
+  FastDiv dHW, dW, dKhKw, dKw;
+  struct State { int base; uint32_t hmask, wmask; int co, ky, kx, delta; };
+  __device__ void init(State& s, int row0, int r_begin, int t) const {
+    const int row = row0 + t;
+    const bool live = row < g.N * g.H * g.W;
+    uint32_t n = 0, pix = 0, h = 0, w = 0;
+    if (live) { dHW.divmod(row, n, pix); dW.divmod(pix, h, w); }
+    const int hb = (int)h + g.ph, wb = (int)w + g.pw;            // output row = hb - ky, col = wb - kx
+    s.base = ((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb;
+    s.hmask = 0; s.wmask = 0;
+    for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) s.hmask |= 1u << k;
+    for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) s.wmask |= 1u << k;
+    if (!live) s.hmask = 0;
+    uint32_t co, tt, ky, kx;
+    dKhKw.divmod(r_begin, co, tt);
+    dKw.divmod(tt, ky, kx);
+    s.co = co; s.ky = ky; s.kx = kx;
+    s.delta = (int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx;
+  }
+  __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int R = g.Og() * g.kh * g.kw;
+#pragma unroll 4
+    for (int k = 0; k < TBK; ++k) {
+      float v = 0.f;
+      if (r0 + k < r_end && r0 + k < R && ((s.hmask >> s.ky) & (s.wmask >> s.kx) & 1u)) v = __ldg(dy + s.base + s.delta);
+      *(float*)(tile + off_mnmajor(t, k)) = to_tf32(v);
+      ++s.kx; --s.delta;
+      if (s.kx == g.kw) {
+        s.kx = 0; ++s.ky; s.delta += g.kw - g.Wo;
+        if (s.ky == g.kh) { s.ky = 0; ++s.co; s.delta += g.kh * g.Wo + g.Ho * g.Wo; }
+      }
+    }
+  }
+};
+// Backward-data B operand: filters viewed as [c][(co,kh,kw)], K-major.  lane = r: its (co, tap) is
+// decomposed once per chunk; rows (input channels) are khkw apart.
+struct LoadFilterDgradK {
+  static constexpr bool kTMA = false, kMN = false;
+  typedef NoState State;
+  const float* w; ConvGeom g; int grp; int rows;
+  FastDiv dKhKw;
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int khkw = g.kh * g.kw, Cg = g.Cg();
+    const int k = t & 31, r = r0 + k;
+    const bool ok = r < r_end && r < g.Og() * khkw;
+    uint32_t co = 0, tap = 0;
+    if (ok) dKhKw.divmod(r, co, tap);
+    const float* q = w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap;
+    for (int row = t >> 5; row < rows; row += 4) {
+      const int c = row0 + row;
+      const float v = (ok && c < Cg) ? __ldg(q + (size_t)c * khkw) : 0.f;
+      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    }
+  }
+};
+// Backward-filter A operand: dY viewed as [co][(n,ho,wo)], K-major.  lane = r = (n, pix).
+struct LoadDyRowsK {
+  static constexpr bool kTMA = false, kMN = false;
+  typedef NoState State;
+  const float* dy; ConvGeom g; int grp;
+  FastDiv dHoWo;
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int HoWo = g.Ho * g.Wo;
+    const int k = t & 31, r = r0 + k;
+    const bool ok = r < r_end && r < g.N * HoWo;
+    uint32_t n = 0, pix = 0;
+    if (ok) dHoWo.divmod(r, n, pix);
+    const float* q = dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix;
+    for (int row = t >> 5; row < TBM; row += 4) {
+      const int co = row0 + row;
+      const float v = (ok && co < g.Og()) ? __ldg(q + (size_t)co * HoWo) : 0.f;
+      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    }
+  }
+};
+// Backward-filter B operand: im2col viewed as [(c,kh,kw)][(n,ho,wo)], K-major.  lane = r: its
+// (n,ho,wo), input base and padding masks are computed once per chunk; the per-row (c,kh,kw) comes
+// from a table built once per CTA in shared memory (row_tab[row] = {input offset, kh | kw << 8}).
+struct LoadIm2colColsK {
+  static constexpr bool kTMA = false, kMN = false;
+  const float* x; ConvGeom g; int grp; int rows;
+  FastDiv dHoWo, dWo, dKhKw, dKw;
+  struct State { const int2* tab; };
+  static constexpr int kTableRows = 256;
+  __device__ void build_table(int2* tab, int row0, int t) const {
+    for (int row = t; row < rows; row += 128) {
+      const int rr = row0 + row;
+      int2 e = make_int2(0, -1);
+      if (rr < g.Kdim()) {
+        uint32_t c, tt, ky, kx;
+        dKhKw.divmod(rr, c, tt);
+        dKw.divmod(tt, ky, kx);
+        e.x = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
+        e.y = (int)(ky | (kx << 8));
+      }
+      tab[row] = e;
+    }
+  }
+  __device__ void init(State&, int, int, int) const {}
+  __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int k = t & 31, r = r0 + k;
+    const bool ok = r < r_end && r < g.N * g.Ho * g.Wo;
+    uint32_t n = 0, pix = 0, ho = 0, wo = 0;
+    if (ok) { dHoWo.divmod(r, n, pix); dWo.divmod(pix, ho, wo); }
+    const int hi0 = (int)ho * g.sh - g.ph, wi0 = (int)wo * g.sw - g.pw;
+    uint32_t hmask = 0, wmask = 0;
+    for (int q = 0; q < g.kh; ++q) if (hi0 + q >= 0 && hi0 + q < g.H) hmask |= 1u << q;
+    for (int q = 0; q < g.kw; ++q) if (wi0 + q >= 0 && wi0 + q < g.W) wmask |= 1u << q;
+    if (!ok) hmask = 0;
+    const float* base = x + ((size_t)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0;
+    for (int row = t >> 5; row < rows; row += 4) {
+      const int2 e = s.tab[row];
+      float v = 0.f;
+      if (e.y >= 0 && ((hmask >> (e.y & 255)) & (wmask >> (e.y >> 8)) & 1u)) v = __ldg(base + e.x);
+      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    }
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// Epilogues: row(m) prepares the per-row context once per thread, store(ctx, n, acc) writes D[m][n].
+// ------------------------------------------------------------------------------------------
+struct TEpiConvFwd {       // m = output pixel, n = co in group; y NCHW; bias + optional ReLU
+  float* y; const float* bias; int P, HoWo, Cout, Og, grp, relu; FastDiv dHoWo;
+  struct Ctx { float* p; bool ok; };
+  __device__ Ctx row(int m) const {
+    Ctx c; c.ok = m < P;
+    uint32_t img = 0, pix = 0;
+    if (c.ok) dHoWo.divmod(m, img, pix);
+    c.p = y + ((size_t)img * Cout + grp * Og) * HoWo + pix;
+    return c;
+  }
+  __device__ void store(const Ctx& c, int n, float v) const {
+    if (!c.ok || n >= Og) return;
+    if (bias) v += __ldg(bias + grp * Og + n);
+    if (relu) v = fmaxf(v, 0.f);
+    c.p[(size_t)n * HoWo] = v;
+  }
+};
+struct TEpiConvDgrad {     // m = input pixel, n = c in group
+  float* dx; int P, HW, C, Cg, grp; FastDiv dHW;
+  struct Ctx { float* p; bool ok; };
+  __device__ Ctx row(int m) const {
+    Ctx c; c.ok = m < P;
+    uint32_t img = 0, pix = 0;
+    if (c.ok) dHW.divmod(m, img, pix);
+    c.p = dx + ((size_t)img * C + grp * Cg) * HW + pix;
+    return c;
+  }
+  __device__ void store(const Ctx& c, int n, float v) const {
+    if (c.ok && n < Cg) c.p[(size_t)n * HW] = v;
+  }
+};
+struct TEpiRowMajor {      // p[m*ld + n] (+)= v
+  float* p; int ld, M, N, accumulate;
+  struct Ctx { float* q; bool ok; };
+  __device__ Ctx row(int m) const { Ctx c; c.ok = m < M; c.q = p + (size_t)m * ld; return c; }
+  __device__ void store(const Ctx& c, int n, float v) const {
+    if (c.ok && n < N) c.q[n] = accumulate ? c.q[n] + v : v;
+  }
+};
+struct TEpiTransposed {    // p[n*ld + m] = v + bias[m] (+ReLU)
+  float* p; int ld, M, N; const float* bias; int relu;
+  struct Ctx { float* q; float b; bool ok; };
+  __device__ Ctx row(int m) const {
+    Ctx c; c.ok = m < M; c.q = p + m; c.b = (c.ok && bias) ? __ldg(bias + m) : 0.f;
+    return c;
+  }
+  __device__ void store(const Ctx& c, int n, float v) const {
+    if (!c.ok || n >= N) return;
+    v += c.b;
+    if (relu) v = fmaxf(v, 0.f);
+    c.q[(size_t)n * ld] = v;
+  }
+};
+
+// ------------------------------------------------------------------------------------------
+// The kernel
+// ------------------------------------------------------------------------------------------
+template <int BN>
+struct TcCfg {
+  static constexpr int kBTileBytes = BN * TBK * 4;
+  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kSmemBytes = TSTAGES * kStageBytes + 1024;     // + slack to align the tiles to 1024 B
+  static constexpr uint32_t kTmemCols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+};
+
+template <class AL, class BL, class EP, int BN, bool SPLIT>
+__global__ void __launch_bounds__(192, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, AL al, BL bl, EP ep,
+               int M, int N, int R, int r_split_len, int n_mma, float* __restrict__ ws) {
+  typedef TcCfg<BN> Cfg;
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tmem_full_bar;
+  __shared__ uint32_t tmem_base_smem;
+  __shared__ int2 row_table[LoadIm2colColsK::kTableRows];
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int m0 = blockIdx.x * TBM, n0 = blockIdx.y * n_mma;
+  const int r_begin = blockIdx.z * r_split_len;
+  const int r_end = min(R, r_begin + r_split_len);
+  const int nchunks = r_end > r_begin ? (r_end - r_begin + TBK - 1) / TBK : 0;
+
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  constexpr bool kAnySimt = !AL::kTMA || !BL::kTMA, kAnyTma = AL::kTMA || BL::kTMA;
+
+  if (tid == 0) {
+    for (int s = 0; s < TSTAGES; ++s) {
+      mbar_init(&full_bar[s], (kAnySimt ? 128u : 0u) + (kAnyTma ? 1u : 0u));
+      mbar_init(&empty_bar[s], 1u);
+    }
+    mbar_init(&tmem_full_bar, 1u);
+    fence_barrier_init();
+    if (AL::kTMA) tma_prefetch_desc(&tmA);
+    if (BL::kTMA) tma_prefetch_desc(&tmB);
+  }
+  if (warp == 4) tmem_alloc<Cfg::kTmemCols>(&tmem_base_smem);
+  if constexpr (std::is_same<BL, LoadIm2colColsK>::value) {
+    if (warp < 4) bl.build_table(row_table, n0, tid);
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp < 4) {
+    // ---------------- gather producers ----------------
+    if (kAnySimt && nchunks > 0) {
+      typename AL::State sa;
+      typename BL::State sb;
+      if constexpr (!AL::kTMA) al.init(sa, m0, r_begin, tid);
+      if constexpr (!BL::kTMA) {
+        bl.init(sb, n0, r_begin, tid);
+        if constexpr (std::is_same<BL, LoadIm2colColsK>::value) sb.tab = row_table;
+      }
+      for (int kc = 0; kc < nchunks; ++kc) {
+        const int s = kc % TSTAGES;
+        mbar_wait(&empty_bar[s], ((kc / TSTAGES) & 1) ^ 1);
+        uint8_t* a_tile = smem + s * Cfg::kStageBytes;
+        uint8_t* b_tile = a_tile + kATileBytes;
+        const int r0 = r_begin + kc * TBK;
+        if constexpr (!AL::kTMA) al.load(sa, a_tile, m0, r0, r_end, tid);
+        if constexpr (!BL::kTMA) bl.load(sb, b_tile, n0, r0, r_end, tid);
+        fence_proxy_async_smem();
+        mbar_arrive(&full_bar[s]);
+      }
+    }
+    // ---------------- epilogue ----------------
+    if (nchunks > 0) {
+      mbar_wait(&tmem_full_bar, 0);
+      tc_fence_after_sync();
+    }
+    const int m = m0 + tid;                                    // TMEM lane == tile row
+    typename EP::Ctx ctx;
+    if constexpr (!SPLIT) ctx = ep.row(m);
+    for (int c0 = 0; c0 < n_mma; c0 += 16) {
+      uint32_t v[16];
+      if (nchunks > 0) {
+        tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = 0u;
+      }
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int n = n0 + c0 + j;
+        const float acc = __uint_as_float(v[j]);
+        if constexpr (SPLIT) {
+          if (m < M && n < N) ws[((size_t)blockIdx.z * M + m) * N + n] = acc;
+        } else {
+          ep.store(ctx, n, acc);
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // ---------------- MMA issuer ----------------
+    if (lane == 0 && nchunks > 0) {
+      const uint32_t idesc = make_idesc_tf32(TBM, n_mma, AL::kMN ? 1 : 0, BL::kMN ? 1 : 0);
+      for (int kc = 0; kc < nchunks; ++kc) {
+        const int s = kc % TSTAGES;
+        mbar_wait(&full_bar[s], (kc / TSTAGES) & 1);
+        tc_fence_after_sync();
+        const uint32_t a_addr = smem_u32(smem + s * Cfg::kStageBytes);
+        const uint32_t b_addr = a_addr + kATileBytes;
+#pragma unroll
+        for (int j = 0; j < TBK / 8; ++j) {
+          const uint64_t adesc = AL::kMN ? make_smem_desc(a_addr + j * 1024, 4096, 1024) : make_smem_desc(a_addr + j * 32, 16, 1024);
+          const uint64_t bdesc = BL::kMN ? make_smem_desc(b_addr + j * 1024, 4096, 1024) : make_smem_desc(b_addr + j * 32, 16, 1024);
+          mma_tf32(tmem_base, adesc, bdesc, idesc, (kc | j) != 0 ? 1u : 0u);
+        }
+        mma_commit(&empty_bar[s]);          // smem stage free once these MMAs have read it
+      }
+      mma_commit(&tmem_full_bar);           // accumulator complete
+    }
+  } else {
+    // ---------------- TMA issuer ----------------
+    if (kAnyTma && lane == 0 && nchunks > 0) {
+      uint32_t bytes = 0;
+      if constexpr (AL::kTMA) bytes += al.bytes();
+      if constexpr (BL::kTMA) bytes += bl.bytes();
+      for (int kc = 0; kc < nchunks; ++kc) {
+        const int s = kc % TSTAGES;
+        mbar_wait(&empty_bar[s], ((kc / TSTAGES) & 1) ^ 1);
+        uint8_t* a_tile = smem + s * Cfg::kStageBytes;
+        uint8_t* b_tile = a_tile + kATileBytes;
+        const int r0 = r_begin + kc * TBK;
+        mbar_arrive_expect_tx(&full_bar[s], bytes);
+        if constexpr (AL::kTMA) al.issue(&tmA, a_tile, &full_bar[s], m0, r0);
+        if constexpr (BL::kTMA) bl.issue(&tmB, b_tile, &full_bar[s], n0, r0);
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 4) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+}
+
+// deterministic slice reduction (ascending z) + the per-element epilogue of gemm_ops.cuh
+template <class E>
+__global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  const size_t total = (size_t)M * N;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    float acc = ws[i];
+    for (int z = 1; z < splits; ++z) acc += ws[(size_t)z * total + i];
+    epi((int)(i / N), (int)(i % N), acc);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    SN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    if (!p || qres != cudaDriverEntryPointSuccess) fatal("cuTensorMapEncodeTiled is not available from this driver");
+    fn = (EncodeTiledFn)p;
+  });
+  return fn;
+}
+// 2-D fp32 tensor {inner (contiguous), outer} with pitch (bytes, multiple of 16); box {box_inner = 32, box_outer}
+static CUtensorMap make_tmap(const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes, uint32_t box_outer) {
+  CUtensorMap m;
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {pitch_bytes};
+  cuuint32_t box[2] = {32, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  if (((uintptr_t)base & 15) || (pitch_bytes & 15)) fatal("TMA tensor map needs 16-byte aligned base and pitch");
+  CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) fatal("cuTensorMapEncodeTiled failed with %d (inner %llu outer %llu pitch %llu box %u)", (int)r,
+                               (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)pitch_bytes, box_outer);
+  return m;
+}
+static CUtensorMap dummy_tmap() {
+  CUtensorMap m;
+  memset(&m, 0, sizeof(m));
+  return m;
+}
+
+static int pick_bn(int N) { return N <= 64 ? 64 : (N <= 128 ? 128 : 256); }
+// N tile width: split N evenly into ceil(N/256) tiles, rounded up to the MMA granularity of 16
+static int pick_n_mma(int N) {
+  const int tiles = (N + 255) / 256;
+  int w = (N + tiles - 1) / tiles;
+  w = (w + 15) / 16 * 16;
+  return w < 16 ? 16 : w;
+}
+
+template <class AL, class BL, class EP, class RE, int BN>
+static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap& tmB, AL al, BL bl, EP ep, RE reduce_epi,
+                      int M, int N, int R, int n_mma) {
+  typedef TcCfg<BN> Cfg;
+  dim3 grid((M + TBM - 1) / TBM, (N + n_mma - 1) / n_mma, 1);
+  const int splits = splitk_slices((int)(grid.x * grid.y), R);
+  static bool attr_done_split = false, attr_done = false;
+  if (splits == 1) {
+    auto kfn = gemm_tc_kernel<AL, BL, EP, BN, false>;
+    if (!attr_done) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes)); attr_done = true; }
+    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
+    count_launch();
+  } else {
+    int len = (R + splits - 1) / splits;
+    len = (len + TBK - 1) / TBK * TBK;
+    grid.z = (R + len - 1) / len;
+    float* ws = get_workspace((size_t)grid.z * M * N);
+    auto kfn = gemm_tc_kernel<AL, BL, EP, BN, true>;
+    if (!attr_done_split) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes)); attr_done_split = true; }
+    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
+    const size_t total = (size_t)M * N;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    tc_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ws, (int)grid.z, M, N, reduce_epi);
+    count_launch(2);
+  }
+  SN_CUDA(cudaGetLastError());
+}
+// rows_setter(n_mma) lets the caller size loaders / TMA boxes for the chosen tile width
+template <class AL, class BL, class EP, class RE>
+static void launch_tc(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap& tmB, AL al, BL bl, EP ep, RE re, int M, int N,
+                      int R, int n_mma) {
+  switch (pick_bn(n_mma)) {
+    case 64: launch_bn<AL, BL, EP, RE, 64>(s, tmA, tmB, al, bl, ep, re, M, N, R, n_mma); break;
+    case 128: launch_bn<AL, BL, EP, RE, 128>(s, tmA, tmB, al, bl, ep, re, M, N, R, n_mma); break;
+    default: launch_bn<AL, BL, EP, RE, 256>(s, tmA, tmB, al, bl, ep, re, M, N, R, n_mma); break;
+  }
+}
+
+bool tc_available() { return true; }
+
+// Rounded (tf32, round-to-nearest) shadow copies of weight blobs for the TMA-fed operands.  Keyed by
+// the fp32 pointer; refreshed by tc_refresh_shadow whenever the runtime knows the weights changed.
+__global__ void round_tf32_kernel(size_t n, const float* __restrict__ src, float* __restrict__ dst) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = to_tf32(src[i]);
+}
+void tc_round_to_tf32(cudaStream_t s, size_t n, const float* src, float* dst) {
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  round_tf32_kernel<<<blocks, 256, 0, s>>>(n, src, dst);
+  count_launch();
+}
+
+// ---- convolution -------------------------------------------------------------------------------
+void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float* w_tf32, const float* bias, float* y, bool relu) {
+  const int P = g.N * g.Ho * g.Wo, K = g.Kdim(), Og = g.Og();
+  const int n_mma = pick_n_mma(Og);
+  for (int grp = 0; grp < g.group; ++grp) {
+    LoadIm2colRowsMN al{x, g, grp, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+    TEpiConvFwd ep{y, bias, P, g.Ho * g.Wo, g.Cout, Og, grp, relu ? 1 : 0, FastDiv(g.Ho * g.Wo)};
+    EpiConvFwd re{y, bias, g, grp, relu ? 1 : 0, FastDiv(g.Ho * g.Wo)};
+    const float* wg = w_tf32 + (size_t)grp * Og * K;
+    if (K % 4 == 0 && ((uintptr_t)wg & 15) == 0) {
+      CUtensorMap tmB = make_tmap(wg, (uint64_t)K, (uint64_t)Og, (uint64_t)K * 4, (uint32_t)n_mma);
+      launch_tc(s, dummy_tmap(), tmB, al, LoadTmaK{n_mma}, ep, re, P, Og, K, n_mma);
+    } else {
+      LoadDenseK bl{wg, K, Og, K, n_mma, 0};
+      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Og, K, n_mma);
+    }
+  }
+}
+void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx) {
+  const int P = g.N * g.H * g.W, R = g.Og() * g.kh * g.kw, Cg = g.Cg();
+  const int n_mma = pick_n_mma(Cg);
+  for (int grp = 0; grp < g.group; ++grp) {
+    TEpiConvDgrad ep{dx, P, g.H * g.W, g.C, Cg, grp, FastDiv(g.H * g.W)};
+    EpiConvDgrad re{dx, g, grp, FastDiv(g.H * g.W)};
+    LoadFilterDgradK bl{w, g, grp, n_mma, FastDiv(g.kh * g.kw)};
+    if (g.sh == 1 && g.sw == 1) {
+      LoadDgradRowsMN al{dy, g, grp, FastDiv(g.H * g.W), FastDiv(g.W), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Cg, R, n_mma);
+    } else {
+      LoadAccMN<DgradRows> al{make_dgrad_rows(dy, g, grp), TBM};
+      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Cg, R, n_mma);
+    }
+  }
+}
+void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate) {
+  const int R = g.N * g.Ho * g.Wo, K = g.Kdim(), Og = g.Og();
+  const int n_mma = pick_n_mma(K);
+  for (int grp = 0; grp < g.group; ++grp) {
+    float* dwg = dw + (size_t)grp * Og * K;
+    LoadDyRowsK al{dy, g, grp, FastDiv(g.Ho * g.Wo)};
+    LoadIm2colColsK bl{x, g, grp, n_mma, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+    TEpiRowMajor ep{dwg, K, Og, K, accumulate ? 1 : 0};
+    EpiRowMajor re{dwg, K, Og, K, accumulate ? 1 : 0};
+    launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, Og, K, R, n_mma);
+  }
+}
+
+// ---- inner product -------------------------------------------------------------------------------
+// D[m = out][n = batch] = sum_k W[m][k] X[n][k];  Y[n][m] = D + bias[m]
+void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu) {
+  const int n_mma = pick_n_mma(batch);
+  LoadDenseK bl{x, K, batch, K, n_mma, (K % 4 == 0 && ((uintptr_t)x & 15) == 0) ? 1 : 0};
+  TEpiTransposed ep{y, out, out, batch, bias, relu ? 1 : 0};
+  EpiTransposed re{y, out, out, batch, bias, relu ? 1 : 0};
+  if (K % 4 == 0 && ((uintptr_t)w_tf32 & 15) == 0) {
+    CUtensorMap tmA = make_tmap(w_tf32, (uint64_t)K, (uint64_t)out, (uint64_t)K * 4, TBM);
+    launch_tc(s, tmA, dummy_tmap(), LoadTmaK{TBM}, bl, ep, re, out, batch, K, n_mma);
+  } else {
+    LoadDenseK al{w_tf32, K, out, K, TBM, 0};
+    launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, out, batch, K, n_mma);
+  }
+}
+// D[m = k_in][n = batch] = sum_o W[o][m] dY[n][o];  dX[n][m] = D
+void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w_tf32, float* dx) {
+  const int n_mma = pick_n_mma(batch);
+  LoadDenseK bl{dy, out, batch, out, n_mma, (out % 4 == 0 && ((uintptr_t)dy & 15) == 0) ? 1 : 0};
+  TEpiTransposed ep{dx, K, K, batch, nullptr, 0};
+  EpiTransposed re{dx, K, K, batch, nullptr, 0};
+  if (K % 4 == 0 && ((uintptr_t)w_tf32 & 15) == 0) {
+    CUtensorMap tmA = make_tmap(w_tf32, (uint64_t)K, (uint64_t)out, (uint64_t)K * 4, 32);
+    launch_tc(s, tmA, dummy_tmap(), LoadTmaMN{TBM}, bl, ep, re, K, batch, out, n_mma);
+  } else {
+    LoadDenseMN al{w_tf32, K, K, out, TBM, 0};
+    launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, K, batch, out, n_mma);
+  }
+}
+// D[m = out][n = k_in] = sum_b dY[b][m] X[b][n];  dW[m][n] (+)= D
+void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate) {
+  const int n_mma = pick_n_mma(K);
+  LoadDenseMN al{dy, out, out, batch, TBM, (out % 4 == 0 && ((uintptr_t)dy & 15) == 0) ? 1 : 0};
+  LoadDenseMN bl{x, K, K, batch, n_mma, (K % 4 == 0 && ((uintptr_t)x & 15) == 0) ? 1 : 0};
+  TEpiRowMajor ep{dw, K, out, K, accumulate ? 1 : 0};
+  EpiRowMajor re{dw, K, out, K, accumulate ? 1 : 0};
+  launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, out, K, batch, n_mma);
+}
+
 }  // namespace sn

@@ -30,12 +30,15 @@ void ffma_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, co
 int splitk_slices(int tiles, int R);
 
 // ---- TF32 tcgen05 contractions (gemm_tc.cu) --------------------------------------------------
-bool tc_available();                           // false until the tcgen05 path is compiled in
-void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float* w, const float* bias, float* y, bool relu);
+bool tc_available();
+// dst[i] = tf32(src[i]) (round to nearest): the pre-rounded weight copy the TMA-fed operands read
+void tc_round_to_tf32(cudaStream_t s, size_t n, const float* src, float* dst);
+// `w_tf32`: weights already rounded to tf32 (tc_round_to_tf32); all other operands are rounded on the fly
+void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);
 void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx);
 void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate);
-void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w, const float* bias, float* y, bool relu);
-void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w, float* dx);
+void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);
+void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w_tf32, float* dx);
 void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);
 
 // ---- bandwidth-bound kernels (kernels.cu) ----------------------------------------------------

@@ -102,6 +102,7 @@ const float* Storage::gpu() {
 float* Storage::mutable_gpu() {
   gpu();
   head = AT_DEVICE;
+  ++gen;
   return dev;
 }
 float* Storage::mutable_cpu() {
@@ -122,6 +123,7 @@ float* Storage::mutable_cpu() {
     default: break;
   }
   head = AT_HOST;
+  ++gen;
   return host;
 }
 void Blob::reshape(const std::vector<int>& s) {
@@ -167,6 +169,16 @@ static void fill_blob(const cp::FillerParameter& f, Blob* b) {
   }
 }
 
+const float* Layer::weights_tf32() {
+  Storage* st = blobs[0]->data.get();
+  const float* w = st->gpu();
+  if (!w_shadow) SN_CUDA(cudaMalloc(&w_shadow, st->count * sizeof(float)));
+  if (w_shadow_gen != st->gen) {
+    tc_round_to_tf32(ctx().compute, st->count, w, w_shadow);
+    w_shadow_gen = st->gen;
+  }
+  return w_shadow;
+}
 void Layer::set_loss_weights(const std::vector<Blob*>& top) {   // layer.hpp:405-427
   loss.assign(top.size(), 0.f);
   for (size_t i = 0; i < lp.loss_weight.size() && i < top.size(); ++i) {
@@ -324,11 +336,10 @@ struct ConvolutionLayer : Layer {
   }
   void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const float* x = bottom[0]->data->gpu();
-    const float* w = blobs[0]->data->gpu();
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
-    if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, w, b, y, fuse_relu);
-    else ffma_conv_fwd(S(), g, x, w, b, y, fuse_relu);
+    if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, weights_tf32(), b, y, fuse_relu);
+    else ffma_conv_fwd(S(), g, x, blobs[0]->data->gpu(), b, y, fuse_relu);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     const float* dy = top[0]->diff->gpu();
@@ -381,11 +392,10 @@ struct InnerProductLayer : Layer {
   }
   void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const float* x = bottom[0]->data->gpu();
-    const float* w = blobs[0]->data->gpu();
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
-    if (net->precision == PREC_TF32) tc_ip_fwd(S(), M, N, K, x, w, b, y, fuse_relu);
-    else ffma_ip_fwd(S(), M, N, K, x, w, b, y, fuse_relu);
+    if (net->precision == PREC_TF32) tc_ip_fwd(S(), M, N, K, x, weights_tf32(), b, y, fuse_relu);
+    else ffma_ip_fwd(S(), M, N, K, x, blobs[0]->data->gpu(), b, y, fuse_relu);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     const float* dy = top[0]->diff->gpu();
@@ -398,10 +408,9 @@ struct InnerProductLayer : Layer {
     }
     if (bias_term && param_propagate_down[1]) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
     if (pd[0]) {
-      const float* w = blobs[0]->data->gpu();
       float* dx = bottom[0]->diff->mutable_gpu();
-      if (net->precision == PREC_TF32) tc_ip_dgrad(S(), M, N, K, dy, w, dx);
-      else ffma_ip_dgrad(S(), M, N, K, dy, w, dx);
+      if (net->precision == PREC_TF32) tc_ip_dgrad(S(), M, N, K, dy, weights_tf32(), dx);
+      else ffma_ip_dgrad(S(), M, N, K, dy, blobs[0]->data->gpu(), dx);
     }
   }
 };
@@ -967,6 +976,7 @@ void Solver::step(int iters) {
     }
     const float rate = get_learning_rate();
     if (net->arena_floats) sgd_update(ctx().compute, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
+    for (Blob* b : net->learnable_params) ++b->data->gen;    // weights changed on the device
     ++iter;
   }
   net->overwrite_param_diffs = false;
@@ -996,6 +1006,7 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
   if (net->arena_floats) sgd_update(s, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
   SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L + 1)], s));
   SN_CUDA(cudaStreamSynchronize(s));
+  for (Blob* b : net->learnable_params) ++b->data->gen;
   ++iter;
   net->overwrite_param_diffs = false;
   net->loss_log = nullptr;

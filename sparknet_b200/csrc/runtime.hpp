@@ -50,6 +50,7 @@ struct Storage {
   float* host = nullptr;
   bool owns_dev = true;
   Head head = UNINIT;
+  uint64_t gen = 0;              // bumped whenever the contents may have changed (host or device write access)
   explicit Storage(size_t n) : count(n) {}
   Storage(size_t n, float* arena_ptr) : count(n), dev(arena_ptr), owns_dev(false) {}
   ~Storage();
@@ -101,6 +102,10 @@ struct Layer {
   virtual void backward(const std::vector<Blob*>& top, const std::vector<bool>& pd, const std::vector<Blob*>& bottom) = 0;
   virtual bool is_loss() const { return false; }
   void set_loss_weights(const std::vector<Blob*>& top);
+  // tf32-rounded copy of blobs[0] for the TMA-fed tensor-core operands, re-rounded when the weights changed
+  float* w_shadow = nullptr;
+  uint64_t w_shadow_gen = ~0ull;
+  const float* weights_tf32();
 };
 
 struct Net {

@@ -1,0 +1,93 @@
+"""TF32 tensor-core mode (tcgen05/TMEM/TMA kernels of csrc/gemm_tc.cu) against the CPU oracle.
+north_star tolerance: per-layer forward and backward outputs within 1e-3 relative (normwise:
+max|a-b| / max|b|).  The same cases run in FFMA mode at 1e-5 in test_gpu_layers.py."""
+import numpy as np
+import pytest
+
+from sparknet_b200 import zoo
+from sparknet_b200.layers import InnerProductLayer, ReLULayer, gaussian
+from sparknet_b200.net import CaffeNet, MinibatchSource
+from tests.harness import assert_mostly_close, fptr, rel_err, synthetic_batches
+from tests.test_gpu_layers import CONV_CASES, assert_close, conv_layer, run_pair
+
+pytestmark = pytest.mark.gpu
+F = np.float32
+TOL = 1e-3
+
+
+def test_tc_kernels_are_built(product):
+    assert product.sparknet_tc_available() == 1
+
+
+@pytest.mark.parametrize("shape,num_output,kw", CONV_CASES)
+def test_convolution_tf32(oracle, product, shape, num_output, kw):
+    x = np.random.default_rng(1701).standard_normal(shape).astype(F)
+    l = conv_layer("conv", "data", num_output, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5), **kw)
+    r = run_pair(oracle, product, {"data": x}, [l], "conv", "conv", precision=1)
+    assert_close(r["fwd"][0]["conv"], r["fwd"][1]["conv"], TOL, "top")
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["conv"])):
+        assert_close(a, b, TOL, f"param diff {j}")
+
+
+def test_convolution_relu_fusion_tf32(oracle, product):
+    x = np.random.default_rng(5).standard_normal((2, 8, 9, 9)).astype(F)
+    l = conv_layer("conv", "data", 16, kernel_size=[3], pad=[1], weight_filler=gaussian(0.1), bias_filler=gaussian(0.1))
+    r = run_pair(oracle, product, {"data": x}, [l, ReLULayer("relu", ["conv"])], "conv", "conv", precision=1)
+    assert np.all(r["fwd"][1]["conv"] >= 0)
+    assert_close(r["fwd"][0]["conv"], r["fwd"][1]["conv"], TOL, "relu(conv)")
+
+
+def test_convolution_stride2_dgrad_generic_path_tf32(oracle, product):
+    x = np.random.default_rng(8).standard_normal((2, 6, 11, 9)).astype(F)
+    l = conv_layer("conv", "data", 10, kernel_size=[3], stride=[2], pad=[1], weight_filler=gaussian(0.1), bias_filler=gaussian(0.1))
+    r = run_pair(oracle, product, {"data": x}, [l], "conv", "conv", precision=1)
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+
+
+@pytest.mark.parametrize("shape,n_out", [((7, 50), 13), ((64, 50, 4, 4), 500), ((8, 256, 6, 6), 512),
+                                         ((100, 64), 10), ((5, 4096), 1000), ((256, 1024), 384), ((33, 500), 10)])
+def test_inner_product_tf32(oracle, product, shape, n_out):
+    x = np.random.default_rng(11).standard_normal(shape).astype(F)
+    l = InnerProductLayer("ip", ["data"], n_out, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5))
+    r = run_pair(oracle, product, {"data": x}, [l], "ip", "ip", precision=1)
+    assert_close(r["fwd"][0]["ip"], r["fwd"][1]["ip"], TOL, "top")
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["ip"])):
+        assert_close(a, b, TOL, f"param diff {j}")
+
+
+def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
+    """The TMA-fed operands read a tf32-rounded copy of the weights; it must track setWeights and SGD."""
+    sol = zoo.solver_with_net("lenet", train_bs=16, test_bs=16, random_seed=1701, display=0)
+    o, p = CaffeNet.from_solver(sol, oracle), CaffeNet.from_solver(sol, product)
+    product.sparknet_set_precision(p.state, 1)
+    imgs, labs = synthetic_batches("lenet", 3, 16)
+    o.setTrainData(MinibatchSource(imgs, labs)); p.setTrainData(MinibatchSource(imgs, labs))
+    p.forward()                                    # shadow built from the product's own fillers
+    p.setWeights(o.getWeights())                   # host write: shadow must be rebuilt
+    o.forward(); p.forward()
+    do, dp = o.getData(), p.getData()
+    for k in ("conv1", "conv2", "ip1", "ip2"):
+        assert rel_err(dp[k], do[k]) <= TOL, k
+    o.train(3); p.train(3)                         # device-side updates: shadow must follow
+    o.forward(); p.forward()
+    do, dp = o.getData(), p.getData()
+    for k in ("conv1", "conv2", "ip1", "ip2"):
+        assert rel_err(dp[k], do[k]) <= 3 * TOL, k
+    o.close(); p.close()
+
+
+@pytest.mark.parametrize("name,batch", [("lenet", 16), ("cifar10_quick", 10), ("cifar10_full", 10)])
+def test_nets_forward_tf32(oracle, product, name, batch):
+    sol = zoo.solver_with_net(name, train_bs=batch, test_bs=batch, random_seed=1701, display=0)
+    o, p = CaffeNet.from_solver(sol, oracle), CaffeNet.from_solver(sol, product)
+    product.sparknet_set_precision(p.state, 1)
+    imgs, labs = synthetic_batches(name, 1, batch)
+    o.setTrainData(MinibatchSource(imgs, labs)); p.setTrainData(MinibatchSource(imgs, labs))
+    p.setWeights(o.getWeights())
+    o.forward(); p.forward()
+    do, dp = o.getData(), p.getData()
+    for k in do:
+        assert rel_err(dp[k], do[k]) <= 3 * TOL, (k, rel_err(dp[k], do[k]))     # error compounds over the depth
+    o.close(); p.close()
