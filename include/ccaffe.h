@@ -127,6 +127,9 @@ int sparknet_get_pool_mask(caffenet_state* state, int layer_idx, int* out, long 
 int sparknet_set_resident_inputs(caffenet_state* state, int n);
 /* Number of kernels launched by this process so far. */
 long sparknet_kernel_launches(caffenet_state* state);
+/* Test hook for the tensor-core GEMM core: D[M][N] = A x B^T, host pointers.  a_mn/b_mn: 0 = operand
+ * stored [rows][R], 1 = stored [R][rows]; tma_a: feed A through TMA. */
+int sparknet_test_tc_gemm(int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D);
 /* CUDA-event stopwatch on the library's compute stream (bench.py times the hot path with it). */
 void sparknet_timer_start(caffenet_state* state);
 float sparknet_timer_stop_ms(caffenet_state* state);

@@ -46,7 +46,8 @@ struct LoadTmaK {
     tma_load_2d(tile, tm, bar, r0, row0);
   }
 };
-// weights through TMA, MN-major: tensor {MN (contiguous), R rows}; box {32, 32}; one box per 32 rows
+// weights through TMA, MN-major: tensor {MN (contiguous), R rows}; box {32, 32} with the 32-byte-atom
+// 128-byte swizzle (CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B); one box per 32 rows
 struct LoadTmaMN {
   static constexpr bool kTMA = true, kMN = true;
   typedef NoState State;
@@ -489,8 +490,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const uint32_t b_addr = a_addr + kATileBytes;
 #pragma unroll
         for (int j = 0; j < TBK / 8; ++j) {
-          const uint64_t adesc = AL::kMN ? make_smem_desc(a_addr + j * 1024, 4096, 1024) : make_smem_desc(a_addr + j * 32, 16, 1024);
-          const uint64_t bdesc = BL::kMN ? make_smem_desc(b_addr + j * 1024, 4096, 1024) : make_smem_desc(b_addr + j * 32, 16, 1024);
+          const uint64_t adesc = AL::kMN ? make_smem_desc(a_addr + j * 1024, 4096, 512, kLayoutSW128Base32)
+                                         : make_smem_desc(a_addr + j * 32, 16, 1024, kLayoutSW128);
+          const uint64_t bdesc = BL::kMN ? make_smem_desc(b_addr + j * 1024, 4096, 512, kLayoutSW128Base32)
+                                         : make_smem_desc(b_addr + j * 32, 16, 1024, kLayoutSW128);
           mma_tf32(tmem_base, adesc, bdesc, idesc, (kc | j) != 0 ? 1u : 0u);
         }
         mma_commit(&empty_bar[s]);          // smem stage free once these MMAs have read it
@@ -550,7 +553,8 @@ static EncodeTiledFn encode_fn() {
   return fn;
 }
 // 2-D fp32 tensor {inner (contiguous), outer} with pitch (bytes, multiple of 16); box {box_inner = 32, box_outer}
-static CUtensorMap make_tmap(const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes, uint32_t box_outer) {
+static CUtensorMap make_tmap(const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes, uint32_t box_outer,
+                             bool mn_major = false) {
   CUtensorMap m;
   cuuint64_t dims[2] = {inner, outer};
   cuuint64_t strides[1] = {pitch_bytes};
@@ -558,7 +562,8 @@ static CUtensorMap make_tmap(const float* base, uint64_t inner, uint64_t outer, 
   cuuint32_t estr[2] = {1, 1};
   if (((uintptr_t)base & 15) || (pitch_bytes & 15)) fatal("TMA tensor map needs 16-byte aligned base and pitch");
   CUresult r = encode_fn()(&m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           mn_major ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) fatal("cuTensorMapEncodeTiled failed with %d (inner %llu outer %llu pitch %llu box %u)", (int)r,
                                (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)pitch_bytes, box_outer);
@@ -702,7 +707,7 @@ void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, con
   TEpiTransposed ep{dx, K, K, batch, nullptr, 0};
   EpiTransposed re{dx, K, K, batch, nullptr, 0};
   if (K % 4 == 0 && ((uintptr_t)w_tf32 & 15) == 0) {
-    CUtensorMap tmA = make_tmap(w_tf32, (uint64_t)K, (uint64_t)out, (uint64_t)K * 4, 32);
+    CUtensorMap tmA = make_tmap(w_tf32, (uint64_t)K, (uint64_t)out, (uint64_t)K * 4, 32, true);
     launch_tc(s, tmA, dummy_tmap(), LoadTmaMN{TBM}, bl, ep, re, K, batch, out, n_mma);
   } else {
     LoadDenseMN al{w_tf32, K, K, out, TBM, 0};
@@ -717,6 +722,31 @@ void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, cons
   TEpiRowMajor ep{dw, K, out, K, accumulate ? 1 : 0};
   EpiRowMajor re{dw, K, out, K, accumulate ? 1 : 0};
   launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, out, K, batch, n_mma);
+}
+
+// Test hook (tools/debug_tc_gemm.py, tests): D[M][N] = A x B^T through the tensor-core kernel with
+// plain dense operands.  a_mn / b_mn select the operand storage: 0 = [rows][R] (K-major), 1 = [R][rows]
+// (MN-major).  tma_a: feed A through TMA instead of the gather warps.  All pointers are device pointers.
+void tc_test_gemm(cudaStream_t s, int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D) {
+  const int n_mma = pick_n_mma(N);
+  TEpiRowMajor ep{D, N, M, N, 0};
+  EpiRowMajor re{D, N, M, N, 0};
+  auto with_b = [&](auto al, const CUtensorMap& tmA) {
+    if (b_mn) {
+      LoadDenseMN bl{B, N, N, R, n_mma, (N % 4 == 0) ? 1 : 0};
+      launch_tc(s, tmA, dummy_tmap(), al, bl, ep, re, M, N, R, n_mma);
+    } else {
+      LoadDenseK bl{B, R, N, R, n_mma, (R % 4 == 0) ? 1 : 0};
+      launch_tc(s, tmA, dummy_tmap(), al, bl, ep, re, M, N, R, n_mma);
+    }
+  };
+  if (tma_a) {
+    if (a_mn) with_b(LoadTmaMN{TBM}, make_tmap(A, (uint64_t)M, (uint64_t)R, (uint64_t)M * 4, 32, true));
+    else with_b(LoadTmaK{TBM}, make_tmap(A, (uint64_t)R, (uint64_t)M, (uint64_t)R * 4, TBM));
+  } else {
+    if (a_mn) with_b(LoadDenseMN{A, M, M, R, TBM, (M % 4 == 0) ? 1 : 0}, dummy_tmap());
+    else with_b(LoadDenseK{A, R, M, R, TBM, (R % 4 == 0) ? 1 : 0}, dummy_tmap());
+  }
 }
 
 }  // namespace sn

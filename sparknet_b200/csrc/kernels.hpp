@@ -35,6 +35,7 @@ bool tc_available();
 void tc_round_to_tf32(cudaStream_t s, size_t n, const float* src, float* dst);
 // `w_tf32`: weights already rounded to tf32 (tc_round_to_tf32); all other operands are rounded on the fly
 void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);
+void tc_test_gemm(cudaStream_t s, int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D);
 void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx);
 void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate);
 void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);

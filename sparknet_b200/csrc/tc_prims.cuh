@@ -118,19 +118,22 @@ __device__ __forceinline__ float to_tf32(float x) {
 }
 
 // ---- descriptors ---------------------------------------------------------------------------------
-// Shared-memory matrix descriptor, 128-byte swizzle.  Bits: [0,14) start>>4, [16,30) LBO>>4,
-// [32,46) SBO>>4, [46,48) version = 1 (sm_100), [49,52) base offset = 0 (atoms are 1024-B aligned),
-// [61,64) layout = 2 (SWIZZLE_128B).
-//   K-major  operand: rows of 128 B (32 tf32 along K); 8-row groups SBO = 1024 B apart; LBO unused.
-//   MN-major operand: atoms of 8 k-rows x 128 B (32 elements along M/N); atoms along M/N are LBO apart;
-//                     groups of 8 k are SBO apart (one tf32 MMA, K = 8, reads a single group).
-__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+// Shared-memory matrix descriptor.  Bits: [0,14) start>>4, [16,30) LBO>>4, [32,46) SBO>>4,
+// [46,48) version = 1 (sm_100), [49,52) base offset = 0 (atoms are aligned to their repeat),
+// [61,64) layout type: 2 = SWIZZLE_128B (16-byte chunks XOR row%8, used for K-major operands),
+//                      1 = SWIZZLE_128B_BASE32B (32-byte chunks XOR row%4) — the ONLY layout the
+//                          tensor core accepts for MN-major 32-bit (tf32) operands.
+//   K-major  operand (type 2): rows of 128 B (32 tf32 along K); 8-row groups SBO = 1024 B apart; LBO unused.
+//   MN-major operand (type 1): atoms of 4 k-rows x 128 B (32 elements along M/N); atoms along M/N are
+//                     LBO apart, atoms along K (4 rows each) are SBO apart; one tf32 MMA (K = 8) reads two.
+constexpr uint32_t kLayoutSW128 = 2, kLayoutSW128Base32 = 1;
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes, uint32_t layout) {
   uint64_t d = 0;
   d |= (uint64_t)((smem_addr >> 4) & 0x3FFF);
   d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
   d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
   d |= (uint64_t)1 << 46;
-  d |= (uint64_t)2 << 61;
+  d |= (uint64_t)layout << 61;
   return d;
 }
 // Instruction descriptor for kind::tf32 with fp32 accumulation: [4,6) D fmt = 1 (f32), [7,10) A fmt = 2
@@ -144,10 +147,11 @@ __host__ __device__ constexpr uint32_t make_idesc_tf32(int m, int n, int a_mn_ma
 __device__ __forceinline__ uint32_t off_kmajor(uint32_t row, uint32_t k) {
   return row * 128u + ((((k >> 2) ^ row) & 7u) << 4) + ((k & 3u) << 2);
 }
-// Byte offset of element (mn, k), k in [0,32), in an MN-major SWIZZLE_128B tile laid out as
-// [mn/32][k/8][k%8][128 B]: atoms along M/N are 4096 B apart, groups of 8 k are 1024 B apart.
+// Byte offset of element (mn, k), k in [0,32), in an MN-major SWIZZLE_128B_BASE32B tile laid out as
+// [mn/32][k][128 B]: k-rows are 128 B apart (atoms of 4 rows = 512 B, contiguous along K), atoms along
+// M/N are 32 rows = 4096 B apart; within a row the 32-byte chunk index is XORed with k % 4.
 __device__ __forceinline__ uint32_t off_mnmajor(uint32_t mn, uint32_t k) {
-  return (mn >> 5) * 4096u + (k >> 3) * 1024u + (k & 7u) * 128u + (((((mn & 31u) >> 2) ^ k) & 7u) << 4) + ((mn & 3u) << 2);
+  return (mn >> 5) * 4096u + k * 128u + (((((mn & 31u) >> 3) ^ k) & 3u) << 5) + ((mn & 7u) << 2);
 }
 
 }  // namespace tc
