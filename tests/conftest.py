@@ -24,6 +24,9 @@ def oracle():
 def product():
     """The product: sparknet_b200/csrc/libccaffe.so.  No fallback: missing library == failure."""
     from sparknet_b200.library import load_library
+    # Tests arbitrate in the fp32 FFMA validation mode unless they ask for TF32 explicitly
+    # (sparknet_set_precision(state, 1)); the library's own default is TF32.
+    os.environ["SPARKNET_PRECISION"] = "ffma"
     lib = load_library()
     lib.set_mode_gpu()
     return lib

@@ -99,16 +99,24 @@ def oracle_self_sensitivity(oracle, name, batch, iters, n_batches, eps=1e-6):
                     a *= (1 + perturb * rng.standard_normal(a.shape)).astype(F)
             n.setWeights(w)
         n.train(iters)
-        out.append(n.getWeights())
+        w = n.getWeights()
+        hist, k = {}, 0
+        for ln in w.layerNames:
+            for j, a in enumerate(w.allWeights[ln]):
+                hist[(ln, j)] = np.ctypeslib.as_array(oracle.oracle_history(n.state, k), shape=(a.size,)).copy()
+                k += 1
+        out.append((w, hist))
         n.close()
-    a, b = out
-    return {(ln, j): rel_err(y, x) for ln in a.layerNames for j, (x, y) in enumerate(zip(a.allWeights[ln], b.allWeights[ln]))}
+    (a, ha), (b, hb) = out
+    sens_w = {(ln, j): rel_err(y, x) for ln in a.layerNames for j, (x, y) in enumerate(zip(a.allWeights[ln], b.allWeights[ln]))}
+    sens_h = {k: rel_err(hb[k], ha[k]) for k in ha}
+    return sens_w, sens_h
 
 
 @pytest.mark.parametrize("name,batch,iters", [("lenet", 16, 5), ("cifar10_quick", 10, 4), ("cifar10_full", 10, 4)])
 def test_solver_steps_match_weights_and_history(oracle, product, name, batch, iters):
     o, p, *_ = make_pair(oracle, product, name, batch, 3)
-    sens = oracle_self_sensitivity(oracle, name, batch, iters, 3)
+    sens, sens_h = oracle_self_sensitivity(oracle, name, batch, iters, 3)
     o.train(iters); p.train(iters)
     assert product.sparknet_get_iter(p.state) == iters == oracle.sparknet_get_iter(o.state)
     wo, wp = o.getWeights(), p.getWeights()
@@ -122,7 +130,7 @@ def test_solver_steps_match_weights_and_history(oracle, product, name, batch, it
             ho = np.ctypeslib.as_array(oracle.oracle_history(o.state, k), shape=(a.size,)).copy()
             hp = np.empty(a.size, dtype=F)
             assert product.sparknet_get_history(p.state, k, fptr(hp), hp.size) == 0
-            tol = max(2e-5 * iters, 30 * sens[(lname, j)])      # history = last update: more volatile than the weights
+            tol = max(2e-5 * iters, 3 * sens_h[(lname, j)])
             assert rel_err(hp, ho) <= tol, (lname, k, rel_err(hp, ho), tol)
             k += 1
     o.close(); p.close()

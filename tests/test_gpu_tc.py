@@ -62,7 +62,7 @@ def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
     sol = zoo.solver_with_net("lenet", train_bs=16, test_bs=16, random_seed=1701, display=0)
     o, p = CaffeNet.from_solver(sol, oracle), CaffeNet.from_solver(sol, product)
     product.sparknet_set_precision(p.state, 1)
-    imgs, labs = synthetic_batches("lenet", 3, 16)
+    imgs, labs = synthetic_batches("lenet", 1, 16)
     o.setTrainData(MinibatchSource(imgs, labs)); p.setTrainData(MinibatchSource(imgs, labs))
     p.forward()                                    # shadow built from the product's own fillers
     p.setWeights(o.getWeights())                   # host write: shadow must be rebuilt
