@@ -143,6 +143,19 @@ int sparknet_average_replicas_device(const void* const* replicas, int n, long co
  * replicas with NCCL on that stream first). */
 int sparknet_average_replicas_async(const void* const* replicas, int n, long count, void* out);
 
+/* No counterpart in the reference (libccaffe/ccaffe.h has nothing like it).
+ * D[M][N] = A x B^T in TF32 on the tensor cores for callers that must not allocate device memory while
+ * running (inside a stream capture, in latency-critical threads, under a fixed memory budget): the
+ * split-reduction scratch is a static 8 MiB device array inside the library instead of the grow-on-demand
+ * workspace; no cudaMalloc/cudaFree happens in this call.  a_mn/b_mn: 0 = operand stored [rows][R],
+ * 1 = stored [R][rows].  A, B, D are DEVICE pointers owned by the caller; stream is a cudaStream_t (NULL =
+ * default stream); the call does not synchronise.  Returns 0, or -1 bad arguments, -2 the problem needs
+ * more scratch than the static array holds (refused, nothing launched), < -9 CUDA errors.  The first call
+ * on a device resolves the array's device address: make it before any stream capture.  All calls share the
+ * array, so calls that can overlap on the GPU race with each other. */
+int sparknet_tc_gemm_static_scratch(int a_mn, int b_mn, int M, int N, int R, const float* A, const float* B,
+                                    float* D, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

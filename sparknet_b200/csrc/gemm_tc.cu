@@ -15,6 +15,7 @@
 // fixed order by splitk_reduce (deterministic, no atomics).
 #include <cuda.h>
 
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 #include <type_traits>
@@ -749,4 +750,133 @@ void tc_test_gemm(cudaStream_t s, int a_mn, int b_mn, int tma_a, int M, int N, i
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Split-reduction GEMM whose scratch lives in a static device array (no allocation at call time).
+//
+// Who needs this: callers that must not allocate device memory while they run — code between
+// cudaStreamBeginCapture/EndCapture, real-time or latency-critical threads where cudaMalloc's implicit
+// device synchronisation is unacceptable, and hosts that hand the library a fixed memory budget.  The
+// regular path takes its split-K slices from a workspace that grows on demand (cudaMalloc/cudaFree);
+// this variant keeps them in `g_static_scratch` below instead.
+//
+// Cost and limits: the array is part of the module image, so every GPU that loads libccaffe.so holds
+// kStaticScratchFloats * 4 bytes (8 MiB) until the process exits, whether or not this entry point is
+// ever called.  Problems whose slices need more than that are refused, never truncated.
+// All calls share the one array and it keeps whatever the previous call left in it.  Nothing has to
+// start at zero: each slice element the reduce kernel reads is written by the GEMM kernel of the same
+// call first.  Two calls whose kernels can overlap on the GPU (different streams, no dependency) would
+// write the same slices concurrently — that is a data race; serialise such calls.
+// ------------------------------------------------------------------------------------------
+constexpr size_t kStaticScratchFloats = 2u * 1024u * 1024u;       // 8 MiB
+static __device__ __align__(256) float g_static_scratch[kStaticScratchFloats];
+
+// Device address of g_static_scratch for the current device.  In host code the array's name is only a
+// host-side stand-in for the device symbol, so it must never be passed to a kernel directly; the address
+// is looked up once per device with that device current.
+static float* static_scratch_ptr(int* err) {
+  constexpr int kMaxDevices = 64;
+  static float* ptrs[kMaxDevices] = {};
+  static std::mutex mu;
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess || dev < 0 || dev >= kMaxDevices) {
+    fprintf(stderr, "libccaffe(b200): static scratch: cannot identify the current device (%s)\n", cudaGetErrorString(e));
+    *err = -10;
+    return nullptr;
+  }
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess || !p) {
+      fprintf(stderr, "libccaffe(b200): cudaGetSymbolAddress(g_static_scratch) failed on device %d: %s\n", dev, cudaGetErrorString(e));
+      *err = -11;
+      return nullptr;
+    }
+    ptrs[dev] = (float*)p;
+  }
+  return ptrs[dev];
+}
+
+template <class AL, class BL, int BN>
+static int launch_static_bn(cudaStream_t s, AL al, BL bl, int M, int N, int R, int n_mma, float* D, float* scratch) {
+  typedef TcCfg<BN> Cfg;
+  TEpiRowMajor ep{D, N, M, N, 0};
+  EpiRowMajor re{D, N, M, N, 0};
+  dim3 grid((M + TBM - 1) / TBM, (N + n_mma - 1) / n_mma, 1);
+  const int splits = splitk_slices((int)(grid.x * grid.y), R);
+  cudaError_t e;
+  if (splits == 1) {                                    // no scratch needed at all
+    auto kfn = gemm_tc_kernel<AL, BL, TEpiRowMajor, BN, false>;
+    e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    if (e != cudaSuccess) return -20;
+    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
+  } else {
+    int len = (R + splits - 1) / splits;
+    len = (len + TBK - 1) / TBK * TBK;
+    grid.z = (R + len - 1) / len;
+    const size_t need = (size_t)grid.z * M * N;
+    if (need > kStaticScratchFloats) {
+      fprintf(stderr, "libccaffe(b200): sparknet_tc_gemm_static_scratch: %d x %d x %d needs %zu scratch floats in %u slices, "
+                      "the static array holds %zu; refused\n", M, N, R, need, grid.z, kStaticScratchFloats);
+      return -2;
+    }
+    auto kfn = gemm_tc_kernel<AL, BL, TEpiRowMajor, BN, true>;
+    e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
+    if (e != cudaSuccess) return -20;
+    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, len, n_mma, scratch);
+    const size_t total = (size_t)M * N;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    tc_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(scratch, (int)grid.z, M, N, re);
+  }
+  e = cudaGetLastError();
+  if (e != cudaSuccess) {
+    fprintf(stderr, "libccaffe(b200): sparknet_tc_gemm_static_scratch: launch failed: %s\n", cudaGetErrorString(e));
+    return -21;
+  }
+  return 0;
+}
+template <class AL, class BL>
+static int launch_static(cudaStream_t s, AL al, BL bl, int M, int N, int R, int n_mma, float* D, float* scratch) {
+  switch (pick_bn(n_mma)) {
+    case 64: return launch_static_bn<AL, BL, 64>(s, al, bl, M, N, R, n_mma, D, scratch);
+    case 128: return launch_static_bn<AL, BL, 128>(s, al, bl, M, N, R, n_mma, D, scratch);
+    default: return launch_static_bn<AL, BL, 256>(s, al, bl, M, N, R, n_mma, D, scratch);
+  }
+}
+
 }  // namespace sn
+
+// D[M][N] = A x B^T in TF32 on the tensor cores, split along the reduction when that is needed to fill
+// the GPU, with NO allocation of any kind: the slice scratch is the static array above.
+//   a_mn / b_mn   storage of the operands: 0 = [rows][R] (reduction index contiguous), 1 = [R][rows]
+//   A, B, D       DEVICE pointers supplied by the caller (D is written, A and B only read)
+//   stream        cudaStream_t to launch on (NULL = the default stream); the call does not synchronise
+// Returns 0 on success; -1 bad arguments; -2 the problem needs more scratch than the static array holds
+// (message on stderr says how much); -10/-11 the scratch address could not be resolved; -20/-21 launch errors.
+// The first call on each device resolves the device address of the scratch array
+// (cudaGetSymbolAddress) and sets the kernels' shared-memory attribute; make that first call before any
+// stream capture begins.  Calls that may overlap on the GPU race on the shared scratch (see above).
+extern "C" int sparknet_tc_gemm_static_scratch(int a_mn, int b_mn, int M, int N, int R, const float* A, const float* B,
+                                               float* D, void* stream) {
+  using namespace sn;
+  if (M <= 0 || N <= 0 || R <= 0 || !A || !B || !D) {
+    fprintf(stderr, "libccaffe(b200): sparknet_tc_gemm_static_scratch: bad arguments (M %d N %d R %d)\n", M, N, R);
+    return -1;
+  }
+  int err = 0;
+  float* scratch = static_scratch_ptr(&err);
+  if (!scratch) return err;
+  cudaStream_t s = (cudaStream_t)stream;
+  const int n_mma = pick_n_mma(N);
+  const int avec = ((uintptr_t)A & 15) == 0, bvec = ((uintptr_t)B & 15) == 0;
+  if (a_mn) {
+    LoadDenseMN al{A, M, M, R, TBM, (avec && M % 4 == 0) ? 1 : 0};
+    if (b_mn) return launch_static(s, al, LoadDenseMN{B, N, N, R, n_mma, (bvec && N % 4 == 0) ? 1 : 0}, M, N, R, n_mma, D, scratch);
+    return launch_static(s, al, LoadDenseK{B, R, N, R, n_mma, (bvec && R % 4 == 0) ? 1 : 0}, M, N, R, n_mma, D, scratch);
+  }
+  LoadDenseK al{A, R, M, R, TBM, (avec && R % 4 == 0) ? 1 : 0};
+  if (b_mn) return launch_static(s, al, LoadDenseMN{B, N, N, R, n_mma, (bvec && N % 4 == 0) ? 1 : 0}, M, N, R, n_mma, D, scratch);
+  return launch_static(s, al, LoadDenseK{B, R, N, R, n_mma, (bvec && R % 4 == 0) ? 1 : 0}, M, N, R, n_mma, D, scratch);
+}
