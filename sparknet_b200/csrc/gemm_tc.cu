@@ -6,11 +6,11 @@
 // caffe/src/caffe/layers/inner_product_layer.cu:10-56).
 //
 // Every contraction is  D[m][n] = sum_r A(m,r) * B(n,r)  with a 128 x BN accumulator tile per CTA:
-//   warps 0-3  gather/convert the operands that cannot come through TMA (fp32 -> tf32 with
+//   warps 0-7  gather/convert the operands that cannot come through TMA (fp32 -> tf32 with
 //              round-to-nearest; TMA-fed weights come from a pre-rounded shadow copy), then run the
-//              epilogue (tcgen05.ld: warp w owns TMEM lanes 32w..32w+31 = tile rows);
-//   warp 4     allocates TMEM and issues tcgen05.mma (one thread), 4 x (128 x n_mma x 8) per 32-deep chunk;
-//   warp 5     issues the TMA loads.
+//              epilogue (tcgen05.ld: warp w owns TMEM lanes 32(w%4)..+31 = tile rows);
+//   warp 8     allocates TMEM and issues tcgen05.mma (one thread), 4 x (128 x n_mma x 8) per 32-deep chunk;
+//   warp 9     issues the TMA loads.
 // Reductions that leave too few tiles for 148 SMs are split along r; the slices are summed in a
 // fixed order by splitk_reduce (deterministic, no atomics).
 #include <cuda.h>
@@ -31,10 +31,14 @@ constexpr int TBM = 128, TBK = 32, TSTAGES = 4;
 constexpr int kATileBytes = TBM * TBK * 4;            // 16 KB
 
 // ------------------------------------------------------------------------------------------
-// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by the 128 gather threads.
-// kMN: MN-major tile (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows
-// actually needed (128 for A, n_mma for B); rows beyond the operand's extent are zero-filled.
+// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by the NT = 256 gather threads
+// (8 warps: two per scheduler, so one can issue while the other waits on memory).  kMN: MN-major tile
+// (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows actually needed (128 for
+// A, n_mma for B); rows beyond the operand's extent are zero-filled.  Every loader first issues ALL its
+// global loads of the chunk into registers and only then converts and stores them, so a thread has 8-16
+// loads in flight (the first version interleaved load/convert/store and was latency bound).
 // ------------------------------------------------------------------------------------------
+constexpr int NT = 256;
 struct NoState {};
 
 // weights through TMA, K-major: tensor {K (contiguous), rows}; box {32, rows_box}
@@ -59,30 +63,40 @@ struct LoadTmaMN {
   }
 };
 
+__device__ __forceinline__ float4 tf32x4(float4 v) {
+  v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
+  return v;
+}
+
 // dense [row][r] (r contiguous), K-major tile.  128-bit path when the pitch allows it.
 struct LoadDenseK {
   static constexpr bool kTMA = false, kMN = false;
   typedef NoState State;
   const float* p; int ld, nrows, nred, rows; int vec;
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
     if (vec) {
       const int c = t & 7;                         // 16-byte chunk within the 128-byte row
       const int r = r0 + 4 * c;
-      for (int row = t >> 3; row < rows; row += 16) {
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int gr = row0 + row;
-        if (gr < nrows && r < r_end) {
+      float4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int row = (t >> 3) + 32 * i, gr = row0 + row;
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < rows && gr < nrows && r < r_end) {
           const float* q = p + (size_t)gr * ld + r;
-          if (r + 3 < r_end) v = __ldg((const float4*)q);
-          else { v.x = __ldg(q); if (r + 1 < r_end) v.y = __ldg(q + 1); if (r + 2 < r_end) v.z = __ldg(q + 2); }
+          if (r + 3 < r_end) v[i] = __ldg((const float4*)q);
+          else { v[i].x = __ldg(q); if (r + 1 < r_end) v[i].y = __ldg(q + 1); if (r + 2 < r_end) v[i].z = __ldg(q + 2); }
         }
-        v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
-        *(float4*)(tile + off_kmajor(row, 4 * c)) = v;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int row = (t >> 3) + 32 * i;
+        if (row < rows) *(float4*)(tile + off_kmajor(row, 4 * c)) = tf32x4(v[i]);
       }
     } else {
       const int k = t & 31, r = r0 + k;
-      for (int row = t >> 5; row < rows; row += 4) {
+      for (int row = t >> 5; row < rows; row += 8) {
         const int gr = row0 + row;
         const float v = (gr < nrows && r < r_end) ? __ldg(p + (size_t)gr * ld + r) : 0.f;
         *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
@@ -90,33 +104,41 @@ struct LoadDenseK {
     }
   }
 };
-// dense [r][mn] (mn contiguous), MN-major tile
+// dense [r][mn] (mn contiguous), MN-major tile.  Warp w owns k = 4w..4w+3, lanes run along mn.
 struct LoadDenseMN {
   static constexpr bool kTMA = false, kMN = true;
   typedef NoState State;
   const float* p; int ld, nrows, nred, rows; int vec;
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+    const int w = t >> 5, lane = t & 31;
     if (vec) {
-      const int ch = rows >> 2;                    // 16-byte chunks per r
-      for (int j = t; j < ch * TBK; j += 128) {
-        const int c = j % ch, k = j / ch;
+      const int ch = rows >> 2;                    // 16-byte chunks per k-row (<= 64)
+      float4 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int k = 4 * w + (i & 3), c = lane + 32 * (i >> 2);
         const int mn = row0 + 4 * c, r = r0 + k;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < r_end && mn < nrows) {
+        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < ch && r < r_end && mn < nrows) {
           const float* q = p + (size_t)r * ld + mn;
-          if (mn + 3 < nrows) v = __ldg((const float4*)q);
-          else { v.x = __ldg(q); if (mn + 1 < nrows) v.y = __ldg(q + 1); if (mn + 2 < nrows) v.z = __ldg(q + 2); }
+          if (mn + 3 < nrows) v[i] = __ldg((const float4*)q);
+          else { v[i].x = __ldg(q); if (mn + 1 < nrows) v[i].y = __ldg(q + 1); if (mn + 2 < nrows) v[i].z = __ldg(q + 2); }
         }
-        v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
-        *(float4*)(tile + off_mnmajor(4 * c, k)) = v;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int k = 4 * w + (i & 3), c = lane + 32 * (i >> 2);
+        if (c < ch) *(float4*)(tile + off_mnmajor(4 * c, k)) = tf32x4(v[i]);
       }
     } else {
-      for (int j = t; j < rows * TBK; j += 128) {
-        const int m = j % rows, k = j / rows;
-        const int mn = row0 + m, r = r0 + k;
-        const float v = (r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
-        *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
+      for (int kk = 0; kk < 4; ++kk) {
+        const int k = 4 * w + kk, r = r0 + k;
+        for (int m = lane; m < rows; m += 32) {
+          const int mn = row0 + m;
+          const float v = (r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
+          *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
+        }
       }
     }
   }
@@ -128,72 +150,75 @@ struct LoadAccK {
   static constexpr bool kTMA = false, kMN = false;
   typedef NoState State;
   Acc acc; int rows;
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
     const int k = t & 31, r = r0 + k;
-    for (int row = t >> 5; row < rows; row += 4) {
+    for (int row = t >> 5; row < rows; row += 8) {
       const float v = r < r_end ? acc(row0 + row, r) : 0.f;
       *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
     }
   }
 };
-// Any accessor as an MN-major tile (thread = row, loop over k): generic.
+// Any accessor as an MN-major tile (thread = row, half the chunk's k each): generic.
 template <class Acc>
 struct LoadAccMN {
   static constexpr bool kTMA = false, kMN = true;
   typedef NoState State;
   Acc acc; int rows;
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    for (int m = t; m < rows; m += 128)
-      for (int k = 0; k < TBK; ++k) {
-        const int r = r0 + k;
-        const float v = r < r_end ? acc(row0 + m, r) : 0.f;
-        *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
-      }
+    const int m = t & 127, kb = (t >> 7) * 16;
+    if (m >= rows) return;
+    for (int k = kb; k < kb + 16; ++k) {
+      const int r = r0 + k;
+      const float v = r < r_end ? acc(row0 + m, r) : 0.f;
+      *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
+    }
   }
 };
 
-// Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t owns
-// pixel row0+t for the whole reduction: its (n,ho,wo) is decomposed once, the (c,kh,kw) counter runs
-// incrementally (warp-uniform), padding is a per-thread bit test.  Lanes = consecutive pixels, so the
-// global reads are coalesced along W and the swizzled 128-byte rows are written conflict-free.
+// Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t owns pixel
+// row0 + (t & 127) and 16 of the chunk's 32 reduction indices (t >> 7 picks the half).  Its (n,ho,wo) is
+// decomposed once per tile; per chunk the (c,kh,kw) of its first index comes from two fast divisions and
+// then runs incrementally; padding is a per-thread bit test.  Lanes = consecutive pixels, so the global
+// reads are coalesced along W and the swizzled 128-byte rows are written conflict-free.
 struct LoadIm2colRowsMN {
   static constexpr bool kTMA = false, kMN = true;
   const float* x; ConvGeom g; int grp;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { int base; uint32_t hmask, wmask; int c, ky, kx, delta; bool live; };
-  __device__ void init(State& s, int row0, int r_begin, int t) const {
-    const int row = row0 + t;
-    s.live = row < g.N * g.Ho * g.Wo;
+  struct State { int base; uint32_t hmask, wmask; };
+  __device__ void init(State& s, int row0, int t) const {
+    const int row = row0 + (t & 127);
+    const bool live = row < g.N * g.Ho * g.Wo;
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
-    if (s.live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
+    if (live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
     const int hi0 = (int)ho * g.sh - g.ph, wi0 = (int)wo * g.sw - g.pw;
     s.base = ((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0;
     s.hmask = 0; s.wmask = 0;
     for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) s.hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) s.wmask |= 1u << k;
-    if (!s.live) s.hmask = 0;
-    uint32_t c, tt, ky, kx;
-    dKhKw.divmod(r_begin, c, tt);
-    dKw.divmod(tt, ky, kx);
-    s.c = c; s.ky = ky; s.kx = kx;
-    s.delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
+    if (!live) s.hmask = 0;
   }
   __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int K = g.Kdim();
-#pragma unroll 4
-    for (int k = 0; k < TBK; ++k) {
-      float v = 0.f;
-      if (r0 + k < r_end && r0 + k < K && ((s.hmask >> s.ky) & (s.wmask >> s.kx) & 1u)) v = __ldg(x + s.base + s.delta);
-      *(float*)(tile + off_mnmajor(t, k)) = to_tf32(v);
-      // advance (c, ky, kx) — identical in every thread
-      ++s.kx; ++s.delta;
-      if (s.kx == g.kw) {
-        s.kx = 0; ++s.ky; s.delta += g.W - g.kw;
-        if (s.ky == g.kh) { s.ky = 0; ++s.c; s.delta += (g.H - g.kh) * g.W; }
+    const int m = t & 127, kb = (t >> 7) * 16;
+    uint32_t c, tt, ky, kx;
+    dKhKw.divmod((uint32_t)(r0 + kb), c, tt);
+    dKw.divmod(tt, ky, kx);
+    int delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
+    const int lim = min(r_end, g.Kdim()) - (r0 + kb);          // valid k' in [0, lim)
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      v[k] = 0.f;
+      if (k < lim && ((s.hmask >> ky) & (s.wmask >> kx) & 1u)) v[k] = __ldg(x + s.base + delta);
+      ++kx; ++delta;
+      if (kx == (uint32_t)g.kw) {
+        kx = 0; ++ky; delta += g.W - g.kw;
+        if (ky == (uint32_t)g.kh) { ky = 0; delta += (g.H - g.kh) * g.W; }
       }
     }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
   }
 };
 
@@ -203,9 +228,9 @@ struct LoadDgradRowsMN {
   static constexpr bool kTMA = false, kMN = true;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHW, dW, dKhKw, dKw;
-  struct State { int base; uint32_t hmask, wmask; int co, ky, kx, delta; };
-  __device__ void init(State& s, int row0, int r_begin, int t) const {
-    const int row = row0 + t;
+  struct State { int base; uint32_t hmask, wmask; };
+  __device__ void init(State& s, int row0, int t) const {
+    const int row = row0 + (t & 127);
     const bool live = row < g.N * g.H * g.W;
     uint32_t n = 0, pix = 0, h = 0, w = 0;
     if (live) { dHW.divmod(row, n, pix); dW.divmod(pix, h, w); }
@@ -215,46 +240,56 @@ struct LoadDgradRowsMN {
     for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) s.hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) s.wmask |= 1u << k;
     if (!live) s.hmask = 0;
-    uint32_t co, tt, ky, kx;
-    dKhKw.divmod(r_begin, co, tt);
-    dKw.divmod(tt, ky, kx);
-    s.co = co; s.ky = ky; s.kx = kx;
-    s.delta = (int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx;
   }
   __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int R = g.Og() * g.kh * g.kw;
-#pragma unroll 4
-    for (int k = 0; k < TBK; ++k) {
-      float v = 0.f;
-      if (r0 + k < r_end && r0 + k < R && ((s.hmask >> s.ky) & (s.wmask >> s.kx) & 1u)) v = __ldg(dy + s.base + s.delta);
-      *(float*)(tile + off_mnmajor(t, k)) = to_tf32(v);
-      ++s.kx; --s.delta;
-      if (s.kx == g.kw) {
-        s.kx = 0; ++s.ky; s.delta += g.kw - g.Wo;
-        if (s.ky == g.kh) { s.ky = 0; ++s.co; s.delta += g.kh * g.Wo + g.Ho * g.Wo; }
+    const int m = t & 127, kb = (t >> 7) * 16;
+    uint32_t co, tt, ky, kx;
+    dKhKw.divmod((uint32_t)(r0 + kb), co, tt);
+    dKw.divmod(tt, ky, kx);
+    int delta = (int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx;
+    const int lim = min(r_end, g.Og() * g.kh * g.kw) - (r0 + kb);
+    float v[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      v[k] = 0.f;
+      if (k < lim && ((s.hmask >> ky) & (s.wmask >> kx) & 1u)) v[k] = __ldg(dy + s.base + delta);
+      ++kx; --delta;
+      if (kx == (uint32_t)g.kw) {
+        kx = 0; ++ky; delta += g.kw - g.Wo;
+        if (ky == (uint32_t)g.kh) { ky = 0; delta += g.kh * g.Wo + g.Ho * g.Wo; }
       }
     }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
   }
 };
 // Backward-data B operand: filters viewed as [c][(co,kh,kw)], K-major.  lane = r: its (co, tap) is
-// decomposed once per chunk; rows (input channels) are khkw apart.
+// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w owns rows w, w+8, ...
 struct LoadFilterDgradK {
   static constexpr bool kTMA = false, kMN = false;
   typedef NoState State;
   const float* w; ConvGeom g; int grp; int rows;
   FastDiv dKhKw;
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
     const int khkw = g.kh * g.kw, Cg = g.Cg();
-    const int k = t & 31, r = r0 + k;
+    const int k = t & 31, r = r0 + k, wp = t >> 5;
     const bool ok = r < r_end && r < g.Og() * khkw;
     uint32_t co = 0, tap = 0;
     if (ok) dKhKw.divmod(r, co, tap);
     const float* q = w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap;
-    for (int row = t >> 5; row < rows; row += 4) {
-      const int c = row0 + row;
-      const float v = (ok && c < Cg) ? __ldg(q + (size_t)c * khkw) : 0.f;
-      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    for (int rb = 0; rb < rows; rb += 128) {
+      float v[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + 8 * i, c = row0 + row;
+        v[i] = (ok && row < rows && c < Cg) ? __ldg(q + (size_t)c * khkw) : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + 8 * i;
+        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+      }
     }
   }
 };
@@ -264,19 +299,22 @@ struct LoadDyRowsK {
   typedef NoState State;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHoWo;
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
     const int HoWo = g.Ho * g.Wo;
-    const int k = t & 31, r = r0 + k;
+    const int k = t & 31, r = r0 + k, wp = t >> 5;
     const bool ok = r < r_end && r < g.N * HoWo;
     uint32_t n = 0, pix = 0;
     if (ok) dHoWo.divmod(r, n, pix);
     const float* q = dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix;
-    for (int row = t >> 5; row < TBM; row += 4) {
-      const int co = row0 + row;
-      const float v = (ok && co < g.Og()) ? __ldg(q + (size_t)co * HoWo) : 0.f;
-      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    float v[16];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int co = row0 + wp + 8 * i;
+      v[i] = (ok && co < g.Og()) ? __ldg(q + (size_t)co * HoWo) : 0.f;
     }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) *(float*)(tile + off_kmajor(wp + 8 * i, k)) = to_tf32(v[i]);
   }
 };
 // Backward-filter B operand: im2col viewed as [(c,kh,kw)][(n,ho,wo)], K-major.  lane = r: its
@@ -289,7 +327,7 @@ struct LoadIm2colColsK {
   struct State { const int2* tab; };
   static constexpr int kTableRows = 256;
   __device__ void build_table(int2* tab, int row0, int t) const {
-    for (int row = t; row < rows; row += 128) {
+    for (int row = t; row < rows; row += NT) {
       const int rr = row0 + row;
       int2 e = make_int2(0, -1);
       if (rr < g.Kdim()) {
@@ -302,9 +340,9 @@ struct LoadIm2colColsK {
       tab[row] = e;
     }
   }
-  __device__ void init(State&, int, int, int) const {}
+  __device__ void init(State&, int, int) const {}
   __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int k = t & 31, r = r0 + k;
+    const int k = t & 31, r = r0 + k, wp = t >> 5;
     const bool ok = r < r_end && r < g.N * g.Ho * g.Wo;
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
     if (ok) { dHoWo.divmod(r, n, pix); dWo.divmod(pix, ho, wo); }
@@ -314,11 +352,22 @@ struct LoadIm2colColsK {
     for (int q = 0; q < g.kw; ++q) if (wi0 + q >= 0 && wi0 + q < g.W) wmask |= 1u << q;
     if (!ok) hmask = 0;
     const float* base = x + ((size_t)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0;
-    for (int row = t >> 5; row < rows; row += 4) {
-      const int2 e = s.tab[row];
-      float v = 0.f;
-      if (e.y >= 0 && ((hmask >> (e.y & 255)) & (wmask >> (e.y >> 8)) & 1u)) v = __ldg(base + e.x);
-      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+    for (int rb = 0; rb < rows; rb += 128) {
+      float v[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + 8 * i;
+        v[i] = 0.f;
+        if (row < rows) {
+          const int2 e = s.tab[row];
+          if (e.y >= 0 && ((hmask >> (e.y & 255)) & (wmask >> (e.y >> 8)) & 1u)) v[i] = __ldg(base + e.x);
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + 8 * i;
+        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+      }
     }
   }
 };
@@ -391,8 +440,11 @@ struct TcCfg {
   static constexpr uint32_t kTmemCols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
 };
 
+constexpr int kTcThreads = NT + 64;          // 8 gather/epilogue warps + MMA warp + TMA warp
+constexpr int kMmaWarp = NT / 32, kTmaWarp = NT / 32 + 1;
+
 template <class AL, class BL, class EP, int BN, bool SPLIT>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kTcThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, AL al, BL bl, EP ep,
                int M, int N, int R, int r_split_len, int n_mma, float* __restrict__ ws) {
   typedef TcCfg<BN> Cfg;
@@ -412,7 +464,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (tid == 0) {
     for (int s = 0; s < TSTAGES; ++s) {
-      mbar_init(&full_bar[s], (kAnySimt ? 128u : 0u) + (kAnyTma ? 1u : 0u));
+      mbar_init(&full_bar[s], (kAnySimt ? (uint32_t)NT : 0u) + (kAnyTma ? 1u : 0u));
       mbar_init(&empty_bar[s], 1u);
     }
     mbar_init(&tmem_full_bar, 1u);
@@ -420,23 +472,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (AL::kTMA) tma_prefetch_desc(&tmA);
     if (BL::kTMA) tma_prefetch_desc(&tmB);
   }
-  if (warp == 4) tmem_alloc<Cfg::kTmemCols>(&tmem_base_smem);
+  if (warp == kMmaWarp) tmem_alloc<Cfg::kTmemCols>(&tmem_base_smem);
   if constexpr (std::is_same<BL, LoadIm2colColsK>::value) {
-    if (warp < 4) bl.build_table(row_table, n0, tid);
+    if (warp < kMmaWarp) bl.build_table(row_table, n0, tid);
   }
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (warp < 4) {
+  if (warp < kMmaWarp) {
     // ---------------- gather producers ----------------
     if (kAnySimt && nchunks > 0) {
       typename AL::State sa;
       typename BL::State sb;
-      if constexpr (!AL::kTMA) al.init(sa, m0, r_begin, tid);
+      if constexpr (!AL::kTMA) al.init(sa, m0, tid);
       if constexpr (!BL::kTMA) {
-        bl.init(sb, n0, r_begin, tid);
+        bl.init(sb, n0, tid);
         if constexpr (std::is_same<BL, LoadIm2colColsK>::value) sb.tab = row_table;
       }
       for (int kc = 0; kc < nchunks; ++kc) {
@@ -456,13 +508,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(&tmem_full_bar, 0);
       tc_fence_after_sync();
     }
-    const int m = m0 + tid;                                    // TMEM lane == tile row
+    // warp w reads TMEM lanes 32*(w%4)..+31 (= tile rows); warps w and w+4 share the rows and take
+    // alternate 16-column groups
+    const int m = m0 + 32 * (warp & 3) + lane;
     typename EP::Ctx ctx;
     if constexpr (!SPLIT) ctx = ep.row(m);
-    for (int c0 = 0; c0 < n_mma; c0 += 16) {
+    for (int c0 = 16 * (warp >> 2); c0 < n_mma; c0 += 32) {
       uint32_t v[16];
       if (nchunks > 0) {
-        tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, v);
+        tmem_ld_32x32b_x16(tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)c0, v);
         tmem_ld_wait();
       } else {
 #pragma unroll
@@ -479,7 +533,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
       }
     }
-  } else if (warp == 4) {
+  } else if (warp == kMmaWarp) {
     // ---------------- MMA issuer ----------------
     if (lane == 0 && nchunks > 0) {
       const uint32_t idesc = make_idesc_tf32(TBM, n_mma, AL::kMN ? 1 : 0, BL::kMN ? 1 : 0);
@@ -521,7 +575,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == 4) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
+  if (warp == kMmaWarp) tmem_dealloc<Cfg::kTmemCols>(tmem_base);
 }
 
 // deterministic slice reduction (ascending z) + the per-element epilogue of gemm_ops.cuh
@@ -595,7 +649,7 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
   if (splits == 1) {
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, false>;
     if (!attr_done) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes)); attr_done = true; }
-    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
+    kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
     count_launch();
   } else {
     int len = (R + splits - 1) / splits;
@@ -604,7 +658,7 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
     float* ws = get_workspace((size_t)grid.z * M * N);
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, true>;
     if (!attr_done_split) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes)); attr_done_split = true; }
-    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
+    kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
     const size_t total = (size_t)M * N;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
@@ -810,7 +864,7 @@ static int launch_static_bn(cudaStream_t s, AL al, BL bl, int M, int N, int R, i
     auto kfn = gemm_tc_kernel<AL, BL, TEpiRowMajor, BN, false>;
     e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return -20;
-    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
+    kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
   } else {
     int len = (R + splits - 1) / splits;
     len = (len + TBK - 1) / TBK * TBK;
@@ -824,7 +878,7 @@ static int launch_static_bn(cudaStream_t s, AL al, BL bl, int M, int N, int R, i
     auto kfn = gemm_tc_kernel<AL, BL, TEpiRowMajor, BN, true>;
     e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return -20;
-    kfn<<<grid, 192, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, len, n_mma, scratch);
+    kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, len, n_mma, scratch);
     const size_t total = (size_t)M * N;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;

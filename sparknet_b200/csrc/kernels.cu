@@ -530,12 +530,14 @@ void accuracy_top1(cudaStream_t s, int rows, int classes, const float* x, const 
 // ------------------------------------------------------------------------------------------
 // bias gradients
 // ------------------------------------------------------------------------------------------
-// one CTA per channel: db[c] (+)= sum_n sum_pix dy[n][c][pix]
-__global__ void conv_bias_grad_kernel(int N, int C, int HW, const float* __restrict__ dy, float* __restrict__ db, int accumulate) {
+// db[c] (+)= sum_n sum_pix dy[n][c][pix].  Two deterministic stages so that small channel counts still
+// fill the GPU: block (c, s) sums the images n = s, s+S, ...; a second tiny kernel adds the S partials of
+// each channel in ascending order.
+__global__ void conv_bias_grad_partial_kernel(int N, int C, int HW, int S, const float* __restrict__ dy, float* __restrict__ part) {
   __shared__ float sh[32];
-  const int c = blockIdx.x;
+  const int c = blockIdx.x, s = blockIdx.y;
   float acc = 0.f;
-  for (int n = 0; n < N; ++n) {
+  for (int n = s; n < N; n += S) {
     const float* p = dy + ((size_t)n * C + c) * HW;
     for (int i = threadIdx.x; i < HW; i += blockDim.x) acc += p[i];
   }
@@ -545,12 +547,25 @@ __global__ void conv_bias_grad_kernel(int N, int C, int HW, const float* __restr
   if (threadIdx.x < 32) {
     float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
     t = warp_sum(t);
-    if (threadIdx.x == 0) db[c] = accumulate ? db[c] + t : t;
+    if (threadIdx.x == 0) part[(size_t)c * S + s] = t;
   }
 }
+__global__ void conv_bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float t = 0.f;
+  for (int s = 0; s < S; ++s) t += part[(size_t)c * S + s];
+  db[c] = accumulate ? db[c] + t : t;
+}
 void conv_bias_grad(cudaStream_t s, int N, int C, int HW, const float* dy, float* db, bool accumulate) {
-  conv_bias_grad_kernel<<<C, 256, 0, s>>>(N, C, HW, dy, db, accumulate ? 1 : 0);
-  count_launch();
+  int S = (4 * kSMs + C - 1) / C;
+  if (S > N) S = N;
+  if (S < 1) S = 1;
+  float* part = get_workspace((size_t)C * S);
+  const int threads = HW >= 256 ? 256 : (HW >= 128 ? 128 : 64);
+  conv_bias_grad_partial_kernel<<<dim3(C, S), threads, 0, s>>>(N, C, HW, S, dy, part);
+  conv_bias_grad_final_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, S, part, db, accumulate ? 1 : 0);
+  count_launch(2);
 }
 __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict__ dy, float* __restrict__ db, int accumulate) {
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
