@@ -99,10 +99,11 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, i
   }
 }
 
-// Number of reduction slices: enough CTAs for two waves of 148 SMs, each slice >= 512 long.
+// Number of reduction slices: as many CTAs as fit in two waves of 148 SMs (never a partial third wave),
+// each slice >= 512 long.
 int splitk_slices(int tiles, int R) {
   if (tiles >= 148 || R < 2048) return 1;
-  int want = (2 * 148 + tiles - 1) / tiles;
+  int want = (2 * 148) / tiles;
   int maxs = R / 512;
   int s = want < maxs ? want : maxs;
   return s < 1 ? 1 : s;

@@ -31,19 +31,20 @@ constexpr int TBM = 128, TBK = 32, TSTAGES = 4;
 constexpr int kATileBytes = TBM * TBK * 4;            // 16 KB
 
 // ------------------------------------------------------------------------------------------
-// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by the NT = 256 gather threads
-// (8 warps: two per scheduler, so one can issue while the other waits on memory).  kMN: MN-major tile
+// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by the NT = 512 gather threads
+// (16 warps: four per scheduler, so some can issue while the others wait on memory).  kMN: MN-major tile
 // (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows actually needed (128 for
 // A, n_mma for B); rows beyond the operand's extent are zero-filled.  Every loader first issues ALL its
 // global loads of the chunk into registers and only then converts and stores them, so a thread has 8-16
 // loads in flight (the first version interleaved load/convert/store and was latency bound).
 // ------------------------------------------------------------------------------------------
-constexpr int NT = 256;
+constexpr int NT = 512;
+constexpr int NW = NT / 32;                   // gather warps
 struct NoState {};
 
 // weights through TMA, K-major: tensor {K (contiguous), rows}; box {32, rows_box}
 struct LoadTmaK {
-  static constexpr bool kTMA = true, kMN = false;
+  static constexpr bool kTMA = true, kMN = false, kKTable = false;
   typedef NoState State;
   int rows_box;
   __device__ uint32_t bytes() const { return (uint32_t)rows_box * 128u; }
@@ -54,7 +55,7 @@ struct LoadTmaK {
 // weights through TMA, MN-major: tensor {MN (contiguous), R rows}; box {32, 32} with the 32-byte-atom
 // 128-byte swizzle (CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B); one box per 32 rows
 struct LoadTmaMN {
-  static constexpr bool kTMA = true, kMN = true;
+  static constexpr bool kTMA = true, kMN = true, kKTable = false;
   typedef NoState State;
   int rows;                                       // multiple of 32
   __device__ uint32_t bytes() const { return (uint32_t)(rows / 32) * 4096u; }
@@ -70,7 +71,7 @@ __device__ __forceinline__ float4 tf32x4(float4 v) {
 
 // dense [row][r] (r contiguous), K-major tile.  128-bit path when the pitch allows it.
 struct LoadDenseK {
-  static constexpr bool kTMA = false, kMN = false;
+  static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
   const float* p; int ld, nrows, nred, rows; int vec;
   __device__ void init(State&, int, int) const {}
@@ -78,10 +79,10 @@ struct LoadDenseK {
     if (vec) {
       const int c = t & 7;                         // 16-byte chunk within the 128-byte row
       const int r = r0 + 4 * c;
-      float4 v[8];
+      float4 v[4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int row = (t >> 3) + 32 * i, gr = row0 + row;
+      for (int i = 0; i < 4; ++i) {
+        const int row = (t >> 3) + 64 * i, gr = row0 + row;
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (row < rows && gr < nrows && r < r_end) {
           const float* q = p + (size_t)gr * ld + r;
@@ -90,13 +91,13 @@ struct LoadDenseK {
         }
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int row = (t >> 3) + 32 * i;
+      for (int i = 0; i < 4; ++i) {
+        const int row = (t >> 3) + 64 * i;
         if (row < rows) *(float4*)(tile + off_kmajor(row, 4 * c)) = tf32x4(v[i]);
       }
     } else {
       const int k = t & 31, r = r0 + k;
-      for (int row = t >> 5; row < rows; row += 8) {
+      for (int row = t >> 5; row < rows; row += NW) {
         const int gr = row0 + row;
         const float v = (gr < nrows && r < r_end) ? __ldg(p + (size_t)gr * ld + r) : 0.f;
         *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
@@ -104,9 +105,9 @@ struct LoadDenseK {
     }
   }
 };
-// dense [r][mn] (mn contiguous), MN-major tile.  Warp w owns k = 4w..4w+3, lanes run along mn.
+// dense [r][mn] (mn contiguous), MN-major tile.  Warp w owns k = 2w, 2w+1; lanes run along mn.
 struct LoadDenseMN {
-  static constexpr bool kTMA = false, kMN = true;
+  static constexpr bool kTMA = false, kMN = true, kKTable = false;
   typedef NoState State;
   const float* p; int ld, nrows, nred, rows; int vec;
   __device__ void init(State&, int, int) const {}
@@ -114,10 +115,10 @@ struct LoadDenseMN {
     const int w = t >> 5, lane = t & 31;
     if (vec) {
       const int ch = rows >> 2;                    // 16-byte chunks per k-row (<= 64)
-      float4 v[8];
+      float4 v[4];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int k = 4 * w + (i & 3), c = lane + 32 * (i >> 2);
+      for (int i = 0; i < 4; ++i) {
+        const int k = 2 * w + (i & 1), c = lane + 32 * (i >> 1);
         const int mn = row0 + 4 * c, r = r0 + k;
         v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (c < ch && r < r_end && mn < nrows) {
@@ -127,13 +128,13 @@ struct LoadDenseMN {
         }
       }
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const int k = 4 * w + (i & 3), c = lane + 32 * (i >> 2);
+      for (int i = 0; i < 4; ++i) {
+        const int k = 2 * w + (i & 1), c = lane + 32 * (i >> 1);
         if (c < ch) *(float4*)(tile + off_mnmajor(4 * c, k)) = tf32x4(v[i]);
       }
     } else {
-      for (int kk = 0; kk < 4; ++kk) {
-        const int k = 4 * w + kk, r = r0 + k;
+      for (int kk = 0; kk < 2; ++kk) {
+        const int k = 2 * w + kk, r = r0 + k;
         for (int m = lane; m < rows; m += 32) {
           const int mn = row0 + m;
           const float v = (r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
@@ -147,13 +148,13 @@ struct LoadDenseMN {
 // Any accessor of gemm_ops.cuh as a K-major tile (lane = r, warp = rows): generic, index math per element.
 template <class Acc>
 struct LoadAccK {
-  static constexpr bool kTMA = false, kMN = false;
+  static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
   Acc acc; int rows;
   __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
     const int k = t & 31, r = r0 + k;
-    for (int row = t >> 5; row < rows; row += 8) {
+    for (int row = t >> 5; row < rows; row += NW) {
       const float v = r < r_end ? acc(row0 + row, r) : 0.f;
       *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
     }
@@ -162,14 +163,14 @@ struct LoadAccK {
 // Any accessor as an MN-major tile (thread = row, half the chunk's k each): generic.
 template <class Acc>
 struct LoadAccMN {
-  static constexpr bool kTMA = false, kMN = true;
+  static constexpr bool kTMA = false, kMN = true, kKTable = false;
   typedef NoState State;
   Acc acc; int rows;
   __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int m = t & 127, kb = (t >> 7) * 16;
+    const int m = t & 127, kb = (t >> 7) * 8;
     if (m >= rows) return;
-    for (int k = kb; k < kb + 16; ++k) {
+    for (int k = kb; k < kb + 8; ++k) {
       const int r = r0 + k;
       const float v = r < r_end ? acc(row0 + m, r) : 0.f;
       *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
@@ -177,96 +178,94 @@ struct LoadAccMN {
   }
 };
 
+// Per-chunk reduction-index table for the two pixel-row gathers below: for each of the chunk's 32
+// reduction indices {input offset delta, 1 << kh, 1 << kw, 0}; an all-zero mask marks an index beyond the
+// reduction.  Built by a dedicated warp one stage ahead, read by the gather warps as broadcast LDS.128 —
+// this replaces ~40 instructions of index arithmetic per gathered element by one shared-memory load.
+//
 // Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t owns pixel
-// row0 + (t & 127) and 16 of the chunk's 32 reduction indices (t >> 7 picks the half).  Its (n,ho,wo) is
-// decomposed once per tile; per chunk the (c,kh,kw) of its first index comes from two fast divisions and
-// then runs incrementally; padding is a per-thread bit test.  Lanes = consecutive pixels, so the global
-// reads are coalesced along W and the swizzled 128-byte rows are written conflict-free.
+// row0 + (t & 127) and 8 of the chunk's 32 reduction indices.  Its (n,ho,wo), input base and padding masks
+// are computed once per tile.  Lanes = consecutive pixels, so global reads are coalesced along W and the
+// swizzled 128-byte rows are written conflict-free.
 struct LoadIm2colRowsMN {
-  static constexpr bool kTMA = false, kMN = true;
+  static constexpr bool kTMA = false, kMN = true, kKTable = true;
   const float* x; ConvGeom g; int grp;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { int base; uint32_t hmask, wmask; };
+  struct State { const float* base; uint32_t hmask, wmask; };
+  __device__ int4 table_entry(int r, int r_end) const {
+    if (r >= r_end || r >= g.Kdim()) return make_int4(0, 0, 0, 0);
+    uint32_t c, tt, ky, kx;
+    dKhKw.divmod((uint32_t)r, c, tt);
+    dKw.divmod(tt, ky, kx);
+    return make_int4((int)c * g.H * g.W + (int)ky * g.W + (int)kx, 1 << ky, 1 << kx, 0);
+  }
   __device__ void init(State& s, int row0, int t) const {
     const int row = row0 + (t & 127);
     const bool live = row < g.N * g.Ho * g.Wo;
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
     if (live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
     const int hi0 = (int)ho * g.sh - g.ph, wi0 = (int)wo * g.sw - g.pw;
-    s.base = ((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0;
+    s.base = x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0);
     s.hmask = 0; s.wmask = 0;
     for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) s.hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) s.wmask |= 1u << k;
     if (!live) s.hmask = 0;
   }
-  __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int m = t & 127, kb = (t >> 7) * 16;
-    uint32_t c, tt, ky, kx;
-    dKhKw.divmod((uint32_t)(r0 + kb), c, tt);
-    dKw.divmod(tt, ky, kx);
-    int delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
-    const int lim = min(r_end, g.Kdim()) - (r0 + kb);          // valid k' in [0, lim)
-    float v[16];
+  __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
+    const int m = t & 127, kb = (t >> 7) * 8;
+    float v[8];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      v[k] = 0.f;
-      if (k < lim && ((s.hmask >> ky) & (s.wmask >> kx) & 1u)) v[k] = __ldg(x + s.base + delta);
-      ++kx; ++delta;
-      if (kx == (uint32_t)g.kw) {
-        kx = 0; ++ky; delta += g.W - g.kw;
-        if (ky == (uint32_t)g.kh) { ky = 0; delta += (g.H - g.kh) * g.W; }
-      }
+    for (int k = 0; k < 8; ++k) {
+      const int4 e = ktab[kb + k];
+      v[k] = ((s.hmask & (uint32_t)e.y) && (s.wmask & (uint32_t)e.z)) ? __ldg(s.base + e.x) : 0.f;
     }
 #pragma unroll
-    for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
+    for (int k = 0; k < 8; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
   }
 };
 
 // Convolution backward-data A operand (stride 1): rows = input pixels, r = (co,kh,kw), MN-major.
 // value = dY[n][co][h+ph-kh][w+pw-kw] when that output position exists.
 struct LoadDgradRowsMN {
-  static constexpr bool kTMA = false, kMN = true;
+  static constexpr bool kTMA = false, kMN = true, kKTable = true;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHW, dW, dKhKw, dKw;
-  struct State { int base; uint32_t hmask, wmask; };
+  struct State { const float* base; uint32_t hmask, wmask; };
+  __device__ int4 table_entry(int r, int r_end) const {
+    if (r >= r_end || r >= g.Og() * g.kh * g.kw) return make_int4(0, 0, 0, 0);
+    uint32_t co, tt, ky, kx;
+    dKhKw.divmod((uint32_t)r, co, tt);
+    dKw.divmod(tt, ky, kx);
+    return make_int4((int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx, 1 << ky, 1 << kx, 0);
+  }
   __device__ void init(State& s, int row0, int t) const {
     const int row = row0 + (t & 127);
     const bool live = row < g.N * g.H * g.W;
     uint32_t n = 0, pix = 0, h = 0, w = 0;
     if (live) { dHW.divmod(row, n, pix); dW.divmod(pix, h, w); }
     const int hb = (int)h + g.ph, wb = (int)w + g.pw;            // output row = hb - ky, col = wb - kx
-    s.base = ((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb;
+    s.base = dy + ((ptrdiff_t)((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb);
     s.hmask = 0; s.wmask = 0;
     for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) s.hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) s.wmask |= 1u << k;
     if (!live) s.hmask = 0;
   }
-  __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int m = t & 127, kb = (t >> 7) * 16;
-    uint32_t co, tt, ky, kx;
-    dKhKw.divmod((uint32_t)(r0 + kb), co, tt);
-    dKw.divmod(tt, ky, kx);
-    int delta = (int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx;
-    const int lim = min(r_end, g.Og() * g.kh * g.kw) - (r0 + kb);
-    float v[16];
+  __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
+    const int m = t & 127, kb = (t >> 7) * 8;
+    float v[8];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-      v[k] = 0.f;
-      if (k < lim && ((s.hmask >> ky) & (s.wmask >> kx) & 1u)) v[k] = __ldg(dy + s.base + delta);
-      ++kx; --delta;
-      if (kx == (uint32_t)g.kw) {
-        kx = 0; ++ky; delta += g.kw - g.Wo;
-        if (ky == (uint32_t)g.kh) { ky = 0; delta += g.kh * g.Wo + g.Ho * g.Wo; }
-      }
+    for (int k = 0; k < 8; ++k) {
+      const int4 e = ktab[kb + k];
+      v[k] = ((s.hmask & (uint32_t)e.y) && (s.wmask & (uint32_t)e.z)) ? __ldg(s.base + e.x) : 0.f;
     }
 #pragma unroll
-    for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
+    for (int k = 0; k < 8; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
   }
 };
 // Backward-data B operand: filters viewed as [c][(co,kh,kw)], K-major.  lane = r: its (co, tap) is
-// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w owns rows w, w+8, ...
+// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w owns rows w, w+16, ...
 struct LoadFilterDgradK {
-  static constexpr bool kTMA = false, kMN = false;
+  static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
   const float* w; ConvGeom g; int grp; int rows;
   FastDiv dKhKw;
@@ -278,24 +277,22 @@ struct LoadFilterDgradK {
     uint32_t co = 0, tap = 0;
     if (ok) dKhKw.divmod(r, co, tap);
     const float* q = w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap;
-    for (int rb = 0; rb < rows; rb += 128) {
-      float v[16];
+    float v[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + 8 * i, c = row0 + row;
-        v[i] = (ok && row < rows && c < Cg) ? __ldg(q + (size_t)c * khkw) : 0.f;
-      }
+    for (int i = 0; i < 16; ++i) {
+      const int row = wp + NW * i, c = row0 + row;
+      v[i] = (ok && row < rows && c < Cg) ? __ldg(q + (size_t)c * khkw) : 0.f;
+    }
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + 8 * i;
-        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
-      }
+    for (int i = 0; i < 16; ++i) {
+      const int row = wp + NW * i;
+      if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
     }
   }
 };
 // Backward-filter A operand: dY viewed as [co][(n,ho,wo)], K-major.  lane = r = (n, pix).
 struct LoadDyRowsK {
-  static constexpr bool kTMA = false, kMN = false;
+  static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHoWo;
@@ -307,35 +304,35 @@ struct LoadDyRowsK {
     uint32_t n = 0, pix = 0;
     if (ok) dHoWo.divmod(r, n, pix);
     const float* q = dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix;
-    float v[16];
+    float v[8];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int co = row0 + wp + 8 * i;
+    for (int i = 0; i < 8; ++i) {
+      const int co = row0 + wp + NW * i;
       v[i] = (ok && co < g.Og()) ? __ldg(q + (size_t)co * HoWo) : 0.f;
     }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) *(float*)(tile + off_kmajor(wp + 8 * i, k)) = to_tf32(v[i]);
+    for (int i = 0; i < 8; ++i) *(float*)(tile + off_kmajor(wp + NW * i, k)) = to_tf32(v[i]);
   }
 };
 // Backward-filter B operand: im2col viewed as [(c,kh,kw)][(n,ho,wo)], K-major.  lane = r: its
 // (n,ho,wo), input base and padding masks are computed once per chunk; the per-row (c,kh,kw) comes
-// from a table built once per CTA in shared memory (row_tab[row] = {input offset, kh | kw << 8}).
+// from a table built once per CTA in shared memory (row_tab[row] = {input offset, 1<<kh, 1<<kw, 0};
+// zero masks mark rows beyond the filter).
 struct LoadIm2colColsK {
-  static constexpr bool kTMA = false, kMN = false;
+  static constexpr bool kTMA = false, kMN = false, kKTable = false;
   const float* x; ConvGeom g; int grp; int rows;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { const int2* tab; };
+  struct State { const int4* tab; };
   static constexpr int kTableRows = 256;
-  __device__ void build_table(int2* tab, int row0, int t) const {
+  __device__ void build_table(int4* tab, int row0, int t) const {
     for (int row = t; row < rows; row += NT) {
       const int rr = row0 + row;
-      int2 e = make_int2(0, -1);
+      int4 e = make_int4(0, 0, 0, 0);
       if (rr < g.Kdim()) {
         uint32_t c, tt, ky, kx;
         dKhKw.divmod(rr, c, tt);
         dKw.divmod(tt, ky, kx);
-        e.x = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
-        e.y = (int)(ky | (kx << 8));
+        e = make_int4((int)c * g.H * g.W + (int)ky * g.W + (int)kx, 1 << ky, 1 << kx, 0);
       }
       tab[row] = e;
     }
@@ -351,23 +348,21 @@ struct LoadIm2colColsK {
     for (int q = 0; q < g.kh; ++q) if (hi0 + q >= 0 && hi0 + q < g.H) hmask |= 1u << q;
     for (int q = 0; q < g.kw; ++q) if (wi0 + q >= 0 && wi0 + q < g.W) wmask |= 1u << q;
     if (!ok) hmask = 0;
-    const float* base = x + ((size_t)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0;
-    for (int rb = 0; rb < rows; rb += 128) {
-      float v[16];
+    const float* base = x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0);
+    float v[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + 8 * i;
-        v[i] = 0.f;
-        if (row < rows) {
-          const int2 e = s.tab[row];
-          if (e.y >= 0 && ((hmask >> (e.y & 255)) & (wmask >> (e.y >> 8)) & 1u)) v[i] = __ldg(base + e.x);
-        }
+    for (int i = 0; i < 16; ++i) {
+      const int row = wp + NW * i;
+      v[i] = 0.f;
+      if (row < rows) {
+        const int4 e = s.tab[row];
+        if ((hmask & (uint32_t)e.y) && (wmask & (uint32_t)e.z)) v[i] = __ldg(base + e.x);
       }
+    }
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + 8 * i;
-        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
-      }
+    for (int i = 0; i < 16; ++i) {
+      const int row = wp + NW * i;
+      if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
     }
   }
 };
@@ -440,8 +435,8 @@ struct TcCfg {
   static constexpr uint32_t kTmemCols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
 };
 
-constexpr int kTcThreads = NT + 64;          // 8 gather/epilogue warps + MMA warp + TMA warp
-constexpr int kMmaWarp = NT / 32, kTmaWarp = NT / 32 + 1;
+constexpr int kTcThreads = NT + 96;          // 16 gather/epilogue warps + MMA warp + TMA warp + table warp
+constexpr int kMmaWarp = NW, kTmaWarp = NW + 1, kTabWarp = NW + 2;
 
 template <class AL, class BL, class EP, int BN, bool SPLIT>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -449,9 +444,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                int M, int N, int R, int r_split_len, int n_mma, float* __restrict__ ws) {
   typedef TcCfg<BN> Cfg;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tmem_full_bar;
+  __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tab_bar[TSTAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
-  __shared__ int2 row_table[LoadIm2colColsK::kTableRows];
+  __shared__ int4 row_table[LoadIm2colColsK::kTableRows];     // backward-filter: per-CTA row table
+  __shared__ int4 k_table[TSTAGES][TBK];                      // pixel-row gathers: per-chunk reduction table
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.x * TBM, n0 = blockIdx.y * n_mma;
@@ -461,11 +457,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   constexpr bool kAnySimt = !AL::kTMA || !BL::kTMA, kAnyTma = AL::kTMA || BL::kTMA;
+  static_assert(!BL::kKTable, "the per-chunk reduction table is wired for the A operand only");
 
   if (tid == 0) {
     for (int s = 0; s < TSTAGES; ++s) {
       mbar_init(&full_bar[s], (kAnySimt ? (uint32_t)NT : 0u) + (kAnyTma ? 1u : 0u));
       mbar_init(&empty_bar[s], 1u);
+      mbar_init(&tab_bar[s], 1u);
     }
     mbar_init(&tmem_full_bar, 1u);
     fence_barrier_init();
@@ -474,14 +472,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   if (warp == kMmaWarp) tmem_alloc<Cfg::kTmemCols>(&tmem_base_smem);
   if constexpr (std::is_same<BL, LoadIm2colColsK>::value) {
-    if (warp < kMmaWarp) bl.build_table(row_table, n0, tid);
+    if (warp < NW) bl.build_table(row_table, n0, tid);
   }
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
 
-  if (warp < kMmaWarp) {
+  if (warp < NW) {
     // ---------------- gather producers ----------------
     if (kAnySimt && nchunks > 0) {
       typename AL::State sa;
@@ -493,11 +491,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       for (int kc = 0; kc < nchunks; ++kc) {
         const int s = kc % TSTAGES;
-        mbar_wait(&empty_bar[s], ((kc / TSTAGES) & 1) ^ 1);
+        const uint32_t ph = (kc / TSTAGES) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);
         uint8_t* a_tile = smem + s * Cfg::kStageBytes;
         uint8_t* b_tile = a_tile + kATileBytes;
         const int r0 = r_begin + kc * TBK;
-        if constexpr (!AL::kTMA) al.load(sa, a_tile, m0, r0, r_end, tid);
+        if constexpr (!AL::kTMA) {
+          if constexpr (AL::kKTable) {
+            mbar_wait(&tab_bar[s], ph);
+            al.load(sa, a_tile, k_table[s], tid);
+          } else {
+            al.load(sa, a_tile, m0, r0, r_end, tid);
+          }
+        }
         if constexpr (!BL::kTMA) bl.load(sb, b_tile, n0, r0, r_end, tid);
         fence_proxy_async_smem();
         mbar_arrive(&full_bar[s]);
@@ -508,12 +514,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       mbar_wait(&tmem_full_bar, 0);
       tc_fence_after_sync();
     }
-    // warp w reads TMEM lanes 32*(w%4)..+31 (= tile rows); warps w and w+4 share the rows and take
-    // alternate 16-column groups
+    // warp w reads TMEM lanes 32*(w%4)..+31 (= tile rows); the four warps sharing a lane quarter take
+    // every fourth 16-column group
     const int m = m0 + 32 * (warp & 3) + lane;
     typename EP::Ctx ctx;
     if constexpr (!SPLIT) ctx = ep.row(m);
-    for (int c0 = 16 * (warp >> 2); c0 < n_mma; c0 += 32) {
+    for (int c0 = 16 * (warp >> 2); c0 < n_mma; c0 += 16 * (NW / 4)) {
       uint32_t v[16];
       if (nchunks > 0) {
         tmem_ld_32x32b_x16(tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)c0, v);
@@ -555,7 +561,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       mma_commit(&tmem_full_bar);           // accumulator complete
     }
-  } else {
+  } else if (warp == kTmaWarp) {
     // ---------------- TMA issuer ----------------
     if (kAnyTma && lane == 0 && nchunks > 0) {
       uint32_t bytes = 0;
@@ -570,6 +576,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_arrive_expect_tx(&full_bar[s], bytes);
         if constexpr (AL::kTMA) al.issue(&tmA, a_tile, &full_bar[s], m0, r0);
         if constexpr (BL::kTMA) bl.issue(&tmB, b_tile, &full_bar[s], n0, r0);
+      }
+    }
+  } else {
+    // ---------------- reduction-index table builder ----------------
+    if constexpr (AL::kKTable) {
+      for (int kc = 0; kc < nchunks; ++kc) {
+        const int s = kc % TSTAGES;
+        mbar_wait(&empty_bar[s], ((kc / TSTAGES) & 1) ^ 1);     // the slot's previous readers are done
+        k_table[s][lane] = al.table_entry(r_begin + kc * TBK + lane, r_end);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&tab_bar[s]);
       }
     }
   }
