@@ -179,25 +179,43 @@ struct LoadAccMN {
 };
 
 // Per-chunk reduction-index table for the two pixel-row gathers below: for each of the chunk's 32
-// reduction indices {input offset delta, 1 << kh, 1 << kw, 0}; an all-zero mask marks an index beyond the
-// reduction.  Built by a dedicated warp one stage ahead, read by the gather warps as broadcast LDS.128 —
-// this replaces ~40 instructions of index arithmetic per gathered element by one shared-memory load.
-//
+// reduction indices {input offset delta, tap mask A, tap mask B, 0}; all-zero masks mark an index beyond
+// the reduction.  Built by a dedicated warp one stage ahead, read by the gather warps as broadcast
+// LDS.128 — this replaces ~40 instructions of index arithmetic per gathered element by one shared-memory
+// load.  Padding test per element: filters with kh*kw <= 32 taps use ONE per-thread 2-D validity mask
+// (bit kh_i*kw + kw_i set when that tap reads inside the image; table mask A = 1 << tap, B = ~0);
+// larger filters (11x11) use separate row / column masks (A = 1 << kh_i against hmask, B = 1 << kw_i
+// against wmask).  Loads are predicated instructions, never branches.
+// Keep a per-thread base pointer as an opaque 64-bit value: without this the compiler re-derives it from
+// the kernel parameter and a 64-bit element offset at every use (4 instructions per gathered element).
+__device__ __forceinline__ const float* opaque(const float* p) {
+  asm volatile("" : "+l"(p));
+  return p;
+}
+__device__ __forceinline__ uint32_t mask2d(uint32_t hmask, uint32_t wmask, int kh, int kw) {
+  uint32_t m = 0;
+  for (int k = 0; k < kh; ++k) if ((hmask >> k) & 1u) m |= wmask << (k * kw);
+  return m;
+}
+
 // Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t owns pixel
 // row0 + (t & 127) and 8 of the chunk's 32 reduction indices.  Its (n,ho,wo), input base and padding masks
 // are computed once per tile.  Lanes = consecutive pixels, so global reads are coalesced along W and the
 // swizzled 128-byte rows are written conflict-free.
+template <bool SMALL>
 struct LoadIm2colRowsMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = true;
   const float* x; ConvGeom g; int grp;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { const float* base; uint32_t hmask, wmask; };
+  struct State { const float* base; uint32_t ma, mb; };
+  __device__ static constexpr bool small() { return SMALL; }
   __device__ int4 table_entry(int r, int r_end) const {
     if (r >= r_end || r >= g.Kdim()) return make_int4(0, 0, 0, 0);
     uint32_t c, tt, ky, kx;
     dKhKw.divmod((uint32_t)r, c, tt);
     dKw.divmod(tt, ky, kx);
-    return make_int4((int)c * g.H * g.W + (int)ky * g.W + (int)kx, 1 << ky, 1 << kx, 0);
+    const int delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
+    return small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
   }
   __device__ void init(State& s, int row0, int t) const {
     const int row = row0 + (t & 127);
@@ -205,11 +223,13 @@ struct LoadIm2colRowsMN {
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
     if (live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
     const int hi0 = (int)ho * g.sh - g.ph, wi0 = (int)wo * g.sw - g.pw;
-    s.base = x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0);
-    s.hmask = 0; s.wmask = 0;
-    for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) s.hmask |= 1u << k;
-    for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) s.wmask |= 1u << k;
-    if (!live) s.hmask = 0;
+    s.base = opaque(x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0));
+    uint32_t hmask = 0, wmask = 0;
+    for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) hmask |= 1u << k;
+    for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) wmask |= 1u << k;
+    if (!live) hmask = 0;
+    if (small()) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = s.ma ? ~0u : 0u; }
+    else { s.ma = hmask; s.mb = wmask; }
   }
   __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
     const int m = t & 127, kb = (t >> 7) * 8;
@@ -217,7 +237,8 @@ struct LoadIm2colRowsMN {
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int4 e = ktab[kb + k];
-      v[k] = ((s.hmask & (uint32_t)e.y) && (s.wmask & (uint32_t)e.z)) ? __ldg(s.base + e.x) : 0.f;
+      v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
+                                          : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
@@ -226,17 +247,20 @@ struct LoadIm2colRowsMN {
 
 // Convolution backward-data A operand (stride 1): rows = input pixels, r = (co,kh,kw), MN-major.
 // value = dY[n][co][h+ph-kh][w+pw-kw] when that output position exists.
+template <bool SMALL>
 struct LoadDgradRowsMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = true;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHW, dW, dKhKw, dKw;
-  struct State { const float* base; uint32_t hmask, wmask; };
+  struct State { const float* base; uint32_t ma, mb; };
+  __device__ static constexpr bool small() { return SMALL; }
   __device__ int4 table_entry(int r, int r_end) const {
     if (r >= r_end || r >= g.Og() * g.kh * g.kw) return make_int4(0, 0, 0, 0);
     uint32_t co, tt, ky, kx;
     dKhKw.divmod((uint32_t)r, co, tt);
     dKw.divmod(tt, ky, kx);
-    return make_int4((int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx, 1 << ky, 1 << kx, 0);
+    const int delta = (int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx;
+    return small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
   }
   __device__ void init(State& s, int row0, int t) const {
     const int row = row0 + (t & 127);
@@ -244,11 +268,13 @@ struct LoadDgradRowsMN {
     uint32_t n = 0, pix = 0, h = 0, w = 0;
     if (live) { dHW.divmod(row, n, pix); dW.divmod(pix, h, w); }
     const int hb = (int)h + g.ph, wb = (int)w + g.pw;            // output row = hb - ky, col = wb - kx
-    s.base = dy + ((ptrdiff_t)((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb);
-    s.hmask = 0; s.wmask = 0;
-    for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) s.hmask |= 1u << k;
-    for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) s.wmask |= 1u << k;
-    if (!live) s.hmask = 0;
+    s.base = opaque(dy + ((ptrdiff_t)((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb));
+    uint32_t hmask = 0, wmask = 0;
+    for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) hmask |= 1u << k;
+    for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) wmask |= 1u << k;
+    if (!live) hmask = 0;
+    if (small()) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = s.ma ? ~0u : 0u; }
+    else { s.ma = hmask; s.mb = wmask; }
   }
   __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
     const int m = t & 127, kb = (t >> 7) * 8;
@@ -256,7 +282,8 @@ struct LoadDgradRowsMN {
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int4 e = ktab[kb + k];
-      v[k] = ((s.hmask & (uint32_t)e.y) && (s.wmask & (uint32_t)e.z)) ? __ldg(s.base + e.x) : 0.f;
+      v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
+                                          : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
     }
 #pragma unroll
     for (int k = 0; k < 8; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
@@ -276,12 +303,13 @@ struct LoadFilterDgradK {
     const bool ok = r < r_end && r < g.Og() * khkw;
     uint32_t co = 0, tap = 0;
     if (ok) dKhKw.divmod(r, co, tap);
-    const float* q = w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap;
+    const float* q = opaque(w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap);
+    const int lim = ok ? min(rows, Cg - row0) : 0;               // valid tile rows
     float v[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const int row = wp + NW * i, c = row0 + row;
-      v[i] = (ok && row < rows && c < Cg) ? __ldg(q + (size_t)c * khkw) : 0.f;
+      const int row = wp + NW * i;
+      v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * khkw, row < lim);
     }
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
@@ -303,12 +331,13 @@ struct LoadDyRowsK {
     const bool ok = r < r_end && r < g.N * HoWo;
     uint32_t n = 0, pix = 0;
     if (ok) dHoWo.divmod(r, n, pix);
-    const float* q = dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix;
+    const float* q = opaque(dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix);
+    const int lim = ok ? g.Og() - row0 : 0;
     float v[8];
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const int co = row0 + wp + NW * i;
-      v[i] = (ok && co < g.Og()) ? __ldg(q + (size_t)co * HoWo) : 0.f;
+      const int row = wp + NW * i;
+      v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * HoWo, row < lim);
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) *(float*)(tile + off_kmajor(wp + NW * i, k)) = to_tf32(v[i]);
@@ -316,14 +345,16 @@ struct LoadDyRowsK {
 };
 // Backward-filter B operand: im2col viewed as [(c,kh,kw)][(n,ho,wo)], K-major.  lane = r: its
 // (n,ho,wo), input base and padding masks are computed once per chunk; the per-row (c,kh,kw) comes
-// from a table built once per CTA in shared memory (row_tab[row] = {input offset, 1<<kh, 1<<kw, 0};
+// from a table built once per CTA in shared memory (same entry format as the per-chunk table above;
 // zero masks mark rows beyond the filter).
+template <bool SMALL>
 struct LoadIm2colColsK {
   static constexpr bool kTMA = false, kMN = false, kKTable = false;
   const float* x; ConvGeom g; int grp; int rows;
   FastDiv dHoWo, dWo, dKhKw, dKw;
   struct State { const int4* tab; };
   static constexpr int kTableRows = 256;
+  __device__ static constexpr bool small() { return SMALL; }
   __device__ void build_table(int4* tab, int row0, int t) const {
     for (int row = t; row < rows; row += NT) {
       const int rr = row0 + row;
@@ -332,7 +363,8 @@ struct LoadIm2colColsK {
         uint32_t c, tt, ky, kx;
         dKhKw.divmod(rr, c, tt);
         dKw.divmod(tt, ky, kx);
-        e = make_int4((int)c * g.H * g.W + (int)ky * g.W + (int)kx, 1 << ky, 1 << kx, 0);
+        const int delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
+        e = small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
       }
       tab[row] = e;
     }
@@ -348,16 +380,16 @@ struct LoadIm2colColsK {
     for (int q = 0; q < g.kh; ++q) if (hi0 + q >= 0 && hi0 + q < g.H) hmask |= 1u << q;
     for (int q = 0; q < g.kw; ++q) if (wi0 + q >= 0 && wi0 + q < g.W) wmask |= 1u << q;
     if (!ok) hmask = 0;
-    const float* base = x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0);
+    uint32_t ma, mb;
+    if (small()) { ma = mask2d(hmask, wmask, g.kh, g.kw); mb = ma ? ~0u : 0u; } else { ma = hmask; mb = wmask; }
+    const float* base = opaque(x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0));
     float v[16];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      const int row = wp + NW * i;
-      v[i] = 0.f;
-      if (row < rows) {
-        const int4 e = s.tab[row];
-        if ((hmask & (uint32_t)e.y) && (wmask & (uint32_t)e.z)) v[i] = __ldg(base + e.x);
-      }
+      const int row = min(wp + NW * i, kTableRows - 1);
+      const int4 e = s.tab[row];
+      v[i] = ldg_pred(base + e.x, (SMALL ? (ma & (uint32_t)e.y) != 0 : ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0)) &
+                                      (wp + NW * i < rows));
     }
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
@@ -427,6 +459,9 @@ struct TEpiTransposed {    // p[n*ld + m] = v + bias[m] (+ReLU)
 // ------------------------------------------------------------------------------------------
 // The kernel
 // ------------------------------------------------------------------------------------------
+template <class L> struct HasRowTable : std::false_type {};
+template <bool S> struct HasRowTable<LoadIm2colColsK<S>> : std::true_type {};
+
 template <int BN>
 struct TcCfg {
   static constexpr int kBTileBytes = BN * TBK * 4;
@@ -446,7 +481,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tab_bar[TSTAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
-  __shared__ int4 row_table[LoadIm2colColsK::kTableRows];     // backward-filter: per-CTA row table
+  __shared__ int4 row_table[256];     // backward-filter: per-CTA row table
   __shared__ int4 k_table[TSTAGES][TBK];                      // pixel-row gathers: per-chunk reduction table
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -471,7 +506,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (BL::kTMA) tma_prefetch_desc(&tmB);
   }
   if (warp == kMmaWarp) tmem_alloc<Cfg::kTmemCols>(&tmem_base_smem);
-  if constexpr (std::is_same<BL, LoadIm2colColsK>::value) {
+  if constexpr (HasRowTable<BL>::value) {
     if (warp < NW) bl.build_table(row_table, n0, tid);
   }
   tc_fence_before_sync();
@@ -487,7 +522,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if constexpr (!AL::kTMA) al.init(sa, m0, tid);
       if constexpr (!BL::kTMA) {
         bl.init(sb, n0, tid);
-        if constexpr (std::is_same<BL, LoadIm2colColsK>::value) sb.tab = row_table;
+        if constexpr (HasRowTable<BL>::value) sb.tab = row_table;
       }
       for (int kc = 0; kc < nchunks; ++kc) {
         const int s = kc % TSTAGES;
@@ -715,17 +750,20 @@ void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float*
   const int P = g.N * g.Ho * g.Wo, K = g.Kdim(), Og = g.Og();
   const int n_mma = pick_n_mma(Og);
   for (int grp = 0; grp < g.group; ++grp) {
-    LoadIm2colRowsMN al{x, g, grp, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
     TEpiConvFwd ep{y, bias, P, g.Ho * g.Wo, g.Cout, Og, grp, relu ? 1 : 0, FastDiv(g.Ho * g.Wo)};
     EpiConvFwd re{y, bias, g, grp, relu ? 1 : 0, FastDiv(g.Ho * g.Wo)};
     const float* wg = w_tf32 + (size_t)grp * Og * K;
-    if (K % 4 == 0 && ((uintptr_t)wg & 15) == 0) {
-      CUtensorMap tmB = make_tmap(wg, (uint64_t)K, (uint64_t)Og, (uint64_t)K * 4, (uint32_t)n_mma);
-      launch_tc(s, dummy_tmap(), tmB, al, LoadTmaK{n_mma}, ep, re, P, Og, K, n_mma);
-    } else {
-      LoadDenseK bl{wg, K, Og, K, n_mma, 0};
-      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Og, K, n_mma);
-    }
+    auto go = [&](auto al) {
+      if (K % 4 == 0 && ((uintptr_t)wg & 15) == 0) {
+        CUtensorMap tmB = make_tmap(wg, (uint64_t)K, (uint64_t)Og, (uint64_t)K * 4, (uint32_t)n_mma);
+        launch_tc(s, dummy_tmap(), tmB, al, LoadTmaK{n_mma}, ep, re, P, Og, K, n_mma);
+      } else {
+        LoadDenseK bl{wg, K, Og, K, n_mma, 0};
+        launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Og, K, n_mma);
+      }
+    };
+    if (g.kh * g.kw <= 32) go(LoadIm2colRowsMN<true>{x, g, grp, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)});
+    else go(LoadIm2colRowsMN<false>{x, g, grp, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)});
   }
 }
 void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx) {
@@ -735,8 +773,11 @@ void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const flo
     TEpiConvDgrad ep{dx, P, g.H * g.W, g.C, Cg, grp, FastDiv(g.H * g.W)};
     EpiConvDgrad re{dx, g, grp, FastDiv(g.H * g.W)};
     LoadFilterDgradK bl{w, g, grp, n_mma, FastDiv(g.kh * g.kw)};
-    if (g.sh == 1 && g.sw == 1) {
-      LoadDgradRowsMN al{dy, g, grp, FastDiv(g.H * g.W), FastDiv(g.W), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+    if (g.sh == 1 && g.sw == 1 && g.kh * g.kw <= 32) {
+      LoadDgradRowsMN<true> al{dy, g, grp, FastDiv(g.H * g.W), FastDiv(g.W), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Cg, R, n_mma);
+    } else if (g.sh == 1 && g.sw == 1) {
+      LoadDgradRowsMN<false> al{dy, g, grp, FastDiv(g.H * g.W), FastDiv(g.W), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
       launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, P, Cg, R, n_mma);
     } else {
       LoadAccMN<DgradRows> al{make_dgrad_rows(dy, g, grp), TBM};
@@ -750,10 +791,15 @@ void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const floa
   for (int grp = 0; grp < g.group; ++grp) {
     float* dwg = dw + (size_t)grp * Og * K;
     LoadDyRowsK al{dy, g, grp, FastDiv(g.Ho * g.Wo)};
-    LoadIm2colColsK bl{x, g, grp, n_mma, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
     TEpiRowMajor ep{dwg, K, Og, K, accumulate ? 1 : 0};
     EpiRowMajor re{dwg, K, Og, K, accumulate ? 1 : 0};
-    launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, Og, K, R, n_mma);
+    if (g.kh * g.kw <= 32) {
+      LoadIm2colColsK<true> bl{x, g, grp, n_mma, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, Og, K, R, n_mma);
+    } else {
+      LoadIm2colColsK<false> bl{x, g, grp, n_mma, FastDiv(g.Ho * g.Wo), FastDiv(g.Wo), FastDiv(g.kh * g.kw), FastDiv(g.kw)};
+      launch_tc(s, dummy_tmap(), dummy_tmap(), al, bl, ep, re, Og, K, R, n_mma);
+    }
   }
 }
 

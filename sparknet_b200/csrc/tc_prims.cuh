@@ -110,6 +110,16 @@ __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t (&v)
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// Predicated read-only global load: returns 0 without touching memory when `pred` is false.  Written as
+// a predicated instruction (not a branch) so that a gather loop stays straight-line code and all its
+// loads can be in flight together.
+__device__ __forceinline__ float ldg_pred(const float* p, bool pred) {
+  float v;
+  asm("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, %2, 0;\n\tmov.b32 %0, 0;\n\t@q ld.global.nc.f32 %0, [%1];\n\t}"
+      : "=f"(v) : "l"(p), "r"((int)pred));
+  return v;
+}
+
 // round-to-nearest fp32 -> tf32 (keeps the fp32 container; low 13 mantissa bits zero)
 __device__ __forceinline__ float to_tf32(float x) {
   uint32_t r;
