@@ -6,11 +6,11 @@
 // caffe/src/caffe/layers/inner_product_layer.cu:10-56).
 //
 // Every contraction is  D[m][n] = sum_r A(m,r) * B(n,r)  with a 128 x BN accumulator tile per CTA:
-//   warps 0-7  gather/convert the operands that cannot come through TMA (fp32 -> tf32 with
+//   warps 0-15 gather/convert (four groups of four warps, one group per pipeline stage) the operands that cannot come through TMA (fp32 -> tf32 with
 //              round-to-nearest; TMA-fed weights come from a pre-rounded shadow copy), then run the
 //              epilogue (tcgen05.ld: warp w owns TMEM lanes 32(w%4)..+31 = tile rows);
-//   warp 8     allocates TMEM and issues tcgen05.mma (one thread), 4 x (128 x n_mma x 8) per 32-deep chunk;
-//   warp 9     issues the TMA loads.
+//   warp 16    allocates TMEM and issues tcgen05.mma (one thread), 4 x (128 x n_mma x 8) per 32-deep chunk;
+//   warp 17    issues the TMA loads; warp 18 builds the per-chunk reduction-index tables.
 // Reductions that leave too few tiles for 148 SMs are split along r; the slices are summed in a
 // fixed order by splitk_reduce (deterministic, no atomics).
 #include <cuda.h>
@@ -31,15 +31,19 @@ constexpr int TBM = 128, TBK = 32, TSTAGES = 4;
 constexpr int kATileBytes = TBM * TBK * 4;            // 16 KB
 
 // ------------------------------------------------------------------------------------------
-// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by the NT = 512 gather threads
-// (16 warps: four per scheduler, so some can issue while the others wait on memory).  kMN: MN-major tile
+// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by ONE gather group of GT = 128
+// threads per chunk.  The NT = 512 gather threads form NG = 4 groups; group g fills pipeline stage g
+// (chunks g, g+4, ...), so four chunks are being gathered at any time and the global-load latency of one
+// overlaps the address arithmetic, conversion and shared-memory stores of the others.  kMN: MN-major tile
 // (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows actually needed (128 for
 // A, n_mma for B); rows beyond the operand's extent are zero-filled.  Every loader first issues ALL its
 // global loads of the chunk into registers and only then converts and stores them, so a thread has 8-16
 // loads in flight (the first version interleaved load/convert/store and was latency bound).
 // ------------------------------------------------------------------------------------------
 constexpr int NT = 512;
-constexpr int NW = NT / 32;                   // gather warps
+constexpr int NW = NT / 32;                   // gather warps (all of them run the epilogue)
+constexpr int GT = 128, GW = GT / 32;         // threads / warps per gather group
+constexpr int NG = NT / GT;                   // gather groups == pipeline stages
 struct NoState {};
 
 // weights through TMA, K-major: tensor {K (contiguous), rows}; box {32, rows_box}
@@ -79,25 +83,27 @@ struct LoadDenseK {
     if (vec) {
       const int c = t & 7;                         // 16-byte chunk within the 128-byte row
       const int r = r0 + 4 * c;
-      float4 v[4];
+      for (int rb = 0; rb < rows; rb += 128) {
+        float4 v[8];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int row = (t >> 3) + 64 * i, gr = row0 + row;
-        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row < rows && gr < nrows && r < r_end) {
-          const float* q = p + (size_t)gr * ld + r;
-          if (r + 3 < r_end) v[i] = __ldg((const float4*)q);
-          else { v[i].x = __ldg(q); if (r + 1 < r_end) v[i].y = __ldg(q + 1); if (r + 2 < r_end) v[i].z = __ldg(q + 2); }
+        for (int i = 0; i < 8; ++i) {
+          const int row = rb + (t >> 3) + 16 * i, gr = row0 + row;
+          v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (row < rows && gr < nrows && r < r_end) {
+            const float* q = p + (size_t)gr * ld + r;
+            if (r + 3 < r_end) v[i] = __ldg((const float4*)q);
+            else { v[i].x = __ldg(q); if (r + 1 < r_end) v[i].y = __ldg(q + 1); if (r + 2 < r_end) v[i].z = __ldg(q + 2); }
+          }
         }
-      }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int row = (t >> 3) + 64 * i;
-        if (row < rows) *(float4*)(tile + off_kmajor(row, 4 * c)) = tf32x4(v[i]);
+        for (int i = 0; i < 8; ++i) {
+          const int row = rb + (t >> 3) + 16 * i;
+          if (row < rows) *(float4*)(tile + off_kmajor(row, 4 * c)) = tf32x4(v[i]);
+        }
       }
     } else {
       const int k = t & 31, r = r0 + k;
-      for (int row = t >> 5; row < rows; row += NW) {
+      for (int row = t >> 5; row < rows; row += GW) {
         const int gr = row0 + row;
         const float v = (gr < nrows && r < r_end) ? __ldg(p + (size_t)gr * ld + r) : 0.f;
         *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
@@ -105,7 +111,7 @@ struct LoadDenseK {
     }
   }
 };
-// dense [r][mn] (mn contiguous), MN-major tile.  Warp w owns k = 2w, 2w+1; lanes run along mn.
+// dense [r][mn] (mn contiguous), MN-major tile.  Warp w of the group owns k = 8w..8w+7; lanes run along mn.
 struct LoadDenseMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = false;
   typedef NoState State;
@@ -115,26 +121,26 @@ struct LoadDenseMN {
     const int w = t >> 5, lane = t & 31;
     if (vec) {
       const int ch = rows >> 2;                    // 16-byte chunks per k-row (<= 64)
-      float4 v[4];
+      for (int cb = 0; cb < ch; cb += 32) {
+        const int c = cb + lane, mn = row0 + 4 * c;
+        float4 v[8];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int k = 2 * w + (i & 1), c = lane + 32 * (i >> 1);
-        const int mn = row0 + 4 * c, r = r0 + k;
-        v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (c < ch && r < r_end && mn < nrows) {
-          const float* q = p + (size_t)r * ld + mn;
-          if (mn + 3 < nrows) v[i] = __ldg((const float4*)q);
-          else { v[i].x = __ldg(q); if (mn + 1 < nrows) v[i].y = __ldg(q + 1); if (mn + 2 < nrows) v[i].z = __ldg(q + 2); }
+        for (int i = 0; i < 8; ++i) {
+          const int r = r0 + 8 * w + i;
+          v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (c < ch && r < r_end && mn < nrows) {
+            const float* q = p + (size_t)r * ld + mn;
+            if (mn + 3 < nrows) v[i] = __ldg((const float4*)q);
+            else { v[i].x = __ldg(q); if (mn + 1 < nrows) v[i].y = __ldg(q + 1); if (mn + 2 < nrows) v[i].z = __ldg(q + 2); }
+          }
         }
-      }
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int k = 2 * w + (i & 1), c = lane + 32 * (i >> 1);
-        if (c < ch) *(float4*)(tile + off_mnmajor(4 * c, k)) = tf32x4(v[i]);
+        for (int i = 0; i < 8; ++i)
+          if (c < ch) *(float4*)(tile + off_mnmajor(4 * c, 8 * w + i)) = tf32x4(v[i]);
       }
     } else {
-      for (int kk = 0; kk < 2; ++kk) {
-        const int k = 2 * w + kk, r = r0 + k;
+      for (int kk = 0; kk < 8; ++kk) {
+        const int k = 8 * w + kk, r = r0 + k;
         for (int m = lane; m < rows; m += 32) {
           const int mn = row0 + m;
           const float v = (r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
@@ -154,13 +160,13 @@ struct LoadAccK {
   __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
     const int k = t & 31, r = r0 + k;
-    for (int row = t >> 5; row < rows; row += NW) {
+    for (int row = t >> 5; row < rows; row += GW) {
       const float v = r < r_end ? acc(row0 + row, r) : 0.f;
       *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
     }
   }
 };
-// Any accessor as an MN-major tile (thread = row, half the chunk's k each): generic.
+// Any accessor as an MN-major tile (thread = row): generic.
 template <class Acc>
 struct LoadAccMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = false;
@@ -168,9 +174,9 @@ struct LoadAccMN {
   Acc acc; int rows;
   __device__ void init(State&, int, int) const {}
   __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int m = t & 127, kb = (t >> 7) * 8;
+    const int m = t;
     if (m >= rows) return;
-    for (int k = kb; k < kb + 8; ++k) {
+    for (int k = 0; k < TBK; ++k) {
       const int r = r0 + k;
       const float v = r < r_end ? acc(row0 + m, r) : 0.f;
       *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
@@ -198,8 +204,8 @@ __device__ __forceinline__ uint32_t mask2d(uint32_t hmask, uint32_t wmask, int k
   return m;
 }
 
-// Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t owns pixel
-// row0 + (t & 127) and 8 of the chunk's 32 reduction indices.  Its (n,ho,wo), input base and padding masks
+// Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t of the
+// group owns pixel row0 + t and all 32 reduction indices of the chunk.  Its (n,ho,wo), input base and padding masks
 // are computed once per tile.  Lanes = consecutive pixels, so global reads are coalesced along W and the
 // swizzled 128-byte rows are written conflict-free.
 template <bool SMALL>
@@ -218,7 +224,7 @@ struct LoadIm2colRowsMN {
     return small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
   }
   __device__ void init(State& s, int row0, int t) const {
-    const int row = row0 + (t & 127);
+    const int row = row0 + t;
     const bool live = row < g.N * g.Ho * g.Wo;
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
     if (live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
@@ -232,16 +238,19 @@ struct LoadIm2colRowsMN {
     else { s.ma = hmask; s.mb = wmask; }
   }
   __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
-    const int m = t & 127, kb = (t >> 7) * 8;
-    float v[8];
+    const int m = t;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int4 e = ktab[kb + k];
-      v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
-                                          : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
+    for (int kb = 0; kb < TBK; kb += 16) {
+      float v[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int4 e = ktab[kb + k];
+        v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
+                                            : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
+      }
+#pragma unroll
+      for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
   }
 };
 
@@ -263,7 +272,7 @@ struct LoadDgradRowsMN {
     return small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
   }
   __device__ void init(State& s, int row0, int t) const {
-    const int row = row0 + (t & 127);
+    const int row = row0 + t;
     const bool live = row < g.N * g.H * g.W;
     uint32_t n = 0, pix = 0, h = 0, w = 0;
     if (live) { dHW.divmod(row, n, pix); dW.divmod(pix, h, w); }
@@ -277,20 +286,23 @@ struct LoadDgradRowsMN {
     else { s.ma = hmask; s.mb = wmask; }
   }
   __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
-    const int m = t & 127, kb = (t >> 7) * 8;
-    float v[8];
+    const int m = t;
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int4 e = ktab[kb + k];
-      v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
-                                          : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
+    for (int kb = 0; kb < TBK; kb += 16) {
+      float v[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        const int4 e = ktab[kb + k];
+        v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
+                                            : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
+      }
+#pragma unroll
+      for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
     }
-#pragma unroll
-    for (int k = 0; k < 8; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
   }
 };
 // Backward-data B operand: filters viewed as [c][(co,kh,kw)], K-major.  lane = r: its (co, tap) is
-// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w owns rows w, w+16, ...
+// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w of the group owns rows w, w+4, ...
 struct LoadFilterDgradK {
   static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
@@ -305,16 +317,18 @@ struct LoadFilterDgradK {
     if (ok) dKhKw.divmod(r, co, tap);
     const float* q = opaque(w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap);
     const int lim = ok ? min(rows, Cg - row0) : 0;               // valid tile rows
-    float v[16];
+    for (int rb = 0; rb < rows; rb += 16 * GW) {
+      float v[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int row = wp + NW * i;
-      v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * khkw, row < lim);
-    }
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + GW * i;
+        v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * khkw, row < lim);
+      }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int row = wp + NW * i;
-      if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + GW * i;
+        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+      }
     }
   }
 };
@@ -333,14 +347,17 @@ struct LoadDyRowsK {
     if (ok) dHoWo.divmod(r, n, pix);
     const float* q = opaque(dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix);
     const int lim = ok ? g.Og() - row0 : 0;
-    float v[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int row = wp + NW * i;
-      v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * HoWo, row < lim);
+    for (int rb = 0; rb < TBM; rb += 16 * GW) {
+      float v[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + GW * i;
+        v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * HoWo, row < lim);
+      }
+#pragma unroll
+      for (int i = 0; i < 16; ++i) *(float*)(tile + off_kmajor(rb + wp + GW * i, k)) = to_tf32(v[i]);
     }
-#pragma unroll
-    for (int i = 0; i < 8; ++i) *(float*)(tile + off_kmajor(wp + NW * i, k)) = to_tf32(v[i]);
   }
 };
 // Backward-filter B operand: im2col viewed as [(c,kh,kw)][(n,ho,wo)], K-major.  lane = r: its
@@ -356,7 +373,7 @@ struct LoadIm2colColsK {
   static constexpr int kTableRows = 256;
   __device__ static constexpr bool small() { return SMALL; }
   __device__ void build_table(int4* tab, int row0, int t) const {
-    for (int row = t; row < rows; row += NT) {
+    for (int row = t; row < rows; row += NT) {          // called with the CTA-wide thread index
       const int rr = row0 + row;
       int4 e = make_int4(0, 0, 0, 0);
       if (rr < g.Kdim()) {
@@ -383,18 +400,20 @@ struct LoadIm2colColsK {
     uint32_t ma, mb;
     if (small()) { ma = mask2d(hmask, wmask, g.kh, g.kw); mb = ma ? ~0u : 0u; } else { ma = hmask; mb = wmask; }
     const float* base = opaque(x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0));
-    float v[16];
+    for (int rb = 0; rb < rows; rb += 16 * GW) {
+      float v[16];
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int row = min(wp + NW * i, kTableRows - 1);
-      const int4 e = s.tab[row];
-      v[i] = ldg_pred(base + e.x, (SMALL ? (ma & (uint32_t)e.y) != 0 : ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0)) &
-                                      (wp + NW * i < rows));
-    }
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + GW * i;
+        const int4 e = s.tab[min(row, kTableRows - 1)];
+        v[i] = ldg_pred(base + e.x, (SMALL ? (ma & (uint32_t)e.y) != 0 : ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0)) &
+                                        (row < rows));
+      }
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      const int row = wp + NW * i;
-      if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + GW * i;
+        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+      }
     }
   }
 };
@@ -496,7 +515,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   if (tid == 0) {
     for (int s = 0; s < TSTAGES; ++s) {
-      mbar_init(&full_bar[s], (kAnySimt ? (uint32_t)NT : 0u) + (kAnyTma ? 1u : 0u));
+      mbar_init(&full_bar[s], (kAnySimt ? (uint32_t)GT : 0u) + (kAnyTma ? 1u : 0u));
       mbar_init(&empty_bar[s], 1u);
       mbar_init(&tab_bar[s], 1u);
     }
@@ -517,29 +536,31 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp < NW) {
     // ---------------- gather producers ----------------
     if (kAnySimt && nchunks > 0) {
+      static_assert(NG == TSTAGES, "one gather group per pipeline stage");
+      const int grp = warp / GW, tg = tid & (GT - 1);          // group g fills stage g: chunks g, g+NG, ...
       typename AL::State sa;
       typename BL::State sb;
-      if constexpr (!AL::kTMA) al.init(sa, m0, tid);
+      if constexpr (!AL::kTMA) al.init(sa, m0, tg);
       if constexpr (!BL::kTMA) {
-        bl.init(sb, n0, tid);
+        bl.init(sb, n0, tg);
         if constexpr (HasRowTable<BL>::value) sb.tab = row_table;
       }
-      for (int kc = 0; kc < nchunks; ++kc) {
-        const int s = kc % TSTAGES;
+      const int s = grp;
+      uint8_t* a_tile = smem + s * Cfg::kStageBytes;
+      uint8_t* b_tile = a_tile + kATileBytes;
+      for (int kc = grp; kc < nchunks; kc += NG) {
         const uint32_t ph = (kc / TSTAGES) & 1;
         mbar_wait(&empty_bar[s], ph ^ 1);
-        uint8_t* a_tile = smem + s * Cfg::kStageBytes;
-        uint8_t* b_tile = a_tile + kATileBytes;
         const int r0 = r_begin + kc * TBK;
         if constexpr (!AL::kTMA) {
           if constexpr (AL::kKTable) {
             mbar_wait(&tab_bar[s], ph);
-            al.load(sa, a_tile, k_table[s], tid);
+            al.load(sa, a_tile, k_table[s], tg);
           } else {
-            al.load(sa, a_tile, m0, r0, r_end, tid);
+            al.load(sa, a_tile, m0, r0, r_end, tg);
           }
         }
-        if constexpr (!BL::kTMA) bl.load(sb, b_tile, n0, r0, r_end, tid);
+        if constexpr (!BL::kTMA) bl.load(sb, b_tile, n0, r0, r_end, tg);
         fence_proxy_async_smem();
         mbar_arrive(&full_bar[s]);
       }
