@@ -212,9 +212,49 @@ __global__ void pool_max_bwd_kernel(PoolGeom g, size_t total, const float* __res
     dx[idx] = acc;
   }
 }
+// Plane-per-CTA form: the pooled plane's (dy, mask) pair is staged in shared memory with coalesced
+// loads, then every input element of the plane checks the <= ceil(k/s)^2 windows that cover it.  Global
+// traffic is exactly the algorithmic 8*out + 4*in bytes; no integer division per element.
+__global__ void pool_max_bwd_plane_kernel(PoolGeom g, const float* __restrict__ dy, const int* __restrict__ mask,
+                                          float* __restrict__ dx) {
+  extern __shared__ float sm_pool[];
+  const int P = g.PH * g.PW;
+  float* sdy = sm_pool;
+  int* smask = (int*)(sm_pool + P);
+  const size_t plane = blockIdx.x;
+  const int lin = threadIdx.y * blockDim.x + threadIdx.x, nthr = blockDim.x * blockDim.y;
+  for (int i = lin; i < P; i += nthr) {
+    sdy[i] = dy[plane * P + i];
+    smask[i] = mask[plane * P + i];
+  }
+  __syncthreads();
+  float* dxp = dx + plane * (size_t)(g.H * g.W);
+  for (int h = threadIdx.y; h < g.H; h += blockDim.y) {
+    const int phs = (h + g.ph < g.kh) ? 0 : (h + g.ph - g.kh) / g.sh + 1;
+    const int phe = min((h + g.ph) / g.sh + 1, g.PH);
+    for (int w = threadIdx.x; w < g.W; w += blockDim.x) {
+      const int pws = (w + g.pw < g.kw) ? 0 : (w + g.pw - g.kw) / g.sw + 1;
+      const int pwe = min((w + g.pw) / g.sw + 1, g.PW);
+      const int me = h * g.W + w;
+      float acc = 0.f;
+      for (int ph = phs; ph < phe; ++ph)
+        for (int pw = pws; pw < pwe; ++pw)
+          if (smask[ph * g.PW + pw] == me) acc += sdy[ph * g.PW + pw];
+      dxp[me] = acc;
+    }
+  }
+}
 void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx) {
-  const size_t total = (size_t)g.N * g.C * g.H * g.W;
-  pool_max_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, mask, dx);
+  const size_t smem = (size_t)g.PH * g.PW * 8;
+  if (smem <= 40 * 1024) {
+    // blockDim.x covers a row (coalesced stores), blockDim.y rows; the loops over threadIdx.x in the
+    // staging phase use the linear thread id
+    const int bx = g.W >= 32 ? 32 : 16, by = 256 / bx;
+    pool_max_bwd_plane_kernel<<<g.N * g.C, dim3(bx, by), smem, s>>>(g, dy, mask, dx);
+  } else {
+    const size_t total = (size_t)g.N * g.C * g.H * g.W;
+    pool_max_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, mask, dx);
+  }
   count_launch();
 }
 __global__ void pool_ave_fwd_kernel(PoolGeom g, size_t total, const float* __restrict__ x, float* __restrict__ y) {

@@ -86,3 +86,47 @@ def sequential_average(weight_lists):
             acc = (acc + p).astype(np.float32)
         out.append((acc / np.float32(n)).astype(np.float32))
     return out
+
+
+class HostAverager:
+    """The same exchange on host memory through the C ABI's weight accessors and any torch.distributed
+    backend (gloo in the CPU tests): every rank gathers all replicas' weights and folds them in rank order.
+    Same arithmetic as `Averager`; used where no GPU exists and as the reference for it."""
+
+    def __init__(self, net, rank: int, world: int):
+        self.net, self.rank, self.world = net, rank, world
+        self.method = "host all_gather + rank-ordered fp32 fold"
+
+    def broadcast_from_rank0(self) -> None:
+        if self.world == 1:
+            return
+        import torch
+        import torch.distributed as dist
+        w = self.net.getWeights()
+        for name in w.layerNames:
+            for a in w.allWeights[name]:
+                t = torch.from_numpy(a)
+                dist.broadcast(t, src=0)
+        self.net.setWeights(w)
+
+    def average(self) -> float:
+        if self.world == 1:
+            return 0.0
+        import torch
+        import torch.distributed as dist
+        w = self.net.getWeights()
+        for name in w.layerNames:
+            for j, a in enumerate(w.allWeights[name]):
+                parts = [torch.empty_like(torch.from_numpy(a)) for _ in range(self.world)]
+                dist.all_gather(parts, torch.from_numpy(a))
+                w.allWeights[name][j] = sequential_average([[p.numpy()] for p in parts])[0]
+        self.net.setWeights(w)
+        return 0.0
+
+
+def run_rounds(net, averager, tau: int, rounds: int) -> None:
+    """The driver loop of src/main/scala/apps/CifarApp.scala:95-136 without the test phase:
+    (broadcast/set weights) -> train(tau) -> average, `rounds` times."""
+    for _ in range(rounds):
+        net.train(tau)
+        averager.average()
