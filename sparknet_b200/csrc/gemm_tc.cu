@@ -213,7 +213,7 @@ struct LoadIm2colRowsMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = true;
   const float* x; ConvGeom g; int grp;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { const float* base; uint32_t ma, mb; };
+  struct State { const float* base; uint32_t ma, mb; int safe; };
   __device__ static constexpr bool small() { return SMALL; }
   __device__ int4 table_entry(int r, int r_end) const {
     if (r >= r_end || r >= g.Kdim()) return make_int4(0, 0, 0, 0);
@@ -229,11 +229,14 @@ struct LoadIm2colRowsMN {
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
     if (live) { dHoWo.divmod(row, n, pix); dWo.divmod(pix, ho, wo); }
     const int hi0 = (int)ho * g.sh - g.ph, wi0 = (int)wo * g.sw - g.pw;
-    s.base = opaque(x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0));
     uint32_t hmask = 0, wmask = 0;
     for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) wmask |= 1u << k;
-    if (!live) hmask = 0;
+    if (!live || !wmask) hmask = 0;
+    // loads are unconditional (plain LDG, no predicate): a padded tap reads a neighbouring row of the
+    // tensor or its guard band (runtime.hpp kGuardFloats) and the value is replaced by zero afterwards
+    s.safe = 0;
+    s.base = opaque(hmask ? x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0) : x);
     if (small()) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = s.ma ? ~0u : 0u; }
     else { s.ma = hmask; s.mb = wmask; }
   }
@@ -242,14 +245,17 @@ struct LoadIm2colRowsMN {
 #pragma unroll
     for (int kb = 0; kb < TBK; kb += 16) {
       float v[16];
+      uint32_t ok = 0;
 #pragma unroll
       for (int k = 0; k < 16; ++k) {
         const int4 e = ktab[kb + k];
-        v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
-                                            : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
+        const bool p = SMALL ? (s.ma & (uint32_t)e.y) != 0 : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0);
+        v[k] = __ldg(s.base + e.x);        // unconditional: a padded tap reads a neighbouring row or the guard band
+        ok |= (p ? 1u : 0u) << k;
       }
 #pragma unroll
-      for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
+      for (int k = 0; k < 16; ++k)
+        *(uint32_t*)(tile + off_mnmajor(m, kb + k)) = ((ok >> k) & 1u) ? __float_as_uint(v[k]) + 0x1000u : 0u;
     }
   }
 };
@@ -261,7 +267,7 @@ struct LoadDgradRowsMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = true;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHW, dW, dKhKw, dKw;
-  struct State { const float* base; uint32_t ma, mb; };
+  struct State { const float* base; uint32_t ma, mb; int safe; };
   __device__ static constexpr bool small() { return SMALL; }
   __device__ int4 table_entry(int r, int r_end) const {
     if (r >= r_end || r >= g.Og() * g.kh * g.kw) return make_int4(0, 0, 0, 0);
@@ -277,11 +283,12 @@ struct LoadDgradRowsMN {
     uint32_t n = 0, pix = 0, h = 0, w = 0;
     if (live) { dHW.divmod(row, n, pix); dW.divmod(pix, h, w); }
     const int hb = (int)h + g.ph, wb = (int)w + g.pw;            // output row = hb - ky, col = wb - kx
-    s.base = opaque(dy + ((ptrdiff_t)((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb));
     uint32_t hmask = 0, wmask = 0;
     for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) wmask |= 1u << k;
-    if (!live) hmask = 0;
+    if (!live || !wmask) hmask = 0;
+    s.safe = 0;
+    s.base = opaque(hmask ? dy + ((ptrdiff_t)((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb) : dy);
     if (small()) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = s.ma ? ~0u : 0u; }
     else { s.ma = hmask; s.mb = wmask; }
   }
@@ -290,14 +297,17 @@ struct LoadDgradRowsMN {
 #pragma unroll
     for (int kb = 0; kb < TBK; kb += 16) {
       float v[16];
+      uint32_t ok = 0;
 #pragma unroll
       for (int k = 0; k < 16; ++k) {
         const int4 e = ktab[kb + k];
-        v[k] = ldg_pred(s.base + e.x, SMALL ? (s.ma & (uint32_t)e.y) != 0
-                                            : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0));
+        const bool p = SMALL ? (s.ma & (uint32_t)e.y) != 0 : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0);
+        v[k] = __ldg(s.base + e.x);        // unconditional: a padded tap reads a neighbouring row or the guard band
+        ok |= (p ? 1u : 0u) << k;
       }
 #pragma unroll
-      for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(m, kb + k)) = to_tf32(v[k]);
+      for (int k = 0; k < 16; ++k)
+        *(uint32_t*)(tile + off_mnmajor(m, kb + k)) = ((ok >> k) & 1u) ? __float_as_uint(v[k]) + 0x1000u : 0u;
     }
   }
 };
@@ -320,14 +330,15 @@ struct LoadFilterDgradK {
     for (int rb = 0; rb < rows; rb += 16 * GW) {
       float v[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + GW * i;
-        v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * khkw, row < lim);
+      for (int i = 0; i < 16; ++i) v[i] = 0.f;
+      if (lim > 0) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __ldg(q + (ptrdiff_t)(row0 + min(rb + wp + GW * i, lim - 1)) * khkw);
       }
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int row = rb + wp + GW * i;
-        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+        if (row < rows) *(uint32_t*)(tile + off_kmajor(row, k)) = row < lim ? __float_as_uint(v[i]) + 0x1000u : 0u;
       }
     }
   }
@@ -351,12 +362,16 @@ struct LoadDyRowsK {
     for (int rb = 0; rb < TBM; rb += 16 * GW) {
       float v[16];
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + GW * i;
-        v[i] = ldg_pred(q + (ptrdiff_t)(row0 + row) * HoWo, row < lim);
+      for (int i = 0; i < 16; ++i) v[i] = 0.f;
+      if (lim > 0) {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = __ldg(q + (ptrdiff_t)(row0 + min(rb + wp + GW * i, lim - 1)) * HoWo);
       }
 #pragma unroll
-      for (int i = 0; i < 16; ++i) *(float*)(tile + off_kmajor(rb + wp + GW * i, k)) = to_tf32(v[i]);
+      for (int i = 0; i < 16; ++i) {
+        const int row = rb + wp + GW * i;
+        *(uint32_t*)(tile + off_kmajor(row, k)) = row < lim ? __float_as_uint(v[i]) + 0x1000u : 0u;
+      }
     }
   }
 };
@@ -373,10 +388,10 @@ struct LoadIm2colColsK {
   static constexpr int kTableRows = 256;
   __device__ static constexpr bool small() { return SMALL; }
   __device__ void build_table(int4* tab, int row0, int t) const {
-    for (int row = t; row < rows; row += NT) {          // called with the CTA-wide thread index
+    for (int row = t; row < kTableRows; row += NT) {    // called with the CTA-wide thread index
       const int rr = row0 + row;
       int4 e = make_int4(0, 0, 0, 0);
-      if (rr < g.Kdim()) {
+      if (row < rows && rr < g.Kdim()) {
         uint32_t c, tt, ky, kx;
         dKhKw.divmod(rr, c, tt);
         dKw.divmod(tt, ky, kx);
@@ -402,17 +417,19 @@ struct LoadIm2colColsK {
     const float* base = opaque(x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0));
     for (int rb = 0; rb < rows; rb += 16 * GW) {
       float v[16];
+      uint32_t okm = 0;
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int row = rb + wp + GW * i;
-        const int4 e = s.tab[min(row, kTableRows - 1)];
-        v[i] = ldg_pred(base + e.x, (SMALL ? (ma & (uint32_t)e.y) != 0 : ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0)) &
-                                        (row < rows));
+        const int4 e = s.tab[min(row, kTableRows - 1)];     // rows beyond the filter have zero masks, offset 0
+        const bool p = SMALL ? (ma & (uint32_t)e.y) != 0 : ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0);
+        v[i] = __ldg(base + e.x);                           // unconditional (guard bands, see LoadIm2colRowsMN)
+        okm |= (p ? 1u : 0u) << i;
       }
 #pragma unroll
       for (int i = 0; i < 16; ++i) {
         const int row = rb + wp + GW * i;
-        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(v[i]);
+        if (row < rows) *(uint32_t*)(tile + off_kmajor(row, k)) = ((okm >> i) & 1u) ? __float_as_uint(v[i]) + 0x1000u : 0u;
       }
     }
   }
@@ -756,7 +773,7 @@ bool tc_available() { return true; }
 // Rounded (tf32, round-to-nearest) shadow copies of weight blobs for the TMA-fed operands.  Keyed by
 // the fp32 pointer; refreshed by tc_refresh_shadow whenever the runtime knows the weights changed.
 __global__ void round_tf32_kernel(size_t n, const float* __restrict__ src, float* __restrict__ dst) {
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = to_tf32(src[i]);
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = to_tf32_exact(src[i]);
 }
 void tc_round_to_tf32(cudaStream_t s, size_t n, const float* src, float* dst) {
   int blocks = (int)((n + 255) / 256);

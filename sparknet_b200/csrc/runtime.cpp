@@ -69,13 +69,19 @@ void count_launch(int n) { ctx().launches += n; }
 // ------------------------------------------------------------------------------------------
 // Storage / Blob
 // ------------------------------------------------------------------------------------------
+float* alloc_guarded(size_t count, float** raw) {
+  SN_CUDA(cudaMalloc(raw, (std::max<size_t>(count, 1) + 2 * Storage::kGuardFloats) * sizeof(float)));
+  SN_CUDA(cudaMemset(*raw, 0, Storage::kGuardFloats * sizeof(float)));
+  SN_CUDA(cudaMemset(*raw + Storage::kGuardFloats + std::max<size_t>(count, 1), 0, Storage::kGuardFloats * sizeof(float)));
+  return *raw + Storage::kGuardFloats;
+}
 Storage::~Storage() {
-  if (dev && owns_dev) cudaFree(dev);
+  if (dev_raw && owns_dev) cudaFree(dev_raw);
   if (host) cudaFreeHost(host);
 }
 void Storage::ensure_dev() {
   if (!dev) {
-    SN_CUDA(cudaMalloc(&dev, std::max<size_t>(count, 1) * sizeof(float)));
+    dev = alloc_guarded(count, &dev_raw);
     owns_dev = true;
   }
 }
@@ -208,6 +214,8 @@ struct JavaDataLayer : Layer {
   size_t count = 0;
   float* pinned[2] = {nullptr, nullptr};
   float* devbuf[2] = {nullptr, nullptr};
+  float* devraw[2] = {nullptr, nullptr};
+  float* pool_raw = nullptr;
   cudaEvent_t h2d_done[2], consumed[2];
   bool consumed_valid[2] = {false, false};
   int parity = 0;
@@ -218,10 +226,10 @@ struct JavaDataLayer : Layer {
   ~JavaDataLayer() override {
     for (int i = 0; i < 2; ++i) {
       if (pinned[i]) cudaFreeHost(pinned[i]);
-      if (devbuf[i]) cudaFree(devbuf[i]);
+      if (devraw[i]) cudaFree(devraw[i]);
       if (count) { cudaEventDestroy(h2d_done[i]); cudaEventDestroy(consumed[i]); }
     }
-    if (pool) cudaFree(pool);
+    if (pool_raw) cudaFree(pool_raw);
   }
   const char* type() const override { return "JavaData"; }
   void setup(const vector<Blob*>&, const vector<Blob*>& top) override {
@@ -235,7 +243,7 @@ struct JavaDataLayer : Layer {
     for (int i = 0; i < 2; ++i) {
       SN_CUDA(cudaMallocHost(&pinned[i], count * sizeof(float)));
       memset(pinned[i], 0, count * sizeof(float));
-      SN_CUDA(cudaMalloc(&devbuf[i], count * sizeof(float)));
+      devbuf[i] = alloc_guarded(count, &devraw[i]);
       SN_CUDA(cudaEventCreateWithFlags(&h2d_done[i], cudaEventDisableTiming));
       SN_CUDA(cudaEventCreateWithFlags(&consumed[i], cudaEventDisableTiming));
     }
@@ -271,11 +279,11 @@ struct JavaDataLayer : Layer {
   void backward(const vector<Blob*>&, const vector<bool>&, const vector<Blob*>&) override {}
   // Pull `n` minibatches through the callback now and keep them in HBM.
   void make_resident(int n) {
-    if (pool) { cudaFree(pool); pool = nullptr; }
+    if (pool_raw) { cudaFree(pool_raw); pool_raw = nullptr; pool = nullptr; }
     pool_n = n; pool_i = 0;
     if (n <= 0) return;
     SN_CHECK(cb, "set the data callback before sparknet_set_resident_inputs");
-    SN_CUDA(cudaMalloc(&pool, (size_t)n * count * sizeof(float)));
+    pool = alloc_guarded((size_t)n * count, &pool_raw);
   }
   void fill_resident_slot(int i) {
     cb((void*)pinned[0], shape[0], (int)shape.size() - 1, java_shape.data());

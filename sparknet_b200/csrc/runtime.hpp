@@ -38,6 +38,7 @@ struct Context {
 };
 Context& ctx();       // initialises the device context on first use
 Context& raw_ctx();   // the same object, without initialising it
+float* alloc_guarded(size_t count, float** raw);   // cudaMalloc with zeroed guard bands on both sides
 
 // ------------------------------------------------------------------------------------------
 // Storage: one buffer with a device copy and a lazily created pinned host mirror.  State machine
@@ -47,8 +48,12 @@ struct Storage {
   enum Head { UNINIT, AT_HOST, AT_DEVICE, SYNCED };
   size_t count = 0;
   float* dev = nullptr;
+  float* dev_raw = nullptr;      // owned allocation: dev = dev_raw + kGuardFloats
   float* host = nullptr;
   bool owns_dev = true;
+  // Every activation buffer is surrounded by guard bands: the implicit-GEMM gathers read padded filter
+  // taps unconditionally (the value is then discarded), which may touch a few rows before/after a tensor.
+  static constexpr size_t kGuardFloats = 4096;
   Head head = UNINIT;
   uint64_t gen = 0;              // bumped whenever the contents may have changed (host or device write access)
   explicit Storage(size_t n) : count(n) {}

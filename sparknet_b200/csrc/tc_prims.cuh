@@ -120,8 +120,13 @@ __device__ __forceinline__ float ldg_pred(const float* p, bool pred) {
   return v;
 }
 
-// round-to-nearest fp32 -> tf32 (keeps the fp32 container; low 13 mantissa bits zero)
-__device__ __forceinline__ float to_tf32(float x) {
+// fp32 -> tf32 with round-to-nearest (ties away from zero), keeping the fp32 container.  The tensor
+// core ignores the low 13 mantissa bits of a tf32 operand, so adding half an ulp of tf32 (0x1000) to the
+// bit pattern is all it takes: one integer add (cvt.rna.tf32.f32 compiles to three instructions here).
+// The sum can only overflow into infinity for |x| >= 2^128 - 2^104, which no activation or weight reaches.
+__device__ __forceinline__ float to_tf32(float x) { return __uint_as_float(__float_as_uint(x) + 0x1000u); }
+// exact cvt.rna.tf32.f32 (low bits cleared): used for the stored weight shadows
+__device__ __forceinline__ float to_tf32_exact(float x) {
   uint32_t r;
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
   return __uint_as_float(r);
