@@ -31,25 +31,41 @@ constexpr int TBM = 128, TBK = 32, TSTAGES = 4;
 constexpr int kATileBytes = TBM * TBK * 4;            // 16 KB
 
 // ------------------------------------------------------------------------------------------
-// Operand loaders.  kTMA: issued by the TMA warp; otherwise `load` is run by ONE gather group of GT = 128
-// threads per chunk.  The NT = 512 gather threads form NG = 4 groups; group g fills pipeline stage g
-// (chunks g, g+4, ...), so four chunks are being gathered at any time and the global-load latency of one
-// overlaps the address arithmetic, conversion and shared-memory stores of the others.  kMN: MN-major tile
-// (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows actually needed (128 for
-// A, n_mma for B); rows beyond the operand's extent are zero-filled.  Every loader first issues ALL its
-// global loads of the chunk into registers and only then converts and stores them, so a thread has 8-16
-// loads in flight (the first version interleaved load/convert/store and was latency bound).
+// Operand loaders.  kTMA: issued by the TMA warp.  Otherwise the operand is gathered by ONE gather group
+// of GT = 128 threads per chunk; the NT = 512 gather threads form NG = 4 groups and group g fills pipeline
+// stage g (chunks g, g+4, ...), so four chunks are in flight.  A gather is split in two phases:
+//   fetch()   issues ALL global loads of the chunk into registers — it does not need the smem stage, so it
+//             runs BEFORE the group waits for the stage to be free (load latency overlaps the MMA that still
+//             reads the stage);
+//   commit()  rounds to tf32 (one integer add) and stores into the swizzled tile.
+// Loaders whose tile has more than 128 K-major rows run fetch/commit a second time (`pass` = 1).
+// kMN: MN-major tile (element (mn, k) at off_mnmajor) else K-major (off_kmajor).  `rows` = tile rows
+// actually needed (128 for A, n_mma for B); rows beyond the operand's extent are zero-filled.
 // ------------------------------------------------------------------------------------------
 constexpr int NT = 512;
 constexpr int NW = NT / 32;                   // gather warps (all of them run the epilogue)
 constexpr int GT = 128, GW = GT / 32;         // threads / warps per gather group
 constexpr int NG = NT / GT;                   // gather groups == pipeline stages
 struct NoState {};
+struct NoRegs {};
+
+__device__ __forceinline__ uint32_t tf32_bits(float x) { return __float_as_uint(x) + 0x1000u; }
+__device__ __forceinline__ float4 tf32x4(float4 v) {
+  v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
+  return v;
+}
+// Keep a per-thread base pointer as an opaque 64-bit value: without this the compiler re-derives it from
+// the kernel parameter and a 64-bit element offset at every use (4 instructions per gathered element).
+__device__ __forceinline__ const float* opaque(const float* p) {
+  asm volatile("" : "+l"(p));
+  return p;
+}
 
 // weights through TMA, K-major: tensor {K (contiguous), rows}; box {32, rows_box}
 struct LoadTmaK {
   static constexpr bool kTMA = true, kMN = false, kKTable = false;
   typedef NoState State;
+  typedef NoRegs Regs;
   int rows_box;
   __device__ uint32_t bytes() const { return (uint32_t)rows_box * 128u; }
   __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
@@ -61,6 +77,7 @@ struct LoadTmaK {
 struct LoadTmaMN {
   static constexpr bool kTMA = true, kMN = true, kKTable = false;
   typedef NoState State;
+  typedef NoRegs Regs;
   int rows;                                       // multiple of 32
   __device__ uint32_t bytes() const { return (uint32_t)(rows / 32) * 4096u; }
   __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
@@ -68,160 +85,171 @@ struct LoadTmaMN {
   }
 };
 
-__device__ __forceinline__ float4 tf32x4(float4 v) {
-  v.x = to_tf32(v.x); v.y = to_tf32(v.y); v.z = to_tf32(v.z); v.w = to_tf32(v.w);
-  return v;
-}
-
-// dense [row][r] (r contiguous), K-major tile.  128-bit path when the pitch allows it.
+// dense [row][r] (r contiguous), K-major tile.  128-bit path when the pitch allows it: thread t owns the
+// 16-byte chunk t%8 of rows t/8 + 16*i.  One pass = 64 rows.
 struct LoadDenseK {
   static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
+  struct Regs { float4 v[4]; };
   const float* p; int ld, nrows, nred, rows; int vec;
+  __device__ int passes() const { return (rows + 63) / 64; }
   __device__ void init(State&, int, int) const {}
-  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+  __device__ void fetch(State&, Regs& rg, int pass, int row0, int r0, int r_end, int t, const void*) const {
+    const int rb = pass * 64;
     if (vec) {
-      const int c = t & 7;                         // 16-byte chunk within the 128-byte row
-      const int r = r0 + 4 * c;
-      for (int rb = 0; rb < rows; rb += 128) {
-        float4 v[8];
+      const int c = t & 7, r = r0 + 4 * c;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int row = rb + (t >> 3) + 16 * i, gr = row0 + row;
-          v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (row < rows && gr < nrows && r < r_end) {
-            const float* q = p + (size_t)gr * ld + r;
-            if (r + 3 < r_end) v[i] = __ldg((const float4*)q);
-            else { v[i].x = __ldg(q); if (r + 1 < r_end) v[i].y = __ldg(q + 1); if (r + 2 < r_end) v[i].z = __ldg(q + 2); }
-          }
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int row = rb + (t >> 3) + 16 * i;
-          if (row < rows) *(float4*)(tile + off_kmajor(row, 4 * c)) = tf32x4(v[i]);
+      for (int i = 0; i < 4; ++i) {
+        const int row = rb + (t >> 3) + 16 * i, gr = row0 + row;
+        rg.v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < rows && gr < nrows && r < r_end) {
+          const float* q = p + (size_t)gr * ld + r;
+          if (r + 3 < r_end) rg.v[i] = __ldg((const float4*)q);
+          else { rg.v[i].x = __ldg(q); if (r + 1 < r_end) rg.v[i].y = __ldg(q + 1); if (r + 2 < r_end) rg.v[i].z = __ldg(q + 2); }
         }
       }
+    } else {                                      // scalar: lane = k, warp w owns rows rb + w + 4*j
+      const int k = t & 31, r = r0 + k, w = t >> 5;
+      float* f = (float*)rg.v;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int row = rb + w + GW * j, gr = row0 + row;
+        f[j] = (row < rows && gr < nrows && r < r_end) ? __ldg(p + (size_t)gr * ld + r) : 0.f;
+      }
+    }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+    const int rb = pass * 64;
+    if (vec) {
+      const int c = t & 7;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = rb + (t >> 3) + 16 * i;
+        if (row < rows) *(float4*)(tile + off_kmajor(row, 4 * c)) = tf32x4(rg.v[i]);
+      }
     } else {
-      const int k = t & 31, r = r0 + k;
-      for (int row = t >> 5; row < rows; row += GW) {
-        const int gr = row0 + row;
-        const float v = (gr < nrows && r < r_end) ? __ldg(p + (size_t)gr * ld + r) : 0.f;
-        *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
+      const int k = t & 31, w = t >> 5;
+      const float* f = (const float*)rg.v;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int row = rb + w + GW * j;
+        if (row < rows) *(float*)(tile + off_kmajor(row, k)) = to_tf32(f[j]);
       }
     }
   }
 };
-// dense [r][mn] (mn contiguous), MN-major tile.  Warp w of the group owns k = 8w..8w+7; lanes run along mn.
+// dense [r][mn] (mn contiguous), MN-major tile.  Warp w of the group owns k = 8w..8w+7; lanes run along
+// mn in 16-byte chunks.  Pass p covers mn block p/2 (128 wide) and k half p%2 (4 of the warp's 8 k).
 struct LoadDenseMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = false;
   typedef NoState State;
+  struct Regs { float4 v[4]; };
   const float* p; int ld, nrows, nred, rows; int vec;
+  __device__ int passes() const { return 2 * ((rows + 127) / 128); }
   __device__ void init(State&, int, int) const {}
-  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int w = t >> 5, lane = t & 31;
+  __device__ void fetch(State&, Regs& rg, int pass, int row0, int r0, int r_end, int t, const void*) const {
+    const int w = t >> 5, lane = t & 31, mb = pass >> 1, kh = (pass & 1) * 4;
     if (vec) {
-      const int ch = rows >> 2;                    // 16-byte chunks per k-row (<= 64)
-      for (int cb = 0; cb < ch; cb += 32) {
-        const int c = cb + lane, mn = row0 + 4 * c;
-        float4 v[8];
+      const int ch = rows >> 2, c = 32 * mb + lane, mn = row0 + 4 * c;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int r = r0 + 8 * w + i;
-          v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (c < ch && r < r_end && mn < nrows) {
-            const float* q = p + (size_t)r * ld + mn;
-            if (mn + 3 < nrows) v[i] = __ldg((const float4*)q);
-            else { v[i].x = __ldg(q); if (mn + 1 < nrows) v[i].y = __ldg(q + 1); if (mn + 2 < nrows) v[i].z = __ldg(q + 2); }
-          }
+      for (int i = 0; i < 4; ++i) {
+        const int r = r0 + 8 * w + kh + i;
+        rg.v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (c < ch && r < r_end && mn < nrows) {
+          const float* q = p + (size_t)r * ld + mn;
+          if (mn + 3 < nrows) rg.v[i] = __ldg((const float4*)q);
+          else { rg.v[i].x = __ldg(q); if (mn + 1 < nrows) rg.v[i].y = __ldg(q + 1); if (mn + 2 < nrows) rg.v[i].z = __ldg(q + 2); }
         }
-#pragma unroll
-        for (int i = 0; i < 8; ++i)
-          if (c < ch) *(float4*)(tile + off_mnmajor(4 * c, 8 * w + i)) = tf32x4(v[i]);
       }
+    } else {                                      // scalar: slot j = (kk, q): k = 8w + kh + kk, mn = 128*mb + lane + 32*q
+      float* f = (float*)rg.v;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int k = 8 * w + kh + (j >> 2), m = 128 * mb + lane + 32 * (j & 3), mn = row0 + m, r = r0 + k;
+        f[j] = (m < rows && r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
+      }
+    }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+    const int w = t >> 5, lane = t & 31, mb = pass >> 1, kh = (pass & 1) * 4;
+    if (vec) {
+      const int ch = rows >> 2, c = 32 * mb + lane;
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+        if (c < ch) *(float4*)(tile + off_mnmajor(4 * c, 8 * w + kh + i)) = tf32x4(rg.v[i]);
     } else {
-      for (int kk = 0; kk < 8; ++kk) {
-        const int k = 8 * w + kk, r = r0 + k;
-        for (int m = lane; m < rows; m += 32) {
-          const int mn = row0 + m;
-          const float v = (r < r_end && mn < nrows) ? __ldg(p + (size_t)r * ld + mn) : 0.f;
-          *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
-        }
+      const float* f = (const float*)rg.v;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int k = 8 * w + kh + (j >> 2), m = 128 * mb + lane + 32 * (j & 3);
+        if (m < rows) *(float*)(tile + off_mnmajor(m, k)) = to_tf32(f[j]);
       }
     }
   }
 };
 
-// Any accessor of gemm_ops.cuh as a K-major tile (lane = r, warp = rows): generic, index math per element.
-template <class Acc>
-struct LoadAccK {
-  static constexpr bool kTMA = false, kMN = false, kKTable = false;
-  typedef NoState State;
-  Acc acc; int rows;
-  __device__ void init(State&, int, int) const {}
-  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int k = t & 31, r = r0 + k;
-    for (int row = t >> 5; row < rows; row += GW) {
-      const float v = r < r_end ? acc(row0 + row, r) : 0.f;
-      *(float*)(tile + off_kmajor(row, k)) = to_tf32(v);
-    }
-  }
-};
-// Any accessor as an MN-major tile (thread = row): generic.
+// Any accessor of gemm_ops.cuh as an MN-major tile (thread = row): generic fallback (strided backward-data).
 template <class Acc>
 struct LoadAccMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = false;
   typedef NoState State;
+  struct Regs { float v[16]; };
   Acc acc; int rows;
+  __device__ int passes() const { return 2; }
   __device__ void init(State&, int, int) const {}
-  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int m = t;
-    if (m >= rows) return;
-    for (int k = 0; k < TBK; ++k) {
-      const int r = r0 + k;
-      const float v = r < r_end ? acc(row0 + m, r) : 0.f;
-      *(float*)(tile + off_mnmajor(m, k)) = to_tf32(v);
+  __device__ void fetch(State&, Regs& rg, int pass, int row0, int r0, int r_end, int t, const void*) const {
+#pragma unroll 4
+    for (int k = 0; k < 16; ++k) {
+      const int r = r0 + 16 * pass + k;
+      rg.v[k] = (t < rows && r < r_end) ? acc(row0 + t, r) : 0.f;
     }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+    if (t >= rows) return;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) *(float*)(tile + off_mnmajor(t, 16 * pass + k)) = to_tf32(rg.v[k]);
   }
 };
 
-// Per-chunk reduction-index table for the two pixel-row gathers below: for each of the chunk's 32
-// reduction indices {input offset delta, tap mask A, tap mask B, 0}; all-zero masks mark an index beyond
-// the reduction.  Built by a dedicated warp one stage ahead, read by the gather warps as broadcast
-// LDS.128 — this replaces ~40 instructions of index arithmetic per gathered element by one shared-memory
-// load.  Padding test per element: filters with kh*kw <= 32 taps use ONE per-thread 2-D validity mask
-// (bit kh_i*kw + kw_i set when that tap reads inside the image; table mask A = 1 << tap, B = ~0);
-// larger filters (11x11) use separate row / column masks (A = 1 << kh_i against hmask, B = 1 << kw_i
-// against wmask).  Loads are predicated instructions, never branches.
-// Keep a per-thread base pointer as an opaque 64-bit value: without this the compiler re-derives it from
-// the kernel parameter and a 64-bit element offset at every use (4 instructions per gathered element).
-__device__ __forceinline__ const float* opaque(const float* p) {
-  asm volatile("" : "+l"(p));
-  return p;
-}
+// Reduction-index table for the two pixel-row gathers below, built once per CTA in shared memory for the
+// CTA's whole reduction range: entry r = {input offset delta, tap mask}.  Filters with kh*kw <= 32 taps
+// (SMALL) test ONE per-thread 2-D validity mask (bit kh_i*kw + kw_i set when that tap reads inside the
+// image) against 1 << tap; larger filters (11x11) carry a second mask word (row mask in .y, column mask in
+// .z against per-thread hmask / wmask).  An all-zero mask marks an index beyond the reduction.  Loads are
+// unconditional plain LDGs: a padded tap reads a neighbouring row of the tensor or its guard band
+// (runtime.hpp kGuardFloats) and the value is replaced by zero at commit time.
+template <bool SMALL> struct KEntry { typedef int2 type; };
+template <> struct KEntry<false> { typedef int4 type; };
 __device__ __forceinline__ uint32_t mask2d(uint32_t hmask, uint32_t wmask, int kh, int kw) {
   uint32_t m = 0;
   for (int k = 0; k < kh; ++k) if ((hmask >> k) & 1u) m |= wmask << (k * kw);
   return m;
 }
+template <bool SMALL> __device__ __forceinline__ typename KEntry<SMALL>::type make_kentry(int delta, uint32_t tap, uint32_t ky, uint32_t kx);
+template <> __device__ __forceinline__ int2 make_kentry<true>(int delta, uint32_t tap, uint32_t, uint32_t) { return make_int2(delta, 1 << tap); }
+template <> __device__ __forceinline__ int4 make_kentry<false>(int delta, uint32_t, uint32_t ky, uint32_t kx) { return make_int4(delta, 1 << ky, 1 << kx, 0); }
+__device__ __forceinline__ int2 zero_kentry(int2) { return make_int2(0, 0); }
+__device__ __forceinline__ int4 zero_kentry(int4) { return make_int4(0, 0, 0, 0); }
 
 // Convolution forward A operand: im2col rows (output pixels) x (c,kh,kw), MN-major.  Thread t of the
-// group owns pixel row0 + t and all 32 reduction indices of the chunk.  Its (n,ho,wo), input base and padding masks
-// are computed once per tile.  Lanes = consecutive pixels, so global reads are coalesced along W and the
-// swizzled 128-byte rows are written conflict-free.
+// group owns pixel row0 + t and all 32 reduction indices of the chunk.  Its (n,ho,wo), input base and
+// padding masks are computed once per tile.  Lanes = consecutive pixels, so global reads are coalesced
+// along W and the swizzled 128-byte rows are written conflict-free.
 template <bool SMALL>
 struct LoadIm2colRowsMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = true;
+  __device__ int passes() const { return 2; }
+  typedef typename KEntry<SMALL>::type Entry;
   const float* x; ConvGeom g; int grp;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { const float* base; uint32_t ma, mb; int safe; };
-  __device__ static constexpr bool small() { return SMALL; }
-  __device__ int4 table_entry(int r, int r_end) const {
-    if (r >= r_end || r >= g.Kdim()) return make_int4(0, 0, 0, 0);
+  struct State { const float* base; uint32_t ma, mb; };
+  struct Regs { float v[16]; uint32_t ok; };
+  __device__ Entry table_entry(int r, int r_end) const {
+    if (r >= r_end || r >= g.Kdim()) return zero_kentry(Entry());
     uint32_t c, tt, ky, kx;
     dKhKw.divmod((uint32_t)r, c, tt);
     dKw.divmod(tt, ky, kx);
-    const int delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
-    return small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
+    return make_kentry<SMALL>((int)c * g.H * g.W + (int)ky * g.W + (int)kx, tt, ky, kx);
   }
   __device__ void init(State& s, int row0, int t) const {
     const int row = row0 + t;
@@ -233,30 +261,26 @@ struct LoadIm2colRowsMN {
     for (int k = 0; k < g.kh; ++k) if (hi0 + k >= 0 && hi0 + k < g.H) hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wi0 + k >= 0 && wi0 + k < g.W) wmask |= 1u << k;
     if (!live || !wmask) hmask = 0;
-    // loads are unconditional (plain LDG, no predicate): a padded tap reads a neighbouring row of the
-    // tensor or its guard band (runtime.hpp kGuardFloats) and the value is replaced by zero afterwards
-    s.safe = 0;
     s.base = opaque(hmask ? x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0) : x);
-    if (small()) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = s.ma ? ~0u : 0u; }
-    else { s.ma = hmask; s.mb = wmask; }
+    if (SMALL) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = 0; } else { s.ma = hmask; s.mb = wmask; }
   }
-  __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
-    const int m = t;
+  __device__ void fetch(State& s, Regs& rg, int pass, int, int, int, int, const void* ktab_chunk) const {
+    const Entry* kt = (const Entry*)ktab_chunk + 16 * pass;
+    rg.ok = 0;
 #pragma unroll
-    for (int kb = 0; kb < TBK; kb += 16) {
-      float v[16];
-      uint32_t ok = 0;
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const int4 e = ktab[kb + k];
-        const bool p = SMALL ? (s.ma & (uint32_t)e.y) != 0 : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0);
-        v[k] = __ldg(s.base + e.x);        // unconditional: a padded tap reads a neighbouring row or the guard band
-        ok |= (p ? 1u : 0u) << k;
-      }
-#pragma unroll
-      for (int k = 0; k < 16; ++k)
-        *(uint32_t*)(tile + off_mnmajor(m, kb + k)) = ((ok >> k) & 1u) ? __float_as_uint(v[k]) + 0x1000u : 0u;
+    for (int k = 0; k < 16; ++k) {
+      const Entry e = kt[k];
+      bool p;
+      if constexpr (SMALL) p = (s.ma & (uint32_t)e.y) != 0;
+      else p = ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0);
+      rg.v[k] = __ldg(s.base + e.x);
+      rg.ok |= (p ? 1u : 0u) << k;
     }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      *(uint32_t*)(tile + off_mnmajor(t, 16 * pass + k)) = ((rg.ok >> k) & 1u) ? tf32_bits(rg.v[k]) : 0u;
   }
 };
 
@@ -265,17 +289,18 @@ struct LoadIm2colRowsMN {
 template <bool SMALL>
 struct LoadDgradRowsMN {
   static constexpr bool kTMA = false, kMN = true, kKTable = true;
+  __device__ int passes() const { return 2; }
+  typedef typename KEntry<SMALL>::type Entry;
   const float* dy; ConvGeom g; int grp;
   FastDiv dHW, dW, dKhKw, dKw;
-  struct State { const float* base; uint32_t ma, mb; int safe; };
-  __device__ static constexpr bool small() { return SMALL; }
-  __device__ int4 table_entry(int r, int r_end) const {
-    if (r >= r_end || r >= g.Og() * g.kh * g.kw) return make_int4(0, 0, 0, 0);
+  struct State { const float* base; uint32_t ma, mb; };
+  struct Regs { float v[16]; uint32_t ok; };
+  __device__ Entry table_entry(int r, int r_end) const {
+    if (r >= r_end || r >= g.Og() * g.kh * g.kw) return zero_kentry(Entry());
     uint32_t co, tt, ky, kx;
     dKhKw.divmod((uint32_t)r, co, tt);
     dKw.divmod(tt, ky, kx);
-    const int delta = (int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx;
-    return small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
+    return make_kentry<SMALL>((int)co * g.Ho * g.Wo - (int)ky * g.Wo - (int)kx, tt, ky, kx);
   }
   __device__ void init(State& s, int row0, int t) const {
     const int row = row0 + t;
@@ -287,59 +312,60 @@ struct LoadDgradRowsMN {
     for (int k = 0; k < g.kh; ++k) if (hb - k >= 0 && hb - k < g.Ho) hmask |= 1u << k;
     for (int k = 0; k < g.kw; ++k) if (wb - k >= 0 && wb - k < g.Wo) wmask |= 1u << k;
     if (!live || !wmask) hmask = 0;
-    s.safe = 0;
     s.base = opaque(hmask ? dy + ((ptrdiff_t)((int)n * g.Cout + grp * g.Og()) * g.Ho * g.Wo + hb * g.Wo + wb) : dy);
-    if (small()) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = s.ma ? ~0u : 0u; }
-    else { s.ma = hmask; s.mb = wmask; }
+    if (SMALL) { s.ma = mask2d(hmask, wmask, g.kh, g.kw); s.mb = 0; } else { s.ma = hmask; s.mb = wmask; }
   }
-  __device__ void load(State& s, uint8_t* tile, const int4* ktab, int t) const {
-    const int m = t;
+  __device__ void fetch(State& s, Regs& rg, int pass, int, int, int, int, const void* ktab_chunk) const {
+    const Entry* kt = (const Entry*)ktab_chunk + 16 * pass;
+    rg.ok = 0;
 #pragma unroll
-    for (int kb = 0; kb < TBK; kb += 16) {
-      float v[16];
-      uint32_t ok = 0;
-#pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        const int4 e = ktab[kb + k];
-        const bool p = SMALL ? (s.ma & (uint32_t)e.y) != 0 : ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0);
-        v[k] = __ldg(s.base + e.x);        // unconditional: a padded tap reads a neighbouring row or the guard band
-        ok |= (p ? 1u : 0u) << k;
-      }
-#pragma unroll
-      for (int k = 0; k < 16; ++k)
-        *(uint32_t*)(tile + off_mnmajor(m, kb + k)) = ((ok >> k) & 1u) ? __float_as_uint(v[k]) + 0x1000u : 0u;
+    for (int k = 0; k < 16; ++k) {
+      const Entry e = kt[k];
+      bool p;
+      if constexpr (SMALL) p = (s.ma & (uint32_t)e.y) != 0;
+      else p = ((s.ma & (uint32_t)e.y) != 0) & ((s.mb & (uint32_t)e.z) != 0);
+      rg.v[k] = __ldg(s.base + e.x);
+      rg.ok |= (p ? 1u : 0u) << k;
     }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+#pragma unroll
+    for (int k = 0; k < 16; ++k)
+      *(uint32_t*)(tile + off_mnmajor(t, 16 * pass + k)) = ((rg.ok >> k) & 1u) ? tf32_bits(rg.v[k]) : 0u;
   }
 };
 // Backward-data B operand: filters viewed as [c][(co,kh,kw)], K-major.  lane = r: its (co, tap) is
-// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w of the group owns rows w, w+4, ...
+// decomposed once per chunk; rows (input channels) are khkw apart.  Warp w of the group owns rows
+// w + 4*j; one pass covers 128 rows.
 struct LoadFilterDgradK {
   static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
+  struct Regs { float v[16]; int lim; };
   const float* w; ConvGeom g; int grp; int rows;
+  __device__ int passes() const { return (rows + 63) / 64; }
   FastDiv dKhKw;
   __device__ void init(State&, int, int) const {}
-  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+  __device__ void fetch(State&, Regs& rg, int pass, int row0, int r0, int r_end, int t, const void*) const {
     const int khkw = g.kh * g.kw, Cg = g.Cg();
-    const int k = t & 31, r = r0 + k, wp = t >> 5;
+    const int k = t & 31, r = r0 + k, wp = t >> 5, rb = 64 * pass;
     const bool ok = r < r_end && r < g.Og() * khkw;
     uint32_t co = 0, tap = 0;
     if (ok) dKhKw.divmod(r, co, tap);
-    const float* q = opaque(w + ((size_t)(grp * g.Og() + co) * Cg) * khkw + tap);
-    const int lim = ok ? min(rows, Cg - row0) : 0;               // valid tile rows
-    for (int rb = 0; rb < rows; rb += 16 * GW) {
-      float v[16];
+    const float* q = opaque(w + ((size_t)(grp * g.Og() + co) * Cg + row0) * khkw + tap);
+    rg.lim = ok ? min(rows, Cg - row0) : 0;                       // valid tile rows
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = 0.f;
-      if (lim > 0) {
+    for (int j = 0; j < 16; ++j) rg.v[j] = 0.f;
+    if (rg.lim > rb) {
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = __ldg(q + (ptrdiff_t)(row0 + min(rb + wp + GW * i, lim - 1)) * khkw);
-      }
+      for (int j = 0; j < 16; ++j) rg.v[j] = __ldg(q + (ptrdiff_t)min(rb + wp + GW * j, rg.lim - 1) * khkw);
+    }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+    const int k = t & 31, wp = t >> 5, rb = 64 * pass;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + GW * i;
-        if (row < rows) *(uint32_t*)(tile + off_kmajor(row, k)) = row < lim ? __float_as_uint(v[i]) + 0x1000u : 0u;
-      }
+    for (int j = 0; j < 16; ++j) {
+      const int row = rb + wp + GW * j;
+      if (row < rows) *(uint32_t*)(tile + off_kmajor(row, k)) = row < rg.lim ? tf32_bits(rg.v[j]) : 0u;
     }
   }
 };
@@ -347,63 +373,67 @@ struct LoadFilterDgradK {
 struct LoadDyRowsK {
   static constexpr bool kTMA = false, kMN = false, kKTable = false;
   typedef NoState State;
+  struct Regs { float v[16]; int lim; };
   const float* dy; ConvGeom g; int grp;
   FastDiv dHoWo;
+  __device__ int passes() const { return 2; }
   __device__ void init(State&, int, int) const {}
-  __device__ void load(State&, uint8_t* tile, int row0, int r0, int r_end, int t) const {
+  __device__ void fetch(State&, Regs& rg, int pass, int row0, int r0, int r_end, int t, const void*) const {
     const int HoWo = g.Ho * g.Wo;
-    const int k = t & 31, r = r0 + k, wp = t >> 5;
+    const int k = t & 31, r = r0 + k, wp = t >> 5, rb = 64 * pass;
     const bool ok = r < r_end && r < g.N * HoWo;
     uint32_t n = 0, pix = 0;
     if (ok) dHoWo.divmod(r, n, pix);
-    const float* q = opaque(dy + ((size_t)n * g.Cout + grp * g.Og()) * HoWo + pix);
-    const int lim = ok ? g.Og() - row0 : 0;
+    const float* q = opaque(dy + ((size_t)n * g.Cout + grp * g.Og() + row0) * HoWo + pix);
+    rg.lim = ok ? min(TBM, g.Og() - row0) : 0;
 #pragma unroll
-    for (int rb = 0; rb < TBM; rb += 16 * GW) {
-      float v[16];
+    for (int j = 0; j < 16; ++j) rg.v[j] = 0.f;
+    if (rg.lim > rb) {
 #pragma unroll
-      for (int i = 0; i < 16; ++i) v[i] = 0.f;
-      if (lim > 0) {
+      for (int j = 0; j < 16; ++j) rg.v[j] = __ldg(q + (ptrdiff_t)min(rb + wp + GW * j, rg.lim - 1) * HoWo);
+    }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+    const int k = t & 31, wp = t >> 5, rb = 64 * pass;
 #pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = __ldg(q + (ptrdiff_t)(row0 + min(rb + wp + GW * i, lim - 1)) * HoWo);
-      }
-#pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + GW * i;
-        *(uint32_t*)(tile + off_kmajor(row, k)) = row < lim ? __float_as_uint(v[i]) + 0x1000u : 0u;
-      }
+    for (int j = 0; j < 16; ++j) {
+      const int row = rb + wp + GW * j;
+      *(uint32_t*)(tile + off_kmajor(row, k)) = row < rg.lim ? tf32_bits(rg.v[j]) : 0u;
     }
   }
 };
 // Backward-filter B operand: im2col viewed as [(c,kh,kw)][(n,ho,wo)], K-major.  lane = r: its
 // (n,ho,wo), input base and padding masks are computed once per chunk; the per-row (c,kh,kw) comes
-// from a table built once per CTA in shared memory (same entry format as the per-chunk table above;
-// zero masks mark rows beyond the filter).
+// from a table built once per CTA in shared memory (same entry format as the reduction-index table;
+// zero masks mark rows beyond the filter).  One pass covers 128 rows.
 template <bool SMALL>
 struct LoadIm2colColsK {
   static constexpr bool kTMA = false, kMN = false, kKTable = false;
+  typedef typename KEntry<SMALL>::type Entry;
   const float* x; ConvGeom g; int grp; int rows;
   FastDiv dHoWo, dWo, dKhKw, dKw;
-  struct State { const int4* tab; };
+  struct State { const Entry* tab; };
+  struct Regs { float v[16]; uint32_t ok; };
+  __device__ int passes() const { return (rows + 63) / 64; }
   static constexpr int kTableRows = 256;
-  __device__ static constexpr bool small() { return SMALL; }
-  __device__ void build_table(int4* tab, int row0, int t) const {
-    for (int row = t; row < kTableRows; row += NT) {    // called with the CTA-wide thread index
+  __device__ void build_table(void* tab_, int row0, int t) const {
+    Entry* tab = (Entry*)tab_;
+    for (int row = t; row < kTableRows; row += kBuildThreads) {
       const int rr = row0 + row;
-      int4 e = make_int4(0, 0, 0, 0);
+      Entry e = zero_kentry(Entry());
       if (row < rows && rr < g.Kdim()) {
         uint32_t c, tt, ky, kx;
         dKhKw.divmod(rr, c, tt);
         dKw.divmod(tt, ky, kx);
-        const int delta = (int)c * g.H * g.W + (int)ky * g.W + (int)kx;
-        e = small() ? make_int4(delta, 1 << tt, -1, 0) : make_int4(delta, 1 << ky, 1 << kx, 0);
+        e = make_kentry<SMALL>((int)c * g.H * g.W + (int)ky * g.W + (int)kx, tt, ky, kx);
       }
       tab[row] = e;
     }
   }
+  static constexpr int kBuildThreads = NT;
   __device__ void init(State&, int, int) const {}
-  __device__ void load(State& s, uint8_t* tile, int row0, int r0, int r_end, int t) const {
-    const int k = t & 31, r = r0 + k, wp = t >> 5;
+  __device__ void fetch(State& s, Regs& rg, int pass, int, int r0, int r_end, int t, const void*) const {
+    const int k = t & 31, r = r0 + k, wp = t >> 5, rb = 64 * pass;
     const bool ok = r < r_end && r < g.N * g.Ho * g.Wo;
     uint32_t n = 0, pix = 0, ho = 0, wo = 0;
     if (ok) { dHoWo.divmod(r, n, pix); dWo.divmod(pix, ho, wo); }
@@ -411,26 +441,27 @@ struct LoadIm2colColsK {
     uint32_t hmask = 0, wmask = 0;
     for (int q = 0; q < g.kh; ++q) if (hi0 + q >= 0 && hi0 + q < g.H) hmask |= 1u << q;
     for (int q = 0; q < g.kw; ++q) if (wi0 + q >= 0 && wi0 + q < g.W) wmask |= 1u << q;
-    if (!ok) hmask = 0;
+    if (!ok || !wmask) hmask = 0;
     uint32_t ma, mb;
-    if (small()) { ma = mask2d(hmask, wmask, g.kh, g.kw); mb = ma ? ~0u : 0u; } else { ma = hmask; mb = wmask; }
-    const float* base = opaque(x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0));
-    for (int rb = 0; rb < rows; rb += 16 * GW) {
-      float v[16];
-      uint32_t okm = 0;
+    if (SMALL) { ma = mask2d(hmask, wmask, g.kh, g.kw); mb = 0; } else { ma = hmask; mb = wmask; }
+    const float* base = opaque(hmask ? x + ((ptrdiff_t)((int)n * g.C + grp * g.Cg()) * g.H * g.W + hi0 * g.W + wi0) : x);
+    rg.ok = 0;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + GW * i;
-        const int4 e = s.tab[min(row, kTableRows - 1)];     // rows beyond the filter have zero masks, offset 0
-        const bool p = SMALL ? (ma & (uint32_t)e.y) != 0 : ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0);
-        v[i] = __ldg(base + e.x);                           // unconditional (guard bands, see LoadIm2colRowsMN)
-        okm |= (p ? 1u : 0u) << i;
-      }
+    for (int j = 0; j < 16; ++j) {
+      const Entry e = s.tab[rb + wp + GW * j];                // rows beyond the filter: zero mask, offset 0
+      bool p;
+      if constexpr (SMALL) p = (ma & (uint32_t)e.y) != 0;
+      else p = ((ma & (uint32_t)e.y) != 0) & ((mb & (uint32_t)e.z) != 0);
+      rg.v[j] = __ldg(base + e.x);
+      rg.ok |= (p ? 1u : 0u) << j;
+    }
+  }
+  __device__ void commit(State&, const Regs& rg, int pass, uint8_t* tile, int t) const {
+    const int k = t & 31, wp = t >> 5, rb = 64 * pass;
 #pragma unroll
-      for (int i = 0; i < 16; ++i) {
-        const int row = rb + wp + GW * i;
-        if (row < rows) *(uint32_t*)(tile + off_kmajor(row, k)) = ((okm >> i) & 1u) ? __float_as_uint(v[i]) + 0x1000u : 0u;
-      }
+    for (int j = 0; j < 16; ++j) {
+      const int row = rb + wp + GW * j;
+      if (row < rows) *(uint32_t*)(tile + off_kmajor(row, k)) = ((rg.ok >> j) & 1u) ? tf32_bits(rg.v[j]) : 0u;
     }
   }
 };
@@ -497,6 +528,8 @@ struct TEpiTransposed {    // p[n*ld + m] = v + bias[m] (+ReLU)
 // ------------------------------------------------------------------------------------------
 template <class L> struct HasRowTable : std::false_type {};
 template <bool S> struct HasRowTable<LoadIm2colColsK<S>> : std::true_type {};
+template <class L, bool K = L::kKTable> struct KTabEntryBytes { static constexpr int value = 0; };
+template <class L> struct KTabEntryBytes<L, true> { static constexpr int value = (int)sizeof(typename L::Entry); };
 
 template <int BN>
 struct TcCfg {
@@ -506,8 +539,8 @@ struct TcCfg {
   static constexpr uint32_t kTmemCols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
 };
 
-constexpr int kTcThreads = NT + 96;          // 16 gather/epilogue warps + MMA warp + TMA warp + table warp
-constexpr int kMmaWarp = NW, kTmaWarp = NW + 1, kTabWarp = NW + 2;
+constexpr int kTcThreads = NT + 64;          // 16 gather/epilogue warps + MMA warp + TMA warp
+constexpr int kMmaWarp = NW, kTmaWarp = NW + 1;
 
 template <class AL, class BL, class EP, int BN, bool SPLIT>
 __global__ void __launch_bounds__(kTcThreads, 1)
@@ -515,10 +548,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                int M, int N, int R, int r_split_len, int n_mma, float* __restrict__ ws) {
   typedef TcCfg<BN> Cfg;
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tab_bar[TSTAGES], tmem_full_bar;
+  __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
-  __shared__ int4 row_table[256];     // backward-filter: per-CTA row table
-  __shared__ int4 k_table[TSTAGES][TBK];                      // pixel-row gathers: per-chunk reduction table
+  __shared__ int4 row_table[256];                              // backward-filter: per-CTA row table
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.x * TBM, n0 = blockIdx.y * n_mma;
@@ -527,14 +559,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int nchunks = r_end > r_begin ? (r_end - r_begin + TBK - 1) / TBK : 0;
 
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  uint8_t* ktab = smem + TSTAGES * Cfg::kStageBytes;           // reduction-index table (pixel-row gathers)
   constexpr bool kAnySimt = !AL::kTMA || !BL::kTMA, kAnyTma = AL::kTMA || BL::kTMA;
-  static_assert(!BL::kKTable, "the per-chunk reduction table is wired for the A operand only");
+  static_assert(!BL::kKTable, "the reduction-index table is wired for the A operand only");
 
   if (tid == 0) {
     for (int s = 0; s < TSTAGES; ++s) {
       mbar_init(&full_bar[s], (kAnySimt ? (uint32_t)GT : 0u) + (kAnyTma ? 1u : 0u));
       mbar_init(&empty_bar[s], 1u);
-      mbar_init(&tab_bar[s], 1u);
     }
     mbar_init(&tmem_full_bar, 1u);
     fence_barrier_init();
@@ -544,6 +576,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == kMmaWarp) tmem_alloc<Cfg::kTmemCols>(&tmem_base_smem);
   if constexpr (HasRowTable<BL>::value) {
     if (warp < NW) bl.build_table(row_table, n0, tid);
+  }
+  if constexpr (AL::kKTable) {
+    typedef typename AL::Entry Entry;
+    for (int i = tid; i < nchunks * TBK; i += kTcThreads) ((Entry*)ktab)[i] = al.table_entry(r_begin + i, r_end);
   }
   tc_fence_before_sync();
   __syncthreads();
@@ -557,27 +593,35 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int grp = warp / GW, tg = tid & (GT - 1);          // group g fills stage g: chunks g, g+NG, ...
       typename AL::State sa;
       typename BL::State sb;
+      typename AL::Regs ra;
+      typename BL::Regs rb;
       if constexpr (!AL::kTMA) al.init(sa, m0, tg);
       if constexpr (!BL::kTMA) {
         bl.init(sb, n0, tg);
-        if constexpr (HasRowTable<BL>::value) sb.tab = row_table;
+        if constexpr (HasRowTable<BL>::value) sb.tab = (decltype(sb.tab))row_table;
       }
+      int a_passes = 0, b_passes = 0;
+      if constexpr (!AL::kTMA) a_passes = al.passes();
+      if constexpr (!BL::kTMA) b_passes = bl.passes();
+      const int max_passes = max(a_passes, b_passes);
       const int s = grp;
       uint8_t* a_tile = smem + s * Cfg::kStageBytes;
       uint8_t* b_tile = a_tile + kATileBytes;
       for (int kc = grp; kc < nchunks; kc += NG) {
-        const uint32_t ph = (kc / TSTAGES) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);
         const int r0 = r_begin + kc * TBK;
-        if constexpr (!AL::kTMA) {
-          if constexpr (AL::kKTable) {
-            mbar_wait(&tab_bar[s], ph);
-            al.load(sa, a_tile, k_table[s], tg);
-          } else {
-            al.load(sa, a_tile, m0, r0, r_end, tg);
-          }
+        const void* kt = ktab + (size_t)kc * TBK * KTabEntryBytes<AL>::value;
+        // pass 0 global loads first: they do not need the stage, so their latency overlaps the MMA still reading it
+        if constexpr (!AL::kTMA) al.fetch(sa, ra, 0, m0, r0, r_end, tg, kt);
+        if constexpr (!BL::kTMA) bl.fetch(sb, rb, 0, n0, r0, r_end, tg, nullptr);
+        mbar_wait(&empty_bar[s], ((kc / TSTAGES) & 1) ^ 1);
+        if constexpr (!AL::kTMA) al.commit(sa, ra, 0, a_tile, tg);
+        if constexpr (!BL::kTMA) bl.commit(sb, rb, 0, b_tile, tg);
+        for (int pass = 1; pass < max_passes; ++pass) {
+          if constexpr (!AL::kTMA) { if (pass < a_passes) al.fetch(sa, ra, pass, m0, r0, r_end, tg, kt); }
+          if constexpr (!BL::kTMA) { if (pass < b_passes) bl.fetch(sb, rb, pass, n0, r0, r_end, tg, nullptr); }
+          if constexpr (!AL::kTMA) { if (pass < a_passes) al.commit(sa, ra, pass, a_tile, tg); }
+          if constexpr (!BL::kTMA) { if (pass < b_passes) bl.commit(sb, rb, pass, b_tile, tg); }
         }
-        if constexpr (!BL::kTMA) bl.load(sb, b_tile, n0, r0, r_end, tg);
         fence_proxy_async_smem();
         mbar_arrive(&full_bar[s]);
       }
@@ -634,7 +678,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
       mma_commit(&tmem_full_bar);           // accumulator complete
     }
-  } else if (warp == kTmaWarp) {
+  } else {
     // ---------------- TMA issuer ----------------
     if (kAnyTma && lane == 0 && nchunks > 0) {
       uint32_t bytes = 0;
@@ -649,17 +693,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         mbar_arrive_expect_tx(&full_bar[s], bytes);
         if constexpr (AL::kTMA) al.issue(&tmA, a_tile, &full_bar[s], m0, r0);
         if constexpr (BL::kTMA) bl.issue(&tmB, b_tile, &full_bar[s], n0, r0);
-      }
-    }
-  } else {
-    // ---------------- reduction-index table builder ----------------
-    if constexpr (AL::kKTable) {
-      for (int kc = 0; kc < nchunks; ++kc) {
-        const int s = kc % TSTAGES;
-        mbar_wait(&empty_bar[s], ((kc / TSTAGES) & 1) ^ 1);     // the slot's previous readers are done
-        k_table[s][lane] = al.table_entry(r_begin + kc * TBK + lane, r_end);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tab_bar[s]);
       }
     }
   }
@@ -735,20 +768,26 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
   typedef TcCfg<BN> Cfg;
   dim3 grid((M + TBM - 1) / TBM, (N + n_mma - 1) / n_mma, 1);
   const int splits = splitk_slices((int)(grid.x * grid.y), R);
-  static bool attr_done_split = false, attr_done = false;
+  static size_t attr_done_split = 0, attr_done = 0;          // largest dynamic smem size opted in so far
+  constexpr size_t kMaxSmem = 227 * 1024;
   if (splits == 1) {
+    const int len = (R + TBK - 1) / TBK * TBK;
+    const size_t smem = Cfg::kSmemBytes + (size_t)len * KTabEntryBytes<AL>::value;
+    if (smem > kMaxSmem) fatal("tensor-core contraction: reduction of %d needs %zu bytes of shared memory (> %zu)", R, smem, kMaxSmem);
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, false>;
-    if (!attr_done) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes)); attr_done = true; }
-    kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, (R + TBK - 1) / TBK * TBK, n_mma, nullptr);
+    if (smem > attr_done) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = smem; }
+    kfn<<<grid, kTcThreads, smem, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, nullptr);
     count_launch();
   } else {
     int len = (R + splits - 1) / splits;
     len = (len + TBK - 1) / TBK * TBK;
     grid.z = (R + len - 1) / len;
     float* ws = get_workspace((size_t)grid.z * M * N);
+    const size_t smem = Cfg::kSmemBytes + (size_t)len * KTabEntryBytes<AL>::value;
+    if (smem > kMaxSmem) fatal("tensor-core contraction: reduction slice of %d needs %zu bytes of shared memory (> %zu)", len, smem, kMaxSmem);
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, true>;
-    if (!attr_done_split) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes)); attr_done_split = true; }
-    kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
+    if (smem > attr_done_split) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done_split = smem; }
+    kfn<<<grid, kTcThreads, smem, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
     const size_t total = (size_t)M * N;
     int blocks = (int)((total + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
