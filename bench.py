@@ -213,6 +213,10 @@ def main():
         print(json.dumps(line))
         return
 
+    # Keep stdout for the ONE JSON line: NCCL / torch may print banners ("NCCL version ...") to fd 1.
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local_rank)
@@ -331,8 +335,10 @@ def main():
                                 "sample": r["sample"]}
     elif rank == 0:
         line["cpu_baseline"] = None
+    sys.stdout.flush()
+    os.dup2(saved_stdout, 1)
     if rank == 0:
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     net.close()
     if world > 1:
         dist.destroy_process_group()
