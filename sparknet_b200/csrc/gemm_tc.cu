@@ -880,6 +880,211 @@ void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const floa
   }
 }
 
+// ---- flat-grid convolution (stride 1): every operand through TMA ------------------------------------
+// The gathers above spend ~8 instructions per staged element.  For stride-1 filters the im2col view can
+// instead be expressed as plain TMA boxes if activations are first repacked channels-last on a "flat grid":
+//   flat[lead + n*Gp + h*Wp + w][c] = tf32(t[n][c][h][w]),  Hp = H + 2*ph = Ho + kh - 1,  Wp likewise, Gp = Hp*Wp,
+// images top-left aligned in their Hp x Wp cell, everything else zero (zeroed once at allocation; the pack
+// kernel only writes image positions).  With output positions on the SAME grid (q = n*Gp + ho*Wp + wo),
+//   y(q)  = sum_{c,ky,kx} xflat[q + ky*Wp + kx - (ph*Wp + pw)][c] * W[co][c][ky][kx]
+//   dx(q) = sum_{co,ky',kx'} dyflat[q + ky'*Wp + kx' - (pad'*Wp + pad')][co] * W[co][c][kh-1-ky'][kw-1-kx'],  pad' = k-1-p
+//   dW[co][c][ky][kx] = sum_q dyflat[q][co] * xflat[q + ky*Wp + kx - (ph*Wp + pw)][c]
+// so a filter tap is a pure shift of the grid row: the zero bands to the right of / below each image double
+// as the left / top padding of the next row / image.  The shift is on the OUTER TMA coordinate (the inner
+// one must stay 16-byte aligned), which is why the packed layout is channels-last.  Grid positions that are
+// not real outputs (w >= Wo or h >= Ho) are computed and dropped by the epilogue: (Hp*Wp)/(Ho*Wo) = 1.3x
+// extra MMA work for AlexNet's 3x3 / 5x5 layers, in exchange for no gather.  The reduction of fwd / dgrad
+// runs over (tap, channel slot) with the group's channels padded to a multiple of 32 slots; the filters are
+// repacked to match with zeros in the extra slots (which read the neighbouring group's channels or TMA
+// zero fill).
+
+static int flat_slots(int ch) { return (ch + 31) / 32 * 32; }
+
+bool tc_flat_supported(const ConvGeom& g) {
+  const int Cg = g.Cg(), Og = g.Og();
+  return g.sh == 1 && g.sw == 1 && Cg % 16 == 0 && Og % 16 == 0 && Cg <= 256 && g.kh * g.kw <= 64 && g.ph < g.kh &&
+         g.pw < g.kw && (long long)g.N * (g.H + 2 * g.ph) * (g.W + 2 * g.pw) < (1ll << 30);
+}
+// zero rows in front of cell 0, so that no TMA coordinate is negative
+static int flat_lead(const ConvGeom& g) {
+  const int Wp = g.W + 2 * g.pw, a = g.ph * Wp + g.pw, b = (g.kh - 1 - g.ph) * Wp + (g.kw - 1 - g.pw);
+  return ((a > b ? a : b) + 31) / 32 * 32;
+}
+size_t tc_flat_rows(const ConvGeom& g) {
+  const size_t cells = (size_t)g.N * (g.H + 2 * g.ph) * (g.W + 2 * g.pw);
+  return (cells + 127) / 128 * 128 + 128 + (size_t)flat_lead(g);
+}
+size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
+  return dgrad ? (size_t)g.C * flat_slots(g.Og()) * g.kh * g.kw : (size_t)g.Cout * flat_slots(g.Cg()) * g.kh * g.kw;
+}
+
+// NCHW -> grid rows x channels (32 x 32 transposes through shared memory).  grid (pixel blocks, channel blocks, N)
+__global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int H, int W,
+                                                         int Wp, int Gp, int lead) {
+  __shared__ float tile[32][33];
+  const int HW = H * W, p0 = blockIdx.x * 32, c0 = blockIdx.y * 32, n = blockIdx.z;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8) {
+    const int c = c0 + j, p = p0 + tx;
+    tile[j][tx] = (c < C && p < HW) ? src[((size_t)n * C + c) * HW + p] : 0.f;
+  }
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8) {
+    const int p = p0 + j, c = c0 + tx;
+    if (p < HW && c < C) {
+      const int h = p / W, w = p - h * W;
+      dst[((size_t)lead + (size_t)n * Gp + h * Wp + w) * C + c] = to_tf32_exact(tile[tx][j]);
+    }
+  }
+}
+void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst) {
+  const int C = output_side ? g.Cout : g.C, H = output_side ? g.Ho : g.H, W = output_side ? g.Wo : g.W;
+  const int Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp;
+  dim3 grid((H * W + 31) / 32, (C + 31) / 32, g.N);
+  flat_pack_kernel<<<grid, 256, 0, s>>>(src, dst, C, H, W, Wp, Gp, flat_lead(g));
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
+// dst[row][tap*slots + ch]: fwd   (dgrad = 0): row = co (all groups), ch = c in group,  value W[co][c][tap]
+//                           dgrad (dgrad = 1): row = grp*Cg + c,      ch = co in group, value W[grp*Og + co][c][T-1-tap]
+__global__ void flat_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ dst, int Cg, int Og, int T, int groups, int dgrad) {
+  const int red = dgrad ? Og : Cg, rows = dgrad ? Cg * groups : Og * groups;
+  const int slots = (red + 31) / 32 * 32, kp = T * slots;
+  const size_t total = (size_t)rows * kp;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int row = (int)(i / kp), k = (int)(i - (size_t)row * kp), tap = k / slots, ch = k - tap * slots;
+    float v = 0.f;
+    if (ch < red) {
+      if (!dgrad) v = w[((size_t)row * Cg + ch) * T + tap];
+      else { const int grp = row / Cg, c = row - grp * Cg; v = w[((size_t)(grp * Og + ch) * Cg + c) * T + (T - 1 - tap)]; }
+    }
+    dst[i] = to_tf32_exact(v);
+  }
+}
+void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst) {
+  const size_t total = tc_flat_filter_floats(g, dgrad);
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  flat_pack_filter_kernel<<<blocks, 256, 0, s>>>(w, dst, g.Cg(), g.Og(), g.kh * g.kw, g.group, dgrad ? 1 : 0);
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
+
+// A operand of flat fwd / dgrad: K-major, tile row = grid position, chunk = one tap x 32 channel slots.
+// tensor {channels (contiguous), grid rows}; box {32, 128}
+struct LoadTmaFlatRowsK {
+  static constexpr bool kTMA = true, kMN = false, kKTable = false;
+  typedef NoState State;
+  typedef NoRegs Regs;
+  int Wp, kw, off, nblk, chan0;          // off = row offset of tap (0,0), lead folded in
+  __device__ uint32_t bytes() const { return (uint32_t)kATileBytes; }
+  __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
+    const int kc = r0 >> 5, tap = kc / nblk, cb = kc - tap * nblk, ky = tap / kw, kx = tap - ky * kw;
+    tma_load_2d(tile, tm, bar, chan0 + cb * 32, row0 + ky * Wp + kx + off);
+  }
+};
+// A operand of flat wgrad: MN-major, tile row = output channel, reduction = grid position.  box {32, 32}
+struct LoadTmaFlatDyMN {
+  static constexpr bool kTMA = true, kMN = true, kKTable = false;
+  typedef NoState State;
+  typedef NoRegs Regs;
+  int chan0, lead;
+  __device__ uint32_t bytes() const { return (uint32_t)kATileBytes; }
+  __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
+    for (int i = 0; i < TBM / 32; ++i) tma_load_2d(tile + i * 4096, tm, bar, chan0 + row0 + 32 * i, lead + r0);
+  }
+};
+// B operand of flat wgrad: MN-major, tile row = (tap, channel slot), reduction = grid position.  box {32, 32}
+struct LoadTmaFlatTapsMN {
+  static constexpr bool kTMA = true, kMN = true, kKTable = false;
+  typedef NoState State;
+  typedef NoRegs Regs;
+  int Wp, kw, T, off, slots, nt, chan0;
+  __device__ uint32_t bytes() const { return (uint32_t)(nt * slots) * 128u; }
+  __device__ void issue(const CUtensorMap* tm, uint8_t* tile, uint64_t* bar, int row0, int r0) const {
+    const int t0 = row0 / slots, nblk = slots >> 5;
+    for (int j = 0; j < nt; ++j) {
+      const int tap = min(t0 + j, T - 1), ky = tap / kw, kx = tap - ky * kw;
+      for (int b = 0; b < nblk; ++b)
+        tma_load_2d(tile + (j * nblk + b) * 4096, tm, bar, chan0 + 32 * b, r0 + ky * Wp + kx + off);
+    }
+  }
+};
+// m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell
+struct TEpiConvFlat {
+  float* dst; const float* bias; int Ptot, Hv, Wv, Ctot, Cgrp, chan0, relu; FastDiv dGp, dWp;
+  struct Ctx { float* p; bool ok; };
+  __device__ Ctx row(int m) const {
+    Ctx c; c.ok = m < Ptot; c.p = dst;
+    if (c.ok) {
+      uint32_t n, rem, h, w;
+      dGp.divmod((uint32_t)m, n, rem);
+      dWp.divmod(rem, h, w);
+      c.ok = (int)h < Hv && (int)w < Wv;
+      c.p = dst + (((size_t)n * Ctot + chan0) * Hv + h) * Wv + w;
+    }
+    return c;
+  }
+  __device__ void store(const Ctx& c, int n, float v) const {
+    if (!c.ok || n >= Cgrp) return;
+    if (bias) v += __ldg(bias + chan0 + n);
+    if (relu) v = fmaxf(v, 0.f);
+    c.p[(size_t)n * Hv * Wv] = v;
+  }
+  __device__ void operator()(int m, int n, float v) const { store(row(m), n, v); }
+};
+// m = co in group, n = tap*slots + c;  dw[co][c][tap] (+)= v
+struct TEpiWgradFlat {
+  float* dw; int Og, Cg, T, accumulate; FastDiv dSlots;
+  struct Ctx { float* q; bool ok; };
+  __device__ Ctx row(int m) const { Ctx c; c.ok = m < Og; c.q = dw + (size_t)m * Cg * T; return c; }
+  __device__ void store(const Ctx& c, int n, float v) const {
+    uint32_t tap, ch;
+    dSlots.divmod((uint32_t)n, tap, ch);
+    if (!c.ok || (int)tap >= T || (int)ch >= Cg) return;
+    float* p = c.q + ch * T + tap;
+    *p = accumulate ? *p + v : v;
+  }
+  __device__ void operator()(int m, int n, float v) const { store(row(m), n, v); }
+};
+
+// `xflat`: packed input (tc_flat_pack, input side); `wf`: tc_flat_pack_filter(dgrad = false)
+void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu) {
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp, Ptot = g.N * Gp;
+  const int slots = flat_slots(Cg), kp = T * slots, n_mma = pick_n_mma(Og), lead = flat_lead(g);
+  CUtensorMap tmA = make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, TBM);
+  for (int grp = 0; grp < g.group; ++grp) {
+    CUtensorMap tmB = make_tmap(wf + (size_t)grp * Og * kp, (uint64_t)kp, (uint64_t)Og, (uint64_t)kp * 4, (uint32_t)n_mma);
+    LoadTmaFlatRowsK al{Wp, g.kw, lead - (g.ph * Wp + g.pw), slots / 32, grp * Cg};
+    TEpiConvFlat ep{y, bias, Ptot, g.Ho, g.Wo, g.Cout, Og, grp * Og, relu ? 1 : 0, FastDiv(Gp), FastDiv(Wp)};
+    launch_tc(s, tmA, tmB, al, LoadTmaK{n_mma}, ep, ep, Ptot, Og, kp, n_mma);
+  }
+}
+// `dyflat`: packed top gradient (tc_flat_pack, output side); `wt`: tc_flat_pack_filter(dgrad = true)
+void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx) {
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp, Ptot = g.N * Gp;
+  const int slots = flat_slots(Og), kp = T * slots, n_mma = pick_n_mma(Cg), lead = flat_lead(g);
+  CUtensorMap tmA = make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, TBM);
+  for (int grp = 0; grp < g.group; ++grp) {
+    CUtensorMap tmB = make_tmap(wt + (size_t)grp * Cg * kp, (uint64_t)kp, (uint64_t)Cg, (uint64_t)kp * 4, (uint32_t)n_mma);
+    LoadTmaFlatRowsK al{Wp, g.kw, lead - ((g.kh - 1 - g.ph) * Wp + (g.kw - 1 - g.pw)), slots / 32, grp * Og};
+    TEpiConvFlat ep{dx, nullptr, Ptot, g.H, g.W, g.C, Cg, grp * Cg, 0, FastDiv(Gp), FastDiv(Wp)};
+    launch_tc(s, tmA, tmB, al, LoadTmaK{n_mma}, ep, ep, Ptot, Cg, kp, n_mma);
+  }
+}
+void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate) {
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp, Ptot = g.N * Gp;
+  const int slots = flat_slots(Cg), nt = 256 / slots < T ? 256 / slots : T, n_mma = nt * slots, lead = flat_lead(g);
+  CUtensorMap tmA = make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, 32, true);
+  CUtensorMap tmB = make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, 32, true);
+  for (int grp = 0; grp < g.group; ++grp) {
+    LoadTmaFlatDyMN al{grp * Og, lead};
+    LoadTmaFlatTapsMN bl{Wp, g.kw, T, lead - (g.ph * Wp + g.pw), slots, nt, grp * Cg};
+    TEpiWgradFlat ep{dw + (size_t)grp * Og * Cg * T, Og, Cg, T, accumulate ? 1 : 0, FastDiv(slots)};
+    launch_tc(s, tmA, tmB, al, bl, ep, ep, Og, (T + nt - 1) / nt * n_mma, Ptot, n_mma);
+  }
+}
+
 // ---- inner product -------------------------------------------------------------------------------
 // D[m = out][n = batch] = sum_k W[m][k] X[n][k];  Y[n][m] = D + bias[m]
 void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu) {

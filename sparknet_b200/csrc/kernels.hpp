@@ -38,6 +38,15 @@ void tc_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* x, const float*
 void tc_test_gemm(cudaStream_t s, int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D);
 void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const float* w, float* dx);
 void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate);
+// flat-grid path for stride-1 convolutions (all operands through TMA); see gemm_tc.cu
+bool tc_flat_supported(const ConvGeom& g);
+size_t tc_flat_rows(const ConvGeom& g);                                // grid rows of a packed tensor (x channels = floats)
+size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad);
+void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst);   // dst zeroed once by the owner
+void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst);
+void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
+void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
+void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
 void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);
 void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w_tf32, float* dx);
 void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);

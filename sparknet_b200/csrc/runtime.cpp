@@ -346,24 +346,78 @@ struct ConvolutionLayer : Layer {
     const float* x = bottom[0]->data->gpu();
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
-    if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, weights_tf32(), b, y, fuse_relu);
+    if (net->precision == PREC_TF32 && use_flat(1)) {
+      tc_conv_fwd_flat(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
+    } else if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, weights_tf32(), b, y, fuse_relu);
     else ffma_conv_fwd(S(), g, x, blobs[0]->data->gpu(), b, y, fuse_relu);
+  }
+  // ---- flat-grid operands (gemm_tc.cu "flat-grid convolution"): packed copies owned by the layer ----
+  float *xflat = nullptr, *dyflat = nullptr, *wflat[2] = {nullptr, nullptr};
+  uint64_t xflat_gen = ~0ull, wflat_gen[2] = {~0ull, ~0ull};
+  const Storage* xflat_src = nullptr;
+  int flat_ok = -1;
+  // SPARKNET_CONV_FLAT: bit 0 forward, bit 1 backward-filter, bit 2 backward-data (default 7; 0 = gather kernels only)
+  bool use_flat(int bit) {
+    if (flat_ok < 0) {
+      const char* e = getenv("SPARKNET_CONV_FLAT");
+      flat_ok = tc_flat_supported(g) ? (e ? atoi(e) : 7) : 0;
+    }
+    return (flat_ok & bit) != 0;
+  }
+  float* flat_alloc(int channels) {
+    float* p = nullptr;
+    const size_t bytes = (size_t)channels * tc_flat_rows(g) * sizeof(float);
+    SN_CUDA(cudaMalloc(&p, bytes));
+    SN_CUDA(cudaMemsetAsync(p, 0, bytes, S()));      // the bands between images stay zero for good
+    return p;
+  }
+  const float* packed_input(Blob* bottom) {
+    const float* x = bottom->data->gpu();
+    if (!xflat) xflat = flat_alloc(g.C);
+    if (xflat_src != bottom->data.get() || xflat_gen != bottom->data->gen) {
+      tc_flat_pack(S(), g, false, x, xflat);
+      xflat_src = bottom->data.get();
+      xflat_gen = bottom->data->gen;
+    }
+    return xflat;
+  }
+  const float* packed_filter(bool dgrad) {
+    Storage* st = blobs[0]->data.get();
+    const float* w = st->gpu();
+    const int i = dgrad ? 1 : 0;
+    if (!wflat[i]) SN_CUDA(cudaMalloc(&wflat[i], tc_flat_filter_floats(g, dgrad) * sizeof(float)));
+    if (wflat_gen[i] != st->gen) {
+      tc_flat_pack_filter(S(), g, dgrad, w, wflat[i]);
+      wflat_gen[i] = st->gen;
+    }
+    return wflat[i];
+  }
+  ~ConvolutionLayer() override {
+    cudaFree(xflat); cudaFree(dyflat); cudaFree(wflat[0]); cudaFree(wflat[1]);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     const float* dy = top[0]->diff->gpu();
     const bool acc = !net->overwrite_param_diffs;
     if (bias_term && param_propagate_down[1])
       conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
+    const bool tf32 = net->precision == PREC_TF32;
+    const bool flat_w = tf32 && use_flat(2) && param_propagate_down[0], flat_d = tf32 && use_flat(4) && pd[0];
+    if (flat_w || flat_d) {
+      if (!dyflat) dyflat = flat_alloc(g.Cout);
+      tc_flat_pack(S(), g, true, dy, dyflat);
+    }
     if (param_propagate_down[0]) {
       const float* x = bottom[0]->data->gpu();
       float* dw = blobs[0]->diff->mutable_gpu();
-      if (net->precision == PREC_TF32) tc_conv_wgrad(S(), g, x, dy, dw, acc);
+      if (flat_w) tc_conv_wgrad_flat(S(), g, packed_input(bottom[0]), dyflat, dw, acc);
+      else if (net->precision == PREC_TF32) tc_conv_wgrad(S(), g, x, dy, dw, acc);
       else ffma_conv_wgrad(S(), g, x, dy, dw, acc);
     }
     if (pd[0]) {
       const float* w = blobs[0]->data->gpu();
       float* dx = bottom[0]->diff->mutable_gpu();
-      if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
+      if (flat_d) tc_conv_dgrad_flat(S(), g, dyflat, packed_filter(true), dx);
+      else if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
       else ffma_conv_dgrad(S(), g, dy, w, dx);
     }
   }

@@ -30,6 +30,30 @@ def test_convolution_tf32(oracle, product, shape, num_output, kw):
         assert_close(a, b, TOL, f"param diff {j}")
 
 
+# stride-1 layers whose channel counts are multiples of 16 take the flat-grid TMA path (csrc/gemm_tc.cu)
+FLAT_CASES = [
+    ((5, 16, 9, 11), 32, dict(kernel_size=[3])),                                   # no padding: Ho = H - 2
+    ((3, 32, 12, 7), 16, dict(kernel_h=3, kernel_w=5, pad_h=1, pad_w=1)),          # rectangular, pad < (k-1)/2 along w
+    ((2, 48, 10, 10), 32, dict(kernel_size=[5], pad=[4])),                         # "full" padding: Ho = H + 4
+    ((40, 64, 13, 13), 96, dict(kernel_size=[3], pad=[1], group=2)),               # many tiles + split reduction
+    ((2, 16, 6, 6), 16, dict(kernel_size=[1])),                                    # 1x1
+    ((3, 96, 8, 8), 48, dict(kernel_size=[2], pad=[1], group=3)),                  # even filter, three groups
+]
+
+
+@pytest.mark.parametrize("flat", ["1", "0"])
+@pytest.mark.parametrize("shape,num_output,kw", FLAT_CASES)
+def test_convolution_flat_grid_and_gather_paths_tf32(oracle, product, monkeypatch, shape, num_output, kw, flat):
+    monkeypatch.setenv("SPARKNET_CONV_FLAT", flat)
+    x = np.random.default_rng(77).standard_normal(shape).astype(F)
+    l = conv_layer("conv", "data", num_output, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5), **kw)
+    r = run_pair(oracle, product, {"data": x}, [l], "conv", "conv", precision=1)
+    assert_close(r["fwd"][0]["conv"], r["fwd"][1]["conv"], TOL, "top")
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["conv"])):
+        assert_close(a, b, TOL, f"param diff {j}")
+
+
 def test_convolution_relu_fusion_tf32(oracle, product):
     x = np.random.default_rng(5).standard_normal((2, 8, 9, 9)).astype(F)
     l = conv_layer("conv", "data", 16, kernel_size=[3], pad=[1], weight_filler=gaussian(0.1), bias_filler=gaussian(0.1))
