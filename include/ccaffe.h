@@ -130,6 +130,9 @@ long sparknet_kernel_launches(caffenet_state* state);
 /* Test hook for the tensor-core GEMM core: D[M][N] = A x B^T, host pointers.  a_mn/b_mn: 0 = operand
  * stored [rows][R], 1 = stored [R][rows]; tma_a: feed A through TMA. */
 int sparknet_test_tc_gemm(int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D);
+/* Development switches of the window convolution kernels (no reference counterpart): what = 1 forces the
+ * number of accumulators per CTA (0 = the planner's choice). */
+void sparknet_debug_set(int what, int value);
 /* CUDA-event stopwatch on the library's compute stream (bench.py times the hot path with it). */
 void sparknet_timer_start(caffenet_state* state);
 float sparknet_timer_stop_ms(caffenet_state* state);

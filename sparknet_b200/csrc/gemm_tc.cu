@@ -747,6 +747,9 @@ static CUtensorMap make_tmap(const float* base, uint64_t inner, uint64_t outer, 
                                (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)pitch_bytes, box_outer);
   return m;
 }
+CUtensorMap tc_make_tmap(const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes, uint32_t box_outer, bool mn_major) {
+  return make_tmap(base, inner, outer, pitch_bytes, box_outer, mn_major);
+}
 static CUtensorMap dummy_tmap() {
   CUtensorMap m;
   memset(&m, 0, sizeof(m));
@@ -903,16 +906,26 @@ static int flat_slots(int ch) { return (ch + 31) / 32 * 32; }
 bool tc_flat_supported(const ConvGeom& g) {
   const int Cg = g.Cg(), Og = g.Og();
   return g.sh == 1 && g.sw == 1 && Cg % 16 == 0 && Og % 16 == 0 && Cg <= 256 && g.kh * g.kw <= 64 && g.ph < g.kh &&
-         g.pw < g.kw && (long long)g.N * (g.H + 2 * g.ph) * (g.W + 2 * g.pw) < (1ll << 30);
+         g.pw < g.kw && (long long)g.N * (g.H + g.kh) * (g.W + g.kw) < (1ll << 30);
 }
-// zero rows in front of cell 0, so that no TMA coordinate is negative
-static int flat_lead(const ConvGeom& g) {
-  const int Wp = g.W + 2 * g.pw, a = g.ph * Wp + g.pw, b = (g.kh - 1 - g.ph) * Wp + (g.kw - 1 - g.pw);
-  return ((a > b ? a : b) + 31) / 32 * 32;
+// Cell geometry.  The zero band to the right of / below each image is shared: it is the right / bottom
+// padding of this image row and the left / top padding of the next one, so it only has to be as wide as the
+// larger of the padding the forward taps need (p) and the padding the backward-data taps need (k - 1 - p).
+FlatGeom tc_flat_geom(const ConvGeom& g) {
+  FlatGeom f;
+  f.bw = g.pw > g.kw - 1 - g.pw ? g.pw : g.kw - 1 - g.pw;
+  f.bh = g.ph > g.kh - 1 - g.ph ? g.ph : g.kh - 1 - g.ph;
+  f.Wp = g.W + f.bw;
+  f.Hp = g.H + f.bh;
+  f.Gp = f.Wp * f.Hp;
+  f.lead = (f.bh * f.Wp + f.bw + 31) / 32 * 32;        // zero rows in front of cell 0: no TMA coordinate is negative
+  return f;
 }
+static int flat_lead(const ConvGeom& g) { return tc_flat_geom(g).lead; }
 size_t tc_flat_rows(const ConvGeom& g) {
-  const size_t cells = (size_t)g.N * (g.H + 2 * g.ph) * (g.W + 2 * g.pw);
-  return (cells + 127) / 128 * 128 + 128 + (size_t)flat_lead(g);
+  const FlatGeom f = tc_flat_geom(g);
+  const size_t cells = (size_t)g.N * f.Gp;
+  return (cells + 127) / 128 * 128 + 128 + (size_t)f.lead;
 }
 size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
   return dgrad ? (size_t)g.C * flat_slots(g.Og()) * g.kh * g.kw : (size_t)g.Cout * flat_slots(g.Cg()) * g.kh * g.kw;
@@ -939,7 +952,8 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
 }
 void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst) {
   const int C = output_side ? g.Cout : g.C, H = output_side ? g.Ho : g.H, W = output_side ? g.Wo : g.W;
-  const int Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp;
+  const FlatGeom f = tc_flat_geom(g);
+  const int Wp = f.Wp, Gp = f.Gp;
   dim3 grid((H * W + 31) / 32, (C + 31) / 32, g.N);
   flat_pack_kernel<<<grid, 256, 0, s>>>(src, dst, C, H, W, Wp, Gp, flat_lead(g));
   count_launch();
@@ -1050,7 +1064,7 @@ struct TEpiWgradFlat {
 
 // `xflat`: packed input (tc_flat_pack, input side); `wf`: tc_flat_pack_filter(dgrad = false)
 void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu) {
-  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp, Ptot = g.N * Gp;
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = tc_flat_geom(g).Wp, Gp = tc_flat_geom(g).Gp, Ptot = g.N * Gp;
   const int slots = flat_slots(Cg), kp = T * slots, n_mma = pick_n_mma(Og), lead = flat_lead(g);
   CUtensorMap tmA = make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, TBM);
   for (int grp = 0; grp < g.group; ++grp) {
@@ -1062,7 +1076,7 @@ void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, con
 }
 // `dyflat`: packed top gradient (tc_flat_pack, output side); `wt`: tc_flat_pack_filter(dgrad = true)
 void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx) {
-  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp, Ptot = g.N * Gp;
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = tc_flat_geom(g).Wp, Gp = tc_flat_geom(g).Gp, Ptot = g.N * Gp;
   const int slots = flat_slots(Og), kp = T * slots, n_mma = pick_n_mma(Cg), lead = flat_lead(g);
   CUtensorMap tmA = make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, TBM);
   for (int grp = 0; grp < g.group; ++grp) {
@@ -1073,7 +1087,7 @@ void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, 
   }
 }
 void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate) {
-  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = g.W + 2 * g.pw, Gp = (g.H + 2 * g.ph) * Wp, Ptot = g.N * Gp;
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Wp = tc_flat_geom(g).Wp, Gp = tc_flat_geom(g).Gp, Ptot = g.N * Gp;
   const int slots = flat_slots(Cg), nt = 256 / slots < T ? 256 / slots : T, n_mma = nt * slots, lead = flat_lead(g);
   CUtensorMap tmA = make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, 32, true);
   CUtensorMap tmB = make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, 32, true);

@@ -40,6 +40,8 @@ void tc_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dy, const flo
 void tc_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const float* dy, float* dw, bool accumulate);
 // flat-grid path for stride-1 convolutions (all operands through TMA); see gemm_tc.cu
 bool tc_flat_supported(const ConvGeom& g);
+struct FlatGeom { int Wp, Hp, Gp, lead, bw, bh; };                    // cell width / height / size, leading zero rows, band widths
+FlatGeom tc_flat_geom(const ConvGeom& g);
 size_t tc_flat_rows(const ConvGeom& g);                                // grid rows of a packed tensor (x channels = floats)
 size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad);
 void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst);   // dst zeroed once by the owner
@@ -47,6 +49,11 @@ void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const fl
 void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
 void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
 void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
+// window kernels (conv_flat.cu): same packed operands, one TMA load of the grid rows per channel block serves every tap
+void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
+void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
+bool tcw_supported(const ConvGeom& g);
+void tcw_set_debug(int what, int value);
 void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);
 void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w_tf32, float* dx);
 void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);

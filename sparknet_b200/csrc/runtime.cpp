@@ -347,7 +347,8 @@ struct ConvolutionLayer : Layer {
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
     if (net->precision == PREC_TF32 && use_flat(1)) {
-      tc_conv_fwd_flat(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
+      if (use_window()) tcw_conv_fwd(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
+      else tc_conv_fwd_flat(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
     } else if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, weights_tf32(), b, y, fuse_relu);
     else ffma_conv_fwd(S(), g, x, blobs[0]->data->gpu(), b, y, fuse_relu);
   }
@@ -363,6 +364,15 @@ struct ConvolutionLayer : Layer {
       flat_ok = tc_flat_supported(g) ? (e ? atoi(e) : 7) : 0;
     }
     return (flat_ok & bit) != 0;
+  }
+  // SPARKNET_FLAT_WINDOW=0 falls back from the window kernels (conv_flat.cu) to the chunk-per-tap flat kernels
+  int window_ok = -1;
+  bool use_window() {
+    if (window_ok < 0) {
+      const char* e = getenv("SPARKNET_FLAT_WINDOW");
+      window_ok = (tcw_supported(g) && !(e && atoi(e) == 0)) ? 1 : 0;
+    }
+    return window_ok != 0;
   }
   float* flat_alloc(int channels) {
     float* p = nullptr;
@@ -416,7 +426,8 @@ struct ConvolutionLayer : Layer {
     if (pd[0]) {
       const float* w = blobs[0]->data->gpu();
       float* dx = bottom[0]->diff->mutable_gpu();
-      if (flat_d) tc_conv_dgrad_flat(S(), g, dyflat, packed_filter(true), dx);
+      if (flat_d && use_window()) tcw_conv_dgrad(S(), g, dyflat, packed_filter(true), dx);
+      else if (flat_d) tc_conv_dgrad_flat(S(), g, dyflat, packed_filter(true), dx);
       else if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
       else ffma_conv_dgrad(S(), g, dy, w, dx);
     }
