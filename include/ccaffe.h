@@ -131,8 +131,12 @@ long sparknet_kernel_launches(caffenet_state* state);
  * stored [rows][R], 1 = stored [R][rows]; tma_a: feed A through TMA. */
 int sparknet_test_tc_gemm(int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D);
 /* Development switches of the window convolution kernels (no reference counterpart): what = 1 forces the
- * number of accumulators per CTA (0 = the planner's choice). */
+ * number of accumulators per CTA (0 = the planner's choice); what = 2 turns per-CTA clock stamps on / off, which
+ * sparknet_debug_read_stamps copies out (8 per CTA of the most recent window launch). */
 void sparknet_debug_set(int what, int value);
+int sparknet_debug_read_stamps(long long* out, int max_ctas);
+/* Development aid: clocks per TF32 tcgen05.mma (128*cg x n_mma x 8) issued back to back on resident tiles. */
+float sparknet_debug_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int ctas, float* issue_only);
 /* CUDA-event stopwatch on the library's compute stream (bench.py times the hot path with it). */
 void sparknet_timer_start(caffenet_state* state);
 float sparknet_timer_stop_ms(caffenet_state* state);

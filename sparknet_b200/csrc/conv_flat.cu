@@ -21,6 +21,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 #include "gemm_ops.cuh"
 #include "kernels.hpp"
@@ -46,23 +47,32 @@ struct WinArgs {
   int b_row_group;          // row coordinate of group g in the filter tensor = g * b_row_group
   int box_rows, nbox;       // a window is nbox TMA boxes of box_rows grid rows
   int nstage;               // filter pipeline depth
+  long long* stamps;        // development aid: 8 clock64 stamps per CTA (null = off)
 };
 // m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell
 struct WinEpi {
   float* dst; const float* bias; int Hv, Wv, Ctot, Cgrp, relu; FastDiv dGp, dWp;
 };
 
+// CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2 along x) runs every MMA with M = 256: each CTA keeps its
+// own grid rows (window + accumulators) and HALF of the filter rows of the chunk, so per SM the filter bytes through the
+// L2 and the shared-memory bytes the tensor core reads per MMA are halved (the TF32 MMA of one CTA is otherwise bound by
+// shared-memory bandwidth: (128 + N) x 32 B per N/2 clocks).
+template <int CG>
 __global__ void __launch_bounds__(kWThreads, 1)
 conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const WinArgs a, const WinEpi ep) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t win_full[2], win_empty[2], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full;
   __shared__ uint32_t tmem_base_smem;
 
+  const long long t_enter = clock64();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
   const int q0 = blockIdx.x * a.MT * 128, n0 = blockIdx.y * a.n_mma, grp = blockIdx.z;
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t win_bytes = (uint32_t)(a.nbox * a.box_rows) * 128u;      // multiple of 1024 (box_rows % 8 == 0)
-  const uint32_t b_bytes = (uint32_t)a.n_mma * 128u;                      // multiple of 2048 (n_mma % 16 == 0)
+  const int nb_local = a.n_mma / CG;                                      // filter rows this CTA stages per chunk
+  const uint32_t b_bytes = (uint32_t)nb_local * 128u;                     // multiple of 1024 (n_mma % 16 == 0)
   uint8_t* bst = smem + 2 * win_bytes;
 
   if (tid == 0) {
@@ -73,116 +83,249 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
   }
-  if (warp == kWEpiWarps) tmem_alloc<512>(&tmem_base_smem);
+  if (warp == kWEpiWarps) {
+    if (CG == 2) tmem_alloc_pair<512>(&tmem_base_smem);
+    else tmem_alloc<512>(&tmem_base_smem);
+  }
   tc_fence_before_sync();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all();
+  else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  long long* stamp = a.stamps ? a.stamps + 8 * ((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) : nullptr;
+  if (stamp && tid == 0) { stamp[0] = t_enter; stamp[1] = clock64(); }
 
   if (warp < kWEpiWarps) {
     // ---------------- epilogue ----------------
     mbar_wait(&tmem_full, 0);
     tc_fence_after_sync();
+    if (stamp && tid == 0) stamp[5] = clock64();
     const int quarter = warp & 3, half = warp >> 2, chan0 = grp * ep.Cgrp;
     const size_t plane = (size_t)ep.Hv * ep.Wv;
-    for (int i = 0; i < a.MT; ++i) {
-      const int m = q0 + i * 128 + 32 * quarter + lane;
-      bool ok = m < a.Ptot;
-      float* p = ep.dst;
-      if (ok) {
-        uint32_t img, rem, h, w;
-        ep.dGp.divmod((uint32_t)m, img, rem);
-        ep.dWp.divmod(rem, h, w);
-        ok = (int)h < ep.Hv && (int)w < ep.Wv;
-        p = ep.dst + (((size_t)img * ep.Ctot + chan0) * ep.Hv + h) * ep.Wv + w;
-      }
-      for (int c0 = 16 * half; c0 < a.n_mma; c0 += 32) {
+    const int ncols = min(a.n_mma, ep.Cgrp - n0);                 // valid columns of this tile (multiple of 16)
+    for (int c0 = 16 * half; c0 < ncols; c0 += 32) {
+      float bias[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) bias[j] = ep.bias ? __ldg(ep.bias + chan0 + n0 + c0 + j) : 0.f;
+      for (int i = 0; i < a.MT; ++i) {
         uint32_t v[16];
         tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(i * a.n_mma + c0), v);
+        const int m = q0 + i * 128 + 32 * quarter + lane;
+        bool ok = m < a.Ptot;
+        float* p = ep.dst;
+        if (ok) {
+          uint32_t img, rem, h, w;
+          ep.dGp.divmod((uint32_t)m, img, rem);
+          ep.dWp.divmod(rem, h, w);
+          ok = (int)h < ep.Hv && (int)w < ep.Wv;
+          p = ep.dst + ((((size_t)img * ep.Ctot + chan0 + n0 + c0) * ep.Hv + h) * ep.Wv + w);
+        }
         tmem_ld_wait();
+        if (ok) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const int n = n0 + c0 + j;
-          if (ok && n < ep.Cgrp) {
-            float acc = __uint_as_float(v[j]);
-            if (ep.bias) acc += __ldg(ep.bias + chan0 + n);
+          for (int j = 0; j < 16; ++j) {
+            float acc = __uint_as_float(v[j]) + bias[j];
             if (ep.relu) acc = fmaxf(acc, 0.f);
-            p[(size_t)n * plane] = acc;
+            p[(size_t)j * plane] = acc;
           }
         }
       }
     }
   } else if (warp == kWEpiWarps) {
-    // ---------------- MMA issuer ----------------
-    if (lane == 0) {
-      const uint32_t idesc = make_idesc_tf32(128, a.n_mma, 0, 0);
-      const uint32_t win_addr = smem_u32(smem), b_addr0 = smem_u32(bst);
-      int it = 0;
+    // ---------------- MMA issuer (rank 0 of a pair): the whole warp walks the pipeline, one elected lane issues ----------------
+    if (rank == 0) {
+      const uint32_t idesc = make_idesc_tf32(128 * CG, a.n_mma, 0, 0);
+      // descriptor = {lo: start >> 4 | LBO 16 B << 16, hi: SBO 1024 B | version 1 | SWIZZLE_128B}; only lo moves
+      const uint32_t desc_hi = (uint32_t)(make_smem_desc(0, 16, 1024, kLayoutSW128) >> 32);
+      const uint32_t lo_flags = 1u << 16;
+      const uint32_t win_lo = (smem_u32(smem) >> 4) | lo_flags, b_lo0 = (smem_u32(bst) >> 4) | lo_flags;
+      const uint32_t win_step = win_bytes >> 4, b_step = b_bytes >> 4;
+      int it = 0, s = 0;
+      uint32_t sphase = 0;
+      long long wait_win = 0, wait_b = 0;
       for (int cb = 0; cb < a.ncb; ++cb) {
         const int wb = cb & 1;
+        long long tw = stamp ? clock64() : 0;
         mbar_wait(&win_full[wb], (cb >> 1) & 1);
-        tc_fence_after_sync();
+        if (stamp) wait_win += clock64() - tw;
         const int left = a.red - cb * 32, ks = left >= 32 ? 4 : (left + 7) / 8;
-        int ky = 0, kx = 0;
+        uint32_t shift_row = 0;                                     // (ky * Wp) in rows
+        int kx = 0;
         for (int tap = 0; tap < a.T; ++tap, ++it) {
-          const int s = it % a.nstage;
-          mbar_wait(&b_full[s], (it / a.nstage) & 1);
+          tw = stamp ? clock64() : 0;
+          mbar_wait(&b_full[s], sphase);
           tc_fence_after_sync();
-          const uint32_t b_addr = b_addr0 + (uint32_t)s * b_bytes;
-          const uint32_t shift = (uint32_t)(ky * a.Wp + kx);
+          if (stamp) wait_b += clock64() - tw;
           // The 128-byte swizzle is a function of the absolute shared-memory address (bits 4-6 ^= bits 7-9), for the
           // TMA write and for the MMA read alike, so a descriptor may start at any row of the window: the
           // base-offset field stays 0 (verified on B200 with tools/debug_window.py).
-          for (int i = 0; i < a.MT; ++i) {
-            const uint32_t a_addr = win_addr + (uint32_t)wb * win_bytes + ((uint32_t)(i * 128) + shift) * 128u;
-            for (int j = 0; j < ks; ++j) {
-              const uint64_t adesc = make_smem_desc(a_addr + j * 32, 16, 1024, kLayoutSW128);
-              const uint64_t bdesc = make_smem_desc(b_addr + j * 32, 16, 1024, kLayoutSW128);
-              mma_tf32(tmem_base + (uint32_t)(i * a.n_mma), adesc, bdesc, idesc, (cb | tap | j) != 0 ? 1u : 0u);
+          if (elect_one_sync()) {
+            const uint32_t a_lo = win_lo + (uint32_t)wb * win_step + (shift_row + (uint32_t)kx) * 8u;   // 128 B per row >> 4
+            const uint32_t b_lo = b_lo0 + (uint32_t)s * b_step;
+            for (int i = 0; i < a.MT; ++i) {
+              const uint32_t d = tmem_base + (uint32_t)(i * a.n_mma);
+#pragma unroll 4
+              for (int j = 0; j < ks; ++j) {
+                if (CG == 2) mma_tf32_lohi_pair(d, a_lo + (uint32_t)(i * 1024 + 2 * j), b_lo + (uint32_t)(2 * j), desc_hi, idesc, (it | j) != 0 ? 1u : 0u);
+                else mma_tf32_lohi(d, a_lo + (uint32_t)(i * 1024 + 2 * j), b_lo + (uint32_t)(2 * j), desc_hi, idesc, (it | j) != 0 ? 1u : 0u);
+              }
+            }
+            const bool last_tap = tap == a.T - 1, last = last_tap && cb == a.ncb - 1;
+            if (CG == 2) {
+              mma_commit_pair(&b_empty[s]);
+              if (last_tap) mma_commit_pair(&win_empty[wb]);
+              if (last) mma_commit_pair(&tmem_full);
+            } else {
+              mma_commit(&b_empty[s]);
+              if (last_tap) mma_commit(&win_empty[wb]);
+              if (last) mma_commit(&tmem_full);
             }
           }
-          mma_commit(&b_empty[s]);
-          if (++kx == a.kw) { kx = 0; ++ky; }
+          __syncwarp();
+          if (++kx == a.kw) { kx = 0; shift_row += (uint32_t)a.Wp; }
+          if (++s == a.nstage) { s = 0; sphase ^= 1u; }
         }
-        mma_commit(&win_empty[wb]);
       }
-      mma_commit(&tmem_full);
+      if (stamp && lane == 0) { stamp[2] = wait_win; stamp[3] = wait_b; }
     }
   } else {
-    // ---------------- TMA issuer ----------------
+    // ---------------- TMA issuer (both CTAs of a pair; completion bytes land on rank 0's barriers) ----------------
     if (lane == 0) {
       int it = 0;
-      const int a_chan0 = grp * a.a_chan_group, b_row0 = grp * a.b_row_group + n0;
+      const int a_chan0 = grp * a.a_chan_group, b_row0 = grp * a.b_row_group + n0 + rank * nb_local;
       for (int cb = 0; cb < a.ncb; ++cb) {
         const int wb = cb & 1;
         mbar_wait(&win_empty[wb], ((cb >> 1) & 1) ^ 1);
-        mbar_arrive_expect_tx(&win_full[wb], win_bytes);
-        for (int b = 0; b < a.nbox; ++b)
-          tma_load_2d(smem + (size_t)wb * win_bytes + (size_t)b * a.box_rows * 128, &tmA, &win_full[wb], a_chan0 + cb * 32,
-                      q0 + a.row_off + b * a.box_rows);
+        if (rank == 0) mbar_arrive_expect_tx(&win_full[wb], win_bytes * CG);
+        for (int b = 0; b < a.nbox; ++b) {
+          uint8_t* dst = smem + (size_t)wb * win_bytes + (size_t)b * a.box_rows * 128;
+          if (CG == 2) tma_load_2d_pair(dst, &tmA, &win_full[wb], a_chan0 + cb * 32, q0 + a.row_off + b * a.box_rows);
+          else tma_load_2d(dst, &tmA, &win_full[wb], a_chan0 + cb * 32, q0 + a.row_off + b * a.box_rows);
+        }
         for (int tap = 0; tap < a.T; ++tap, ++it) {
           const int s = it % a.nstage;
           mbar_wait(&b_empty[s], ((it / a.nstage) & 1) ^ 1);
-          mbar_arrive_expect_tx(&b_full[s], b_bytes);
-          tma_load_2d(bst + (size_t)s * b_bytes, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          if (rank == 0) mbar_arrive_expect_tx(&b_full[s], b_bytes * CG);
+          if (CG == 2) tma_load_2d_pair(bst + (size_t)s * b_bytes, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          else tma_load_2d(bst + (size_t)s * b_bytes, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
         }
       }
     }
   }
+  if (stamp && lane == 0 && warp == kWEpiWarps) stamp[4] = clock64();        // all MMAs issued
+  if (stamp && lane == 0 && warp == 0) stamp[6] = clock64();                 // this warp's share of the epilogue done
   tc_fence_before_sync();
-  __syncthreads();
-  if (warp == kWEpiWarps) tmem_dealloc<512>(tmem_base);
+  if (CG == 2) cluster_sync_all();
+  else __syncthreads();
+  if (stamp && tid == 0) stamp[7] = clock64();
+  if (warp == kWEpiWarps) {
+    if (CG == 2) tmem_dealloc_pair<512>(tmem_base);
+    else tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// Development aid: clocks per tcgen05.mma (TF32, operands in shared memory) when one thread issues `iters` of them
+// back to back on resident tiles — the ceiling the pipelines above are compared with.  mode 0: A K-major, B K-major.
+template <int CG>
+__global__ void __launch_bounds__(128, 1) mma_rate_kernel(int n_mma, int iters, int shift_rows, int nacc, long long* out) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t done;
+  __shared__ uint32_t tmem_base_smem;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  for (int i = tid; i < 96 * 1024 / 4; i += blockDim.x) ((float*)smem)[i] = 0.f;
+  if (tid == 0) { mbar_init(&done, 1u); fence_barrier_init(); }
+  if (warp == 0) { if (CG == 2) tmem_alloc_pair<512>(&tmem_base_smem); else tmem_alloc<512>(&tmem_base_smem); }
+  fence_proxy_async_smem();
+  tc_fence_before_sync();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_smem;
+  if (warp == 1 && rank == 0) {
+    const uint32_t idesc = make_idesc_tf32(128 * CG, n_mma, 0, 0);
+    const uint32_t desc_hi = (uint32_t)(make_smem_desc(0, 16, 1024, kLayoutSW128) >> 32);
+    const uint32_t a_lo = ((smem_u32(smem) >> 4) | (1u << 16)) + (uint32_t)shift_rows * 8u;
+    const uint32_t b_lo = ((smem_u32(smem) + 48 * 1024) >> 4) | (1u << 16);
+    long long t0 = 0, t1 = 0;
+    if (elect_one_sync()) {
+      t0 = clock64();
+      for (int it = 0; it < iters; ++it) {
+        const uint32_t d = tmem_base + (uint32_t)((it % nacc) * n_mma);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          if (CG == 2) mma_tf32_lohi_pair(d, a_lo + 2 * j, b_lo + 2 * j, desc_hi, idesc, 1u);
+          else mma_tf32_lohi(d, a_lo + 2 * j, b_lo + 2 * j, desc_hi, idesc, 1u);
+        }
+      }
+      t1 = clock64();
+      if (CG == 2) mma_commit_pair(&done); else mma_commit(&done);
+    }
+    __syncwarp();
+    mbar_wait(&done, 0);
+    const long long t2 = clock64();
+    if (elect_one_sync()) { out[blockIdx.x * 2] = t1 - t0; out[blockIdx.x * 2 + 1] = t2 - t0; }
+  } else if (warp == 1) {
+    mbar_wait(&done, 0);
+  }
+  tc_fence_before_sync();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 0) { if (CG == 2) tmem_dealloc_pair<512>(tmem_base); else tmem_dealloc<512>(tmem_base); }
+}
+// returns clocks per MMA (issue .. all complete) averaged over the CTAs; out2 (nullable) gets the issue-only figure
+float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int ctas, float* issue_only) {
+  long long* d = nullptr;
+  SN_CUDA(cudaMalloc(&d, sizeof(long long) * 2 * ctas));
+  SN_CUDA(cudaMemset(d, 0, sizeof(long long) * 2 * ctas));
+  const size_t smem = 97 * 1024 + 1024;
+  if (cg == 2) {
+    SN_CUDA(cudaFuncSetAttribute(mma_rate_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(ctas); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = smem; cfg.stream = 0;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    SN_CUDA(cudaLaunchKernelEx(&cfg, mma_rate_kernel<2>, n_mma, iters, shift_rows, nacc, d));
+  } else {
+    SN_CUDA(cudaFuncSetAttribute(mma_rate_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    mma_rate_kernel<1><<<ctas, 128, smem>>>(n_mma, iters, shift_rows, nacc, d);
+  }
+  SN_CUDA(cudaDeviceSynchronize());
+  std::vector<long long> h(2 * ctas);
+  SN_CUDA(cudaMemcpy(h.data(), d, sizeof(long long) * 2 * ctas, cudaMemcpyDeviceToHost));
+  cudaFree(d);
+  double a = 0, b = 0; int n = 0;
+  for (int i = 0; i < ctas; i += cg) { a += (double)h[2 * i]; b += (double)h[2 * i + 1]; ++n; }
+  if (issue_only) *issue_only = (float)(a / n / (iters * 4.0));
+  return (float)(b / n / (iters * 4.0));
 }
 
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-static int g_force_mt = 0;
+static int g_force_mt = 0, g_force_cg = 0;
+static long long* g_stamps = nullptr;
+static int g_stamp_ctas = 0;
+constexpr int kMaxStampCtas = 4096;
 void tcw_set_debug(int what, int value) {
   if (what == 1) g_force_mt = value;
+  if (what == 3) g_force_cg = value;                  // 1 = single-CTA MMAs only, 2 = CTA pairs whenever possible, 0 = auto
+  if (what == 2) {                                      // per-CTA clock stamps of the next window launches on / off
+    if (value && !g_stamps) SN_CUDA(cudaMalloc(&g_stamps, sizeof(long long) * 8 * kMaxStampCtas));
+    if (!value && g_stamps) { cudaFree(g_stamps); g_stamps = nullptr; }
+  }
+}
+// copies the stamps of the most recent window launch (8 per CTA) to `out`; returns the number of CTAs
+int tcw_read_stamps(long long* out, int max_ctas) {
+  if (!g_stamps) return 0;
+  SN_CUDA(cudaDeviceSynchronize());
+  const int n = g_stamp_ctas < max_ctas ? g_stamp_ctas : max_ctas;
+  SN_CUDA(cudaMemcpy(out, g_stamps, sizeof(long long) * 8 * n, cudaMemcpyDeviceToHost));
+  return n;
 }
 
-struct WinPlan { int MT, n_mma, nstage, box_rows, nbox; size_t smem; bool ok; };
+struct WinPlan { int MT, n_mma, nstage, box_rows, nbox, cg; size_t smem; bool ok; };
 
 static int win_n_mma(int N) {
   const int tiles = (N + 255) / 256;
@@ -191,7 +334,7 @@ static int win_n_mma(int N) {
   return w < 16 ? 16 : w;
 }
 // Pick the number of accumulators: fewest estimated clocks over all waves.  Per tile: MMA time MT*T*ksteps*n_mma/2,
-// L2 time bytes / 40, plus the serial prologue / epilogue.
+// L2 time bytes / 25, shared-memory time of the operand reads, plus the serial prologue / epilogue.
 static WinPlan plan_window(int Ptot, int N, int groups, int T, int span, int red) {
   WinPlan best{};
   best.ok = false;
@@ -205,7 +348,8 @@ static WinPlan plan_window(int Ptot, int N, int groups, int T, int span, int red
     const int win_rows = MT * 128 + span;
     const int nbox = (win_rows + 255) / 256;
     const int box_rows = ((win_rows + nbox - 1) / nbox + 7) / 8 * 8;
-    const size_t win_bytes = (size_t)nbox * box_rows * 128, b_bytes = (size_t)n_mma * 128;
+    const int cg = g_force_cg == 1 ? 1 : 2;                     // CTA pairs: half the filter bytes per SM
+    const size_t win_bytes = (size_t)nbox * box_rows * 128, b_bytes = (size_t)n_mma * 128 / cg;
     const size_t fixed = 2 * win_bytes + 1024 + 512;             // + alignment slack + static shared (barriers)
     if (fixed + 3 * b_bytes > kWSmemLimit) continue;
     int nstage = (int)((kWSmemLimit - fixed) / b_bytes);
@@ -213,11 +357,13 @@ static WinPlan plan_window(int Ptot, int N, int groups, int T, int span, int red
     const long long tiles = (long long)((Ptot + MT * 128 - 1) / (MT * 128)) * n_tiles * groups;
     const long long waves = (tiles + 147) / 148;
     const double t_mma = (double)MT * T * ksteps * n_mma / 2.0;
-    const double t_l2 = ((double)ncb * win_bytes + (double)ncb * T * b_bytes) / 40.0;
+    const double t_l2 = ((double)ncb * win_bytes + (double)ncb * T * b_bytes) / 25.0;   // measured: ~25 B/clk per SM with all SMs pulling
+    const double t_smem = (double)MT * T * ksteps * ((128.0 + n_mma / cg) * 32.0) / 110.0;   // operand reads of the tensor core
     const double t_epi = (double)MT * 128 * n_mma * 4 / 48.0;
-    const double cost = (double)waves * ((t_mma > t_l2 ? t_mma : t_l2) + t_epi + 4000.0);
+    const double t_main = t_mma > t_l2 ? (t_mma > t_smem ? t_mma : t_smem) : (t_l2 > t_smem ? t_l2 : t_smem);
+    const double cost = (double)waves * (t_main + t_epi + 4000.0);
     if (!best.ok || cost < best_cost) {
-      best = WinPlan{MT, n_mma, nstage, box_rows, nbox, 2 * win_bytes + (size_t)nstage * b_bytes + 1024, true};
+      best = WinPlan{MT, n_mma, nstage, box_rows, nbox, cg, 2 * win_bytes + (size_t)nstage * b_bytes + 1024, true};
       best_cost = cost;
     }
   }
@@ -228,11 +374,31 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
                           const WinPlan& pl, int N, int groups) {
   static bool attr_done = false;
   if (!attr_done) {
-    SN_CUDA(cudaFuncSetAttribute(conv_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemLimit - 1024));
+    SN_CUDA(cudaFuncSetAttribute(conv_window_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemLimit - 1024));
+    SN_CUDA(cudaFuncSetAttribute(conv_window_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemLimit - 1024));
     attr_done = true;
   }
   dim3 grid((a.Ptot + a.MT * 128 - 1) / (a.MT * 128), (N + a.n_mma - 1) / a.n_mma, groups);
-  conv_window_kernel<<<grid, kWThreads, pl.smem, s>>>(tmA, tmB, a, ep);
+  if (pl.cg == 2) grid.x = (grid.x + 1) / 2 * 2;          // whole pairs: the odd CTA works on rows past the end (zero-filled)
+  WinArgs aa = a;
+  const int ctas = (int)(grid.x * grid.y * grid.z);
+  aa.stamps = (g_stamps && ctas <= kMaxStampCtas) ? g_stamps : nullptr;
+  if (aa.stamps) g_stamp_ctas = ctas;
+  if (pl.cg == 2) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(kWThreads);
+    cfg.dynamicSmemBytes = pl.smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SN_CUDA(cudaLaunchKernelEx(&cfg, conv_window_kernel<2>, tmA, tmB, aa, ep));
+  } else {
+    conv_window_kernel<1><<<grid, kWThreads, pl.smem, s>>>(tmA, tmB, aa, ep);
+  }
   count_launch();
   SN_CUDA(cudaGetLastError());
 }
@@ -255,9 +421,9 @@ void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const f
   const WinPlan pl = plan_window(Ptot, Og, g.group, T, span, Cg);
   if (!pl.ok) fatal("window convolution: no tile plan for this layer (forward)");
   const CUtensorMap tmA = tc_make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, (uint32_t)pl.box_rows, false);
-  const CUtensorMap tmB = tc_make_tmap(wf, (uint64_t)kp, (uint64_t)g.Cout, (uint64_t)kp * 4, (uint32_t)pl.n_mma, false);
+  const CUtensorMap tmB = tc_make_tmap(wf, (uint64_t)kp, (uint64_t)g.Cout, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - (g.ph * f.Wp + g.pw), pl.MT, pl.n_mma, slots / 32, Cg, slots, Cg, Og,
-            pl.box_rows, pl.nbox, pl.nstage};
+            pl.box_rows, pl.nbox, pl.nstage, nullptr};
   WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp)};
   launch_window(s, tmA, tmB, a, ep, pl, Og, g.group);
 }
@@ -269,9 +435,9 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
   const WinPlan pl = plan_window(Ptot, Cg, g.group, T, span, Og);
   if (!pl.ok) fatal("window convolution: no tile plan for this layer (backward data)");
   const CUtensorMap tmA = tc_make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, (uint32_t)pl.box_rows, false);
-  const CUtensorMap tmB = tc_make_tmap(wt, (uint64_t)kp, (uint64_t)g.C, (uint64_t)kp * 4, (uint32_t)pl.n_mma, false);
+  const CUtensorMap tmB = tc_make_tmap(wt, (uint64_t)kp, (uint64_t)g.C, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - ((g.kh - 1 - g.ph) * f.Wp + (g.kw - 1 - g.pw)), pl.MT, pl.n_mma, slots / 32, Og, slots,
-            Og, Cg, pl.box_rows, pl.nbox, pl.nstage};
+            Og, Cg, pl.box_rows, pl.nbox, pl.nstage, nullptr};
   WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp)};
   launch_window(s, tmA, tmB, a, ep, pl, Cg, g.group);
 }

@@ -54,6 +54,8 @@ void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const f
 void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
 bool tcw_supported(const ConvGeom& g);
 void tcw_set_debug(int what, int value);
+int tcw_read_stamps(long long* out, int max_ctas);
+float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int ctas, float* issue_only);
 void tc_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w_tf32, const float* bias, float* y, bool relu);
 void tc_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w_tf32, float* dx);
 void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);

@@ -15,6 +15,7 @@ from sparknet_b200.layers import gaussian
 from sparknet_b200.library import load_library
 oracle = load_oracle(); product = load_library()
 product.sparknet_debug_set(1, int(os.environ.get("MT", "0")))
+product.sparknet_debug_set(3, int(os.environ.get("CG", "0")))
 shape, nout, kw = eval(os.environ["CASE"])
 x = np.random.default_rng(1).standard_normal(shape).astype(np.float32)
 l = conv_layer("conv", "data", nout, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5), **kw)
@@ -28,10 +29,10 @@ CASES = [
     "((6, 256, 13, 13), 384, dict(kernel_size=[3], pad=[1]))",
     "((2, 16, 6, 6), 16, dict(kernel_size=[1]))",
 ]
-for bo in ["0"]:
+for bo in (os.environ.get("CGS") or "1 2").split():
     for mt in (os.environ.get("MTS") or "0 1").split():
         for case in CASES:
-            print("bo", bo, "mt", mt, case, flush=True)
-            env = dict(os.environ, SPARKNET_CONV_FLAT="7", SPARKNET_FLAT_BO=bo, MT=mt, CASE=case)
+            print("cg", bo, "mt", mt, case, flush=True)
+            env = dict(os.environ, SPARKNET_CONV_FLAT="7", CG=bo, MT=mt, CASE=case)
             p = subprocess.run([sys.executable, "-c", CHILD], env=env, capture_output=True, text=True, timeout=300)
             print(p.stdout[-600:], p.stderr[-400:] if p.returncode else "", flush=True)
