@@ -442,4 +442,243 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
   launch_window(s, tmA, tmB, a, ep, pl, Cg, g.group);
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Backward-filter on the flat grid:  dW[co][c][tap] = sum_q dyflat[q][co] * xflat[q + shift(tap) - pad][c].
+// The reduction runs over grid positions q, 32 per chunk.  A = top-gradient tile (32 q x 128 co, MN-major), B = the
+// rows [q0 + shift(t0) - pad, + 32 + span) of the packed input for n_mma channels (MN-major, one TMA box per 32
+// channels): the taps t0 .. t0 + nt - 1 of one CTA read it through descriptors whose start advances by
+// (shift(t) - shift(t0)) rows, each tap into its own accumulator (nt * n_mma <= 512 TMEM columns).  One load of the
+// top-gradient tile therefore serves nt taps (the chunk-per-tap kernel re-read it for every 256 / slots taps and
+// re-read the input rows for every tap).  Slices of the reduction go to the workspace as [slice][co][tap][c] and
+// wgrad_reduce_kernel sums them in slice order into dW's (co, c, tap) layout: deterministic, no atomics.
+// ------------------------------------------------------------------------------------------
+struct WgArgs {
+  int Ptot_chunks;          // number of 32-row chunks of the reduction
+  int chunks_per_split;
+  int Wp, kw, T;
+  int nt, n_groups_t;       // taps per CTA, number of tap groups
+  int m_tiles, n_tiles, n_mma, nblk;      // 128-row tiles of Og, channel tiles of Cg (n_mma wide, nblk = ceil(n_mma / 32) boxes)
+  int Og, Cg;
+  int lead, pad_off;        // leading zero rows of the packed tensors; ph * Wp + pw
+  int KR;                   // rows of one input window (multiple of 8)
+  int nstage;
+  float* ws;                // [split][Cout][T][Cg]
+  size_t split_stride;      // Cout * T * Cg
+};
+
+__global__ void __launch_bounds__(kWThreads, 1)
+wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_constant__ CUtensorMap tmX, const WgArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ uint64_t full[kWMaxStages], empty[kWMaxStages], tmem_full;
+  __shared__ uint32_t tmem_base_smem;
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  // work item: (group, m tile, n tile, tap group)
+  int w = blockIdx.x;
+  const int tg = w % a.n_groups_t; w /= a.n_groups_t;
+  const int nti = w % a.n_tiles; w /= a.n_tiles;
+  const int mti = w % a.m_tiles; w /= a.m_tiles;
+  const int grp = w;
+  const int t0 = tg * a.nt, nt = min(a.nt, a.T - t0);
+  const int m0 = mti * 128, n0 = nti * a.n_mma;
+  const int kc_begin = blockIdx.y * a.chunks_per_split, kc_end = min(a.Ptot_chunks, kc_begin + a.chunks_per_split);
+  const int nchunks = max(kc_end - kc_begin, 0);
+
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+  const uint32_t a_bytes = 4u * 4096u, blk_bytes = (uint32_t)a.KR * 128u, b_bytes = (uint32_t)a.nblk * blk_bytes;
+  const uint32_t stage_bytes = a_bytes + b_bytes;                          // multiple of 1024 (KR % 8 == 0)
+
+  if (tid == 0) {
+    for (int i = 0; i < a.nstage; ++i) { mbar_init(&full[i], 1u); mbar_init(&empty[i], 1u); }
+    mbar_init(&tmem_full, 1u);
+    fence_barrier_init();
+    tma_prefetch_desc(&tmDY);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == kWEpiWarps) tmem_alloc<512>(&tmem_base_smem);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_smem;
+  const int sh0 = (t0 / a.kw) * a.Wp + t0 % a.kw;                          // row shift of the group's first tap
+
+  if (warp < kWEpiWarps) {
+    // ---------------- epilogue: TMEM -> workspace slice [co][tap][c] ----------------
+    if (nchunks > 0) {
+      mbar_wait(&tmem_full, 0);
+      tc_fence_after_sync();
+    }
+    const int quarter = warp & 3, half = warp >> 2;
+    const int row = m0 + 32 * quarter + lane;                              // output channel within the group
+    const int ncols = min(a.n_mma, a.Cg - n0);
+    const bool live = row < a.Og;                                          // the TMEM loads are warp-collective: every lane runs them
+    float* dst_row = a.ws + (size_t)blockIdx.y * a.split_stride + (size_t)(grp * a.Og + (live ? row : 0)) * a.T * a.Cg + n0;
+    for (int ts = 0; ts < nt; ++ts) {
+      float* dst = dst_row + (size_t)(t0 + ts) * a.Cg;
+      for (int c0 = 16 * half; c0 < ncols; c0 += 32) {
+        uint32_t v[16];
+        if (nchunks > 0) {
+          tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(ts * a.n_mma + c0), v);
+          tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = 0u;
+        }
+        if (live) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            *(float4*)(dst + c0 + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+        }
+      }
+    }
+  } else if (warp == kWEpiWarps) {
+    // ---------------- MMA issuer ----------------
+    const uint32_t idesc = make_idesc_tf32(128, a.n_mma, 1, 1);
+    // MN-major descriptors: A blocks (32 co) are 4096 B apart, B blocks (32 c) KR * 128 B apart; 4-row atoms 512 B apart
+    const uint32_t a_hi = (uint32_t)(make_smem_desc(0, 4096, 512, kLayoutSW128Base32) >> 32);
+    const uint32_t a_lo_flags = (4096u >> 4) << 16, b_lo_flags = (blk_bytes >> 4) << 16;
+    int s = 0;
+    uint32_t phase = 0;
+    for (int kc = 0; kc < nchunks; ++kc) {
+      mbar_wait(&full[s], phase);
+      tc_fence_after_sync();
+      if (elect_one_sync()) {
+        const uint32_t a_addr = smem_u32(smem) + (uint32_t)s * stage_bytes, b_addr = a_addr + a_bytes;
+        int ky = t0 / a.kw, kx = t0 % a.kw;
+        for (int ts = 0; ts < nt; ++ts) {
+          const uint32_t shift = (uint32_t)(ky * a.Wp + kx - sh0);
+          const uint32_t a_lo = (a_addr >> 4) | a_lo_flags, b_lo = ((b_addr + shift * 128u) >> 4) | b_lo_flags;
+          const uint32_t d = tmem_base + (uint32_t)(ts * a.n_mma);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) mma_tf32_lohi(d, a_lo + 64u * j, b_lo + 64u * j, a_hi, idesc, (kc | j) != 0 ? 1u : 0u);
+          if (++kx == a.kw) { kx = 0; ++ky; }
+        }
+        mma_commit(&empty[s]);
+        if (kc == nchunks - 1) mma_commit(&tmem_full);
+      }
+      __syncwarp();
+      if (++s == a.nstage) { s = 0; phase ^= 1u; }
+    }
+  } else {
+    // ---------------- TMA issuer ----------------
+    if (lane == 0) {
+      int s = 0;
+      uint32_t phase = 0;
+      const int a_chan = grp * a.Og + m0, b_chan = grp * a.Cg + n0;
+      for (int kc = 0; kc < nchunks; ++kc) {
+        const int q0 = (kc_begin + kc) * 32;
+        mbar_wait(&empty[s], phase ^ 1u);
+        uint8_t* a_tile = smem + (size_t)s * stage_bytes;
+        uint8_t* b_tile = a_tile + a_bytes;
+        mbar_arrive_expect_tx(&full[s], stage_bytes);
+        for (int i = 0; i < 4; ++i) tma_load_2d(a_tile + i * 4096, &tmDY, &full[s], a_chan + 32 * i, a.lead + q0);
+        for (int j = 0; j < a.nblk; ++j)
+          tma_load_2d(b_tile + (size_t)j * blk_bytes, &tmX, &full[s], b_chan + 32 * j, a.lead + q0 + sh0 - a.pad_off);
+        if (++s == a.nstage) { s = 0; phase ^= 1u; }
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == kWEpiWarps) tmem_dealloc<512>(tmem_base);
+}
+
+// dw[(co, c, tap)] (+)= sum over slices of ws[slice][(co, tap, c)], slices in ascending order
+__global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
+                                    int accumulate) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < split_stride; i += (size_t)gridDim.x * blockDim.x) {
+    // i walks the workspace layout (co, tap, c): coalesced reads
+    const size_t co = i / ((size_t)T * Cg);
+    const int rem = (int)(i - co * (size_t)T * Cg), tap = rem / Cg, c = rem - tap * Cg;
+    float acc = ws[i];
+    for (int z = 1; z < splits; ++z) acc += ws[(size_t)z * split_stride + i];
+    float* p = dw + (co * Cg + c) * T + tap;
+    *p = accumulate ? *p + acc : acc;
+  }
+}
+
+struct WgPlan { int n_mma, nt, KR, nstage, splits, chunks_per_split; size_t smem; bool ok; };
+static int span_of_taps(int t0, int nt, int kw, int Wp) {
+  const int t1 = t0 + nt - 1;
+  return (t1 / kw) * Wp + t1 % kw - ((t0 / kw) * Wp + t0 % kw);
+}
+static WgPlan plan_wgrad(int Ptot, int Og, int Cg, int groups, int T, int kw, int Wp) {
+  WgPlan best{};
+  best.ok = false;
+  double best_cost = 0;
+  const int chunks = (Ptot + 31) / 32, m_tiles = (Og + 127) / 128;
+  for (int n_tiles = 1; n_tiles <= 16; ++n_tiles) {
+    int n_mma = ((Cg + n_tiles - 1) / n_tiles + 15) / 16 * 16;
+    if (n_mma > 256) continue;
+    if (n_tiles > 1 && n_mma * (n_tiles - 1) >= Cg) continue;          // an empty last tile
+    const int nt_max = 512 / n_mma < T ? 512 / n_mma : T;
+    const int n_groups_t = (T + nt_max - 1) / nt_max, nt = (T + n_groups_t - 1) / n_groups_t;
+    int span = 0;
+    for (int t0 = 0; t0 < T; t0 += nt) { const int sp = span_of_taps(t0, nt < T - t0 ? nt : T - t0, kw, Wp); if (sp > span) span = sp; }
+    const int KR = (32 + span + 7) / 8 * 8;
+    if (KR > 256) continue;
+    const int nblk = (n_mma + 31) / 32;
+    const size_t stage = 16384 + (size_t)nblk * KR * 128;
+    if (3 * stage + 2048 > kWSmemLimit) continue;
+    int nstage = (int)((kWSmemLimit - 2048) / stage);
+    if (nstage > kWMaxStages) nstage = kWMaxStages;
+    const long long tiles = (long long)m_tiles * n_tiles * n_groups_t * groups;
+    int splits = (int)(148 / tiles);
+    if (splits < 1) splits = 1;
+    if (splits > chunks / 8) splits = chunks / 8 > 0 ? chunks / 8 : 1;
+    const int cps = (chunks + splits - 1) / splits;
+    splits = (chunks + cps - 1) / cps;
+    const long long waves = (tiles * splits + 147) / 148;
+    const double mma_clk = nt * 4.0 * (n_mma / 2.0 > 44.0 ? n_mma / 2.0 : 44.0);
+    const double l2_clk = (double)stage / 25.0;
+    const double per_chunk = mma_clk > l2_clk ? mma_clk : l2_clk;
+    const double cost = (double)waves * (cps * per_chunk + 128.0 * nt * n_mma * 4 / 30.0 + 5000.0);
+    if (!best.ok || cost < best_cost) {
+      best = WgPlan{n_mma, nt, KR, nstage, splits, cps, (size_t)nstage * stage + 1024, true};
+      best_cost = cost;
+    }
+  }
+  return best;
+}
+
+bool tcw_wgrad_supported(const ConvGeom& g) {
+  if (!tc_flat_supported(g)) return false;
+  const FlatGeom f = tc_flat_geom(g);
+  return plan_wgrad(g.N * f.Gp, g.Og(), g.Cg(), g.group, g.kh * g.kw, g.kw, f.Wp).ok;
+}
+
+void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate) {
+  const FlatGeom f = tc_flat_geom(g);
+  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Ptot = g.N * f.Gp;
+  const WgPlan pl = plan_wgrad(Ptot, Og, Cg, g.group, T, g.kw, f.Wp);
+  if (!pl.ok) fatal("window convolution: no tile plan for this layer (backward filter)");
+  static bool attr_done = false;
+  if (!attr_done) {
+    SN_CUDA(cudaFuncSetAttribute(wgrad_window_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemLimit - 1024));
+    attr_done = true;
+  }
+  WgArgs a;
+  a.Ptot_chunks = (Ptot + 31) / 32;
+  a.chunks_per_split = pl.chunks_per_split;
+  a.Wp = f.Wp; a.kw = g.kw; a.T = T;
+  a.nt = pl.nt; a.n_groups_t = (T + pl.nt - 1) / pl.nt;
+  a.m_tiles = (Og + 127) / 128;
+  a.n_mma = pl.n_mma; a.n_tiles = (Cg + pl.n_mma - 1) / pl.n_mma; a.nblk = (pl.n_mma + 31) / 32;
+  a.Og = Og; a.Cg = Cg;
+  a.lead = f.lead; a.pad_off = g.ph * f.Wp + g.pw;
+  a.KR = pl.KR; a.nstage = pl.nstage;
+  a.split_stride = (size_t)g.Cout * T * Cg;
+  a.ws = get_workspace((size_t)pl.splits * a.split_stride);
+  const CUtensorMap tmDY = tc_make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, 32, true);
+  const CUtensorMap tmX = tc_make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, (uint32_t)pl.KR, true);
+  dim3 grid(a.m_tiles * a.n_tiles * a.n_groups_t * g.group, pl.splits, 1);
+  wgrad_window_kernel<<<grid, kWThreads, pl.smem, s>>>(tmDY, tmX, a);
+  int blocks = (int)((a.split_stride + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  wgrad_reduce_kernel<<<blocks, 256, 0, s>>>(a.ws, pl.splits, a.split_stride, T, Cg, dw, accumulate ? 1 : 0);
+  count_launch(2);
+  SN_CUDA(cudaGetLastError());
+}
+
 }  // namespace sn

@@ -53,6 +53,8 @@ void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, c
 void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
 void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
 bool tcw_supported(const ConvGeom& g);
+bool tcw_wgrad_supported(const ConvGeom& g);
+void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
 void tcw_set_debug(int what, int value);
 int tcw_read_stamps(long long* out, int max_ctas);
 float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int ctas, float* issue_only);

@@ -419,7 +419,8 @@ struct ConvolutionLayer : Layer {
     if (param_propagate_down[0]) {
       const float* x = bottom[0]->data->gpu();
       float* dw = blobs[0]->diff->mutable_gpu();
-      if (flat_w) tc_conv_wgrad_flat(S(), g, packed_input(bottom[0]), dyflat, dw, acc);
+      if (flat_w && use_window() && tcw_wgrad_supported(g)) tcw_conv_wgrad(S(), g, packed_input(bottom[0]), dyflat, dw, acc);
+      else if (flat_w) tc_conv_wgrad_flat(S(), g, packed_input(bottom[0]), dyflat, dw, acc);
       else if (net->precision == PREC_TF32) tc_conv_wgrad(S(), g, x, dy, dw, acc);
       else ffma_conv_wgrad(S(), g, x, dy, dw, acc);
     }
