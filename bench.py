@@ -236,6 +236,7 @@ def main():
     precision = lib.sparknet_get_precision(st)
     imgs, labs = synthetic_pool(name, batch, args.pool, 1701 + rank)
     src = MinibatchSource(imgs, labs)
+    net.copy_threads = max(1, min(8, (os.cpu_count() or 1) // max(1, world)))   # host threads of the data callback's copy
     net.setTrainData(src)
     averager = Averager(lib, net, rank, world)
     averager.broadcast_from_rank0()                     # all replicas start from the same weights (CifarApp.scala:92-99)
@@ -319,10 +320,12 @@ def main():
     line = {"metric": f"{name}_train_images_per_sec", "value": value, "unit": "images/s", "n_gpus": args.gpus,
             "steps": steps, "warmup": warmup, "ms_per_step": ms / steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "tf32" if precision == 1 else "f32", "data": "synthetic", "config": config,
-            "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 0,
+            "e2e": {"value": e2e, "unit": "images/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                     "ms_per_step": e2e_ms / steps,
-                    "note": "solver_step through the C ABI with Python data callbacks filling the library's pinned buffers; "
-                            "the loss stays on the device (read only on request), so no D2H per step"},
+                    "host_copy_threads": net.copy_threads,
+                    "note": "solver_step through the C ABI; Python data callbacks copy every minibatch from pageable host memory into "
+                            "the library's pinned buffers (sparknet_host_copy), H2D on the copy stream, and every iteration's loss "
+                            "is copied back to a pinned host ring (4 bytes, asynchronous)"},
             "gpu_launches": int(launches), "clocks": clk,
             "averaging": {"rounds": n_rounds, "ms_per_round": avg_ms / n_rounds, "share_of_round": avg_ms / ms if ms else None,
                           "method": averager.method},

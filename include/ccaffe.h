@@ -109,6 +109,9 @@ int sparknet_get_iter(caffenet_state* state);
 float sparknet_last_loss(caffenet_state* state);
 /* Copies the losses of the last n solver iterations (oldest first) kept on the device; returns count. */
 int sparknet_get_loss_history(caffenet_state* state, float* out, int n);
+/* memcpy on `threads` host threads, for data callbacks that fill the library's pinned staging buffer (no reference
+ * counterpart: the JVM callback of Net.scala:194-221 copies element by element). */
+void sparknet_host_copy(void* dst, const void* src, long bytes, int threads);
 /* Make Dropout layer `layer_idx` of the train net use `mask` (count values, 0 = drop, non-zero = keep)
  * instead of drawing one; NULL restores drawing.  0 ok, -1 bad index, -2 not Dropout, -3 bad count. */
 int sparknet_inject_dropout_mask(caffenet_state* state, int layer_idx, const unsigned* mask, int count);

@@ -681,4 +681,106 @@ void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const
   SN_CUDA(cudaGetLastError());
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Strided convolutions (AlexNet conv1: 11x11, stride 4) through the same window kernels: with s x s pixel blocks
+// folded into channels ("space to depth"), a stride-s convolution with a k x k filter IS a stride-1 convolution
+// with a ceil(k/s) x ceil(k/s) filter over C*s*s channels on the H/s x W/s grid:
+//   y[n][co][ho][wo] = sum_{ky',kx'} sum_{c,dy,dx} xs[n][ho+ky'][wo+kx'][(c,dy,dx)] * w[co][c][s*ky'+dy][s*kx'+dx]
+// (filter taps beyond k are zero).  conv1: 3 -> 48 channels, 11x11 -> 3x3, 227 -> 57, reduction 363 -> 432.
+// ------------------------------------------------------------------------------------------
+bool tcw_s2d_supported(const ConvGeom& g) {
+  if (g.sh != g.sw || g.sh < 2 || g.sh > 8 || g.ph != 0 || g.pw != 0 || g.group != 1) return false;
+  if ((g.C * g.sh * g.sw) % 16 != 0 || g.C * g.sh * g.sw > 256 || g.Cout % 16 != 0) return false;
+  const ConvGeom e = tcw_s2d_geom(g);
+  return tcw_supported(e) && tcw_wgrad_supported(e);
+}
+ConvGeom tcw_s2d_geom(const ConvGeom& g) {
+  ConvGeom e = g;
+  const int s = g.sh;
+  e.C = g.C * s * s;
+  e.H = (g.H + s - 1) / s; e.W = (g.W + s - 1) / s;
+  e.kh = (g.kh + s - 1) / s; e.kw = (g.kw + s - 1) / s;
+  e.sh = e.sw = 1; e.ph = e.pw = 0;
+  // every output the strided layer has must exist on the folded grid: Ho <= H' - kh' + 1
+  e.Ho = g.Ho; e.Wo = g.Wo;
+  if (e.H - e.kh + 1 < g.Ho) e.H = g.Ho + e.kh - 1;
+  if (e.W - e.kw + 1 < g.Wo) e.W = g.Wo + e.kw - 1;
+  return e;
+}
+// one block per (image, folded row): s*C image rows in, W' positions x C*s*s channels out (contiguous)
+__global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__ x, float* __restrict__ dst, int C, int H, int W, int s,
+                                                        int Hs, int Ws, int Wp, int Gp, int lead) {
+  extern __shared__ float rows[];                      // [C*s][Ws*s]
+  const int hs = blockIdx.x, n = blockIdx.y, Wpad = Ws * s, nrows = C * s;
+  for (int i = threadIdx.x; i < nrows * Wpad; i += blockDim.x) {
+    const int r = i / Wpad, w = i - r * Wpad, c = r / s, dy = r - c * s, h = hs * s + dy;
+    rows[i] = (h < H && w < W) ? x[(((size_t)n * C + c) * H + h) * W + w] : 0.f;
+  }
+  __syncthreads();
+  const int Cs = C * s * s;
+  float* out = dst + ((size_t)lead + (size_t)n * Gp + (size_t)hs * Wp) * Cs;
+  for (int i = threadIdx.x; i < Ws * Cs; i += blockDim.x) {
+    const int ws = i / Cs, ch = i - ws * Cs, dx = ch % s, r = ch / s;          // r = c*s + dy
+    out[i] = to_tf32_exact(rows[r * Wpad + ws * s + dx]);
+  }
+}
+void tcw_s2d_pack_input(cudaStream_t st, const ConvGeom& g, const float* x, float* xflat) {
+  const ConvGeom e = tcw_s2d_geom(g);
+  const FlatGeom f = tc_flat_geom(e);
+  const int s = g.sh, Hs = (g.H + s - 1) / s, Ws = (g.W + s - 1) / s;
+  const size_t smem = (size_t)g.C * s * Ws * s * sizeof(float);
+  static size_t attr = 48 * 1024;
+  if (smem > attr) { SN_CUDA(cudaFuncSetAttribute(s2d_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = smem; }
+  s2d_pack_kernel<<<dim3(Hs, g.N), 256, smem, st>>>(x, xflat, g.C, g.H, g.W, s, Hs, Ws, f.Wp, f.Gp, f.lead);
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
+// wf[co][tap'][slot]: slot = (c*s + dy)*s + dx < C*s*s holds w[co][c][s*ky'+dy][s*kx'+dx] (0 beyond the filter), tf32-rounded
+__global__ void s2d_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ wf, int Cout, int C, int kh, int kw, int s, int khs,
+                                       int kws, int slots) {
+  const size_t total = (size_t)Cout * khs * kws * slots;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int slot = (int)(i % slots);
+    size_t r = i / slots;
+    const int tap = (int)(r % (khs * kws)), co = (int)(r / (khs * kws));
+    float v = 0.f;
+    if (slot < C * s * s) {
+      const int dx = slot % s, dy = (slot / s) % s, c = slot / (s * s), ky = s * (tap / kws) + dy, kx = s * (tap % kws) + dx;
+      if (ky < kh && kx < kw) v = w[(((size_t)co * C + c) * kh + ky) * kw + kx];
+    }
+    wf[i] = to_tf32_exact(v);
+  }
+}
+void tcw_s2d_pack_filter(cudaStream_t st, const ConvGeom& g, const float* w, float* wf) {
+  const ConvGeom e = tcw_s2d_geom(g);
+  const int slots = slots_of(e.C);
+  const size_t total = (size_t)g.Cout * e.kh * e.kw * slots;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  s2d_pack_filter_kernel<<<blocks, 256, 0, st>>>(w, wf, g.Cout, g.C, g.kh, g.kw, g.sh, e.kh, e.kw, slots);
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
+// dw[co][c][ky][kx] (+)= dws[co][(c,dy,dx)][tap']  (the folded filter gradient, layout of tcw_conv_wgrad's output)
+__global__ void s2d_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int kh, int kw, int s, int khs,
+                                        int kws, int accumulate) {
+  const size_t total = (size_t)Cout * C * kh * kw;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const int kx = (int)(i % kw), ky = (int)((i / kw) % kh), c = (int)((i / ((size_t)kw * kh)) % C), co = (int)(i / ((size_t)kw * kh * C));
+    const int ch = (c * s + ky % s) * s + kx % s, tap = (ky / s) * kws + kx / s;
+    const float v = dws[((size_t)co * C * s * s + ch) * (khs * kws) + tap];
+    dw[i] = accumulate ? dw[i] + v : v;
+  }
+}
+void tcw_s2d_unpack_wgrad(cudaStream_t st, const ConvGeom& g, const float* dws, float* dw, bool accumulate) {
+  const ConvGeom e = tcw_s2d_geom(g);
+  const size_t total = (size_t)g.Cout * g.C * g.kh * g.kw;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  s2d_unpack_wgrad_kernel<<<blocks, 256, 0, st>>>(dws, dw, g.Cout, g.C, g.kh, g.kw, g.sh, e.kh, e.kw, accumulate ? 1 : 0);
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
+
 }  // namespace sn

@@ -931,32 +931,70 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
   return dgrad ? (size_t)g.C * flat_slots(g.Og()) * g.kh * g.kw : (size_t)g.Cout * flat_slots(g.Cg()) * g.kh * g.kw;
 }
 
-// NCHW -> grid rows x channels (32 x 32 transposes through shared memory).  grid (pixel blocks, channel blocks, N)
-__global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, int C, int H, int W,
-                                                         int Wp, int Gp, int lead) {
+// NCHW -> grid rows x channels (32 x 32 transposes through shared memory).  One block owns 32 channels of one image
+// and walks its pixels; with BIAS it also sums every value it reads per channel (the bias gradient of this image,
+// conv_layer.cpp:52-55: gemv against the all-ones multiplier) into part[c][n], which bias_grad_final_kernel adds up
+// in image order.  The top gradient is therefore read from HBM once for both purposes.
+template <bool BIAS>
+__global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
+                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW) {
   __shared__ float tile[32][33];
-  const int HW = H * W, p0 = blockIdx.x * 32, c0 = blockIdx.y * 32, n = blockIdx.z;
+  const int HW = H * W, c0 = blockIdx.x * 32, n = blockIdx.y;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  for (int j = ty; j < 32; j += 8) {
-    const int c = c0 + j, p = p0 + tx;
-    tile[j][tx] = (c < C && p < HW) ? src[((size_t)n * C + c) * HW + p] : 0.f;
+  const float* sp = src + ((size_t)n * C + c0) * HW;
+  float* dp = dst + ((size_t)lead + (size_t)n * Gp) * C + c0 + tx;
+  float bsum[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int p0 = 0; p0 < HW; p0 += 32) {
+    const int p = p0 + tx;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int j = ty + 8 * k;
+      const float v = (c0 + j < C && p < HW) ? sp[(size_t)j * HW + p] : 0.f;
+      tile[j][tx] = v;
+      if (BIAS) bsum[k] += v;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int q = p0 + ty + 8 * k;
+      if (q < HW && c0 + tx < C) {
+        uint32_t h, w;
+        dW.divmod((uint32_t)q, h, w);
+        dp[(size_t)(h * Wp + w) * C] = to_tf32_exact(tile[tx][ty + 8 * k]);
+      }
+    }
+    __syncthreads();
   }
-  __syncthreads();
-  for (int j = ty; j < 32; j += 8) {
-    const int p = p0 + j, c = c0 + tx;
-    if (p < HW && c < C) {
-      const int h = p / W, w = p - h * W;
-      dst[((size_t)lead + (size_t)n * Gp + h * Wp + w) * C + c] = to_tf32_exact(tile[tx][j]);
+  if (BIAS) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float v = bsum[k];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (tx == 0 && c0 + ty + 8 * k < C) part[(size_t)(c0 + ty + 8 * k) * N + n] = v;
     }
   }
 }
-void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst) {
+__global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float t = 0.f;
+  for (int s = 0; s < S; ++s) t += part[(size_t)c * S + s];
+  db[c] = accumulate ? db[c] + t : t;
+}
+// db (nullable): bias gradient, summed here when the packed tensor is the top gradient
+void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db, bool accumulate) {
   const int C = output_side ? g.Cout : g.C, H = output_side ? g.Ho : g.H, W = output_side ? g.Wo : g.W;
   const FlatGeom f = tc_flat_geom(g);
-  const int Wp = f.Wp, Gp = f.Gp;
-  dim3 grid((H * W + 31) / 32, (C + 31) / 32, g.N);
-  flat_pack_kernel<<<grid, 256, 0, s>>>(src, dst, C, H, W, Wp, Gp, flat_lead(g));
-  count_launch();
+  dim3 grid((C + 31) / 32, g.N);
+  if (db) {
+    float* part = get_workspace((size_t)C * g.N);
+    flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W));
+    bias_grad_final_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, g.N, part, db, accumulate ? 1 : 0);
+    count_launch(2);
+  } else {
+    flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W));
+    count_launch();
+  }
   SN_CUDA(cudaGetLastError());
 }
 // dst[row][tap*slots + ch]: fwd   (dgrad = 0): row = co (all groups), ch = c in group,  value W[co][c][tap]

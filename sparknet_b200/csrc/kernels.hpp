@@ -44,7 +44,8 @@ struct FlatGeom { int Wp, Hp, Gp, lead, bw, bh; };                    // cell wi
 FlatGeom tc_flat_geom(const ConvGeom& g);
 size_t tc_flat_rows(const ConvGeom& g);                                // grid rows of a packed tensor (x channels = floats)
 size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad);
-void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst);   // dst zeroed once by the owner
+// dst zeroed once by the owner; db (nullable) = bias gradient summed in the same pass over the top gradient
+void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db = nullptr, bool accumulate = false);
 void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst);
 void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
 void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
@@ -55,6 +56,12 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
 bool tcw_supported(const ConvGeom& g);
 bool tcw_wgrad_supported(const ConvGeom& g);
 void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
+// strided layers folded to stride 1 ("space to depth", conv_flat.cu): e = tcw_s2d_geom(g) is the equivalent stride-1 layer
+bool tcw_s2d_supported(const ConvGeom& g);
+ConvGeom tcw_s2d_geom(const ConvGeom& g);
+void tcw_s2d_pack_input(cudaStream_t s, const ConvGeom& g, const float* x, float* xflat);
+void tcw_s2d_pack_filter(cudaStream_t s, const ConvGeom& g, const float* w, float* wf);
+void tcw_s2d_unpack_wgrad(cudaStream_t s, const ConvGeom& g, const float* dws, float* dw, bool accumulate);
 void tcw_set_debug(int what, int value);
 int tcw_read_stamps(long long* out, int max_ctas);
 float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int ctas, float* issue_only);

@@ -9,6 +9,7 @@
 #include <cstring>
 #include <random>
 #include <sstream>
+#include <thread>
 
 namespace sn {
 
@@ -258,6 +259,7 @@ struct JavaDataLayer : Layer {
     if (pool) {                                   // resident inputs: no callback, no copy
       st->dev = pool + (size_t)(pool_i % pool_n) * count;
       st->head = Storage::AT_DEVICE;
+      ++st->gen;                                  // new contents: consumers that cache a repacked copy must redo it
       ++pool_i;
       return;
     }
@@ -274,6 +276,7 @@ struct JavaDataLayer : Layer {
     SN_CUDA(cudaStreamWaitEvent(c.compute, h2d_done[p], 0));
     st->dev = devbuf[p];
     st->head = Storage::AT_DEVICE;
+    ++st->gen;
     parity = q;
   }
   void backward(const vector<Blob*>&, const vector<bool>&, const vector<Blob*>&) override {}
@@ -346,7 +349,9 @@ struct ConvolutionLayer : Layer {
     const float* x = bottom[0]->data->gpu();
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
-    if (net->precision == PREC_TF32 && use_flat(1)) {
+    if (net->precision == PREC_TF32 && use_s2d()) {
+      tcw_conv_fwd(S(), gs, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
+    } else if (net->precision == PREC_TF32 && use_flat(1)) {
       if (use_window()) tcw_conv_fwd(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
       else tc_conv_fwd_flat(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
     } else if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, weights_tf32(), b, y, fuse_relu);
@@ -374,18 +379,32 @@ struct ConvolutionLayer : Layer {
     }
     return window_ok != 0;
   }
+  // strided layers folded to stride 1 (space to depth): gs is the equivalent stride-1 layer the window kernels run
+  ConvGeom gs;
+  int s2d_ok = -1;
+  float* dws = nullptr;                               // filter gradient in the folded layout
+  bool use_s2d() {
+    if (s2d_ok < 0) {
+      const char* e = getenv("SPARKNET_CONV_S2D");
+      s2d_ok = (tcw_s2d_supported(g) && !(e && atoi(e) == 0)) ? 1 : 0;
+      if (s2d_ok) gs = tcw_s2d_geom(g);
+    }
+    return s2d_ok != 0;
+  }
+  const ConvGeom& fg() { return use_s2d() ? gs : g; } // geometry of the flat grid in use
   float* flat_alloc(int channels) {
     float* p = nullptr;
-    const size_t bytes = (size_t)channels * tc_flat_rows(g) * sizeof(float);
+    const size_t bytes = (size_t)channels * tc_flat_rows(fg()) * sizeof(float);
     SN_CUDA(cudaMalloc(&p, bytes));
     SN_CUDA(cudaMemsetAsync(p, 0, bytes, S()));      // the bands between images stay zero for good
     return p;
   }
   const float* packed_input(Blob* bottom) {
     const float* x = bottom->data->gpu();
-    if (!xflat) xflat = flat_alloc(g.C);
+    if (!xflat) xflat = flat_alloc(fg().C);
     if (xflat_src != bottom->data.get() || xflat_gen != bottom->data->gen) {
-      tc_flat_pack(S(), g, false, x, xflat);
+      if (use_s2d()) tcw_s2d_pack_input(S(), g, x, xflat);
+      else tc_flat_pack(S(), g, false, x, xflat);
       xflat_src = bottom->data.get();
       xflat_gen = bottom->data->gen;
     }
@@ -395,26 +414,39 @@ struct ConvolutionLayer : Layer {
     Storage* st = blobs[0]->data.get();
     const float* w = st->gpu();
     const int i = dgrad ? 1 : 0;
-    if (!wflat[i]) SN_CUDA(cudaMalloc(&wflat[i], tc_flat_filter_floats(g, dgrad) * sizeof(float)));
+    if (!wflat[i]) SN_CUDA(cudaMalloc(&wflat[i], tc_flat_filter_floats(fg(), dgrad) * sizeof(float)));
     if (wflat_gen[i] != st->gen) {
-      tc_flat_pack_filter(S(), g, dgrad, w, wflat[i]);
+      if (use_s2d()) tcw_s2d_pack_filter(S(), g, w, wflat[i]);
+      else tc_flat_pack_filter(S(), g, dgrad, w, wflat[i]);
       wflat_gen[i] = st->gen;
     }
     return wflat[i];
   }
   ~ConvolutionLayer() override {
-    cudaFree(xflat); cudaFree(dyflat); cudaFree(wflat[0]); cudaFree(wflat[1]);
+    cudaFree(xflat); cudaFree(dyflat); cudaFree(wflat[0]); cudaFree(wflat[1]); cudaFree(dws);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     const float* dy = top[0]->diff->gpu();
     const bool acc = !net->overwrite_param_diffs;
-    if (bias_term && param_propagate_down[1])
-      conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
     const bool tf32 = net->precision == PREC_TF32;
     const bool flat_w = tf32 && use_flat(2) && param_propagate_down[0], flat_d = tf32 && use_flat(4) && pd[0];
+    const bool want_db = bias_term && param_propagate_down[1];
+    if (tf32 && use_s2d() && param_propagate_down[0]) {
+      // folded layer: pack the top gradient on the folded grid (+ bias gradient), window backward-filter, unfold dW
+      if (!dyflat) dyflat = flat_alloc(gs.Cout);
+      tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
+      if (!dws) SN_CUDA(cudaMalloc(&dws, (size_t)gs.Cout * gs.C * gs.kh * gs.kw * sizeof(float)));
+      tcw_conv_wgrad(S(), gs, packed_input(bottom[0]), dyflat, dws, false);
+      tcw_s2d_unpack_wgrad(S(), g, dws, blobs[0]->diff->mutable_gpu(), acc);
+      if (pd[0]) tc_conv_dgrad(S(), g, dy, blobs[0]->data->gpu(), bottom[0]->diff->mutable_gpu());
+      return;
+    }
     if (flat_w || flat_d) {
       if (!dyflat) dyflat = flat_alloc(g.Cout);
-      tc_flat_pack(S(), g, true, dy, dyflat);
+      // one pass over the top gradient packs it and sums the bias gradient
+      tc_flat_pack(S(), g, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
+    } else if (want_db) {
+      conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
     }
     if (param_propagate_down[0]) {
       const float* x = bottom[0]->data->gpu();
@@ -1011,6 +1043,8 @@ Solver::Solver(const cp::SolverParameter& p) : param(p) {
   }
   SN_CUDA(cudaMalloc(&loss_hist, kLossHist * sizeof(float)));
   SN_CUDA(cudaMemset(loss_hist, 0, kLossHist * sizeof(float)));
+  SN_CUDA(cudaMallocHost(&loss_hist_host, kLossHist * sizeof(float)));
+  memset(loss_hist_host, 0, kLossHist * sizeof(float));
 }
 Solver::~Solver() {
   test_net.reset();
@@ -1018,6 +1052,7 @@ Solver::~Solver() {
   if (arena_h) cudaFree(arena_h);
   if (chunk_table) cudaFree(chunk_table);
   if (loss_hist) cudaFree(loss_hist);
+  if (loss_hist_host) cudaFreeHost(loss_hist_host);
 }
 float Solver::get_learning_rate() {   // sgd_solver.cpp:27-63, same expression types
   const string& pol = param.lr_policy;
@@ -1051,6 +1086,9 @@ void Solver::step(int iters) {
     const float rate = get_learning_rate();
     if (net->arena_floats) sgd_update(ctx().compute, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
     for (Blob* b : net->learnable_params) ++b->data->gen;    // weights changed on the device
+    // this iteration's loss goes to the pinned host ring too: 4 bytes, asynchronous, read after the caller's next sync
+    SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost,
+                            ctx().compute));
     ++iter;
   }
   net->overwrite_param_diffs = false;
@@ -1079,6 +1117,7 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
   const float rate = get_learning_rate();
   if (net->arena_floats) sgd_update(s, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
   SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L + 1)], s));
+  SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost, s));
   SN_CUDA(cudaStreamSynchronize(s));
   for (Blob* b : net->learnable_params) ++b->data->gen;
   ++iter;

@@ -155,6 +155,7 @@ struct Solver {
   float* arena_h = nullptr;             // momentum history, same layout as the net's arena
   SgdChunk* chunk_table = nullptr;      // device, one entry per 1024 floats
   float* loss_hist = nullptr;           // device ring of per-iteration losses
+  float* loss_hist_host = nullptr;      // pinned mirror: every iteration copies its loss here asynchronously (4 bytes D2H per step)
   static constexpr int kLossHist = 4096;
   float smoothed_loss = 0.f;
   explicit Solver(const cp::SolverParameter& p);

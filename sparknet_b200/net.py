@@ -72,6 +72,7 @@ class CaffeNet:
         self.dtypeSize = lib.get_dtype_size()
         self.intSize = lib.get_int_size()
         self.numTestBatches: Optional[int] = None
+        self.copy_threads = 1          # > 1: image callbacks copy with sparknet_host_copy on that many host threads
 
     # -- construction (object CaffeNet.apply, Net.scala:253-262) -----------------------------
     @classmethod
@@ -96,7 +97,11 @@ class CaffeNet:
             for i in range(num_dims):
                 size *= shape[i]
             assert batch.dtype == np.float32 and batch.size == batch_size * size
-            ctypes.memmove(data, batch.ctypes.data, batch.nbytes)
+            if self.copy_threads > 1 and batch.nbytes >= (1 << 22):
+                # large minibatch (CaffeNet: 158 MB): the product's multi-threaded host copy; the oracle has none
+                self.lib.sparknet_host_copy(data, batch.ctypes.data, batch.nbytes, self.copy_threads)
+            else:
+                ctypes.memmove(data, batch.ctypes.data, batch.nbytes)
         return java_callback_t(invoke)
 
     def _label_cb(self, src: MinibatchSource):                      # makeLabelCallback, Net.scala:223-233

@@ -54,6 +54,29 @@ def test_convolution_flat_grid_and_gather_paths_tf32(oracle, product, monkeypatc
         assert_close(a, b, TOL, f"param diff {j}")
 
 
+# strided, unpadded layers whose folded channel count C*s*s is a multiple of 16 run as stride-1 window convolutions on
+# the space-to-depth grid (csrc/conv_flat.cu); SPARKNET_CONV_S2D=0 keeps them on the gather kernels
+S2D_CASES = [
+    ((3, 3, 35, 39), 16, dict(kernel_size=[11], stride=[4])),                      # conv1-like, H and W not multiples of 4
+    ((2, 4, 17, 15), 32, dict(kernel_size=[5], stride=[2])),                       # stride 2, 4 -> 16 folded channels
+    ((5, 16, 12, 12), 48, dict(kernel_size=[2], stride=[2])),                      # filter == stride (1x1 after folding)
+    ((2, 1, 29, 29), 16, dict(kernel_size=[7], stride=[4])),                       # one input channel -> 16
+]
+
+
+@pytest.mark.parametrize("s2d", ["1", "0"])
+@pytest.mark.parametrize("shape,num_output,kw", S2D_CASES)
+def test_convolution_space_to_depth_tf32(oracle, product, monkeypatch, shape, num_output, kw, s2d):
+    monkeypatch.setenv("SPARKNET_CONV_S2D", s2d)
+    x = np.random.default_rng(78).standard_normal(shape).astype(F)
+    l = conv_layer("conv", "data", num_output, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5), **kw)
+    r = run_pair(oracle, product, {"data": x}, [l], "conv", "conv", precision=1)
+    assert_close(r["fwd"][0]["conv"], r["fwd"][1]["conv"], TOL, "top")
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["conv"])):
+        assert_close(a, b, TOL, f"param diff {j}")
+
+
 def test_convolution_relu_fusion_tf32(oracle, product):
     x = np.random.default_rng(5).standard_normal((2, 8, 9, 9)).astype(F)
     l = conv_layer("conv", "data", 16, kernel_size=[3], pad=[1], weight_filler=gaussian(0.1), bias_filler=gaussian(0.1))
