@@ -5,6 +5,7 @@
 // roofline.  Common rules: 128-bit accesses where the layout allows, grid = multiple of the SM
 // count with grid-stride loops, warp-shuffle reductions, no atomics on floating point (fixed
 // reduction order => run-to-run deterministic), IEEE arithmetic (no -use_fast_math).
+#include <algorithm>
 #include <cfloat>
 #include <cstdarg>
 #include <cstdio>
@@ -188,9 +189,45 @@ __global__ void pool_max_fwd_kernel(PoolGeom g, size_t total, const float* __res
     mask[idx] = bi;
   }
 }
+// Plane-per-CTA form: the input plane is staged in shared memory with linear, coalesced loads; every pooled
+// element then scans its window there (same scan order and strict '>' as above).  Global traffic is the algorithmic
+// 4*in + 8*out bytes; the strided window reads never leave the SM.
+__global__ void __launch_bounds__(256) pool_max_fwd_plane_kernel(PoolGeom g, FastDiv dPW, const float* __restrict__ x, float* __restrict__ y,
+                                                                 int* __restrict__ mask) {
+  extern __shared__ float sm_plane[];
+  const int HW = g.H * g.W, P = g.PH * g.PW;
+  for (size_t plane = blockIdx.x; plane < (size_t)g.N * g.C; plane += gridDim.x) {
+    const float* xp = x + plane * (size_t)HW;
+    for (int i = threadIdx.x; i < HW; i += blockDim.x) sm_plane[i] = xp[i];
+    __syncthreads();
+    for (int j = threadIdx.x; j < P; j += blockDim.x) {
+      uint32_t ph, pw;
+      dPW.divmod((uint32_t)j, ph, pw);
+      int hs = (int)ph * g.sh - g.ph, ws = (int)pw * g.sw - g.pw;
+      const int he = min(hs + g.kh, g.H), we = min(ws + g.kw, g.W);
+      hs = max(hs, 0); ws = max(ws, 0);
+      float best = -FLT_MAX;
+      int bi = -1;
+      for (int h = hs; h < he; ++h)
+        for (int w = ws; w < we; ++w) {
+          const float v = sm_plane[h * g.W + w];
+          if (v > best) { best = v; bi = h * g.W + w; }
+        }
+      y[plane * P + j] = best;
+      mask[plane * P + j] = bi;
+    }
+    __syncthreads();
+  }
+}
 void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask) {
-  const size_t total = (size_t)g.N * g.C * g.PH * g.PW;
-  pool_max_fwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, x, y, mask);
+  const size_t total = (size_t)g.N * g.C * g.PH * g.PW, smem = (size_t)g.H * g.W * sizeof(float);
+  if (smem <= 40 * 1024 && g.H * g.W >= 64) {
+    const size_t planes = (size_t)g.N * g.C;
+    const int blocks = (int)std::min<size_t>(planes, (size_t)kSMs * 16);
+    pool_max_fwd_plane_kernel<<<blocks, 256, smem, s>>>(g, FastDiv((uint32_t)g.PW), x, y, mask);
+  } else {
+    pool_max_fwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, x, y, mask);
+  }
   count_launch();
 }
 // gather form: every input element sums the top diffs of the windows whose argmax it is
@@ -212,30 +249,45 @@ __global__ void pool_max_bwd_kernel(PoolGeom g, size_t total, const float* __res
     dx[idx] = acc;
   }
 }
-// Plane-per-CTA form: the pooled plane's (dy, mask) pair is staged in shared memory with coalesced
-// loads, then every input element of the plane checks the <= ceil(k/s)^2 windows that cover it.  Global
-// traffic is exactly the algorithmic 8*out + 4*in bytes; no integer division per element.
-__global__ void pool_max_bwd_plane_kernel(PoolGeom g, const float* __restrict__ dy, const int* __restrict__ mask,
-                                          float* __restrict__ dx) {
+// Plane-per-CTA form: the pooled plane's (dy, mask) pair is staged in shared memory with coalesced loads, the
+// window range of every input row / column is tabulated once per CTA (no integer division per element), and the
+// plane is then written linearly: every input element checks the <= ceil(k/s)^2 windows that cover it, in the
+// reference's (ph, pw) order.  Global traffic is exactly the algorithmic 8*out + 4*in bytes.
+// `gate` (nullable) = the pooled OUTPUT values: when the pooling input is the output of an in-place ReLU whose
+// backward would run next (relu_layer.cpp:26-36: dx = dy * (y > 0)), that test is applied here — the element that
+// won a window is > 0 exactly when the pooled value is — and the separate 12 B/element ReLU pass disappears.
+__global__ void __launch_bounds__(256) pool_max_bwd_plane_kernel(PoolGeom g, FastDiv dW, const float* __restrict__ dy,
+                                                                 const int* __restrict__ mask, const float* __restrict__ gate,
+                                                                 float* __restrict__ dx) {
   extern __shared__ float sm_pool[];
-  const int P = g.PH * g.PW;
+  const int P = g.PH * g.PW, HW = g.H * g.W;
   float* sdy = sm_pool;
   int* smask = (int*)(sm_pool + P);
-  const size_t plane = blockIdx.x;
-  const int lin = threadIdx.y * blockDim.x + threadIdx.x, nthr = blockDim.x * blockDim.y;
-  for (int i = lin; i < P; i += nthr) {
-    sdy[i] = dy[plane * P + i];
-    smask[i] = mask[plane * P + i];
+  int* rowr = smask + P;                           // packed (first window | one-past-last window << 16) per input row
+  int* colr = rowr + g.H;
+  for (int h = threadIdx.x; h < g.H; h += blockDim.x) {
+    const int phs = (h + g.ph < g.kh) ? 0 : (h + g.ph - g.kh) / g.sh + 1, phe = min((h + g.ph) / g.sh + 1, g.PH);
+    rowr[h] = phs | (phe << 16);
   }
-  __syncthreads();
-  float* dxp = dx + plane * (size_t)(g.H * g.W);
-  for (int h = threadIdx.y; h < g.H; h += blockDim.y) {
-    const int phs = (h + g.ph < g.kh) ? 0 : (h + g.ph - g.kh) / g.sh + 1;
-    const int phe = min((h + g.ph) / g.sh + 1, g.PH);
-    for (int w = threadIdx.x; w < g.W; w += blockDim.x) {
-      const int pws = (w + g.pw < g.kw) ? 0 : (w + g.pw - g.kw) / g.sw + 1;
-      const int pwe = min((w + g.pw) / g.sw + 1, g.PW);
-      const int me = h * g.W + w;
+  for (int w = threadIdx.x; w < g.W; w += blockDim.x) {
+    const int pws = (w + g.pw < g.kw) ? 0 : (w + g.pw - g.kw) / g.sw + 1, pwe = min((w + g.pw) / g.sw + 1, g.PW);
+    colr[w] = pws | (pwe << 16);
+  }
+  for (size_t plane = blockIdx.x; plane < (size_t)g.N * g.C; plane += gridDim.x) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < P; i += blockDim.x) {
+      float v = dy[plane * P + i];
+      if (gate && !(gate[plane * P + i] > 0.f)) v = 0.f;
+      sdy[i] = v;
+      smask[i] = mask[plane * P + i];
+    }
+    __syncthreads();
+    float* dxp = dx + plane * (size_t)HW;
+    for (int me = threadIdx.x; me < HW; me += blockDim.x) {
+      uint32_t h, w;
+      dW.divmod((uint32_t)me, h, w);
+      const int rr = rowr[h], cr = colr[w];
+      const int phs = rr & 0xffff, phe = rr >> 16, pws = cr & 0xffff, pwe = cr >> 16;
       float acc = 0.f;
       for (int ph = phs; ph < phe; ++ph)
         for (int pw = pws; pw < pwe; ++pw)
@@ -244,15 +296,25 @@ __global__ void pool_max_bwd_plane_kernel(PoolGeom g, const float* __restrict__ 
     }
   }
 }
-void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx) {
-  const size_t smem = (size_t)g.PH * g.PW * 8;
+__global__ void pool_gate_kernel(size_t n, const float* __restrict__ dy, const float* __restrict__ gate, float* __restrict__ out) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    out[i] = gate[i] > 0.f ? dy[i] : 0.f;
+}
+void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx, const float* gate) {
+  const size_t smem = (size_t)g.PH * g.PW * 8 + (size_t)(g.H + g.W) * 4;
   if (smem <= 40 * 1024) {
-    // blockDim.x covers a row (coalesced stores), blockDim.y rows; the loops over threadIdx.x in the
-    // staging phase use the linear thread id
-    const int bx = g.W >= 32 ? 32 : 16, by = 256 / bx;
-    pool_max_bwd_plane_kernel<<<g.N * g.C, dim3(bx, by), smem, s>>>(g, dy, mask, dx);
+    const size_t planes = (size_t)g.N * g.C;
+    const int blocks = (int)std::min<size_t>(planes, (size_t)kSMs * 16);
+    pool_max_bwd_plane_kernel<<<blocks, 256, smem, s>>>(g, FastDiv((uint32_t)g.W), dy, mask, gate, dx);
   } else {
     const size_t total = (size_t)g.N * g.C * g.H * g.W;
+    if (gate) {                                    // large planes: gate into the workspace first
+      const size_t n = (size_t)g.N * g.C * g.PH * g.PW;
+      float* tmp = get_workspace(n);
+      pool_gate_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, dy, gate, tmp);
+      count_launch();
+      dy = tmp;
+    }
     pool_max_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, mask, dx);
   }
   count_launch();
@@ -353,7 +415,56 @@ __global__ void lrn_across_fwd_kernel(LrnGeom g, int nthreads, const float* __re
     }
   }
 }
+// Chunked form (local_size 3 or 5): one thread owns CH consecutive channels of one pixel, loads them plus the halo in
+// one batch (independent loads in flight instead of a serial walk over all C channels), and sums each window directly:
+//   scale_c = k + alpha/n * sum_{|j-c| <= pre} x_j^2 ,   y_c = x_c * scale_c^-beta .
+// Nothing but y is written: the backward kernel recomputes scale from x (cheaper than 8 B/element of scale traffic),
+// so the forward pass moves 8 B per element.
+__device__ __forceinline__ float lrn_pow_neg(float sc, float beta, bool is075) {
+  if (is075) { const float r = rsqrtf(sc); return r * sqrtf(r); }          // sc^-0.5 * sc^-0.25
+  return __powf(sc, -beta);
+}
+constexpr int kLrnCH = 16;
+template <int SIZE>
+__global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x, float* __restrict__ y) {
+  constexpr int PRE = (SIZE - 1) / 2;
+  const int HW = g.H * g.W;
+  const float aos = g.alpha / g.size;
+  const bool is075 = g.beta == 0.75f;
+  const size_t total = (size_t)g.N * chunks * HW;
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int pix = (int)(idx % HW);
+    const int ck = (int)((idx / HW) % chunks), n = (int)(idx / ((size_t)HW * chunks));
+    const int c0 = ck * kLrnCH;
+    const float* xp = x + ((size_t)n * g.C) * HW + pix;
+    float v[kLrnCH + 2 * PRE];
+#pragma unroll
+    for (int j = 0; j < kLrnCH + 2 * PRE; ++j) {
+      const int c = c0 - PRE + j;
+      v[j] = (c >= 0 && c < g.C) ? xp[(size_t)c * HW] : 0.f;
+    }
+    float* yp = y + ((size_t)n * g.C) * HW + pix;
+#pragma unroll
+    for (int j = 0; j < kLrnCH; ++j) {
+      if (c0 + j < g.C) {
+        float acc = 0.f;
+#pragma unroll
+        for (int t = 0; t < SIZE; ++t) acc += v[j + t] * v[j + t];
+        const float sc = g.k + acc * aos;
+        yp[(size_t)(c0 + j) * HW] = v[j + PRE] * lrn_pow_neg(sc, g.beta, is075);
+      }
+    }
+  }
+}
 void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, float* scale) {
+  if (g.size == 5 || g.size == 3) {
+    const int chunks = (g.C + kLrnCH - 1) / kLrnCH;
+    const size_t total = (size_t)g.N * chunks * g.H * g.W;
+    if (g.size == 5) lrn_across_fwd_chunk_kernel<5><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y);
+    else lrn_across_fwd_chunk_kernel<3><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y);
+    count_launch();
+    return;
+  }
   const int nthreads = g.N * g.H * g.W;
   lrn_across_fwd_kernel<<<grid_for(nthreads, 128, 16), 128, 0, s>>>(g, nthreads, x, y, scale);
   count_launch();
@@ -387,8 +498,67 @@ __global__ void lrn_across_bwd_kernel(LrnGeom g, int nthreads, const float* __re
     }
   }
 }
+// Chunked backward (local_size 3 or 5), reference LRNComputeDiff (lrn_layer.cu:122-177) / CrossChannelBackward_cpu
+// (lrn_layer.cpp:180-232):   dx_c = dy_c * scale_c^-beta - (2 alpha beta / n) * x_c * sum_{|j-c| <= pre} dy_j * y_j / scale_j
+// with scale and y recomputed from x (halo 2*pre).  Reads x and dy, writes dx: 12 B per element.
+template <int SIZE>
+__global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x,
+                                                                   const float* __restrict__ dy, float* __restrict__ dx) {
+  constexpr int PRE = (SIZE - 1) / 2;
+  const int HW = g.H * g.W;
+  const float aos = g.alpha / g.size;
+  const float cache_ratio = 2.f * g.alpha * g.beta / g.size;
+  const bool is075 = g.beta == 0.75f;
+  const size_t total = (size_t)g.N * chunks * HW;
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int pix = (int)(idx % HW);
+    const int ck = (int)((idx / HW) % chunks), n = (int)(idx / ((size_t)HW * chunks));
+    const int c0 = ck * kLrnCH;
+    const size_t base = ((size_t)n * g.C) * HW + pix;
+    float v[kLrnCH + 4 * PRE], r[kLrnCH + 2 * PRE], p[kLrnCH + 2 * PRE];
+#pragma unroll
+    for (int j = 0; j < kLrnCH + 4 * PRE; ++j) {
+      const int c = c0 - 2 * PRE + j;
+      v[j] = (c >= 0 && c < g.C) ? x[base + (size_t)c * HW] : 0.f;
+    }
+#pragma unroll
+    for (int j = 0; j < kLrnCH + 2 * PRE; ++j) {
+      const int c = c0 - PRE + j;
+      r[j] = (c >= 0 && c < g.C) ? dy[base + (size_t)c * HW] : 0.f;          // r holds dy for now
+    }
+#pragma unroll
+    for (int j = 0; j < kLrnCH + 2 * PRE; ++j) {                             // channel c0 - PRE + j
+      float acc = 0.f;
+#pragma unroll
+      for (int t = 0; t < SIZE; ++t) acc += v[j + t] * v[j + t];
+      const float sc = g.k + acc * aos;
+      const float pw = lrn_pow_neg(sc, g.beta, is075);
+      p[j] = pw;
+      r[j] = __fdiv_rn(__fmul_rn(r[j], __fmul_rn(v[j + PRE], pw)), sc) ;      // dy * y / scale; the raw dy is recovered below
+    }
+#pragma unroll
+    for (int j = 0; j < kLrnCH; ++j) {
+      const int c = c0 + j;
+      if (c < g.C) {
+        float acc = 0.f;
+#pragma unroll
+        for (int t = 0; t < SIZE; ++t) acc += r[j + t];
+        const float g_c = dy[base + (size_t)c * HW];                           // L1 hit: loaded a few instructions ago
+        dx[base + (size_t)c * HW] = g_c * p[j + PRE] - cache_ratio * v[j + 2 * PRE] * acc;
+      }
+    }
+  }
+}
 void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* y, const float* scale,
                     const float* dy, float* dx) {
+  if (g.size == 5 || g.size == 3) {
+    const int chunks = (g.C + kLrnCH - 1) / kLrnCH;
+    const size_t total = (size_t)g.N * chunks * g.H * g.W;
+    if (g.size == 5) lrn_across_bwd_chunk_kernel<5><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, dy, dx);
+    else lrn_across_bwd_chunk_kernel<3><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, dy, dx);
+    count_launch();
+    return;
+  }
   const int nthreads = g.N * g.H * g.W;
   lrn_across_bwd_kernel<<<grid_for(nthreads, 128, 16), 128, 0, s>>>(g, nthreads, x, y, scale, dy, dx);
   count_launch();

@@ -72,7 +72,8 @@ void tc_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, cons
 // ---- bandwidth-bound kernels (kernels.cu) ----------------------------------------------------
 struct PoolGeom { int N, C, H, W, kh, kw, sh, sw, ph, pw, PH, PW; };
 void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask);
-void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx);
+// gate (nullable): pooled output values; windows whose value is <= 0 pass no gradient (fused in-place ReLU backward)
+void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx, const float* gate = nullptr);
 void pool_ave_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y);
 void pool_ave_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, float* dx);
 

@@ -526,6 +526,7 @@ struct PoolingLayer : Layer {
   PoolGeom g;
   int method = 0;
   int* mask = nullptr;
+  bool gate_relu = false;     // the bottom is the output of an in-place ReLU whose backward is folded into this layer's
   using Layer::Layer;
   ~PoolingLayer() override { if (mask) cudaFree(mask); }
   const char* type() const override { return "Pooling"; }
@@ -563,7 +564,8 @@ struct PoolingLayer : Layer {
     if (!pd[0]) return;
     const float* dy = top[0]->diff->gpu();
     float* dx = bottom[0]->diff->mutable_gpu();
-    if (method == 0) pool_max_bwd(S(), g, dy, mask, dx); else pool_ave_bwd(S(), g, dy, dx);
+    if (method == 0) pool_max_bwd(S(), g, dy, mask, dx, gate_relu ? top[0]->data->gpu() : nullptr);
+    else pool_ave_bwd(S(), g, dy, dx);
   }
 };
 
@@ -571,6 +573,7 @@ struct PoolingLayer : Layer {
 // (fused_by_producer), forward is a no-op; backward is unchanged (tests y > 0, same predicate in place).
 struct ReLULayer : Layer {
   bool fused_by_producer = false;
+  bool bwd_fused_by_consumer = false;   // a max-pooling consumer applies dx = dy * (y > 0) while it scatters (PoolingLayer::gate_relu)
   using Layer::Layer;
   const char* type() const override { return "ReLU"; }
   void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
@@ -582,7 +585,7 @@ struct ReLULayer : Layer {
     relu_fwd(S(), bottom[0]->count(), x, top[0]->data->mutable_gpu(), lp.relu_negative_slope);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
-    if (!pd[0]) return;
+    if (!pd[0] || bwd_fused_by_consumer) return;
     const float* dy = top[0]->diff->gpu();
     const float* x = bottom[0]->data->gpu();
     relu_bwd(S(), bottom[0]->count(), dy, x, bottom[0]->diff->mutable_gpu(), lp.relu_negative_slope);
@@ -942,6 +945,28 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
     if (bottom_vecs[(size_t)li + 1][0] != top_vecs[(size_t)li + 1][0] || bottom_vecs[(size_t)li + 1][0] != top_vecs[(size_t)li][0]) continue;
     if (ConvolutionLayer* c = dynamic_cast<ConvolutionLayer*>(layers[(size_t)li].get())) { c->fuse_relu = true; r->fused_by_producer = true; }
     else if (InnerProductLayer* ip = dynamic_cast<InnerProductLayer*>(layers[(size_t)li].get())) { ip->fuse_relu = true; r->fused_by_producer = true; }
+  }
+  // ReLU-backward / max-pool fusion: an in-place ReLU (slope 0) whose blob is read by exactly one later layer, a MAX
+  // pooling layer, hands its backward to that layer (pool_max_bwd gate).  SPARKNET_FUSE_RELU_POOL=0 turns it off.
+  {
+    const char* e = getenv("SPARKNET_FUSE_RELU_POOL");
+    const bool enabled = !(e && atoi(e) == 0);
+    for (int li = 0; enabled && li < L; ++li) {
+      ReLULayer* r = dynamic_cast<ReLULayer*>(layers[(size_t)li].get());
+      if (!r || r->lp.relu_negative_slope != 0.f || bottom_vecs[(size_t)li][0] != top_vecs[(size_t)li][0]) continue;
+      Blob* blob = top_vecs[(size_t)li][0];
+      int consumers = 0, consumer = -1;
+      bool rewritten = false;
+      for (int lj = li + 1; lj < L; ++lj) {
+        for (Blob* b : bottom_vecs[(size_t)lj]) if (b == blob) { ++consumers; consumer = lj; }
+        for (Blob* t : top_vecs[(size_t)lj]) if (t == blob) rewritten = true;      // another in-place layer on the same blob
+      }
+      if (consumers != 1 || rewritten) continue;
+      PoolingLayer* pl = dynamic_cast<PoolingLayer*>(layers[(size_t)consumer].get());
+      if (!pl || pl->method != 0) continue;
+      pl->gate_relu = true;
+      r->bwd_fused_by_consumer = true;
+    }
   }
   // Parameter arena: one contiguous device allocation for all weights and one for all gradients;
   // every blob starts on a 1024-float boundary (lets one SGD launch and one all-reduce cover the net).
