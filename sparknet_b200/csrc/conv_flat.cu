@@ -710,18 +710,22 @@ ConvGeom tcw_s2d_geom(const ConvGeom& g) {
 }
 // one block per (image, folded row): s*C image rows in, W' positions x C*s*s channels out (contiguous)
 __global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__ x, float* __restrict__ dst, int C, int H, int W, int s,
-                                                        int Hs, int Ws, int Wp, int Gp, int lead) {
+                                                        int Hs, int Ws, int Wp, int Gp, int lead, FastDiv dCs, FastDiv dS) {
   extern __shared__ float rows[];                      // [C*s][Ws*s]
   const int hs = blockIdx.x, n = blockIdx.y, Wpad = Ws * s, nrows = C * s;
-  for (int i = threadIdx.x; i < nrows * Wpad; i += blockDim.x) {
-    const int r = i / Wpad, w = i - r * Wpad, c = r / s, dy = r - c * s, h = hs * s + dy;
-    rows[i] = (h < H && w < W) ? x[(((size_t)n * C + c) * H + h) * W + w] : 0.f;
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  for (int r = ty; r < nrows; r += 4) {
+    const int c = r / s, dy = r - c * s, h = hs * s + dy;
+    const float* xp = x + (((size_t)n * C + c) * H + h) * W;
+    for (int w = tx; w < Wpad; w += 64) rows[r * Wpad + w] = (h < H && w < W) ? xp[w] : 0.f;
   }
   __syncthreads();
   const int Cs = C * s * s;
   float* out = dst + ((size_t)lead + (size_t)n * Gp + (size_t)hs * Wp) * Cs;
   for (int i = threadIdx.x; i < Ws * Cs; i += blockDim.x) {
-    const int ws = i / Cs, ch = i - ws * Cs, dx = ch % s, r = ch / s;          // r = c*s + dy
+    uint32_t ws, ch, r, dx;
+    dCs.divmod((uint32_t)i, ws, ch);
+    dS.divmod(ch, r, dx);                              // r = c*s + dy
     out[i] = to_tf32_exact(rows[r * Wpad + ws * s + dx]);
   }
 }
@@ -732,7 +736,8 @@ void tcw_s2d_pack_input(cudaStream_t st, const ConvGeom& g, const float* x, floa
   const size_t smem = (size_t)g.C * s * Ws * s * sizeof(float);
   static size_t attr = 48 * 1024;
   if (smem > attr) { SN_CUDA(cudaFuncSetAttribute(s2d_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = smem; }
-  s2d_pack_kernel<<<dim3(Hs, g.N), 256, smem, st>>>(x, xflat, g.C, g.H, g.W, s, Hs, Ws, f.Wp, f.Gp, f.lead);
+  s2d_pack_kernel<<<dim3(Hs, g.N), 256, smem, st>>>(x, xflat, g.C, g.H, g.W, s, Hs, Ws, f.Wp, f.Gp, f.lead, FastDiv((uint32_t)(g.C * s * s)),
+                                                    FastDiv((uint32_t)s));
   count_launch();
   SN_CUDA(cudaGetLastError());
 }

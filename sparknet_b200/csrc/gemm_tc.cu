@@ -937,30 +937,40 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
 // in image order.  The top gradient is therefore read from HBM once for both purposes.
 template <bool BIAS>
 __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
-                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW) {
-  __shared__ float tile[32][33];
+                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span) {
+  __shared__ float tile[32][129];
   const int HW = H * W, c0 = blockIdx.x * 32, n = blockIdx.y;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   const float* sp = src + ((size_t)n * C + c0) * HW;
   float* dp = dst + ((size_t)lead + (size_t)n * Gp) * C + c0 + tx;
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};
-  for (int p0 = 0; p0 < HW; p0 += 32) {
-    const int p = p0 + tx;
+  const int p_begin = blockIdx.z * span, p_end = min(HW, p_begin + span);     // this block's share of the image's pixels
+  for (int p0 = p_begin; p0 < p_end; p0 += 128) {
+    float v[4][4];
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int j = ty + 8 * k;
-      const float v = (c0 + j < C && p < HW) ? sp[(size_t)j * HW + p] : 0.f;
-      tile[j][tx] = v;
-      if (BIAS) bsum[k] += v;
-    }
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int j = ty + 8 * k, p = p0 + tx + 32 * q;
+        v[k][q] = (c0 + j < C && p < p_end) ? sp[(size_t)j * HW + p] : 0.f;
+      }
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        tile[ty + 8 * k][tx + 32 * q] = v[k][q];
+        if (BIAS) bsum[k] += v[k][q];
+      }
     __syncthreads();
+    if (c0 + tx < C) {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-      const int q = p0 + ty + 8 * k;
-      if (q < HW && c0 + tx < C) {
-        uint32_t h, w;
-        dW.divmod((uint32_t)q, h, w);
-        dp[(size_t)(h * Wp + w) * C] = to_tf32_exact(tile[tx][ty + 8 * k]);
+      for (int k = 0; k < 16; ++k) {
+        const int pl = ty + 8 * k, q = p0 + pl;
+        if (q < p_end) {
+          uint32_t h, w;
+          dW.divmod((uint32_t)q, h, w);
+          dp[(size_t)(h * Wp + w) * C] = to_tf32_exact(tile[tx][pl]);
+        }
       }
     }
     __syncthreads();
@@ -970,7 +980,7 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
     for (int k = 0; k < 4; ++k) {
       float v = bsum[k];
       for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (tx == 0 && c0 + ty + 8 * k < C) part[(size_t)(c0 + ty + 8 * k) * N + n] = v;
+      if (tx == 0 && c0 + ty + 8 * k < C) part[(size_t)(c0 + ty + 8 * k) * (N * gridDim.z) + n * gridDim.z + blockIdx.z] = v;
     }
   }
 }
@@ -985,14 +995,19 @@ __global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ p
 void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db, bool accumulate) {
   const int C = output_side ? g.Cout : g.C, H = output_side ? g.Ho : g.H, W = output_side ? g.Wo : g.W;
   const FlatGeom f = tc_flat_geom(g);
-  dim3 grid((C + 31) / 32, g.N);
+  const int HW = H * W;
+  int Z = (HW + 1023) / 1024;                          // large planes: several blocks per (image, channel block)
+  if (Z > 4) Z = 4;
+  const int span = ((HW + Z - 1) / Z + 127) / 128 * 128;
+  Z = (HW + span - 1) / span;
+  dim3 grid((C + 31) / 32, g.N, Z);
   if (db) {
-    float* part = get_workspace((size_t)C * g.N);
-    flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W));
-    bias_grad_final_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, g.N, part, db, accumulate ? 1 : 0);
+    float* part = get_workspace((size_t)C * g.N * Z);
+    flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span);
+    bias_grad_final_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, g.N * Z, part, db, accumulate ? 1 : 0);
     count_launch(2);
   } else {
-    flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W));
+    flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span);
     count_launch();
   }
   SN_CUDA(cudaGetLastError());

@@ -219,9 +219,43 @@ __global__ void __launch_bounds__(256) pool_max_fwd_plane_kernel(PoolGeom g, Fas
     __syncthreads();
   }
 }
+// Thread-per-output form for the window shapes of the four nets (compile-time kernel size and stride, no padding):
+// 32-bit index arithmetic with multiply-shift division, all window loads issued before the compare chain.  Window
+// elements are read straight from global memory: neighbouring outputs share them through the L1, HBM sees them once.
+template <int KH, int KW, int SH, int SW>
+__global__ void __launch_bounds__(256) pool_max_fwd_fixed_kernel(PoolGeom g, uint32_t total, FastDiv dPW, FastDiv dPH, const float* __restrict__ x,
+                                                                 float* __restrict__ y, int* __restrict__ mask) {
+  const int HW = g.H * g.W;
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    uint32_t t, pw, plane, ph;
+    dPW.divmod(idx, t, pw);
+    dPH.divmod(t, plane, ph);
+    const int hs = (int)ph * SH, ws = (int)pw * SW;
+    const float* xp = x + (size_t)plane * HW + hs * g.W + ws;
+    float v[KH][KW];
+#pragma unroll
+    for (int a = 0; a < KH; ++a)
+#pragma unroll
+      for (int b = 0; b < KW; ++b) v[a][b] = (hs + a < g.H && ws + b < g.W) ? __ldg(xp + a * g.W + b) : -FLT_MAX;
+    float best = -FLT_MAX;
+    int bi = -1;
+#pragma unroll
+    for (int a = 0; a < KH; ++a)
+#pragma unroll
+      for (int b = 0; b < KW; ++b)
+        if (v[a][b] > best) { best = v[a][b]; bi = (hs + a) * g.W + ws + b; }
+    y[idx] = best;
+    mask[idx] = bi;
+  }
+}
 void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask) {
   const size_t total = (size_t)g.N * g.C * g.PH * g.PW, smem = (size_t)g.H * g.W * sizeof(float);
-  if (smem <= 40 * 1024 && g.H * g.W >= 64) {
+  const bool fixed = g.ph == 0 && g.pw == 0 && total < (1ull << 31) && (size_t)g.N * g.C * g.H * g.W < (1ull << 31);
+  if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
+    pool_max_fwd_fixed_kernel<3, 3, 2, 2><<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)g.PW), FastDiv((uint32_t)g.PH), x, y, mask);
+  } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
+    pool_max_fwd_fixed_kernel<2, 2, 2, 2><<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)g.PW), FastDiv((uint32_t)g.PH), x, y, mask);
+  } else if (smem <= 40 * 1024 && g.H * g.W >= 64) {
     const size_t planes = (size_t)g.N * g.C;
     const int blocks = (int)std::min<size_t>(planes, (size_t)kSMs * 16);
     pool_max_fwd_plane_kernel<<<blocks, 256, smem, s>>>(g, FastDiv((uint32_t)g.PW), x, y, mask);
@@ -296,13 +330,55 @@ __global__ void __launch_bounds__(256) pool_max_bwd_plane_kernel(PoolGeom g, Fas
     }
   }
 }
+// Thread-per-input-element gather for the same fixed window shapes: at most ceil(K/S)^2 = 4 candidate windows, tested
+// in the reference's (ph, pw) order; 32-bit index arithmetic, divisions by compile-time strides.
+template <int KH, int KW, int SH, int SW>
+__global__ void __launch_bounds__(256) pool_max_bwd_fixed_kernel(PoolGeom g, uint32_t total, FastDiv dW, FastDiv dH, const float* __restrict__ dy,
+                                                                 const int* __restrict__ mask, const float* __restrict__ gate,
+                                                                 float* __restrict__ dx) {
+  constexpr int NH = (KH + SH - 1) / SH, NW = (KW + SW - 1) / SW;
+  const int P = g.PH * g.PW;
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    uint32_t t, w, plane, h;
+    dW.divmod(idx, t, w);
+    dH.divmod(t, plane, h);
+    const int phe = min((int)h / SH + 1, g.PH), pwe = min((int)w / SW + 1, g.PW);       // one past the last covering window
+    const int phs = (int)h < KH ? 0 : ((int)h - KH) / SH + 1, pws = (int)w < KW ? 0 : ((int)w - KW) / SW + 1;
+    const int me = (int)h * g.W + (int)w;
+    const int* mp = mask + (size_t)plane * P;
+    const float* gp = dy + (size_t)plane * P;
+    int m[NH][NW];
+#pragma unroll
+    for (int a = 0; a < NH; ++a)
+#pragma unroll
+      for (int b = 0; b < NW; ++b) m[a][b] = (phs + a < phe && pws + b < pwe) ? __ldg(mp + (phs + a) * g.PW + pws + b) : -2;
+    float acc = 0.f;
+#pragma unroll
+    for (int a = 0; a < NH; ++a)
+#pragma unroll
+      for (int b = 0; b < NW; ++b)
+        if (m[a][b] == me) {
+          const int j = (phs + a) * g.PW + pws + b;
+          float v = __ldg(gp + j);
+          if (gate && !(__ldg(gate + (size_t)plane * P + j) > 0.f)) v = 0.f;
+          acc += v;
+        }
+    dx[idx] = acc;
+  }
+}
 __global__ void pool_gate_kernel(size_t n, const float* __restrict__ dy, const float* __restrict__ gate, float* __restrict__ out) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = gate[i] > 0.f ? dy[i] : 0.f;
 }
 void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx, const float* gate) {
   const size_t smem = (size_t)g.PH * g.PW * 8 + (size_t)(g.H + g.W) * 4;
-  if (smem <= 40 * 1024) {
+  const size_t total_in = (size_t)g.N * g.C * g.H * g.W;
+  const bool fixed = g.ph == 0 && g.pw == 0 && total_in < (1ull << 31);
+  if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
+    pool_max_bwd_fixed_kernel<3, 3, 2, 2><<<grid_for(total_in, 256, 32), 256, 0, s>>>(g, (uint32_t)total_in, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx);
+  } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
+    pool_max_bwd_fixed_kernel<2, 2, 2, 2><<<grid_for(total_in, 256, 32), 256, 0, s>>>(g, (uint32_t)total_in, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx);
+  } else if (smem <= 40 * 1024) {
     const size_t planes = (size_t)g.N * g.C;
     const int blocks = (int)std::min<size_t>(planes, (size_t)kSMs * 16);
     pool_max_bwd_plane_kernel<<<blocks, 256, smem, s>>>(g, FastDiv((uint32_t)g.W), dy, mask, gate, dx);
