@@ -48,10 +48,16 @@ struct WinArgs {
   int box_rows, nbox;       // a window is nbox TMA boxes of box_rows grid rows
   int nstage;               // filter pipeline depth
   long long* stamps;        // development aid: 8 clock64 stamps per CTA (null = off)
+  // --- plain matrix products (inner-product layers run as 1-tap "convolutions" over the batch rows) ---
+  int nwin;                 // window buffers (2 for convolutions: a window lives for T taps; up to 8 when T = 1)
+  int splits, cb_per_split; // the reduction's channel blocks are cut into `splits` ranges (blockIdx.z = group * splits + split)
+  int b_mn;                 // B operand stored [reduction][n] (n contiguous): MN-major tiles of 32 n x 32 rows per TMA box
 };
-// m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell
+// m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell.
+// ld > 0 selects the matrix epilogue instead: dst[split][m][ld] row-major (bias / ReLU only when splits == 1).
 struct WinEpi {
   float* dst; const float* bias; int Hv, Wv, Ctot, Cgrp, relu; FastDiv dGp, dWp;
+  int ld; size_t split_stride;
 };
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2 along x) runs every MMA with M = 256: each CTA keeps its
@@ -62,21 +68,22 @@ template <int CG>
 __global__ void __launch_bounds__(kWThreads, 1)
 conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const WinArgs a, const WinEpi ep) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t win_full[2], win_empty[2], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full;
+  __shared__ uint64_t win_full[kWMaxStages], win_empty[kWMaxStages], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full;
   __shared__ uint32_t tmem_base_smem;
 
   const long long t_enter = clock64();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
-  const int q0 = blockIdx.x * a.MT * 128, n0 = blockIdx.y * a.n_mma, grp = blockIdx.z;
+  const int q0 = blockIdx.x * a.MT * 128, n0 = blockIdx.y * a.n_mma, grp = blockIdx.z / a.splits, split = blockIdx.z % a.splits;
+  const int cb_begin = split * a.cb_per_split, cb_end = min(a.ncb, cb_begin + a.cb_per_split);   // never empty (host)
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t win_bytes = (uint32_t)(a.nbox * a.box_rows) * 128u;      // multiple of 1024 (box_rows % 8 == 0)
   const int nb_local = a.n_mma / CG;                                      // filter rows this CTA stages per chunk
   const uint32_t b_bytes = (uint32_t)nb_local * 128u;                     // multiple of 1024 (n_mma % 16 == 0)
-  uint8_t* bst = smem + 2 * win_bytes;
+  uint8_t* bst = smem + a.nwin * win_bytes;
 
   if (tid == 0) {
-    for (int i = 0; i < 2; ++i) { mbar_init(&win_full[i], 1u); mbar_init(&win_empty[i], 1u); }
+    for (int i = 0; i < a.nwin; ++i) { mbar_init(&win_full[i], 1u); mbar_init(&win_empty[i], 1u); }
     for (int i = 0; i < a.nstage; ++i) { mbar_init(&b_full[i], 1u); mbar_init(&b_empty[i], 1u); }
     mbar_init(&tmem_full, 1u);
     fence_barrier_init();
@@ -103,6 +110,32 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     const int quarter = warp & 3, half = warp >> 2, chan0 = grp * ep.Cgrp;
     const size_t plane = (size_t)ep.Hv * ep.Wv;
     const int ncols = min(a.n_mma, ep.Cgrp - n0);                 // valid columns of this tile (multiple of 16)
+    if (ep.ld > 0) {
+      // matrix epilogue: row m of D goes to dst[split][m][n0 ..] (16 consecutive floats per TMEM load)
+      const bool plain = a.splits == 1;
+      for (int i = 0; i < a.MT; ++i) {
+        const int m = q0 + i * 128 + 32 * quarter + lane;
+        float* p = ep.dst + (size_t)split * ep.split_stride + (size_t)min(m, a.Ptot - 1) * ep.ld + n0;
+        for (int c0 = 16 * half; c0 < ncols; c0 += 32) {
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(i * a.n_mma + c0), v);
+          tmem_ld_wait();
+          if (m < a.Ptot) {
+#pragma unroll
+            for (int j = 0; j < 16; j += 4) {
+              if (c0 + j >= ncols) break;                       // ncols is a multiple of 4 (N % 4 == 0)
+              float4 o = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+              if (plain && ep.bias) {
+                const float* bp = ep.bias + n0 + c0 + j;
+                o.x += __ldg(bp); o.y += __ldg(bp + 1); o.z += __ldg(bp + 2); o.w += __ldg(bp + 3);
+              }
+              if (plain && ep.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+              *(float4*)(p + c0 + j) = o;
+            }
+          }
+        }
+      }
+    } else
     for (int c0 = 16 * half; c0 < ncols; c0 += 32) {
       float bias[16];
 #pragma unroll
@@ -134,19 +167,20 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   } else if (warp == kWEpiWarps) {
     // ---------------- MMA issuer (rank 0 of a pair): the whole warp walks the pipeline, one elected lane issues ----------------
     if (rank == 0) {
-      const uint32_t idesc = make_idesc_tf32(128 * CG, a.n_mma, 0, 0);
-      // descriptor = {lo: start >> 4 | LBO 16 B << 16, hi: SBO 1024 B | version 1 | SWIZZLE_128B}; only lo moves
+      const uint32_t idesc = make_idesc_tf32(128 * CG, a.n_mma, 0, a.b_mn);
+      // descriptor = {lo: start >> 4 | LBO << 16, hi: SBO | version 1 | layout}; only lo moves.
+      // K-major (SWIZZLE_128B): LBO 16 B (unused), SBO 1024 B, +32 B per k-step of 8.
+      // MN-major B (SWIZZLE_128B_BASE32B): 32-column blocks 4096 B apart (LBO), 4-row atoms 512 B apart (SBO), +1024 B per k-step.
       const uint32_t desc_hi = (uint32_t)(make_smem_desc(0, 16, 1024, kLayoutSW128) >> 32);
-      const uint32_t lo_flags = 1u << 16;
-      const uint32_t win_lo = (smem_u32(smem) >> 4) | lo_flags, b_lo0 = (smem_u32(bst) >> 4) | lo_flags;
-      const uint32_t win_step = win_bytes >> 4, b_step = b_bytes >> 4;
-      int it = 0, s = 0;
-      uint32_t sphase = 0;
+      const uint32_t b_hi = a.b_mn ? (uint32_t)(make_smem_desc(0, 4096, 512, kLayoutSW128Base32) >> 32) : desc_hi;
+      const uint32_t win_lo = (smem_u32(smem) >> 4) | (1u << 16), b_lo0 = (smem_u32(bst) >> 4) | (a.b_mn ? (4096u >> 4) << 16 : 1u << 16);
+      const uint32_t win_step = win_bytes >> 4, b_step = b_bytes >> 4, b_kstep = a.b_mn ? 64u : 2u;
+      int it = 0, s = 0, wb = 0;
+      uint32_t sphase = 0, wphase = 0;
       long long wait_win = 0, wait_b = 0;
-      for (int cb = 0; cb < a.ncb; ++cb) {
-        const int wb = cb & 1;
+      for (int cb = cb_begin; cb < cb_end; ++cb) {
         long long tw = stamp ? clock64() : 0;
-        mbar_wait(&win_full[wb], (cb >> 1) & 1);
+        mbar_wait(&win_full[wb], wphase);
         if (stamp) wait_win += clock64() - tw;
         const int left = a.red - cb * 32, ks = left >= 32 ? 4 : (left + 7) / 8;
         uint32_t shift_row = 0;                                     // (ky * Wp) in rows
@@ -166,11 +200,11 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
               const uint32_t d = tmem_base + (uint32_t)(i * a.n_mma);
 #pragma unroll 4
               for (int j = 0; j < ks; ++j) {
-                if (CG == 2) mma_tf32_lohi_pair(d, a_lo + (uint32_t)(i * 1024 + 2 * j), b_lo + (uint32_t)(2 * j), desc_hi, idesc, (it | j) != 0 ? 1u : 0u);
-                else mma_tf32_lohi(d, a_lo + (uint32_t)(i * 1024 + 2 * j), b_lo + (uint32_t)(2 * j), desc_hi, idesc, (it | j) != 0 ? 1u : 0u);
+                if (CG == 2) mma_tf32_lohi2_pair(d, a_lo + (uint32_t)(i * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
+                else mma_tf32_lohi2(d, a_lo + (uint32_t)(i * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
               }
             }
-            const bool last_tap = tap == a.T - 1, last = last_tap && cb == a.ncb - 1;
+            const bool last_tap = tap == a.T - 1, last = last_tap && cb == cb_end - 1;
             if (CG == 2) {
               mma_commit_pair(&b_empty[s]);
               if (last_tap) mma_commit_pair(&win_empty[wb]);
@@ -185,30 +219,39 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           if (++kx == a.kw) { kx = 0; shift_row += (uint32_t)a.Wp; }
           if (++s == a.nstage) { s = 0; sphase ^= 1u; }
         }
+        if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
       }
       if (stamp && lane == 0) { stamp[2] = wait_win; stamp[3] = wait_b; }
     }
   } else {
     // ---------------- TMA issuer (both CTAs of a pair; completion bytes land on rank 0's barriers) ----------------
     if (lane == 0) {
-      int it = 0;
+      int s = 0, wb = 0;
+      uint32_t sphase = 0, wphase = 0;
       const int a_chan0 = grp * a.a_chan_group, b_row0 = grp * a.b_row_group + n0 + rank * nb_local;
-      for (int cb = 0; cb < a.ncb; ++cb) {
-        const int wb = cb & 1;
-        mbar_wait(&win_empty[wb], ((cb >> 1) & 1) ^ 1);
+      for (int cb = cb_begin; cb < cb_end; ++cb) {
+        mbar_wait(&win_empty[wb], wphase ^ 1u);
         if (rank == 0) mbar_arrive_expect_tx(&win_full[wb], win_bytes * CG);
         for (int b = 0; b < a.nbox; ++b) {
           uint8_t* dst = smem + (size_t)wb * win_bytes + (size_t)b * a.box_rows * 128;
           if (CG == 2) tma_load_2d_pair(dst, &tmA, &win_full[wb], a_chan0 + cb * 32, q0 + a.row_off + b * a.box_rows);
           else tma_load_2d(dst, &tmA, &win_full[wb], a_chan0 + cb * 32, q0 + a.row_off + b * a.box_rows);
         }
-        for (int tap = 0; tap < a.T; ++tap, ++it) {
-          const int s = it % a.nstage;
-          mbar_wait(&b_empty[s], ((it / a.nstage) & 1) ^ 1);
+        for (int tap = 0; tap < a.T; ++tap) {
+          mbar_wait(&b_empty[s], sphase ^ 1u);
           if (rank == 0) mbar_arrive_expect_tx(&b_full[s], b_bytes * CG);
-          if (CG == 2) tma_load_2d_pair(bst + (size_t)s * b_bytes, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
-          else tma_load_2d(bst + (size_t)s * b_bytes, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          uint8_t* dst = bst + (size_t)s * b_bytes;
+          if (a.b_mn) {
+            // B stored [reduction row][n]: one box of 32 n x 32 rows per 32 columns of this CTA's share
+            for (int blk = 0; blk < nb_local / 32; ++blk) {
+              if (CG == 2) tma_load_2d_pair(dst + blk * 4096, &tmB, &b_full[s], b_row0 + 32 * blk, cb * 32);
+              else tma_load_2d(dst + blk * 4096, &tmB, &b_full[s], b_row0 + 32 * blk, cb * 32);
+            }
+          } else if (CG == 2) tma_load_2d_pair(dst, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          else tma_load_2d(dst, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          if (++s == a.nstage) { s = 0; sphase ^= 1u; }
         }
+        if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
       }
     }
   }
@@ -378,7 +421,7 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
     SN_CUDA(cudaFuncSetAttribute(conv_window_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemLimit - 1024));
     attr_done = true;
   }
-  dim3 grid((a.Ptot + a.MT * 128 - 1) / (a.MT * 128), (N + a.n_mma - 1) / a.n_mma, groups);
+  dim3 grid((a.Ptot + a.MT * 128 - 1) / (a.MT * 128), (N + a.n_mma - 1) / a.n_mma, groups * a.splits);
   if (pl.cg == 2) grid.x = (grid.x + 1) / 2 * 2;          // whole pairs: the odd CTA works on rows past the end (zero-filled)
   WinArgs aa = a;
   const int ctas = (int)(grid.x * grid.y * grid.z);
@@ -423,8 +466,8 @@ void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const f
   const CUtensorMap tmA = tc_make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, (uint32_t)pl.box_rows, false);
   const CUtensorMap tmB = tc_make_tmap(wf, (uint64_t)kp, (uint64_t)g.Cout, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - (g.ph * f.Wp + g.pw), pl.MT, pl.n_mma, slots / 32, Cg, slots, Cg, Og,
-            pl.box_rows, pl.nbox, pl.nstage, nullptr};
-  WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp)};
+            pl.box_rows, pl.nbox, pl.nstage, nullptr, 2, 1, slots / 32, 0};
+  WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0};
   launch_window(s, tmA, tmB, a, ep, pl, Og, g.group);
 }
 // `dyflat`: packed top gradient (tc_flat_pack, output side); `wt`: tc_flat_pack_filter(dgrad = true)
@@ -437,11 +480,75 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
   const CUtensorMap tmA = tc_make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, (uint32_t)pl.box_rows, false);
   const CUtensorMap tmB = tc_make_tmap(wt, (uint64_t)kp, (uint64_t)g.C, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - ((g.kh - 1 - g.ph) * f.Wp + (g.kw - 1 - g.pw)), pl.MT, pl.n_mma, slots / 32, Og, slots,
-            Og, Cg, pl.box_rows, pl.nbox, pl.nstage, nullptr};
-  WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp)};
+            Og, Cg, pl.box_rows, pl.nbox, pl.nstage, nullptr, 2, 1, slots / 32, 0};
+  WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0};
   launch_window(s, tmA, tmB, a, ep, pl, Cg, g.group);
 }
 
+
+// ------------------------------------------------------------------------------------------
+// Plain matrix products for the inner-product layers (inner_product_layer.cpp:78-117) on the same kernel: a one-tap
+// "convolution" whose grid positions are the batch rows.  out[m][n] = sum_k A[m][k] * B(n, k) (+ bias[n], ReLU);
+//   A  [M][K] row-major, already rounded to tf32;   B  [N][K] row-major (b_mn = false) or [K][N] row-major (b_mn = true).
+// The weight matrix streams from HBM exactly once; CTA pairs split its rows, the reduction is cut into ranges so that
+// ~148 CTAs are busy, and the slices are summed in range order (deterministic) with bias / ReLU applied there.
+// ------------------------------------------------------------------------------------------
+__global__ void mat_reduce_kernel(const float* __restrict__ ws, int splits, size_t total, int N, const float* __restrict__ bias, int relu,
+                                  float* __restrict__ out) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    float acc = ws[i];
+    for (int z = 1; z < splits; ++z) acc += ws[(size_t)z * total + i];
+    if (bias) acc += __ldg(bias + (int)(i % N));
+    if (relu) acc = fmaxf(acc, 0.f);
+    out[i] = acc;
+  }
+}
+bool tcw_matmul_supported(int M, int N, int K, const float* A, const float* B, bool b_mn, const float* out) {
+  if (M < 1 || N < 16 || K < 8 || N % 4 != 0 || K % 4 != 0) return false;
+  if (((uintptr_t)A | (uintptr_t)B | (uintptr_t)out) & 15) return false;
+  (void)b_mn;
+  return true;
+}
+void tcw_matmul(cudaStream_t s, int M, int N, int K, const float* A, const float* B, bool b_mn, const float* bias, bool relu, float* out) {
+  WinPlan pl{};
+  pl.cg = (M > 128 && g_force_cg != 1) ? 2 : 1;
+  pl.MT = M > 128 * pl.cg ? 2 : 1;                     // 2 accumulators of 256 columns fill the 512 TMEM columns
+  const int gran = b_mn ? 32 * pl.cg : 16;
+  int n_mma = N >= 256 ? 256 : (N + gran - 1) / gran * gran;
+  if (pl.MT * n_mma > 512) n_mma = 256;
+  pl.n_mma = n_mma;
+  const int win_rows = pl.MT * 128;
+  pl.nbox = 1; pl.box_rows = win_rows;
+  const size_t win_bytes = (size_t)win_rows * 128, b_bytes = (size_t)n_mma * 128 / pl.cg;
+  int depth = (int)((kWSmemLimit - 2048) / (win_bytes + b_bytes));
+  if (depth > kWMaxStages) depth = kWMaxStages;
+  pl.nstage = depth;
+  pl.smem = (size_t)depth * (win_bytes + b_bytes) + 1024;
+  const int ncb = (K + 31) / 32, m_ctas = (M + win_rows - 1) / win_rows, n_tiles = (N + n_mma - 1) / n_mma;
+  const int tiles = ((pl.cg == 2 ? (m_ctas + 1) / 2 * 2 : m_ctas)) * n_tiles;
+  int splits = 148 / tiles;
+  if (splits < 1) splits = 1;
+  if (splits > ncb / 4) splits = ncb / 4 > 0 ? ncb / 4 : 1;
+  const int cps = (ncb + splits - 1) / splits;
+  splits = (ncb + cps - 1) / cps;
+  const CUtensorMap tmA = tc_make_tmap(A, (uint64_t)K, (uint64_t)M, (uint64_t)K * 4, (uint32_t)pl.box_rows, false);
+  const CUtensorMap tmB = b_mn ? tc_make_tmap(B, (uint64_t)N, (uint64_t)K, (uint64_t)N * 4, 32, true)
+                               : tc_make_tmap(B, (uint64_t)K, (uint64_t)N, (uint64_t)K * 4, (uint32_t)(n_mma / pl.cg), false);
+  WinArgs a{M, 1, 1, 1, 0, pl.MT, n_mma, ncb, K, 0, 0, 0, pl.box_rows, pl.nbox, pl.nstage, nullptr, depth, splits, cps, b_mn ? 1 : 0};
+  float* dst = out;
+  size_t stride = 0;
+  if (splits > 1) { stride = (size_t)M * N; dst = get_workspace(stride * splits); }
+  WinEpi ep{dst, bias, 1, 1, N, N, relu ? 1 : 0, FastDiv(1), FastDiv(1), N, stride};
+  launch_window(s, tmA, tmB, a, ep, pl, N, 1);
+  if (splits > 1) {
+    const size_t total = (size_t)M * N;
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    mat_reduce_kernel<<<blocks, 256, 0, s>>>(dst, splits, total, N, bias, relu ? 1 : 0, out);
+    count_launch();
+  }
+  SN_CUDA(cudaGetLastError());
+}
 
 // ------------------------------------------------------------------------------------------
 // Backward-filter on the flat grid:  dW[co][c][tap] = sum_q dyflat[q][co] * xflat[q + shift(tap) - pad][c].
@@ -608,8 +715,9 @@ static WgPlan plan_wgrad(int Ptot, int Og, int Cg, int groups, int T, int kw, in
   best.ok = false;
   double best_cost = 0;
   const int chunks = (Ptot + 31) / 32, m_tiles = (Og + 127) / 128;
-  for (int n_tiles = 1; n_tiles <= 16; ++n_tiles) {
+  for (int n_tiles = 1; n_tiles <= 512; ++n_tiles) {
     int n_mma = ((Cg + n_tiles - 1) / n_tiles + 15) / 16 * 16;
+    if (n_mma < 16) break;
     if (n_mma > 256) continue;
     if (n_tiles > 1 && n_mma * (n_tiles - 1) >= Cg) continue;          // an empty last tile
     const int nt_max = 512 / n_mma < T ? 512 / n_mma : T;
@@ -648,10 +756,10 @@ bool tcw_wgrad_supported(const ConvGeom& g) {
   return plan_wgrad(g.N * f.Gp, g.Og(), g.Cg(), g.group, g.kh * g.kw, g.kw, f.Wp).ok;
 }
 
-void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate) {
-  const FlatGeom f = tc_flat_geom(g);
-  const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Ptot = g.N * f.Gp;
-  const WgPlan pl = plan_wgrad(Ptot, Og, Cg, g.group, T, g.kw, f.Wp);
+// x: [rows][x_chan] and dy: [rows][dy_chan] packed tensors (tf32-rounded, channels contiguous); Ptot reduction rows
+static void wgrad_core(cudaStream_t s, const float* xflat, int x_chan, const float* dyflat, int dy_chan, size_t rows_total, int Ptot, int Og, int Cg,
+                       int groups, int T, int kw, int Wp, int lead, int pad_off, float* dw, bool accumulate) {
+  const WgPlan pl = plan_wgrad(Ptot, Og, Cg, groups, T, kw, Wp);
   if (!pl.ok) fatal("window convolution: no tile plan for this layer (backward filter)");
   static bool attr_done = false;
   if (!attr_done) {
@@ -661,26 +769,44 @@ void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const
   WgArgs a;
   a.Ptot_chunks = (Ptot + 31) / 32;
   a.chunks_per_split = pl.chunks_per_split;
-  a.Wp = f.Wp; a.kw = g.kw; a.T = T;
+  a.Wp = Wp; a.kw = kw; a.T = T;
   a.nt = pl.nt; a.n_groups_t = (T + pl.nt - 1) / pl.nt;
   a.m_tiles = (Og + 127) / 128;
   a.n_mma = pl.n_mma; a.n_tiles = (Cg + pl.n_mma - 1) / pl.n_mma; a.nblk = (pl.n_mma + 31) / 32;
   a.Og = Og; a.Cg = Cg;
-  a.lead = f.lead; a.pad_off = g.ph * f.Wp + g.pw;
+  a.lead = lead; a.pad_off = pad_off;
   a.KR = pl.KR; a.nstage = pl.nstage;
-  a.split_stride = (size_t)g.Cout * T * Cg;
-  a.ws = get_workspace((size_t)pl.splits * a.split_stride);
-  const CUtensorMap tmDY = tc_make_tmap(dyflat, (uint64_t)g.Cout, tc_flat_rows(g), (uint64_t)g.Cout * 4, 32, true);
-  const CUtensorMap tmX = tc_make_tmap(xflat, (uint64_t)g.C, tc_flat_rows(g), (uint64_t)g.C * 4, (uint32_t)pl.KR, true);
-  dim3 grid(a.m_tiles * a.n_tiles * a.n_groups_t * g.group, pl.splits, 1);
+  a.split_stride = (size_t)Og * groups * T * Cg;
+  // one tap, one slice, plain store: the slice layout [co][tap][c] IS dW, so the kernel writes it directly
+  const bool direct = T == 1 && pl.splits == 1 && !accumulate;
+  a.ws = direct ? dw : get_workspace((size_t)pl.splits * a.split_stride);
+  const CUtensorMap tmDY = tc_make_tmap(dyflat, (uint64_t)dy_chan, rows_total, (uint64_t)dy_chan * 4, 32, true);
+  const CUtensorMap tmX = tc_make_tmap(xflat, (uint64_t)x_chan, rows_total, (uint64_t)x_chan * 4, (uint32_t)pl.KR, true);
+  dim3 grid(a.m_tiles * a.n_tiles * a.n_groups_t * groups, pl.splits, 1);
   wgrad_window_kernel<<<grid, kWThreads, pl.smem, s>>>(tmDY, tmX, a);
-  int blocks = (int)((a.split_stride + 255) / 256);
-  if (blocks > 148 * 8) blocks = 148 * 8;
-  wgrad_reduce_kernel<<<blocks, 256, 0, s>>>(a.ws, pl.splits, a.split_stride, T, Cg, dw, accumulate ? 1 : 0);
-  count_launch(2);
+  count_launch();
+  if (!direct) {
+    int blocks = (int)((a.split_stride + 255) / 256);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    wgrad_reduce_kernel<<<blocks, 256, 0, s>>>(a.ws, pl.splits, a.split_stride, T, Cg, dw, accumulate ? 1 : 0);
+    count_launch();
+  }
   SN_CUDA(cudaGetLastError());
 }
-
+void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate) {
+  const FlatGeom f = tc_flat_geom(g);
+  wgrad_core(s, xflat, g.C, dyflat, g.Cout, tc_flat_rows(g), g.N * f.Gp, g.Og(), g.Cg(), g.group, g.kh * g.kw, g.kw, f.Wp, f.lead,
+             g.ph * f.Wp + g.pw, dw, accumulate);
+}
+// inner-product backward-filter (inner_product_layer.cpp:96-102): dW[o][k] (+)= sum_b dY[b][o] * X[b][k]
+bool tcw_matmul_wgrad_supported(int batch, int out, int K, const float* dy, const float* x, const float* dw) {
+  if (batch < 1 || out % 4 != 0 || K % 16 != 0 || out < 16) return false;
+  if (((uintptr_t)dy | (uintptr_t)x | (uintptr_t)dw) & 15) return false;
+  return plan_wgrad(batch, out, K, 1, 1, 1, 1).ok;
+}
+void tcw_matmul_wgrad(cudaStream_t s, int batch, int out, int K, const float* dy_r, const float* x_r, float* dw, bool accumulate) {
+  wgrad_core(s, x_r, K, dy_r, out, (size_t)batch, batch, out, K, 1, 1, 1, 1, 0, 0, dw, accumulate);
+}
 
 // ------------------------------------------------------------------------------------------
 // Strided convolutions (AlexNet conv1: 11x11, stride 4) through the same window kernels: with s x s pixel blocks

@@ -366,6 +366,58 @@ __global__ void __launch_bounds__(256) pool_max_bwd_fixed_kernel(PoolGeom g, uin
     dx[idx] = acc;
   }
 }
+// 3x3 / stride 2 / no padding (every max pooling of the four nets but LeNet's): one thread owns a 2x2 block of
+// input elements (rows 2a, 2a+1; columns 2b, 2b+1).  Only the four windows (a-1|a, b-1|b) can cover them, so four
+// (mask, dy, gate) loads serve four outputs, with no branches: the even/even element tests all four windows, the
+// even/odd and odd/even elements two, the odd/odd element one, always in the reference's (ph, pw) order.
+__global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_kernel(PoolGeom g, uint32_t total, FastDiv dB, FastDiv dA, const float* __restrict__ dy,
+                                                                 const int* __restrict__ mask, const float* __restrict__ gate,
+                                                                 float* __restrict__ dx) {
+  const int P = g.PH * g.PW, HW = g.H * g.W;
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    uint32_t t, b, plane, a;
+    dB.divmod(idx, t, b);
+    dA.divmod(t, plane, a);
+    const int h0 = 2 * (int)a, w0 = 2 * (int)b;
+    const int* mp = mask + (size_t)plane * P;
+    const float* gp = dy + (size_t)plane * P;
+    const float* tp = gate ? gate + (size_t)plane * P : nullptr;
+    int m[2][2];
+    float v[2][2];
+#pragma unroll
+    for (int i = 0; i < 2; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int ph = (int)a - 1 + i, pw = (int)b - 1 + j;
+        const bool ok = ph >= 0 && ph < g.PH && pw >= 0 && pw < g.PW;
+        const int o = ph * g.PW + pw;
+        m[i][j] = ok ? __ldg(mp + o) : -2;
+        float d = ok ? __ldg(gp + o) : 0.f;
+        if (tp && ok && !(__ldg(tp + o) > 0.f)) d = 0.f;
+        v[i][j] = d;
+      }
+    const int me00 = h0 * g.W + w0;
+    float* dp = dx + (size_t)plane * HW + me00;
+    float acc;
+    // (2a, 2b): windows (a-1,b-1), (a-1,b), (a,b-1), (a,b)
+    acc = (m[0][0] == me00 ? v[0][0] : 0.f);
+    acc += (m[0][1] == me00 ? v[0][1] : 0.f);
+    acc += (m[1][0] == me00 ? v[1][0] : 0.f);
+    acc += (m[1][1] == me00 ? v[1][1] : 0.f);
+    dp[0] = acc;
+    if (w0 + 1 < g.W) {                               // (2a, 2b+1): windows (a-1,b), (a,b)
+      acc = (m[0][1] == me00 + 1 ? v[0][1] : 0.f);
+      acc += (m[1][1] == me00 + 1 ? v[1][1] : 0.f);
+      dp[1] = acc;
+    }
+    if (h0 + 1 < g.H) {
+      acc = (m[1][0] == me00 + g.W ? v[1][0] : 0.f);  // (2a+1, 2b): windows (a,b-1), (a,b)
+      acc += (m[1][1] == me00 + g.W ? v[1][1] : 0.f);
+      dp[g.W] = acc;
+      if (w0 + 1 < g.W) dp[g.W + 1] = (m[1][1] == me00 + g.W + 1 ? v[1][1] : 0.f);   // (2a+1, 2b+1): window (a,b)
+    }
+  }
+}
 __global__ void pool_gate_kernel(size_t n, const float* __restrict__ dy, const float* __restrict__ gate, float* __restrict__ out) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = gate[i] > 0.f ? dy[i] : 0.f;
@@ -375,7 +427,9 @@ void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int*
   const size_t total_in = (size_t)g.N * g.C * g.H * g.W;
   const bool fixed = g.ph == 0 && g.pw == 0 && total_in < (1ull << 31);
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
-    pool_max_bwd_fixed_kernel<3, 3, 2, 2><<<grid_for(total_in, 256, 32), 256, 0, s>>>(g, (uint32_t)total_in, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx);
+    const int A = (g.H + 1) / 2, B = (g.W + 1) / 2;
+    const size_t total = (size_t)g.N * g.C * A * B;
+    pool_max_bwd_3x3s2_kernel<<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)B), FastDiv((uint32_t)A), dy, mask, gate, dx);
   } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
     pool_max_bwd_fixed_kernel<2, 2, 2, 2><<<grid_for(total_in, 256, 32), 256, 0, s>>>(g, (uint32_t)total_in, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx);
   } else if (smem <= 40 * 1024) {

@@ -62,6 +62,12 @@ ConvGeom tcw_s2d_geom(const ConvGeom& g);
 void tcw_s2d_pack_input(cudaStream_t s, const ConvGeom& g, const float* x, float* xflat);
 void tcw_s2d_pack_filter(cudaStream_t s, const ConvGeom& g, const float* w, float* wf);
 void tcw_s2d_unpack_wgrad(cudaStream_t s, const ConvGeom& g, const float* dws, float* dw, bool accumulate);
+// out[m][n] = sum_k A[m][k] * B(n,k) (+ bias[n], ReLU) on the window kernel; A [M][K] tf32-rounded, B [N][K] or (b_mn) [K][N]
+bool tcw_matmul_supported(int M, int N, int K, const float* A, const float* B, bool b_mn, const float* out);
+void tcw_matmul(cudaStream_t s, int M, int N, int K, const float* A, const float* B, bool b_mn, const float* bias, bool relu, float* out);
+// dW[o][k] (+)= sum_b dY[b][o] * X[b][k], both operands tf32-rounded row-major matrices
+bool tcw_matmul_wgrad_supported(int batch, int out, int K, const float* dy, const float* x, const float* dw);
+void tcw_matmul_wgrad(cudaStream_t s, int batch, int out, int K, const float* dy_r, const float* x_r, float* dw, bool accumulate);
 void tcw_set_debug(int what, int value);
 int tcw_read_stamps(long long* out, int max_ctas);
 float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int ctas, float* issue_only);

@@ -496,26 +496,60 @@ struct InnerProductLayer : Layer {
     ts.push_back(N);
     top[0]->reshape(ts);
   }
+  // ---- all-TMA path (conv_flat.cu tcw_matmul*): operands that are not weights get a tf32-rounded copy first ----
+  float *x_r = nullptr, *dy_r = nullptr;
+  uint64_t x_r_gen = ~0ull;
+  const Storage* x_r_src = nullptr;
+  int tma_ok = -1;
+  bool use_tma() {                                     // SPARKNET_IP_TMA=0 keeps the gather kernels of gemm_tc.cu
+    if (tma_ok < 0) {
+      const char* e = getenv("SPARKNET_IP_TMA");
+      tma_ok = (e && atoi(e) == 0) ? 0 : 1;
+    }
+    return tma_ok != 0;
+  }
+  const float* rounded_input(Blob* bottom) {
+    const float* x = bottom->data->gpu();
+    if (!x_r) SN_CUDA(cudaMalloc(&x_r, (size_t)M * K * sizeof(float)));
+    if (x_r_src != bottom->data.get() || x_r_gen != bottom->data->gen) {
+      tc_round_to_tf32(S(), (size_t)M * K, x, x_r);
+      x_r_src = bottom->data.get();
+      x_r_gen = bottom->data->gen;
+    }
+    return x_r;
+  }
+  ~InnerProductLayer() override { cudaFree(x_r); cudaFree(dy_r); }
   void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const float* x = bottom[0]->data->gpu();
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
-    if (net->precision == PREC_TF32) tc_ip_fwd(S(), M, N, K, x, weights_tf32(), b, y, fuse_relu);
+    if (net->precision == PREC_TF32 && use_tma() && tcw_matmul_supported(M, N, K, x, blobs[0]->data->gpu(), false, y))
+      tcw_matmul(S(), M, N, K, rounded_input(bottom[0]), weights_tf32(), false, b, fuse_relu, y);
+    else if (net->precision == PREC_TF32) tc_ip_fwd(S(), M, N, K, x, weights_tf32(), b, y, fuse_relu);
     else ffma_ip_fwd(S(), M, N, K, x, blobs[0]->data->gpu(), b, y, fuse_relu);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     const float* dy = top[0]->diff->gpu();
     const bool acc = !net->overwrite_param_diffs;
+    const bool tf32 = net->precision == PREC_TF32;
+    const float* x = bottom[0]->data->gpu();
+    const bool tma_w = tf32 && use_tma() && param_propagate_down[0] && tcw_matmul_wgrad_supported(M, N, K, dy, x, blobs[0]->diff->gpu());
+    const bool tma_d = tf32 && use_tma() && pd[0] && tcw_matmul_supported(M, K, N, dy, blobs[0]->data->gpu(), true, bottom[0]->diff->gpu());
+    if (tma_w || tma_d) {
+      if (!dy_r) SN_CUDA(cudaMalloc(&dy_r, (size_t)M * N * sizeof(float)));
+      tc_round_to_tf32(S(), (size_t)M * N, dy, dy_r);
+    }
     if (param_propagate_down[0]) {
-      const float* x = bottom[0]->data->gpu();
       float* dw = blobs[0]->diff->mutable_gpu();
-      if (net->precision == PREC_TF32) tc_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
+      if (tma_w) tcw_matmul_wgrad(S(), M, N, K, dy_r, rounded_input(bottom[0]), dw, acc);
+      else if (tf32) tc_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
       else ffma_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
     }
     if (bias_term && param_propagate_down[1]) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
     if (pd[0]) {
       float* dx = bottom[0]->diff->mutable_gpu();
-      if (net->precision == PREC_TF32) tc_ip_dgrad(S(), M, N, K, dy, weights_tf32(), dx);
+      if (tma_d) tcw_matmul(S(), M, K, N, dy_r, weights_tf32(), true, nullptr, false, dx);
+      else if (tf32) tc_ip_dgrad(S(), M, N, K, dy, weights_tf32(), dx);
       else ffma_ip_dgrad(S(), M, N, K, dy, blobs[0]->data->gpu(), dx);
     }
   }
