@@ -929,7 +929,12 @@ void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db
 // Blobs start on 1024-element boundaries in the arena, so chunk_table[i/1024] gives the blob's
 // (lr_mult, local_decay); local_rate = rate * lr_mult is formed in fp32 as in the reference.
 // ------------------------------------------------------------------------------------------
-__global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ h,
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ h, float4* __restrict__ shadow,
                                   const SgdChunk* __restrict__ table, float rate, float mu) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const SgdChunk ck = table[i >> 8];           // 1024 floats = 256 float4
@@ -945,12 +950,14 @@ __global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __r
     SN_SGD1(x) SN_SGD1(y) SN_SGD1(z) SN_SGD1(w)
 #undef SN_SGD1
     w[i] = wv; g[i] = gv; h[i] = hv;
+    // tf32-rounded copy for the TMA-fed tensor-core operands (saves a separate 8 B/parameter rounding pass per step)
+    if (shadow) shadow[i] = make_float4(round_tf32(wv.x), round_tf32(wv.y), round_tf32(wv.z), round_tf32(wv.w));
   }
 }
-void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, const SgdChunk* chunk_table, float rate,
+void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, float* shadow, const SgdChunk* chunk_table, float rate,
                 float momentum) {
   if (n % 1024) fatal("sgd_update: arena length %zu is not a multiple of 1024", n);
-  sgd_update_kernel<<<grid_for(n / 4, 256), 256, 0, s>>>(n / 4, (float4*)w, (float4*)g, (float4*)h, chunk_table, rate, momentum);
+  sgd_update_kernel<<<grid_for(n / 4, 256), 256, 0, s>>>(n / 4, (float4*)w, (float4*)g, (float4*)h, (float4*)shadow, chunk_table, rate, momentum);
   count_launch();
 }
 

@@ -116,7 +116,8 @@ void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db
 // fused SGD step over the whole parameter arena (sgd_solver.cpp:145-239 + blob.cpp:154-162):
 //   g += decay*w ; h = momentum*h + rate*g ; g = h ; w -= h       per 1024-element chunk table
 struct SgdChunk { float lr_mult, decay; };     // per-chunk lr_mult and local_decay (= weight_decay * decay_mult)
-void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, const SgdChunk* chunk_table, float rate,
+// shadow (nullable): receives the tf32-rounded new weights, same layout as w
+void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, float* shadow, const SgdChunk* chunk_table, float rate,
                 float momentum);
 
 void fill(cudaStream_t s, size_t n, float* p, float v);

@@ -176,10 +176,20 @@ static void fill_blob(const cp::FillerParameter& f, Blob* b) {
   }
 }
 
+Layer::~Layer() {
+  if (w_shadow && !w_shadow_in_arena) cudaFree(w_shadow);
+}
 const float* Layer::weights_tf32() {
   Storage* st = blobs[0]->data.get();
   const float* w = st->gpu();
-  if (!w_shadow) SN_CUDA(cudaMalloc(&w_shadow, st->count * sizeof(float)));
+  if (!w_shadow) {
+    if (net && net->arena_s && w >= net->arena_w && w < net->arena_w + net->arena_floats) {
+      w_shadow = net->arena_s + (w - net->arena_w);
+      w_shadow_in_arena = true;
+    } else {
+      SN_CUDA(cudaMalloc(&w_shadow, st->count * sizeof(float)));
+    }
+  }
   if (w_shadow_gen != st->gen) {
     tc_round_to_tf32(ctx().compute, st->count, w, w_shadow);
     w_shadow_gen = st->gen;
@@ -1015,6 +1025,8 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
     SN_CUDA(cudaMalloc(&arena_g, arena_floats * sizeof(float)));
     SN_CUDA(cudaMemset(arena_w, 0, arena_floats * sizeof(float)));
     SN_CUDA(cudaMemset(arena_g, 0, arena_floats * sizeof(float)));
+    SN_CUDA(cudaMalloc(&arena_s, arena_floats * sizeof(float)));
+    SN_CUDA(cudaMemset(arena_s, 0, arena_floats * sizeof(float)));
     owns_arena = true;
     for (size_t i = 0; i < learnable_params.size(); ++i) {
       Blob* b = learnable_params[i];
@@ -1033,7 +1045,13 @@ Net::~Net() {
   if (owns_arena) {
     cudaFree(arena_w);
     cudaFree(arena_g);
+    cudaFree(arena_s);
   }
+}
+// after sgd_update wrote the rounded weights into the shadow arena: layers whose shadow lives there need no re-rounding
+void Net::mark_shadows_current() {
+  for (auto& l : layers)
+    if (l->w_shadow_in_arena && !l->blobs.empty()) l->w_shadow_gen = l->blobs[0]->data->gen;
 }
 void Net::forward_from_to(int start, int end) {
   for (int i = start; i <= end; ++i) layers[(size_t)i]->forward(bottom_vecs[(size_t)i], top_vecs[(size_t)i]);
@@ -1143,8 +1161,9 @@ void Solver::step(int iters) {
       fprintf(stderr, "Iteration %d, loss = %g, lr = %g\n", iter, loss, get_learning_rate());
     }
     const float rate = get_learning_rate();
-    if (net->arena_floats) sgd_update(ctx().compute, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
+    if (net->arena_floats) sgd_update(ctx().compute, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum);
     for (Blob* b : net->learnable_params) ++b->data->gen;    // weights changed on the device
+    net->mark_shadows_current();                              // ... and sgd_update rounded them into the shadow arena
     // this iteration's loss goes to the pinned host ring too: 4 bytes, asynchronous, read after the caller's next sync
     SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost,
                             ctx().compute));
@@ -1174,11 +1193,12 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
   }
   SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L)], s));
   const float rate = get_learning_rate();
-  if (net->arena_floats) sgd_update(s, net->arena_floats, net->arena_w, net->arena_g, arena_h, chunk_table, rate, param.momentum);
+  if (net->arena_floats) sgd_update(s, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum);
   SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L + 1)], s));
   SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost, s));
   SN_CUDA(cudaStreamSynchronize(s));
   for (Blob* b : net->learnable_params) ++b->data->gen;
+  net->mark_shadows_current();
   ++iter;
   net->overwrite_param_diffs = false;
   net->loss_log = nullptr;

@@ -100,7 +100,7 @@ struct Layer {
   std::vector<bool> param_propagate_down;
   std::vector<float> loss;
   explicit Layer(const cp::LayerParameter& p) : lp(p) {}
-  virtual ~Layer() {}
+  virtual ~Layer();
   virtual const char* type() const = 0;
   virtual void setup(const std::vector<Blob*>& bottom, const std::vector<Blob*>& top) = 0;
   virtual void forward(const std::vector<Blob*>& bottom, const std::vector<Blob*>& top) = 0;
@@ -109,6 +109,7 @@ struct Layer {
   void set_loss_weights(const std::vector<Blob*>& top);
   // tf32-rounded copy of blobs[0] for the TMA-fed tensor-core operands, re-rounded when the weights changed
   float* w_shadow = nullptr;
+  bool w_shadow_in_arena = false;       // points into the net's shadow arena, which the fused SGD update keeps current
   uint64_t w_shadow_gen = ~0ull;
   const float* weights_tf32();
 };
@@ -136,12 +137,14 @@ struct Net {
   // parameter arena (weights | gradients), blobs start on 1024-float boundaries
   float* arena_w = nullptr;
   float* arena_g = nullptr;
+  float* arena_s = nullptr;             // tf32-rounded shadow of arena_w (same layout), written by sgd_update
   size_t arena_floats = 0;
   std::vector<size_t> param_offsets;
   bool owns_arena = false;
 
   Net(const cp::NetParameter& param, int phase, uint64_t seed);
   ~Net();
+  void mark_shadows_current();
   void forward_from_to(int start, int end);
   void backward_from_to(int start, int end);
   void share_trained_layers_with(const Net& other);
