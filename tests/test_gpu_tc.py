@@ -5,9 +5,9 @@ import numpy as np
 import pytest
 
 from sparknet_b200 import zoo
-from sparknet_b200.layers import InnerProductLayer, ReLULayer, gaussian
+from sparknet_b200.layers import InnerProductLayer, LRNLayer, PoolingLayer, ReLULayer, gaussian
 from sparknet_b200.net import CaffeNet, MinibatchSource
-from tests.harness import assert_mostly_close, fptr, rel_err, synthetic_batches
+from tests.harness import LayerNet, assert_mostly_close, fptr, rel_err, synthetic_batches
 from tests.test_gpu_layers import CONV_CASES, assert_close, conv_layer, run_pair
 
 pytestmark = pytest.mark.gpu
@@ -102,6 +102,57 @@ def test_inner_product_tf32(oracle, product, shape, n_out):
     assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
     for j, (a, b) in enumerate(zip(*r["wdiff"]["ip"])):
         assert_close(a, b, TOL, f"param diff {j}")
+
+
+# shapes that take the all-TMA matrix path (csrc/conv_flat.cu tcw_matmul*): single CTA, CTA pair, two accumulators per
+# CTA, partial last column tile, reduction not a multiple of 32; SPARKNET_IP_TMA=0 keeps them on the gather kernels
+IP_TMA_CASES = [((96, 200), 64), ((129, 512), 320), ((300, 96), 272), ((256, 36, 4, 4), 1000), ((40, 100), 16)]
+
+
+@pytest.mark.parametrize("tma", ["1", "0"])
+@pytest.mark.parametrize("shape,n_out", IP_TMA_CASES)
+def test_inner_product_tma_and_gather_paths_tf32(oracle, product, monkeypatch, shape, n_out, tma):
+    monkeypatch.setenv("SPARKNET_IP_TMA", tma)
+    x = np.random.default_rng(12).standard_normal(shape).astype(F)
+    l = InnerProductLayer("ip", ["data"], n_out, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5))
+    r = run_pair(oracle, product, {"data": x}, [l], "ip", "ip", precision=1)
+    assert_close(r["fwd"][0]["ip"], r["fwd"][1]["ip"], TOL, "top")
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["ip"])):
+        assert_close(a, b, TOL, f"param diff {j}")
+
+
+@pytest.mark.parametrize("shape,kernel,stride", [((3, 16, 27, 27), 3, 2), ((2, 16, 32, 30), 3, 2), ((2, 16, 12, 12), 2, 2)])
+def test_relu_backward_folded_into_max_pool_backward(oracle, product, monkeypatch, shape, kernel, stride):
+    """conv -> in-place ReLU -> MAX pool -> LRN, the CaffeNet pattern.  With SPARKNET_FUSE_RELU_POOL=1 (default) the pool's
+    backward applies the ReLU gate and the ReLU layer's own backward is skipped: the result must be BIT-identical to the
+    unfused product (same forward, same gates), and match the oracle."""
+    x = np.random.default_rng(9).standard_normal(shape).astype(F)
+    layers = [conv_layer("conv", "data", 32, kernel_size=[3], pad=[1], weight_filler=gaussian(0.1), bias_filler=gaussian(0.1)),
+              ReLULayer("relu", ["conv"]), PoolingLayer("pool", ["conv"], "MAX", kernel, stride),
+              LRNLayer("norm", ["pool"], 5, 1e-4, 0.75)]
+    # fp32 FFMA mode: the forward passes agree to ~1e-6, so oracle and product open the same gates
+    monkeypatch.setenv("SPARKNET_FUSE_RELU_POOL", "1")
+    r = run_pair(oracle, product, {"data": x}, layers, "norm", "conv", precision=0)
+    # the unfused product on the same weights and the same top gradient (the switch is read when a net is built)
+    monkeypatch.setenv("SPARKNET_FUSE_RELU_POOL", "0")
+    o, fused = r["nets"]
+    u = LayerNet(product, {"data": x}, layers)
+    product.sparknet_set_precision(u.state, 0)
+    u.set_weights("conv", o.weights("conv"))
+    u.forward()
+    u.zero_param_diffs()
+    u.set_diff("norm", np.random.default_rng(3).standard_normal(r["fwd"][0]["norm"].shape).astype(F))
+    ub = u.backward()
+    for k in ("conv", "data"):
+        assert np.array_equal(r["bwd"][1][k], ub[k]), k
+    for a, b in zip(r["wdiff"]["conv"][1], u.weights("conv", True)):
+        assert np.array_equal(a, b)
+    assert_close(r["fwd"][0]["norm"], r["fwd"][1]["norm"], 1e-5, "top")
+    assert_mostly_close(r["bwd"][1]["conv"], r["bwd"][0]["conv"], 1e-4, "diff behind the ReLU")
+    assert_mostly_close(r["bwd"][1]["data"], r["bwd"][0]["data"], 1e-4, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["conv"])):
+        assert_mostly_close(b, a, 1e-4, f"param diff {j}")
 
 
 def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
