@@ -236,7 +236,7 @@ def main():
     precision = lib.sparknet_get_precision(st)
     imgs, labs = synthetic_pool(name, batch, args.pool, 1701 + rank)
     src = MinibatchSource(imgs, labs)
-    net.copy_threads = int(os.environ.get("SPARKNET_COPY_THREADS", 0)) or max(1, min(8, (os.cpu_count() or 1) // max(1, world)))   # host threads of the data callback's copy
+    net.copy_threads = int(os.environ.get("SPARKNET_COPY_THREADS", 0)) or max(1, min(16, (os.cpu_count() or 1) // max(1, world)))   # host threads of the data callback's copy
     net.setTrainData(src)
     averager = Averager(lib, net, rank, world)
     averager.broadcast_from_rank0()                     # all replicas start from the same weights (CifarApp.scala:92-99)
