@@ -33,7 +33,12 @@ using namespace tc;
 CUtensorMap tc_make_tmap(const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes, uint32_t box_outer, bool mn_major);
 
 constexpr int kWEpiWarps = 8;
-constexpr int kWThreads = (kWEpiWarps + 2) * 32;
+// One thread issuing every tcgen05.mma is latency-bound on its own instruction stream (~150-250 dependent uniform-datapath
+// instructions per tap at ~5 clocks each: measured 900-1250 clocks per tap where the tensor pipe needs 512-768).  Up to
+// four warps issue instead, one accumulator (forward / backward-data) or every fourth tap (backward-filter) each.
+constexpr int kWMmaWarps = 4;
+constexpr int kWTmaWarp = kWEpiWarps + kWMmaWarps;
+constexpr int kWThreads = (kWEpiWarps + kWMmaWarps + 1) * 32;
 constexpr int kWMaxStages = 8;
 constexpr size_t kWSmemLimit = 227 * 1024;
 
@@ -83,9 +88,10 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   uint8_t* bst = smem + a.nwin * win_bytes;
 
   if (tid == 0) {
-    for (int i = 0; i < a.nwin; ++i) { mbar_init(&win_full[i], 1u); mbar_init(&win_empty[i], 1u); }
-    for (int i = 0; i < a.nstage; ++i) { mbar_init(&b_full[i], 1u); mbar_init(&b_empty[i], 1u); }
-    mbar_init(&tmem_full, 1u);
+    // every accumulator has its own issuing warp: MT commits free a stage / complete the tile
+    for (int i = 0; i < a.nwin; ++i) { mbar_init(&win_full[i], 1u); mbar_init(&win_empty[i], (uint32_t)a.MT); }
+    for (int i = 0; i < a.nstage; ++i) { mbar_init(&b_full[i], 1u); mbar_init(&b_empty[i], (uint32_t)a.MT); }
+    mbar_init(&tmem_full, (uint32_t)a.MT);
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -164,9 +170,11 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
       }
     }
-  } else if (warp == kWEpiWarps) {
-    // ---------------- MMA issuer (rank 0 of a pair): the whole warp walks the pipeline, one elected lane issues ----------------
-    if (rank == 0) {
+  } else if (warp < kWTmaWarp) {
+    // ---------------- MMA issuers (rank 0 of a pair): warp mi owns accumulator mi; the whole warp walks the pipeline,
+    // one elected lane issues ----------------
+    const int mi = warp - kWEpiWarps;
+    if (rank == 0 && mi < a.MT) {
       const uint32_t idesc = make_idesc_tf32(128 * CG, a.n_mma, 0, a.b_mn);
       // descriptor = {lo: start >> 4 | LBO << 16, hi: SBO | version 1 | layout}; only lo moves.
       // K-major (SWIZZLE_128B): LBO 16 B (unused), SBO 1024 B, +32 B per k-step of 8.
@@ -179,29 +187,29 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       uint32_t sphase = 0, wphase = 0;
       long long wait_win = 0, wait_b = 0;
       for (int cb = cb_begin; cb < cb_end; ++cb) {
-        long long tw = stamp ? clock64() : 0;
+        long long tw = (stamp && mi == 0) ? clock64() : 0;
         mbar_wait(&win_full[wb], wphase);
-        if (stamp) wait_win += clock64() - tw;
+        if (stamp && mi == 0) wait_win += clock64() - tw;
         const int left = a.red - cb * 32, ks = left >= 32 ? 4 : (left + 7) / 8;
         uint32_t shift_row = 0;                                     // (ky * Wp) in rows
         int kx = 0;
         for (int tap = 0; tap < a.T; ++tap, ++it) {
-          tw = stamp ? clock64() : 0;
+          tw = (stamp && mi == 0) ? clock64() : 0;
           mbar_wait(&b_full[s], sphase);
           tc_fence_after_sync();
-          if (stamp) wait_b += clock64() - tw;
+          if (stamp && mi == 0) wait_b += clock64() - tw;
           // The 128-byte swizzle is a function of the absolute shared-memory address (bits 4-6 ^= bits 7-9), for the
           // TMA write and for the MMA read alike, so a descriptor may start at any row of the window: the
           // base-offset field stays 0 (verified on B200 with tools/debug_window.py).
           if (elect_one_sync()) {
             const uint32_t a_lo = win_lo + (uint32_t)wb * win_step + (shift_row + (uint32_t)kx) * 8u;   // 128 B per row >> 4
             const uint32_t b_lo = b_lo0 + (uint32_t)s * b_step;
-            for (int i = 0; i < a.MT; ++i) {
-              const uint32_t d = tmem_base + (uint32_t)(i * a.n_mma);
+            {
+              const uint32_t d = tmem_base + (uint32_t)(mi * a.n_mma);
 #pragma unroll 4
               for (int j = 0; j < ks; ++j) {
-                if (CG == 2) mma_tf32_lohi2_pair(d, a_lo + (uint32_t)(i * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
-                else mma_tf32_lohi2(d, a_lo + (uint32_t)(i * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
+                if (CG == 2) mma_tf32_lohi2_pair(d, a_lo + (uint32_t)(mi * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
+                else mma_tf32_lohi2(d, a_lo + (uint32_t)(mi * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
               }
             }
             const bool last_tap = tap == a.T - 1, last = last_tap && cb == cb_end - 1;
@@ -221,7 +229,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
         if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
       }
-      if (stamp && lane == 0) { stamp[2] = wait_win; stamp[3] = wait_b; }
+      if (stamp && lane == 0 && mi == 0) { stamp[2] = wait_win; stamp[3] = wait_b; }
     }
   } else {
     // ---------------- TMA issuer (both CTAs of a pair; completion bytes land on rank 0's barriers) ----------------
@@ -272,13 +280,13 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 template <int CG>
 __global__ void __launch_bounds__(128, 1) mma_rate_kernel(int n_mma, int iters, int shift_rows, int nacc, long long* out) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t done;
+  __shared__ uint64_t done, scratch_bar;
   __shared__ uint32_t tmem_base_smem;
   const int tid = threadIdx.x, warp = tid >> 5;
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  for (int i = tid; i < 96 * 1024 / 4; i += blockDim.x) ((float*)smem)[i] = 0.f;
-  if (tid == 0) { mbar_init(&done, 1u); fence_barrier_init(); }
+  for (int i = tid; i < 216 * 1024 / 4; i += blockDim.x) ((float*)smem)[i] = 0.f;
+  if (tid == 0) { mbar_init(&done, 1u); mbar_init(&scratch_bar, 1u << 20); fence_barrier_init(); }
   if (warp == 0) { if (CG == 2) tmem_alloc_pair<512>(&tmem_base_smem); else tmem_alloc<512>(&tmem_base_smem); }
   fence_proxy_async_smem();
   tc_fence_before_sync();
@@ -289,16 +297,32 @@ __global__ void __launch_bounds__(128, 1) mma_rate_kernel(int n_mma, int iters, 
     const uint32_t idesc = make_idesc_tf32(128 * CG, n_mma, 0, 0);
     const uint32_t desc_hi = (uint32_t)(make_smem_desc(0, 16, 1024, kLayoutSW128) >> 32);
     const uint32_t a_lo = ((smem_u32(smem) >> 4) | (1u << 16)) + (uint32_t)shift_rows * 8u;
-    const uint32_t b_lo = ((smem_u32(smem) + 48 * 1024) >> 4) | (1u << 16);
+    const uint32_t b_lo = ((smem_u32(smem) + 88 * 1024) >> 4) | (1u << 16);
     long long t0 = 0, t1 = 0;
     if (elect_one_sync()) {
       t0 = clock64();
+      // shift_rows >= 1000 selects the pipeline-like pattern: per "tap" nacc accumulators x 4 k-steps, a commit after every
+      // tap (to a barrier nobody waits on), the A start row and the B stage changing from tap to tap
+      const bool piped = shift_rows >= 1000;
       for (int it = 0; it < iters; ++it) {
-        const uint32_t d = tmem_base + (uint32_t)((it % nacc) * n_mma);
+        if (!piped) {
+          const uint32_t d = tmem_base + (uint32_t)((it % nacc) * n_mma);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          if (CG == 2) mma_tf32_lohi_pair(d, a_lo + 2 * j, b_lo + 2 * j, desc_hi, idesc, 1u);
-          else mma_tf32_lohi(d, a_lo + 2 * j, b_lo + 2 * j, desc_hi, idesc, 1u);
+          for (int j = 0; j < 4; ++j) {
+            if (CG == 2) mma_tf32_lohi_pair(d, a_lo + 2 * j, b_lo + 2 * j, desc_hi, idesc, 1u);
+            else mma_tf32_lohi(d, a_lo + 2 * j, b_lo + 2 * j, desc_hi, idesc, 1u);
+          }
+        } else {
+          const uint32_t ash = (uint32_t)((it % 9) * 3) * 8u, bsh = (uint32_t)(it % 4) * (uint32_t)(n_mma * 128 / CG / 16);
+          for (int i = 0; i < nacc; ++i) {
+            const uint32_t d = tmem_base + (uint32_t)(i * n_mma);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              if (CG == 2) mma_tf32_lohi_pair(d, a_lo + ash + (uint32_t)(i * 1024 + 2 * j), b_lo + bsh + 2 * j, desc_hi, idesc, 1u);
+              else mma_tf32_lohi(d, a_lo + ash + (uint32_t)(i * 1024 + 2 * j), b_lo + bsh + 2 * j, desc_hi, idesc, 1u);
+            }
+          }
+          if (shift_rows == 1001) { if (CG == 2) mma_commit_pair(&scratch_bar); else mma_commit(&scratch_bar); }
         }
       }
       t1 = clock64();
@@ -320,7 +344,7 @@ float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int c
   long long* d = nullptr;
   SN_CUDA(cudaMalloc(&d, sizeof(long long) * 2 * ctas));
   SN_CUDA(cudaMemset(d, 0, sizeof(long long) * 2 * ctas));
-  const size_t smem = 97 * 1024 + 1024;
+  const size_t smem = 217 * 1024 + 1024;
   if (cg == 2) {
     SN_CUDA(cudaFuncSetAttribute(mma_rate_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaLaunchConfig_t cfg = {};
@@ -340,8 +364,9 @@ float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int c
   cudaFree(d);
   double a = 0, b = 0; int n = 0;
   for (int i = 0; i < ctas; i += cg) { a += (double)h[2 * i]; b += (double)h[2 * i + 1]; ++n; }
-  if (issue_only) *issue_only = (float)(a / n / (iters * 4.0));
-  return (float)(b / n / (iters * 4.0));
+  const double per = shift_rows >= 1000 ? iters * 4.0 * nacc : iters * 4.0;
+  if (issue_only) *issue_only = (float)(a / n / per);
+  return (float)(b / n / per);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -597,8 +622,9 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
   const uint32_t stage_bytes = a_bytes + b_bytes;                          // multiple of 1024 (KR % 8 == 0)
 
   if (tid == 0) {
-    for (int i = 0; i < a.nstage; ++i) { mbar_init(&full[i], 1u); mbar_init(&empty[i], 1u); }
-    mbar_init(&tmem_full, 1u);
+    const uint32_t issuers = (uint32_t)min(kWMmaWarps, nt);            // MMA warps that commit on every stage
+    for (int i = 0; i < a.nstage; ++i) { mbar_init(&full[i], 1u); mbar_init(&empty[i], issuers); }
+    mbar_init(&tmem_full, issuers);
     fence_barrier_init();
     tma_prefetch_desc(&tmDY);
     tma_prefetch_desc(&tmX);
@@ -639,33 +665,42 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
         }
       }
     }
-  } else if (warp == kWEpiWarps) {
-    // ---------------- MMA issuer ----------------
-    const uint32_t idesc = make_idesc_tf32(128, a.n_mma, 1, 1);
-    // MN-major descriptors: A blocks (32 co) are 4096 B apart, B blocks (32 c) KR * 128 B apart; 4-row atoms 512 B apart
-    const uint32_t a_hi = (uint32_t)(make_smem_desc(0, 4096, 512, kLayoutSW128Base32) >> 32);
-    const uint32_t a_lo_flags = (4096u >> 4) << 16, b_lo_flags = (blk_bytes >> 4) << 16;
-    int s = 0;
-    uint32_t phase = 0;
-    for (int kc = 0; kc < nchunks; ++kc) {
-      mbar_wait(&full[s], phase);
-      tc_fence_after_sync();
-      if (elect_one_sync()) {
-        const uint32_t a_addr = smem_u32(smem) + (uint32_t)s * stage_bytes, b_addr = a_addr + a_bytes;
-        int ky = t0 / a.kw, kx = t0 % a.kw;
-        for (int ts = 0; ts < nt; ++ts) {
-          const uint32_t shift = (uint32_t)(ky * a.Wp + kx - sh0);
-          const uint32_t a_lo = (a_addr >> 4) | a_lo_flags, b_lo = ((b_addr + shift * 128u) >> 4) | b_lo_flags;
-          const uint32_t d = tmem_base + (uint32_t)(ts * a.n_mma);
-#pragma unroll
-          for (int j = 0; j < 4; ++j) mma_tf32_lohi(d, a_lo + 64u * j, b_lo + 64u * j, a_hi, idesc, (kc | j) != 0 ? 1u : 0u);
-          if (++kx == a.kw) { kx = 0; ++ky; }
-        }
-        mma_commit(&empty[s]);
-        if (kc == nchunks - 1) mma_commit(&tmem_full);
+  } else if (warp < kWTmaWarp) {
+    // ---------------- MMA issuers: warp mi takes the taps t0 + mi, t0 + mi + issuers, ... (one accumulator each) ----------------
+    const int mi = warp - kWEpiWarps, issuers = min(kWMmaWarps, nt);
+    if (mi < issuers) {
+      const uint32_t idesc = make_idesc_tf32(128, a.n_mma, 1, 1);
+      // MN-major descriptors: A blocks (32 co) are 4096 B apart, B blocks (32 c) KR * 128 B apart; 4-row atoms 512 B apart
+      const uint32_t a_hi = (uint32_t)(make_smem_desc(0, 4096, 512, kLayoutSW128Base32) >> 32);
+      const uint32_t a_lo_flags = (4096u >> 4) << 16, b_lo_flags = (blk_bytes >> 4) << 16;
+      constexpr int kMaxMine = 16;                                          // taps per issuing warp (nt <= 64)
+      uint32_t shift8[kMaxMine];                                            // (row shift of my k-th tap) * 128 B >> 4
+      int mine = 0;
+      for (int ts = mi; ts < nt && mine < kMaxMine; ts += issuers, ++mine) {
+        const int t = t0 + ts;
+        shift8[mine] = (uint32_t)((t / a.kw) * a.Wp + t % a.kw - sh0) * 8u;
       }
-      __syncwarp();
-      if (++s == a.nstage) { s = 0; phase ^= 1u; }
+      int s = 0;
+      uint32_t phase = 0;
+      for (int kc = 0; kc < nchunks; ++kc) {
+        mbar_wait(&full[s], phase);
+        tc_fence_after_sync();
+        if (elect_one_sync()) {
+          const uint32_t a_addr = smem_u32(smem) + (uint32_t)s * stage_bytes, b_addr = a_addr + a_bytes;
+          const uint32_t a_lo = (a_addr >> 4) | a_lo_flags, b_lo0 = (b_addr >> 4) | b_lo_flags;
+#pragma unroll 1
+          for (int k = 0; k < mine; ++k) {
+            const uint32_t b_lo = b_lo0 + shift8[k];
+            const uint32_t d = tmem_base + (uint32_t)((mi + k * issuers) * a.n_mma);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) mma_tf32_lohi(d, a_lo + 64u * j, b_lo + 64u * j, a_hi, idesc, (kc | j) != 0 ? 1u : 0u);
+          }
+          mma_commit(&empty[s]);
+          if (kc == nchunks - 1) mma_commit(&tmem_full);
+        }
+        __syncwarp();
+        if (++s == a.nstage) { s = 0; phase ^= 1u; }
+      }
     }
   } else {
     // ---------------- TMA issuer ----------------

@@ -7,7 +7,14 @@ lib.set_mode_gpu()
 f = lib.sparknet_debug_mma_rate
 f.restype = ctypes.c_float
 f.argtypes = [ctypes.c_int] * 6 + [ctypes.POINTER(ctypes.c_float)]
-for ctas in (2, 148):
+print("pipeline-like pattern (per tap: nacc accumulators x 4 k-steps; A row start and B stage change per tap):")
+for cg in (1, 2):
+    for n, nacc in ((48, 4), (96, 4), (128, 4), (128, 2), (192, 2), (256, 2), (256, 1)):
+        for mode, name in ((1000, "no commit"), (1001, "commit per tap")):
+            io = ctypes.c_float(0)
+            r = f(cg, n, 500, mode, nacc, 148, ctypes.byref(io))
+            print(f"  cg {cg} N {n:3d} nacc {nacc} {name:15s}: {r:7.1f} clk/MMA (ideal {n/2:5.1f})", flush=True)
+for ctas in (148,):
     for cg in (1, 2):
         for n in (48, 96, 128, 192, 256):
             for shift, nacc in ((0, 1), (3, 1), (0, 2)):
