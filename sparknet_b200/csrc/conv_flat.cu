@@ -57,6 +57,8 @@ struct WinArgs {
   int nwin;                 // window buffers (2 for convolutions: a window lives for T taps; up to 8 when T = 1)
   int splits, cb_per_split; // the reduction's channel blocks are cut into `splits` ranges (blockIdx.z = group * splits + split)
   int b_mn;                 // B operand stored [reduction][n] (n contiguous): MN-major tiles of 32 n x 32 rows per TMA box
+  // --- persistent CTAs: cluster c works on tiles c, c + #clusters, ...; tile t = (m unit, n tile, z) with the m unit fastest ---
+  int m_units, n_tiles, total_tiles;   // m unit = MT*128 rows per CTA, one per CTA of the cluster
 };
 // m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell.
 // ld > 0 selects the matrix epilogue instead: dst[split][m][ld] row-major (bias / ReLU only when splits == 1).
@@ -73,14 +75,13 @@ template <int CG>
 __global__ void __launch_bounds__(kWThreads, 1)
 conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const WinArgs a, const WinEpi ep) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t win_full[kWMaxStages], win_empty[kWMaxStages], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full;
+  __shared__ uint64_t win_full[kWMaxStages], win_empty[kWMaxStages], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full, tmem_empty;
   __shared__ uint32_t tmem_base_smem;
 
   const long long t_enter = clock64();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int rank = CG == 2 ? (int)cluster_ctarank() : 0;
-  const int q0 = blockIdx.x * a.MT * 128, n0 = blockIdx.y * a.n_mma, grp = blockIdx.z / a.splits, split = blockIdx.z % a.splits;
-  const int cb_begin = split * a.cb_per_split, cb_end = min(a.ncb, cb_begin + a.cb_per_split);   // never empty (host)
+  const int cluster_id = blockIdx.x / CG, n_clusters = gridDim.x / CG;
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const uint32_t win_bytes = (uint32_t)(a.nbox * a.box_rows) * 128u;      // multiple of 1024 (box_rows % 8 == 0)
   const int nb_local = a.n_mma / CG;                                      // filter rows this CTA stages per chunk
@@ -92,6 +93,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     for (int i = 0; i < a.nwin; ++i) { mbar_init(&win_full[i], 1u); mbar_init(&win_empty[i], (uint32_t)a.MT); }
     for (int i = 0; i < a.nstage; ++i) { mbar_init(&b_full[i], 1u); mbar_init(&b_empty[i], (uint32_t)a.MT); }
     mbar_init(&tmem_full, (uint32_t)a.MT);
+    mbar_init(&tmem_empty, (uint32_t)(CG * kWEpiWarps));     // every epilogue warp of the cluster, once per tile (rank 0's barrier counts)
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -105,16 +107,33 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   else __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
-  long long* stamp = a.stamps ? a.stamps + 8 * ((size_t)(blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) : nullptr;
+  long long* stamp = a.stamps ? a.stamps + 8 * (size_t)blockIdx.x : nullptr;      // stamps describe the CTA's FIRST tile
   if (stamp && tid == 0) { stamp[0] = t_enter; stamp[1] = clock64(); }
+  // tile t -> rows q0.., columns n0.., group, reduction range
+  struct Tile { int q0, n0, grp, split, cb_begin, cb_end; };
+  auto decode = [&](int t) {
+    Tile tl;
+    const int mu = t % a.m_units, r = t / a.m_units, nt = r % a.n_tiles, z = r / a.n_tiles;
+    tl.q0 = (mu * CG + rank) * a.MT * 128;
+    tl.n0 = nt * a.n_mma;
+    tl.grp = z / a.splits;
+    tl.split = z % a.splits;
+    tl.cb_begin = tl.split * a.cb_per_split;
+    tl.cb_end = min(a.ncb, tl.cb_begin + a.cb_per_split);       // never empty (host)
+    return tl;
+  };
 
   if (warp < kWEpiWarps) {
     // ---------------- epilogue ----------------
-    mbar_wait(&tmem_full, 0);
-    tc_fence_after_sync();
-    if (stamp && tid == 0) stamp[5] = clock64();
-    const int quarter = warp & 3, half = warp >> 2, chan0 = grp * ep.Cgrp;
+    const int quarter = warp & 3, half = warp >> 2;
     const size_t plane = (size_t)ep.Hv * ep.Wv;
+    uint32_t tphase = 0;
+    for (int t = cluster_id; t < a.total_tiles; t += n_clusters, tphase ^= 1u) {
+    const Tile tl = decode(t);
+    const int q0 = tl.q0, n0 = tl.n0, split = tl.split, chan0 = tl.grp * ep.Cgrp;
+    mbar_wait(&tmem_full, tphase);
+    tc_fence_after_sync();
+    if (stamp && tid == 0 && t == cluster_id) stamp[5] = clock64();
     const int ncols = min(a.n_mma, ep.Cgrp - n0);                 // valid columns of this tile (multiple of 16)
     if (ep.ld > 0) {
       // matrix epilogue: row m of D goes to dst[split][m][n0 ..] (16 consecutive floats per TMEM load)
@@ -170,6 +189,15 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
       }
     }
+    // this warp has read its share of the accumulators: the next tile's MMAs may overwrite them
+    tc_fence_before_sync();
+    __syncwarp();
+    if (lane == 0) {
+      if (stamp && warp == 0 && t == cluster_id) stamp[6] = clock64();
+      if (CG == 2) mbar_arrive_rank0(&tmem_empty);
+      else mbar_arrive(&tmem_empty);
+    }
+    }
   } else if (warp < kWTmaWarp) {
     // ---------------- MMA issuers (rank 0 of a pair): warp mi owns accumulator mi; the whole warp walks the pipeline,
     // one elected lane issues ----------------
@@ -183,9 +211,15 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const uint32_t b_hi = a.b_mn ? (uint32_t)(make_smem_desc(0, 4096, 512, kLayoutSW128Base32) >> 32) : desc_hi;
       const uint32_t win_lo = (smem_u32(smem) >> 4) | (1u << 16), b_lo0 = (smem_u32(bst) >> 4) | (a.b_mn ? (4096u >> 4) << 16 : 1u << 16);
       const uint32_t win_step = win_bytes >> 4, b_step = b_bytes >> 4, b_kstep = a.b_mn ? 64u : 2u;
-      int it = 0, s = 0, wb = 0;
-      uint32_t sphase = 0, wphase = 0;
+      int s = 0, wb = 0;
+      uint32_t sphase = 0, wphase = 0, ephase = 1;
       long long wait_win = 0, wait_b = 0;
+      for (int t = cluster_id; t < a.total_tiles; t += n_clusters, ephase ^= 1u) {
+      const Tile tl = decode(t);
+      const int cb_begin = tl.cb_begin, cb_end = tl.cb_end;
+      int it = 0;
+      mbar_wait(&tmem_empty, ephase);                           // the epilogue has drained the previous tile's accumulators
+      tc_fence_after_sync();
       for (int cb = cb_begin; cb < cb_end; ++cb) {
         long long tw = (stamp && mi == 0) ? clock64() : 0;
         mbar_wait(&win_full[wb], wphase);
@@ -229,14 +263,18 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
         if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
       }
-      if (stamp && lane == 0 && mi == 0) { stamp[2] = wait_win; stamp[3] = wait_b; }
+      if (stamp && lane == 0 && mi == 0 && t == cluster_id) { stamp[2] = wait_win; stamp[3] = wait_b; stamp[4] = clock64(); }
+      }
     }
   } else {
     // ---------------- TMA issuer (both CTAs of a pair; completion bytes land on rank 0's barriers) ----------------
     if (lane == 0) {
       int s = 0, wb = 0;
       uint32_t sphase = 0, wphase = 0;
-      const int a_chan0 = grp * a.a_chan_group, b_row0 = grp * a.b_row_group + n0 + rank * nb_local;
+      for (int t = cluster_id; t < a.total_tiles; t += n_clusters) {
+      const Tile tl = decode(t);
+      const int q0 = tl.q0, cb_begin = tl.cb_begin, cb_end = tl.cb_end;
+      const int a_chan0 = tl.grp * a.a_chan_group, b_row0 = tl.grp * a.b_row_group + tl.n0 + rank * nb_local;
       for (int cb = cb_begin; cb < cb_end; ++cb) {
         mbar_wait(&win_empty[wb], wphase ^ 1u);
         if (rank == 0) mbar_arrive_expect_tx(&win_full[wb], win_bytes * CG);
@@ -261,10 +299,9 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
         if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
       }
+      }
     }
   }
-  if (stamp && lane == 0 && warp == kWEpiWarps) stamp[4] = clock64();        // all MMAs issued
-  if (stamp && lane == 0 && warp == 0) stamp[6] = clock64();                 // this warp's share of the epilogue done
   tc_fence_before_sync();
   if (CG == 2) cluster_sync_all();
   else __syncthreads();
@@ -446,10 +483,16 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
     SN_CUDA(cudaFuncSetAttribute(conv_window_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWSmemLimit - 1024));
     attr_done = true;
   }
-  dim3 grid((a.Ptot + a.MT * 128 - 1) / (a.MT * 128), (N + a.n_mma - 1) / a.n_mma, groups * a.splits);
-  if (pl.cg == 2) grid.x = (grid.x + 1) / 2 * 2;          // whole pairs: the odd CTA works on rows past the end (zero-filled)
+  // persistent CTAs: one cluster per SM (pair), each walking the tile list with stride #clusters
   WinArgs aa = a;
-  const int ctas = (int)(grid.x * grid.y * grid.z);
+  const int m_ctas = (a.Ptot + a.MT * 128 - 1) / (a.MT * 128);
+  aa.m_units = (m_ctas + pl.cg - 1) / pl.cg;              // whole pairs: an odd last CTA works on rows past the end (zero-filled)
+  aa.n_tiles = (N + a.n_mma - 1) / a.n_mma;
+  aa.total_tiles = aa.m_units * aa.n_tiles * groups * a.splits;
+  const int max_clusters = 148 / pl.cg;
+  const int clusters = aa.total_tiles < max_clusters ? aa.total_tiles : max_clusters;
+  dim3 grid(clusters * pl.cg, 1, 1);
+  const int ctas = (int)grid.x;
   aa.stamps = (g_stamps && ctas <= kMaxStampCtas) ? g_stamps : nullptr;
   if (aa.stamps) g_stamp_ctas = ctas;
   if (pl.cg == 2) {

@@ -132,6 +132,10 @@ __device__ __forceinline__ void mma_tf32_lohi_pair(uint32_t tmem_d, uint32_t a_l
       ::"r"(tmem_d), "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// arrive on the barrier at this offset in the pair's rank-0 CTA (from either CTA)
+__device__ __forceinline__ void mbar_arrive_rank0(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kPeerBitMask) : "memory");
+}
 // the same two with separate high words for A and B (operands of different majorness)
 __device__ __forceinline__ void mma_tf32_lohi2(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
                                                uint32_t accumulate) {
