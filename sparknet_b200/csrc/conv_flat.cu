@@ -59,6 +59,7 @@ struct WinArgs {
   int b_mn;                 // B operand stored [reduction][n] (n contiguous): MN-major tiles of 32 n x 32 rows per TMA box
   // --- persistent CTAs: cluster c works on tiles c, c + #clusters, ...; tile t = (m unit, n tile, z) with the m unit fastest ---
   int m_units, n_tiles, total_tiles;   // m unit = MT*128 rows per CTA, one per CTA of the cluster
+  int acc_stages;           // 2 when two accumulator sets fit in TMEM (MT * n_mma <= 256): the epilogue of tile k overlaps the MMAs of tile k+1
 };
 // m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell.
 // ld > 0 selects the matrix epilogue instead: dst[split][m][ld] row-major (bias / ReLU only when splits == 1).
@@ -75,7 +76,7 @@ template <int CG>
 __global__ void __launch_bounds__(kWThreads, 1)
 conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const WinArgs a, const WinEpi ep) {
   extern __shared__ uint8_t smem_raw[];
-  __shared__ uint64_t win_full[kWMaxStages], win_empty[kWMaxStages], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full, tmem_empty;
+  __shared__ uint64_t win_full[kWMaxStages], win_empty[kWMaxStages], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full[2], tmem_empty[2];
   __shared__ uint32_t tmem_base_smem;
 
   const long long t_enter = clock64();
@@ -92,8 +93,10 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     // every accumulator has its own issuing warp: MT commits free a stage / complete the tile
     for (int i = 0; i < a.nwin; ++i) { mbar_init(&win_full[i], 1u); mbar_init(&win_empty[i], (uint32_t)a.MT); }
     for (int i = 0; i < a.nstage; ++i) { mbar_init(&b_full[i], 1u); mbar_init(&b_empty[i], (uint32_t)a.MT); }
-    mbar_init(&tmem_full, (uint32_t)a.MT);
-    mbar_init(&tmem_empty, (uint32_t)(CG * kWEpiWarps));     // every epilogue warp of the cluster, once per tile (rank 0's barrier counts)
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&tmem_full[i], (uint32_t)a.MT);
+      mbar_init(&tmem_empty[i], (uint32_t)(CG * kWEpiWarps));   // every epilogue warp of the cluster, once per tile (rank 0's barrier counts)
+    }
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
@@ -127,11 +130,13 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     // ---------------- epilogue ----------------
     const int quarter = warp & 3, half = warp >> 2;
     const size_t plane = (size_t)ep.Hv * ep.Wv;
-    uint32_t tphase = 0;
-    for (int t = cluster_id; t < a.total_tiles; t += n_clusters, tphase ^= 1u) {
+    int ti = 0;
+    for (int t = cluster_id; t < a.total_tiles; t += n_clusters, ++ti) {
     const Tile tl = decode(t);
     const int q0 = tl.q0, n0 = tl.n0, split = tl.split, chan0 = tl.grp * ep.Cgrp;
-    mbar_wait(&tmem_full, tphase);
+    const int buf = ti % a.acc_stages;
+    const uint32_t tmem_acc = tmem_base + (uint32_t)buf * 256u;
+    mbar_wait(&tmem_full[buf], (uint32_t)(ti / a.acc_stages) & 1u);
     tc_fence_after_sync();
     if (stamp && tid == 0 && t == cluster_id) stamp[5] = clock64();
     const int ncols = min(a.n_mma, ep.Cgrp - n0);                 // valid columns of this tile (multiple of 16)
@@ -143,7 +148,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         float* p = ep.dst + (size_t)split * ep.split_stride + (size_t)min(m, a.Ptot - 1) * ep.ld + n0;
         for (int c0 = 16 * half; c0 < ncols; c0 += 32) {
           uint32_t v[16];
-          tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(i * a.n_mma + c0), v);
+          tmem_ld_32x32b_x16(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(i * a.n_mma + c0), v);
           tmem_ld_wait();
           if (m < a.Ptot) {
 #pragma unroll
@@ -167,7 +172,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       for (int j = 0; j < 16; ++j) bias[j] = ep.bias ? __ldg(ep.bias + chan0 + n0 + c0 + j) : 0.f;
       for (int i = 0; i < a.MT; ++i) {
         uint32_t v[16];
-        tmem_ld_32x32b_x16(tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(i * a.n_mma + c0), v);
+        tmem_ld_32x32b_x16(tmem_acc + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(i * a.n_mma + c0), v);
         const int m = q0 + i * 128 + 32 * quarter + lane;
         bool ok = m < a.Ptot;
         float* p = ep.dst;
@@ -194,8 +199,8 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
     __syncwarp();
     if (lane == 0) {
       if (stamp && warp == 0 && t == cluster_id) stamp[6] = clock64();
-      if (CG == 2) mbar_arrive_rank0(&tmem_empty);
-      else mbar_arrive(&tmem_empty);
+      if (CG == 2) mbar_arrive_rank0(&tmem_empty[buf]);
+      else mbar_arrive(&tmem_empty[buf]);
     }
     }
   } else if (warp < kWTmaWarp) {
@@ -212,13 +217,16 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
       const uint32_t win_lo = (smem_u32(smem) >> 4) | (1u << 16), b_lo0 = (smem_u32(bst) >> 4) | (a.b_mn ? (4096u >> 4) << 16 : 1u << 16);
       const uint32_t win_step = win_bytes >> 4, b_step = b_bytes >> 4, b_kstep = a.b_mn ? 64u : 2u;
       int s = 0, wb = 0;
-      uint32_t sphase = 0, wphase = 0, ephase = 1;
+      uint32_t sphase = 0, wphase = 0;
       long long wait_win = 0, wait_b = 0;
-      for (int t = cluster_id; t < a.total_tiles; t += n_clusters, ephase ^= 1u) {
+      int ti = 0;
+      for (int t = cluster_id; t < a.total_tiles; t += n_clusters, ++ti) {
       const Tile tl = decode(t);
       const int cb_begin = tl.cb_begin, cb_end = tl.cb_end;
       int it = 0;
-      mbar_wait(&tmem_empty, ephase);                           // the epilogue has drained the previous tile's accumulators
+      const int buf = ti % a.acc_stages;
+      // the epilogue has drained what this accumulator set held before (passes at once the first time round)
+      mbar_wait(&tmem_empty[buf], ((uint32_t)(ti / a.acc_stages) & 1u) ^ 1u);
       tc_fence_after_sync();
       for (int cb = cb_begin; cb < cb_end; ++cb) {
         long long tw = (stamp && mi == 0) ? clock64() : 0;
@@ -239,7 +247,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             const uint32_t a_lo = win_lo + (uint32_t)wb * win_step + (shift_row + (uint32_t)kx) * 8u;   // 128 B per row >> 4
             const uint32_t b_lo = b_lo0 + (uint32_t)s * b_step;
             {
-              const uint32_t d = tmem_base + (uint32_t)(mi * a.n_mma);
+              const uint32_t d = tmem_base + (uint32_t)buf * 256u + (uint32_t)(mi * a.n_mma);
 #pragma unroll 4
               for (int j = 0; j < ks; ++j) {
                 if (CG == 2) mma_tf32_lohi2_pair(d, a_lo + (uint32_t)(mi * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
@@ -250,11 +258,11 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             if (CG == 2) {
               mma_commit_pair(&b_empty[s]);
               if (last_tap) mma_commit_pair(&win_empty[wb]);
-              if (last) mma_commit_pair(&tmem_full);
+              if (last) mma_commit_pair(&tmem_full[buf]);
             } else {
               mma_commit(&b_empty[s]);
               if (last_tap) mma_commit(&win_empty[wb]);
-              if (last) mma_commit(&tmem_full);
+              if (last) mma_commit(&tmem_full[buf]);
             }
           }
           __syncwarp();
@@ -409,12 +417,13 @@ float tcw_mma_rate(int cg, int n_mma, int iters, int shift_rows, int nacc, int c
 // ------------------------------------------------------------------------------------------
 // host side
 // ------------------------------------------------------------------------------------------
-static int g_force_mt = 0, g_force_cg = 0;
+static int g_force_mt = 0, g_force_cg = 0, g_force_n = 0;
 static long long* g_stamps = nullptr;
 static int g_stamp_ctas = 0;
 constexpr int kMaxStampCtas = 4096;
 void tcw_set_debug(int what, int value) {
   if (what == 1) g_force_mt = value;
+  if (what == 4) g_force_n = value;                   // force the column tile width of the window kernels (0 = planner's choice)
   if (what == 3) g_force_cg = value;                  // 1 = single-CTA MMAs only, 2 = CTA pairs whenever possible, 0 = auto
   if (what == 2) {                                      // per-CTA clock stamps of the next window launches on / off
     if (value && !g_stamps) SN_CUDA(cudaMalloc(&g_stamps, sizeof(long long) * 8 * kMaxStampCtas));
@@ -438,41 +447,64 @@ static int win_n_mma(int N) {
   w = (w + 15) / 16 * 16;
   return w < 16 ? 16 : w;
 }
-// Pick the number of accumulators: fewest estimated clocks over all waves.  Per tile: MMA time MT*T*ksteps*n_mma/2,
-// L2 time bytes / 25, shared-memory time of the operand reads, plus the serial prologue / epilogue.
-static WinPlan plan_window(int Ptot, int N, int groups, int T, int span, int red) {
+// Pick the column tile width and the number of accumulators per CTA: fewest estimated clocks for the busiest cluster.
+// The per-tile model below is calibrated on the sweep of tools/sweep_window.py (within ~10 % for AlexNet's layers); the
+// epilogue costs output bytes / 19 per clock, and tiles whose accumulators fit twice in TMEM (MT * n_mma <= 256) hide it
+// behind the next tile's MMAs.
+static WinPlan plan_window_impl(int Ptot, int N, int groups, int T, int span, int red, bool forced) {
   WinPlan best{};
   best.ok = false;
-  const int n_mma = win_n_mma(N), n_tiles = (N + n_mma - 1) / n_mma, ncb = (red + 31) / 32;
-  int ksteps = 0;
-  for (int cb = 0; cb < ncb; ++cb) { const int left = red - cb * 32; ksteps += left >= 32 ? 4 : (left + 7) / 8; }
+  const int ncb = (red + 31) / 32;
   double best_cost = 0;
-  for (int MT = 4; MT >= 1; MT >>= 1) {
-    if (MT * n_mma > 512) continue;
-    if (g_force_mt && MT != g_force_mt) continue;
-    const int win_rows = MT * 128 + span;
-    const int nbox = (win_rows + 255) / 256;
-    const int box_rows = ((win_rows + nbox - 1) / nbox + 7) / 8 * 8;
-    const int cg = g_force_cg == 1 ? 1 : 2;                     // CTA pairs: half the filter bytes per SM
-    const size_t win_bytes = (size_t)nbox * box_rows * 128, b_bytes = (size_t)n_mma * 128 / cg;
-    const size_t fixed = 2 * win_bytes + 1024 + 512;             // + alignment slack + static shared (barriers)
-    if (fixed + 3 * b_bytes > kWSmemLimit) continue;
-    int nstage = (int)((kWSmemLimit - fixed) / b_bytes);
-    if (nstage > kWMaxStages) nstage = kWMaxStages;
-    const long long tiles = (long long)((Ptot + MT * 128 - 1) / (MT * 128)) * n_tiles * groups;
-    const long long waves = (tiles + 147) / 148;
-    const double t_mma = (double)MT * T * ksteps * n_mma / 2.0;
-    const double t_l2 = ((double)ncb * win_bytes + (double)ncb * T * b_bytes) / 25.0;   // measured: ~25 B/clk per SM with all SMs pulling
-    const double t_smem = (double)MT * T * ksteps * ((128.0 + n_mma / cg) * 32.0) / 110.0;   // operand reads of the tensor core
-    const double t_epi = (double)MT * 128 * n_mma * 4 / 48.0;
-    const double t_main = t_mma > t_l2 ? (t_mma > t_smem ? t_mma : t_smem) : (t_l2 > t_smem ? t_l2 : t_smem);
-    const double cost = (double)waves * (t_main + t_epi + 4000.0);
-    if (!best.ok || cost < best_cost) {
-      best = WinPlan{MT, n_mma, nstage, box_rows, nbox, cg, 2 * win_bytes + (size_t)nstage * b_bytes + 1024, true};
-      best_cost = cost;
+  const int cg = g_force_cg == 1 ? 1 : 2;                       // CTA pairs: half the filter bytes per SM
+  for (int n_tiles = (N + 255) / 256; n_tiles <= (N + 31) / 32; ++n_tiles) {
+    const int n_mma = ((N + n_tiles - 1) / n_tiles + 15) / 16 * 16;
+    if (n_mma > 256 || (n_tiles > 1 && n_mma * (n_tiles - 1) >= N)) continue;
+    if (forced && g_force_n && n_mma != g_force_n) continue;
+    for (int MT = 4; MT >= 1; MT >>= 1) {
+      if (MT * n_mma > 512) continue;
+      if (forced && g_force_mt && MT != g_force_mt) continue;
+      const int win_rows = MT * 128 + span;
+      const int nbox = (win_rows + 255) / 256;
+      const int box_rows = ((win_rows + nbox - 1) / nbox + 7) / 8 * 8;
+      const size_t win_bytes = (size_t)nbox * box_rows * 128, b_bytes = (size_t)n_mma * 128 / cg;
+      const size_t fixed = 2 * win_bytes + 1024 + 512;             // + alignment slack + static shared (barriers)
+      if (fixed + 3 * b_bytes > kWSmemLimit) continue;
+      int nstage = (int)((kWSmemLimit - fixed) / b_bytes);
+      if (nstage > kWMaxStages) nstage = kWMaxStages;
+      const long long m_ctas = (Ptot + MT * 128 - 1) / (MT * 128);
+      const long long tiles = (m_ctas + cg - 1) / cg * n_tiles * groups;
+      const long long per_cluster = (tiles + 148 / cg - 1) / (148 / cg);
+      // per tap (measured with tools/sweep_window.py): ~600 clocks of pipeline bookkeeping at least, else 1.2 x the MMA
+      // clocks of the MT accumulators (one MMA = max(n_mma / 2, 42) clocks), else the L2 bytes of the tap at 25 B/clk
+      const double mma1 = n_mma / 2.0 > 42.0 ? n_mma / 2.0 : 42.0;
+      const double l2_tap = ((double)win_bytes / T + (double)b_bytes) / 25.0;
+      double t_main = 0;
+      for (int cb = 0; cb < ncb; ++cb) {
+        const int left = red - cb * 32, ks = left >= 32 ? 4 : (left + 7) / 8;
+        double tap = 1.2 * MT * ks * mma1;
+        if (tap < 600.0) tap = 600.0;
+        if (tap < l2_tap) tap = l2_tap;
+        t_main += T * tap;
+      }
+      const double t_epi = (double)MT * 128 * n_mma * 4 / 19.0;
+      const bool dbl = MT * n_mma <= 256;
+      const double cost = dbl ? per_cluster * (t_main > t_epi ? t_main : t_epi) + t_epi + 6000.0
+                              : per_cluster * (t_main + t_epi) + 6000.0;
+      if (!best.ok || cost < best_cost) {
+        best = WinPlan{MT, n_mma, nstage, box_rows, nbox, cg, 2 * win_bytes + (size_t)nstage * b_bytes + 1024, true};
+        best_cost = cost;
+      }
     }
   }
   return best;
+}
+
+// the development switches (forced tile shape) apply where they can be met, else the planner decides
+static WinPlan plan_window(int Ptot, int N, int groups, int T, int span, int red) {
+  WinPlan p = plan_window_impl(Ptot, N, groups, T, span, red, true);
+  if (!p.ok && (g_force_n || g_force_mt)) p = plan_window_impl(Ptot, N, groups, T, span, red, false);
+  return p;
 }
 
 static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap& tmB, const WinArgs& a, const WinEpi& ep,
@@ -489,6 +521,11 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
   aa.m_units = (m_ctas + pl.cg - 1) / pl.cg;              // whole pairs: an odd last CTA works on rows past the end (zero-filled)
   aa.n_tiles = (N + a.n_mma - 1) / a.n_mma;
   aa.total_tiles = aa.m_units * aa.n_tiles * groups * a.splits;
+  aa.acc_stages = a.MT * a.n_mma <= 256 ? 2 : 1;
+  static const bool plan_debug = getenv("SPARKNET_PLAN_DEBUG") != nullptr;
+  if (plan_debug)
+    fprintf(stderr, "window plan: rows %d N %d T %d ncb %d -> MT %d n_mma %d cg %d stages %d tiles %d acc_stages %d splits %d\n", a.Ptot, N, a.T,
+            a.ncb, a.MT, a.n_mma, pl.cg, a.nstage, aa.total_tiles, aa.acc_stages, a.splits);
   const int max_clusters = 148 / pl.cg;
   const int clusters = aa.total_tiles < max_clusters ? aa.total_tiles : max_clusters;
   dim3 grid(clusters * pl.cg, 1, 1);
