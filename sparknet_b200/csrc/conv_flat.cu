@@ -59,6 +59,7 @@ struct WinArgs {
   int b_mn;                 // B operand stored [reduction][n] (n contiguous): MN-major tiles of 32 n x 32 rows per TMA box
   // --- persistent CTAs: cluster c works on tiles c, c + #clusters, ...; tile t = (m unit, n tile, z) with the m unit fastest ---
   int m_units, n_tiles, total_tiles;   // m unit = MT*128 rows per CTA, one per CTA of the cluster
+  int tpg;                  // taps per pipeline stage: one barrier hand-shake serves tpg filter chunks (a stage = tpg * b_bytes)
   int acc_stages;           // 2 when two accumulator sets fit in TMEM (MT * n_mma <= 256): the epilogue of tile k overlaps the MMAs of tile k+1
 };
 // m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell.
@@ -235,7 +236,8 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         const int left = a.red - cb * 32, ks = left >= 32 ? 4 : (left + 7) / 8;
         uint32_t shift_row = 0;                                     // (ky * Wp) in rows
         int kx = 0;
-        for (int tap = 0; tap < a.T; ++tap, ++it) {
+        for (int tap0 = 0; tap0 < a.T; tap0 += a.tpg) {
+          const int ng = min(a.tpg, a.T - tap0);                   // filter chunks in this stage
           tw = (stamp && mi == 0) ? clock64() : 0;
           mbar_wait(&b_full[s], sphase);
           tc_fence_after_sync();
@@ -244,17 +246,19 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           // TMA write and for the MMA read alike, so a descriptor may start at any row of the window: the
           // base-offset field stays 0 (verified on B200 with tools/debug_window.py).
           if (elect_one_sync()) {
-            const uint32_t a_lo = win_lo + (uint32_t)wb * win_step + (shift_row + (uint32_t)kx) * 8u;   // 128 B per row >> 4
-            const uint32_t b_lo = b_lo0 + (uint32_t)s * b_step;
-            {
-              const uint32_t d = tmem_base + (uint32_t)buf * 256u + (uint32_t)(mi * a.n_mma);
+            const uint32_t d = tmem_base + (uint32_t)buf * 256u + (uint32_t)(mi * a.n_mma);
+            uint32_t b_lo = b_lo0 + (uint32_t)s * b_step * (uint32_t)a.tpg, sr = shift_row;
+            int kxl = kx, itl = it;
+            for (int g = 0; g < ng; ++g, ++itl, b_lo += b_step) {
+              const uint32_t a_lo = win_lo + (uint32_t)wb * win_step + (sr + (uint32_t)kxl) * 8u + (uint32_t)(mi * 1024);   // 128 B per row >> 4
 #pragma unroll 4
               for (int j = 0; j < ks; ++j) {
-                if (CG == 2) mma_tf32_lohi2_pair(d, a_lo + (uint32_t)(mi * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
-                else mma_tf32_lohi2(d, a_lo + (uint32_t)(mi * 1024 + 2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (it | j) != 0 ? 1u : 0u);
+                if (CG == 2) mma_tf32_lohi2_pair(d, a_lo + (uint32_t)(2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (itl | j) != 0 ? 1u : 0u);
+                else mma_tf32_lohi2(d, a_lo + (uint32_t)(2 * j), desc_hi, b_lo + b_kstep * (uint32_t)j, b_hi, idesc, (itl | j) != 0 ? 1u : 0u);
               }
+              if (++kxl == a.kw) { kxl = 0; sr += (uint32_t)a.Wp; }
             }
-            const bool last_tap = tap == a.T - 1, last = last_tap && cb == cb_end - 1;
+            const bool last_tap = tap0 + ng == a.T, last = last_tap && cb == cb_end - 1;
             if (CG == 2) {
               mma_commit_pair(&b_empty[s]);
               if (last_tap) mma_commit_pair(&win_empty[wb]);
@@ -266,7 +270,10 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             }
           }
           __syncwarp();
-          if (++kx == a.kw) { kx = 0; shift_row += (uint32_t)a.Wp; }
+          for (int g = 0; g < ng; ++g) {                           // every lane tracks the tap position
+            ++it;
+            if (++kx == a.kw) { kx = 0; shift_row += (uint32_t)a.Wp; }
+          }
           if (++s == a.nstage) { s = 0; sphase ^= 1u; }
         }
         if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
@@ -291,18 +298,22 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           if (CG == 2) tma_load_2d_pair(dst, &tmA, &win_full[wb], a_chan0 + cb * 32, q0 + a.row_off + b * a.box_rows);
           else tma_load_2d(dst, &tmA, &win_full[wb], a_chan0 + cb * 32, q0 + a.row_off + b * a.box_rows);
         }
-        for (int tap = 0; tap < a.T; ++tap) {
+        for (int tap0 = 0; tap0 < a.T; tap0 += a.tpg) {
+          const int ng = min(a.tpg, a.T - tap0);
           mbar_wait(&b_empty[s], sphase ^ 1u);
-          if (rank == 0) mbar_arrive_expect_tx(&b_full[s], b_bytes * CG);
-          uint8_t* dst = bst + (size_t)s * b_bytes;
-          if (a.b_mn) {
-            // B stored [reduction row][n]: one box of 32 n x 32 rows per 32 columns of this CTA's share
-            for (int blk = 0; blk < nb_local / 32; ++blk) {
-              if (CG == 2) tma_load_2d_pair(dst + blk * 4096, &tmB, &b_full[s], b_row0 + 32 * blk, cb * 32);
-              else tma_load_2d(dst + blk * 4096, &tmB, &b_full[s], b_row0 + 32 * blk, cb * 32);
-            }
-          } else if (CG == 2) tma_load_2d_pair(dst, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
-          else tma_load_2d(dst, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          if (rank == 0) mbar_arrive_expect_tx(&b_full[s], b_bytes * CG * ng);
+          for (int g = 0; g < ng; ++g) {
+            const int tap = tap0 + g;
+            uint8_t* dst = bst + ((size_t)s * a.tpg + g) * b_bytes;
+            if (a.b_mn) {
+              // B stored [reduction row][n]: one box of 32 n x 32 rows per 32 columns of this CTA's share
+              for (int blk = 0; blk < nb_local / 32; ++blk) {
+                if (CG == 2) tma_load_2d_pair(dst + blk * 4096, &tmB, &b_full[s], b_row0 + 32 * blk, cb * 32);
+                else tma_load_2d(dst + blk * 4096, &tmB, &b_full[s], b_row0 + 32 * blk, cb * 32);
+              }
+            } else if (CG == 2) tma_load_2d_pair(dst, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+            else tma_load_2d(dst, &tmB, &b_full[s], tap * a.slots + cb * 32, b_row0);
+          }
           if (++s == a.nstage) { s = 0; sphase ^= 1u; }
         }
         if (++wb == a.nwin) { wb = 0; wphase ^= 1u; }
@@ -522,10 +533,29 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
   aa.n_tiles = (N + a.n_mma - 1) / a.n_mma;
   aa.total_tiles = aa.m_units * aa.n_tiles * groups * a.splits;
   aa.acc_stages = a.MT * a.n_mma <= 256 ? 2 : 1;
+  size_t smem_bytes = pl.smem;
+  {
+    // taps per stage: a divisor of T up to 5 when at least three stages still fit, else the largest group that does
+    const size_t b_bytes = (size_t)a.n_mma * 128 / pl.cg, win_total = (size_t)a.nwin * a.nbox * a.box_rows * 128;
+    const size_t avail = kWSmemLimit - 2048 - win_total;
+    int best_g = 1;
+    for (int g = 5; g >= 2; --g) {
+      if (g > a.T || avail / (g * b_bytes) < 3) continue;
+      if (a.T % g == 0) { best_g = g; break; }
+      if (best_g == 1) best_g = g;
+    }
+    if (getenv("SPARKNET_TPG")) best_g = atoi(getenv("SPARKNET_TPG")) > 0 ? (atoi(getenv("SPARKNET_TPG")) < a.T ? atoi(getenv("SPARKNET_TPG")) : a.T) : best_g;
+    if (avail / (best_g * b_bytes) < 2) best_g = 1;
+    aa.tpg = best_g;
+    int nst = (int)(avail / (best_g * b_bytes));
+    aa.nstage = nst > kWMaxStages ? kWMaxStages : nst;
+    smem_bytes = win_total + (size_t)aa.nstage * best_g * b_bytes + 1024;
+  }
   static const bool plan_debug = getenv("SPARKNET_PLAN_DEBUG") != nullptr;
   if (plan_debug)
     fprintf(stderr, "window plan: rows %d N %d T %d ncb %d -> MT %d n_mma %d cg %d stages %d tiles %d acc_stages %d splits %d\n", a.Ptot, N, a.T,
-            a.ncb, a.MT, a.n_mma, pl.cg, a.nstage, aa.total_tiles, aa.acc_stages, a.splits);
+            a.ncb, a.MT, a.n_mma, pl.cg, aa.nstage, aa.total_tiles, aa.acc_stages, a.splits);
+  if (plan_debug) fprintf(stderr, "   taps per stage %d, smem %zu\n", aa.tpg, smem_bytes);
   const int max_clusters = 148 / pl.cg;
   const int clusters = aa.total_tiles < max_clusters ? aa.total_tiles : max_clusters;
   dim3 grid(clusters * pl.cg, 1, 1);
@@ -536,7 +566,7 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = grid;
     cfg.blockDim = dim3(kWThreads);
-    cfg.dynamicSmemBytes = pl.smem;
+    cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeClusterDimension;
@@ -545,7 +575,7 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
     cfg.numAttrs = 1;
     SN_CUDA(cudaLaunchKernelEx(&cfg, conv_window_kernel<2>, tmA, tmB, aa, ep));
   } else {
-    conv_window_kernel<1><<<grid, kWThreads, pl.smem, s>>>(tmA, tmB, aa, ep);
+    conv_window_kernel<1><<<grid, kWThreads, smem_bytes, s>>>(tmA, tmB, aa, ep);
   }
   count_launch();
   SN_CUDA(cudaGetLastError());
