@@ -486,7 +486,7 @@ static WinPlan plan_window_impl(int Ptot, int N, int groups, int T, int span, in
       const long long m_ctas = (Ptot + MT * 128 - 1) / (MT * 128);
       const long long tiles = (m_ctas + cg - 1) / cg * n_tiles * groups;
       const long long per_cluster = (tiles + 148 / cg - 1) / (148 / cg);
-      // per tap (measured with tools/sweep_window.py): ~600 clocks of pipeline bookkeeping at least, else 1.2 x the MMA
+      // per tap (measured with tools/sweep_window.py): ~300 clocks of pipeline bookkeeping at least (several taps share one stage), else 1.2 x the MMA
       // clocks of the MT accumulators (one MMA = max(n_mma / 2, 42) clocks), else the L2 bytes of the tap at 25 B/clk
       const double mma1 = n_mma / 2.0 > 42.0 ? n_mma / 2.0 : 42.0;
       const double l2_tap = ((double)win_bytes / T + (double)b_bytes) / 25.0;
@@ -494,7 +494,7 @@ static WinPlan plan_window_impl(int Ptot, int N, int groups, int T, int span, in
       for (int cb = 0; cb < ncb; ++cb) {
         const int left = red - cb * 32, ks = left >= 32 ? 4 : (left + 7) / 8;
         double tap = 1.2 * MT * ks * mma1;
-        if (tap < 600.0) tap = 600.0;
+        if (tap < 300.0) tap = 300.0;
         if (tap < l2_tap) tap = l2_tap;
         t_main += T * tap;
       }

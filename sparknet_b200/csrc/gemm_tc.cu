@@ -984,12 +984,14 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
     }
   }
 }
+// one warp per channel: lane l adds partials l, l + 32, ... in ascending order, then a fixed butterfly: deterministic
 __global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int c = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
   float t = 0.f;
-  for (int s = 0; s < S; ++s) t += part[(size_t)c * S + s];
-  db[c] = accumulate ? db[c] + t : t;
+  for (int s = lane; s < S; s += 32) t += part[(size_t)c * S + s];
+  for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  if (lane == 0) db[c] = accumulate ? db[c] + t : t;
 }
 // db (nullable): bias gradient, summed here when the packed tensor is the top gradient
 void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db, bool accumulate) {
@@ -1004,7 +1006,7 @@ void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const flo
   if (db) {
     float* part = get_workspace((size_t)C * g.N * Z);
     flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span);
-    bias_grad_final_kernel<<<(C + 127) / 128, 128, 0, s>>>(C, g.N * Z, part, db, accumulate ? 1 : 0);
+    bias_grad_final_kernel<<<(C * 32 + 127) / 128, 128, 0, s>>>(C, g.N * Z, part, db, accumulate ? 1 : 0);
     count_launch(2);
   } else {
     flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span);
