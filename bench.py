@@ -173,6 +173,10 @@ def measure_tf32_peak():
         torch.backends.cuda.matmul.allow_tf32 = old
 
 
+# measured once per round with ncu (see profiles/): DRAM bytes moved by the conv / inner-product kernels of one iteration
+NCU_GEMM_TRAFFIC_BYTES = {"caffenet": 3490.5e6}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -304,7 +308,10 @@ def main():
     achieved_tflops = GEMM_GFLOP_PER_ITER[name] / gemm_ms if gemm_ms > 0 else 0.0     # GFLOP / ms = TFLOP/s
     roofline = {"bound": "tensor", "kernel": "conv + inner-product implicit GEMMs (fwd, dgrad, wgrad) of one iteration",
                 "achieved": achieved_tflops, "peak": tf32_peak, "unit": "TFLOP/s",
-                "frac": achieved_tflops / tf32_peak if tf32_peak else None, "traffic": None,
+                "frac": achieved_tflops / tf32_peak if tf32_peak else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum summed over the 23 tensor-core launches of ONE iteration
+                # (ncu --set full capture of this command, profiles/r1_ncu_gemm_iteration.md); null for other workloads
+                "traffic": NCU_GEMM_TRAFFIC_BYTES.get(name), "traffic_unit": "bytes per iteration (all launches of the group)",
                 "peak_source": "torch.matmul TF32 8192^3 best of 10, measured in this run (MEASURED_PEAKS.json has bf16 only)",
                 "algorithmic_gflop_per_launch_group": GEMM_GFLOP_PER_ITER[name], "ms": gemm_ms,
                 "share_of_step": gemm_ms / (gemm_ms + other_ms + u.value) if gemm_ms else None}
