@@ -109,6 +109,11 @@ int sparknet_get_iter(caffenet_state* state);
 float sparknet_last_loss(caffenet_state* state);
 /* Copies the losses of the last n solver iterations (oldest first) kept on the device; returns count. */
 int sparknet_get_loss_history(caffenet_state* state, float* out, int n);
+/* Model + solver-state snapshot in Caffe's binaryproto formats (Solver::Snapshot, solver.cpp:447-470 /
+ * sgd_solver.cpp:255-272; the reference triggers it from SolverParameter.snapshot, here it is a call): writes the
+ * NetParameter with every layer's blobs to model_filename and SolverState {iter, learned_net = model_filename,
+ * current_step, history} to state_filename; restore_solver_from_file reads the pair back. */
+int sparknet_snapshot(caffenet_state* state, const char* model_filename, const char* state_filename);
 /* memcpy on `threads` host threads, for data callbacks that fill the library's pinned staging buffer (no reference
  * counterpart: the JVM callback of Net.scala:194-221 copies element by element). */
 void sparknet_host_copy(void* dst, const void* src, long bytes, int threads);

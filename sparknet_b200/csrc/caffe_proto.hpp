@@ -456,7 +456,9 @@ struct LayerParameter {                  // caffe.proto:310-400
   int softmax_axis = 1;                  // SoftmaxParameter, caffe.proto:849-861
   bool has_java_data_param = false;
   BlobShape java_data_shape;             // JavaDataParameter (SparkNet), caffe.proto:991-993
+  std::string raw;                       // the serialized message as received (Layer::ToProto copies layer_param_ verbatim)
   void parse(Reader r) {
+    raw.assign((const char*)r.p, (size_t)(r.end - r.p));
     while (!r.done()) {
       uint64_t k = r.varint();
       int f = (int)(k >> 3), wt = (int)(k & 7);
@@ -538,10 +540,24 @@ struct NetParameter {                    // caffe.proto:64-100
         case 6: state.parse(r.sub()); has_state = true; break;
         case 7: debug_info = rd_bool(r); break;
         case 100: { layer.emplace_back(); layer.back().parse(r.sub()); break; }
+        case 2: {   // V1LayerParameter (caffe.proto:1063-1160), as in the published bvlc caffemodels: only name (4) and blobs (6) matter here
+          Reader s = r.sub();
+          LayerParameter l;
+          while (!s.done()) {
+            uint64_t kk = s.varint();
+            const int ff = (int)(kk >> 3), ww = (int)(kk & 7);
+            if (ff == 4) l.name = s.str();
+            else if (ff == 6) { l.blobs.emplace_back(); l.blobs.back().parse(s.sub()); }
+            else s.skip(ww);
+          }
+          v1_layers.push_back(std::move(l));
+          break;
+        }
         default: r.skip(wt);
       }
     }
   }
+  std::vector<LayerParameter> v1_layers;   // legacy `layers` entries (name + blobs only)
 };
 
 struct SolverParameter {                 // caffe.proto:102-243

@@ -550,8 +550,20 @@ __global__ void lrn_across_fwd_kernel(LrnGeom g, int nthreads, const float* __re
 //   scale_c = k + alpha/n * sum_{|j-c| <= pre} x_j^2 ,   y_c = x_c * scale_c^-beta .
 // Nothing but y is written: the backward kernel recomputes scale from x (cheaper than 8 B/element of scale traffic),
 // so the forward pass moves 8 B per element.
-__device__ __forceinline__ float lrn_pow_neg(float sc, float beta, bool is075) {
-  if (is075) { const float r = rsqrtf(sc); return r * sqrtf(r); }          // sc^-0.5 * sc^-0.25
+__device__ __forceinline__ float sqrt_approx(float x) {
+  float r;
+  asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+}
+// sc^-beta and 1/sc from two special-function instructions when beta = 0.75 (AlexNet / CaffeNet): q = sc^-1/2,
+// sc^-3/4 = q * sqrt(q), 1/sc = q * q; relative error ~3e-7, far inside the 1e-5 of the fp32 validation mode
+__device__ __forceinline__ float lrn_pow_neg(float sc, float beta, bool is075, float* inv_sc = nullptr) {
+  if (is075) {
+    const float q = rsqrtf(sc);
+    if (inv_sc) *inv_sc = q * q;
+    return q * sqrt_approx(q);
+  }
+  if (inv_sc) *inv_sc = __fdividef(1.f, sc);
   return __powf(sc, -beta);
 }
 constexpr int kLrnCH = 16;
@@ -662,9 +674,10 @@ __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, in
 #pragma unroll
       for (int t = 0; t < SIZE; ++t) acc += v[j + t] * v[j + t];
       const float sc = g.k + acc * aos;
-      const float pw = lrn_pow_neg(sc, g.beta, is075);
+      float inv;
+      const float pw = lrn_pow_neg(sc, g.beta, is075, &inv);
       p[j] = pw;
-      r[j] = __fdiv_rn(__fmul_rn(r[j], __fmul_rn(v[j + PRE], pw)), sc) ;      // dy * y / scale; the raw dy is recovered below
+      r[j] = r[j] * (v[j + PRE] * pw) * inv;                                  // dy * y / scale; the raw dy is re-read below
     }
 #pragma unroll
     for (int j = 0; j < kLrnCH; ++j) {

@@ -1293,4 +1293,5 @@ void Solver::test_and_store(int num_steps, std::vector<float>* score) {   // sol
 }
 
 }  // namespace sn
+#include "caffe_text.hpp"
 #include "ccaffe_abi.inc"

@@ -87,6 +87,7 @@ _EXTENSIONS = {
     "sparknet_profile_step": (c_int, [c_void_p, POINTER(c_float), POINTER(c_float), POINTER(c_float), c_int]),
     "sparknet_get_loss_history": (c_int, [c_void_p, POINTER(c_float), c_int]),
     "sparknet_host_copy": (None, [c_void_p, c_void_p, ctypes.c_long, c_int]),
+    "sparknet_snapshot": (c_int, [c_void_p, c_char_p, c_char_p]),
     "sparknet_get_history": (c_int, [c_void_p, c_int, POINTER(c_float), ctypes.c_long]),
     "sparknet_get_pool_mask": (c_int, [c_void_p, c_int, POINTER(c_int), ctypes.c_long]),
     # oracle-only helpers
