@@ -21,6 +21,9 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <array>
+#include <map>
+#include <mutex>
 #include <vector>
 
 #include "gemm_ops.cuh"
@@ -512,9 +515,17 @@ static WinPlan plan_window_impl(int Ptot, int N, int groups, int T, int span, in
 }
 
 // the development switches (forced tile shape) apply where they can be met, else the planner decides
+// Plans are memoised: the launchers run every iteration, the enumeration is host time a small net would notice.
 static WinPlan plan_window(int Ptot, int N, int groups, int T, int span, int red) {
+  static std::map<std::array<int, 9>, WinPlan> memo;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  const std::array<int, 9> key{Ptot, N, groups, T, span, red, g_force_n, g_force_mt, g_force_cg};
+  auto it = memo.find(key);
+  if (it != memo.end()) return it->second;
   WinPlan p = plan_window_impl(Ptot, N, groups, T, span, red, true);
   if (!p.ok && (g_force_n || g_force_mt)) p = plan_window_impl(Ptot, N, groups, T, span, red, false);
+  memo[key] = p;
   return p;
 }
 
@@ -544,7 +555,8 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
       if (a.T % g == 0) { best_g = g; break; }
       if (best_g == 1) best_g = g;
     }
-    if (getenv("SPARKNET_TPG")) best_g = atoi(getenv("SPARKNET_TPG")) > 0 ? (atoi(getenv("SPARKNET_TPG")) < a.T ? atoi(getenv("SPARKNET_TPG")) : a.T) : best_g;
+    static const int forced_tpg = getenv("SPARKNET_TPG") ? atoi(getenv("SPARKNET_TPG")) : 0;
+    if (forced_tpg > 0) best_g = forced_tpg < a.T ? forced_tpg : a.T;
     if (avail / (best_g * b_bytes) < 2) best_g = 1;
     aa.tpg = best_g;
     int nst = (int)(avail / (best_g * b_bytes));
@@ -855,7 +867,17 @@ static int span_of_taps(int t0, int nt, int kw, int Wp) {
   const int t1 = t0 + nt - 1;
   return (t1 / kw) * Wp + t1 % kw - ((t0 / kw) * Wp + t0 % kw);
 }
+static WgPlan plan_wgrad_impl(int Ptot, int Og, int Cg, int groups, int T, int kw, int Wp);
 static WgPlan plan_wgrad(int Ptot, int Og, int Cg, int groups, int T, int kw, int Wp) {
+  static std::map<std::array<int, 7>, WgPlan> memo;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  const std::array<int, 7> key{Ptot, Og, Cg, groups, T, kw, Wp};
+  auto it = memo.find(key);
+  if (it != memo.end()) return it->second;
+  return memo[key] = plan_wgrad_impl(Ptot, Og, Cg, groups, T, kw, Wp);
+}
+static WgPlan plan_wgrad_impl(int Ptot, int Og, int Cg, int groups, int T, int kw, int Wp) {
   WgPlan best{};
   best.ok = false;
   double best_cost = 0;

@@ -17,7 +17,9 @@
 
 #include <cstdio>
 #include <cstring>
+#include <map>
 #include <mutex>
+#include <tuple>
 #include <type_traits>
 
 #include "gemm_ops.cuh"
@@ -747,8 +749,20 @@ static CUtensorMap make_tmap(const float* base, uint64_t inner, uint64_t outer, 
                                (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)pitch_bytes, box_outer);
   return m;
 }
+// Encoded descriptors are cached: buffers and shapes repeat every iteration, cuTensorMapEncodeTiled is ~1 us of host time.
 CUtensorMap tc_make_tmap(const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes, uint32_t box_outer, bool mn_major) {
-  return make_tmap(base, inner, outer, pitch_bytes, box_outer, mn_major);
+  struct Key {
+    const float* base; uint64_t inner, outer, pitch; uint32_t box; bool mn;
+    bool operator<(const Key& o) const { return std::tie(base, inner, outer, pitch, box, mn) < std::tie(o.base, o.inner, o.outer, o.pitch, o.box, o.mn); }
+  };
+  static std::map<Key, CUtensorMap> cache;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  const Key k{base, inner, outer, pitch_bytes, box_outer, mn_major};
+  auto it = cache.find(k);
+  if (it != cache.end()) return it->second;
+  if (cache.size() > 4096) cache.clear();
+  return cache[k] = make_tmap(base, inner, outer, pitch_bytes, box_outer, mn_major);
 }
 static CUtensorMap dummy_tmap() {
   CUtensorMap m;
