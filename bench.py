@@ -227,7 +227,7 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     from sparknet_b200.library import load_library
-    from sparknet_b200.parallel import Averager
+    from sparknet_b200.parallel import make_averager
     lib = load_library()
     lib.set_device(local_rank)
     lib.set_mode_gpu()
@@ -242,7 +242,7 @@ def main():
     src = MinibatchSource(imgs, labs)
     net.copy_threads = int(os.environ.get("SPARKNET_COPY_THREADS", 0)) or max(1, min(16, (os.cpu_count() or 1) // max(1, world)))   # host threads of the data callback's copy
     net.setTrainData(src)
-    averager = Averager(lib, net, rank, world)
+    averager = make_averager(lib, net, rank, world)
     averager.broadcast_from_rank0()                     # all replicas start from the same weights (CifarApp.scala:92-99)
 
     def barrier():

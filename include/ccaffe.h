@@ -158,6 +158,25 @@ int sparknet_average_replicas_device(const void* const* replicas, int n, long co
  * replicas with NCCL on that stream first). */
 int sparknet_average_replicas_async(const void* const* replicas, int n, long count, void* out);
 
+/* Weight averaging over peer memory — replaces the driver's collect / reduce(WeightCollection.add) /
+ * scalarDivide / broadcast / setWeights round (src/main/scala/apps/CifarApp.scala:92-99,133-134;
+ * src/main/scala/libs/Net.scala:14-47,132-172; src/main/java/libs/JavaNDArray.java:84-117) for the replicas
+ * of one box, one process per GPU.  Result on every replica: (((w0 + w1) + ...) + w_{n-1}) / (float)n in
+ * IEEE fp32, rank order — bit-exact against the reference's sequential sum.
+ *   sparknet_peer_handle_bytes   size of one handle (a cudaIpcMemHandle_t, 64 bytes)
+ *   sparknet_peer_export         writes this replica's two handles (weight arena, flag block)
+ *   sparknet_peer_attach         takes all replicas' handles (nranks x handle_bytes each, rank order)
+ *   sparknet_average_peers       one round, enqueued on the compute stream; all replicas must call it
+ *   sparknet_peer_status         synchronises; 0 = all rounds completed, 1 = a peer did not arrive in time */
+int sparknet_peer_handle_bytes(void);
+int sparknet_peer_export(caffenet_state* state, void* arena_handle, void* flags_handle);
+int sparknet_peer_attach(caffenet_state* state, int rank, int nranks, const void* arena_handles, const void* flags_handles);
+int sparknet_average_peers(caffenet_state* state);
+int sparknet_peer_status(caffenet_state* state);
+/* Test hook: the same kernel and flag protocol with n replicas on ONE GPU (n streams, small grids).  in / out are
+ * host arrays [n][count]; every replica's arena is returned after `rounds` exchanges.  0 = ok, 1 = time-out. */
+int sparknet_test_average_peers(int n, long count, const float* in, float* out, int rounds);
+
 /* No counterpart in the reference (libccaffe/ccaffe.h has nothing like it).
  * D[M][N] = A x B^T in TF32 on the tensor cores for callers that must not allocate device memory while
  * running (inside a stream capture, in latency-critical threads, under a fixed memory budget): the

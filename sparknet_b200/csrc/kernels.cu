@@ -992,4 +992,130 @@ void average_replicas(cudaStream_t s, const float* const* replicas_dev, int nrep
   count_launch();
 }
 
+// ------------------------------------------------------------------------------------------
+// Weight averaging over peer memory: the whole exchange of one round in ONE kernel per GPU
+// (replaces collect / reduce(WeightCollection.add) / scalarDivide / broadcast / setWeights,
+// CifarApp.scala:92-99,133-134, Net.scala:14-47,132-172).  Every GPU owns one slice of the weight
+// arena.  It reads that slice from every replica through NVLink loads IN RANK ORDER, folds it
+// sequentially in fp32 (((w0 + w1) + w2) + ...), divides once by (float)N and stores the result into
+// the same slice of every replica's arena — reduce-scatter and all-gather in one pass, 2(N-1)/N·P bytes
+// over NVLink per GPU instead of the (N-1)·P of an all-gather followed by a local fold.
+//
+// Ordering across GPUs is by flags in each GPU's own memory that the peers write:
+//   ready[p] = epoch   "replica p finished its local iterations; its arena may be read and written"
+//   done[p]  = epoch   "replica p has stored its slice into every arena"
+// A block starts reading once all ready flags show this epoch (every block polls its OWN GPU's
+// memory); the last block to finish publishes `done` to all peers and the kernel ends only after all
+// peers' done flags arrived, so the next kernel on the stream sees the complete averaged arena.
+// Slices are disjoint: rank r alone reads and writes slice r of any arena during the exchange.
+// No grid-wide co-residency is needed.  A wait that exceeds `timeout_ns` sets *err and gives up
+// (the result is then undefined, the host reports it) instead of hanging the GPU.
+// Plain ld/st only: no TMA, no multicast touches another GPU's memory here.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ float4 ld_peer_f4(const float4* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ld_peer_f(const float* p) {
+  float v;
+  asm volatile("ld.volatile.global.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ unsigned ld_flag(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_flag(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+// flags layout per GPU: [0..7] ready, [8..15] done, [16] finished-block counter, [17] error
+__device__ bool wait_flags(const unsigned* mine, int base, int n, unsigned epoch, unsigned long long timeout_ns) {
+  const unsigned long long t0 = global_ns();
+  for (int p = 0; p < n; ++p) {
+    while ((int)(ld_flag(mine + base + p) - epoch) < 0) {
+      if (global_ns() - t0 > timeout_ns) return false;
+      __nanosleep(200);
+    }
+  }
+  return true;
+}
+template <int N>
+__global__ void __launch_bounds__(512) average_peers_kernel(PeerTable t, int rank, size_t count, unsigned epoch,
+                                                            unsigned long long timeout_ns) {
+  unsigned* mine = t.flags[rank];
+  __shared__ int ok;
+  if (threadIdx.x == 0) {
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      for (int p = 0; p < N; ++p) st_flag(t.flags[p] + rank, epoch);
+    }
+    ok = wait_flags(mine, 0, N, epoch, timeout_ns) ? 1 : 0;
+    if (!ok) mine[17] = 1u;
+  }
+  __syncthreads();
+  if (ok) {
+    // slice of this rank, in float4 units; the arena's tail (count % 4) is folded by rank N-1
+    const size_t n4 = count / 4;
+    const size_t per = (n4 + N - 1) / N;
+    const size_t lo = per * (size_t)rank, hi = lo + per < n4 ? lo + per : n4;
+    const float denom = (float)N;
+    for (size_t i = lo + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < hi; i += (size_t)gridDim.x * blockDim.x) {
+      float4 v[N];
+#pragma unroll
+      for (int r = 0; r < N; ++r) v[r] = ld_peer_f4(reinterpret_cast<const float4*>(t.w[r]) + i);
+      float4 a = v[0];
+#pragma unroll
+      for (int r = 1; r < N; ++r) {
+        a.x = __fadd_rn(a.x, v[r].x); a.y = __fadd_rn(a.y, v[r].y);
+        a.z = __fadd_rn(a.z, v[r].z); a.w = __fadd_rn(a.w, v[r].w);
+      }
+      a.x = __fdiv_rn(a.x, denom); a.y = __fdiv_rn(a.y, denom); a.z = __fdiv_rn(a.z, denom); a.w = __fdiv_rn(a.w, denom);
+#pragma unroll
+      for (int r = 0; r < N; ++r) reinterpret_cast<float4*>(t.w[r])[i] = a;
+    }
+    if (rank == N - 1 && blockIdx.x == 0) {
+      for (size_t i = n4 * 4 + threadIdx.x; i < count; i += blockDim.x) {
+        float a = ld_peer_f(t.w[0] + i);
+        for (int r = 1; r < N; ++r) a = __fadd_rn(a, ld_peer_f(t.w[r] + i));
+        a = __fdiv_rn(a, denom);
+        for (int r = 0; r < N; ++r) t.w[r][i] = a;
+      }
+    }
+  }
+  // last block out tells the peers that this rank's slice is in place everywhere, then waits for theirs
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned prev = atomicAdd(mine + 16, 1u);
+    if (prev == gridDim.x - 1) {
+      mine[16] = 0u;                               // next call starts from zero
+      __threadfence_system();
+      for (int p = 0; p < N; ++p) st_flag(t.flags[p] + 8 + rank, epoch);
+      if (!wait_flags(mine, 8, N, epoch, timeout_ns)) mine[17] = 1u;
+    }
+  }
+}
+void average_peers(cudaStream_t s, const PeerTable& t, int nranks, int rank, size_t count, unsigned epoch,
+                   unsigned long long timeout_ns, int max_grid) {
+  const size_t per4 = (count / 4 + nranks - 1) / nranks;
+  int grid = (int)std::min<size_t>((per4 + 511) / 512 + 1, (size_t)148 * 4);
+  if (max_grid > 0 && grid > max_grid) grid = max_grid;
+  if (grid < 1) grid = 1;
+  switch (nranks) {
+#define SN_PEERS(NR) case NR: average_peers_kernel<NR><<<grid, 512, 0, s>>>(t, rank, count, epoch, timeout_ns); break;
+    SN_PEERS(1) SN_PEERS(2) SN_PEERS(3) SN_PEERS(4) SN_PEERS(5) SN_PEERS(6) SN_PEERS(7) SN_PEERS(8)
+#undef SN_PEERS
+    default: fatal("average_peers: 1..8 replicas per box, got %d", nranks);
+  }
+  count_launch();
+}
+
+
 }  // namespace sn

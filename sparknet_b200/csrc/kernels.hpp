@@ -127,5 +127,13 @@ void axpy(cudaStream_t s, size_t n, float a, const float* x, float* y);
 // averaging: out[i] = (((r0[i] + r1[i]) + r2[i]) + ...) / (float)nrep, IEEE fp32, rank order
 // (src/main/java/libs/JavaNDArray.java:84-117, src/main/scala/apps/CifarApp.scala:133-134)
 void average_replicas(cudaStream_t s, const float* const* replicas_dev, int nrep, size_t n, float* out);
+// Peer-memory exchange (kernels.cu "Weight averaging over peer memory"): w[r] = replica r's weight arena and
+// flags[r] = replica r's 32-word flag block, both addressable from this GPU (own memory or an IPC mapping).
+struct PeerTable {
+  float* w[8];
+  unsigned* flags[8];
+};
+void average_peers(cudaStream_t s, const PeerTable& t, int nranks, int rank, size_t count, unsigned epoch,
+                   unsigned long long timeout_ns, int max_grid = 0);
 
 }  // namespace sn

@@ -4,10 +4,15 @@ collect / reduce(WeightCollection.add) / scalarDivide / broadcast / setWeights r
 
 One process per GPU.  Every rank contributes its whole weight arena; the result on every rank is
     (((w_0 + w_1) + w_2) + ... + w_{N-1}) / (float)N
-in IEEE fp32, summed in RANK ORDER — bit-exact against the reference's sequential JVM sum.  NCCL is
-only the transport (all-gather over NVLink/NVSwitch); the arithmetic is this library's own kernel
-(csrc/kernels.cu average_replicas), which reads the gathered replicas in rank order.  NCCL's own
-all-reduce is not used because its ring/tree order is not the reference's order.
+in IEEE fp32, summed in RANK ORDER — bit-exact against the reference's sequential JVM sum.
+
+`PeerAverager` (the default): ONE kernel per GPU does the whole exchange over NVLink peer memory
+(csrc/kernels.cu average_peers_kernel): every GPU folds its slice of the arena from all replicas in rank
+order and stores the result into every replica — 2(N-1)/N * P bytes per GPU.  torch.distributed only
+carries the 64-byte IPC handles at set-up.
+`Averager` (SPARKNET_AVG=nccl, kept for comparison): NCCL all-gather of the whole arena as the transport,
+then this library's fold kernel (average_replicas) over the gathered copies, (N-1) * P bytes per GPU.
+NCCL's own all-reduce is not used because its ring/tree order is not the reference's order.
 
 torch / torch.distributed are plumbing here (process group, device buffer for the gather)."""
 from __future__ import annotations
@@ -74,6 +79,72 @@ class Averager:
         self.ev1.record(self.stream)
         self.ev1.synchronize()
         return float(self.ev0.elapsed_time(self.ev1))
+
+
+class PeerAverager:
+    """Weight averaging in one kernel per GPU over peer memory (include/ccaffe.h sparknet_peer_*)."""
+
+    def __init__(self, lib, net, rank: int, world: int):
+        self.lib, self.net, self.rank, self.world = lib, net, rank, world
+        self.method = "identity (1 replica)" if world == 1 else \
+            "one fused kernel per GPU over NVLink peer memory: rank-ordered fp32 fold of the own slice + store to all replicas"
+        if world == 1:
+            return
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        hb = lib.sparknet_peer_handle_bytes()
+        mine = np.zeros(2 * hb, dtype=np.uint8)
+        rc = lib.sparknet_peer_export(net.state, ctypes.c_void_p(mine.ctypes.data), ctypes.c_void_p(mine.ctypes.data + hb))
+        assert rc == 0, rc
+        everyone = [torch.empty(2 * hb, dtype=torch.uint8, device="cuda") for _ in range(world)]
+        dist.all_gather(everyone, torch.from_numpy(mine).cuda())
+        allh = np.stack([t.cpu().numpy() for t in everyone])                      # [world][2 * hb]
+        arena_h = np.ascontiguousarray(allh[:, :hb])
+        flags_h = np.ascontiguousarray(allh[:, hb:])
+        rc = lib.sparknet_peer_attach(net.state, rank, world, ctypes.c_void_p(arena_h.ctypes.data),
+                                      ctypes.c_void_p(flags_h.ctypes.data))
+        assert rc == 0, rc
+        dist.barrier()
+        ptr, cnt = ctypes.c_void_p(), ctypes.c_long()
+        assert lib.sparknet_param_arena(net.state, ctypes.byref(ptr), ctypes.byref(cnt)) == 0
+        self.n = int(cnt.value)
+        self.arena = torch.as_tensor(_DevArray(ptr.value, self.n), device="cuda")
+        self.stream = torch.cuda.ExternalStream(lib.sparknet_compute_stream(net.state))
+        self.ev0 = torch.cuda.Event(enable_timing=True)
+        self.ev1 = torch.cuda.Event(enable_timing=True)
+
+    def broadcast_from_rank0(self) -> None:
+        """All replicas start from rank 0's weights (the driver's first broadcast, CifarApp.scala:92-99)."""
+        if self.world == 1:
+            return
+        ptr, cnt = ctypes.c_void_p(), ctypes.c_long()
+        self.lib.sparknet_param_arena(self.net.state, ctypes.byref(ptr), ctypes.byref(cnt))   # heads -> device
+        with self.torch.cuda.stream(self.stream):
+            self.dist.broadcast(self.arena, src=0)
+        self.stream.synchronize()
+
+    def average(self) -> float:
+        """Average the weights of all replicas in place; returns the device time in ms (includes waiting for the
+        slowest replica to arrive)."""
+        if self.world == 1:
+            return 0.0
+        self.ev0.record(self.stream)
+        rc = self.lib.sparknet_average_peers(self.net.state)
+        assert rc == 0, rc
+        self.ev1.record(self.stream)
+        self.ev1.synchronize()
+        return float(self.ev0.elapsed_time(self.ev1))
+
+    def check(self) -> None:
+        assert self.world == 1 or self.lib.sparknet_peer_status(self.net.state) == 0, \
+            "a replica did not arrive at an averaging round within the time-out"
+
+
+def make_averager(lib, net, rank: int, world: int):
+    """The multi-GPU driver's choice: peer-memory kernel unless SPARKNET_AVG=nccl."""
+    import os
+    return (Averager if os.environ.get("SPARKNET_AVG", "peer") == "nccl" else PeerAverager)(lib, net, rank, world)
 
 
 def sequential_average(weight_lists):

@@ -262,6 +262,27 @@ def test_averaging_kernel_is_bit_exact_rank_ordered(oracle, product, nrep):
     assert got.tobytes() == want.tobytes()                           # memcmp, incl. -0.0 and denormals
 
 
+@pytest.mark.parametrize("nrep", [1, 2, 3, 5, 8])
+def test_peer_memory_exchange_kernel_is_bit_exact_rank_ordered(oracle, product, nrep):
+    """The one-kernel exchange of the multi-GPU driver (kernels.cu average_peers_kernel: rank-ordered fold of the own
+    slice from every replica, result stored into every replica, ready/done flags) run with nrep replicas on ONE GPU;
+    two rounds, every replica's arena against the oracle's sequential fold (NDArraySpec.scala:34-56 arithmetic)."""
+    rng = np.random.default_rng(100 + nrep)
+    n = 1024 * 37 + (3 if nrep % 2 else 0)                              # ragged tail when odd
+    reps = np.stack([(rng.standard_normal(n) * 10.0 ** rng.integers(-30, 30, n)).astype(F) for _ in range(nrep)])
+    reps[0][:7] = [0.0, -0.0, 1e-45, -1e-45, 3.4e38, 1.0, 1e-38]
+    want = reps.copy()
+    for _ in range(2):
+        ptrs = (ctypes.POINTER(ctypes.c_float) * nrep)(*[fptr(want[r]) for r in range(nrep)])
+        avg = np.empty(n, dtype=F)
+        oracle.oracle_average(ptrs, nrep, n, fptr(avg))
+        want = np.stack([avg] * nrep)
+    got = np.empty_like(reps)
+    assert product.sparknet_test_average_peers(nrep, n, fptr(reps), fptr(got), 2) == 0
+    for r in range(nrep):
+        assert got[r].tobytes() == want[r].tobytes(), r
+
+
 def test_two_replicas_two_rounds_momentum_is_not_averaged(oracle, product):
     """The SparkNet round loop (src/main/scala/apps/CifarApp.scala:95-136) on two replicas: local
     steps, average weights only, continue with each replica's own momentum history."""

@@ -1,5 +1,5 @@
 """Run under torchrun with >= 2 GPUs: trains each replica for a few steps, averages through the CUDA path
-(NCCL all-gather + rank-ordered reduce kernel) and checks the result BIT-EXACTLY against the sequential
+(the peer-memory kernel, or with SPARKNET_AVG=nccl the NCCL all-gather + rank-ordered reduce kernel) and checks the result BIT-EXACTLY against the sequential
 host fold (((w0+w1)+w2)+...)/N of the gathered pre-average weights."""
 import ctypes, os, sys
 import numpy as np
@@ -9,7 +9,7 @@ import torch.distributed as dist
 from sparknet_b200 import zoo
 from sparknet_b200.library import load_library
 from sparknet_b200.net import CaffeNet, MinibatchSource
-from sparknet_b200.parallel import Averager
+from sparknet_b200.parallel import make_averager
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
@@ -23,7 +23,7 @@ rng = np.random.default_rng(1701 + rank)
 imgs = [np.ascontiguousarray(rng.random((batch, c, h, w), dtype=np.float32) * 255 - 128) for _ in range(2)]
 labs = [rng.integers(0, classes, size=(batch,)).astype(np.float32) for _ in range(2)]
 net.setTrainData(MinibatchSource(imgs, labs))
-avg = Averager(lib, net, rank, world)
+avg = make_averager(lib, net, rank, world)
 avg.broadcast_from_rank0()
 ok = True
 for rnd in range(2):
@@ -45,6 +45,10 @@ for rnd in range(2):
     if rank == 0:
         print(f"round {rnd}: {n} params, averaging {ms:.3f} ms, bit-exact vs sequential rank-order fold: {same}; "
               f"replicas differed before averaging: {not np.array_equal(allw[0].cpu().numpy(), allw[-1].cpu().numpy())}", flush=True)
+if hasattr(avg, "check"):
+    avg.check()
+if rank == 0:
+    print("method:", avg.method, flush=True)
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
