@@ -188,6 +188,9 @@ def main():
     ap.add_argument("--precision", default=None, choices=[None, "ffma", "tf32"])
     ap.add_argument("--pool", type=int, default=8, help="distinct synthetic minibatches replayed cyclically")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tau-sweep", default=None,
+                    help="comma list of tau values (BASELINE.json configs[4]: 1,10,50,200): adds averaging cost vs compute per "
+                         "round for each, measured after the main run with the inputs resident in HBM")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -261,16 +264,24 @@ def main():
             done += k
         return avg_ms
 
+    exchange = {}                                       # device-side clock of the last timed region's exchanges
+
+    def peer_clock():
+        return averager.timing() if hasattr(averager, "timing") else (0, 0.0, 0.0)
+
     def timed(n):
         barrier()
+        peer_clock()                                    # reset the kernel's own clock
         l0 = lib.sparknet_kernel_launches(st)
         lib.sparknet_timer_start(st)
         avg_ms = run_steps(n)
         ms = lib.sparknet_timer_stop_ms(st)
         barrier()
-        t = torch.tensor([ms, avg_ms], device="cuda", dtype=torch.float64)
+        _, wait_ms, xchg_ms = peer_clock()
+        t = torch.tensor([ms, avg_ms, wait_ms, xchg_ms], device="cuda", dtype=torch.float64)
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        exchange.update(wait_ms=float(t[2]), exchange_ms=float(t[3]))
         return float(t[0]), float(t[1]), lib.sparknet_kernel_launches(st) - l0
 
     # ---- (1) e2e: host buffers through the callback ABI, H2D inside the timed region ----------
@@ -282,10 +293,42 @@ def main():
     run_steps(warmup)
     clocks = ClockSampler(local_rank) if rank == 0 else None
     ms, avg_ms, launches = timed(steps)
+    exchange_value = dict(exchange)
     clk = clocks.stop() if clocks else None
     n_rounds = (steps + tau - 1) // tau
     value = args.gpus * batch * steps / (ms * 1e-3)
     e2e = args.gpus * batch * steps / (e2e_ms * 1e-3)
+
+    # ---- (2b) tau sweep: averaging cost against compute per round (BASELINE.json configs[4]) ----------
+    sweep = None
+    if args.tau_sweep:
+        sweep = []
+        for t in [int(x) for x in args.tau_sweep.split(",")]:
+            rounds = max(2, min(20, 200 // t))
+            def run_rounds(nr, t=t):
+                a = 0.0
+                for _ in range(nr):
+                    lib.solver_step(st, t)
+                    a += averager.average()
+                return a
+            run_rounds(1)
+            barrier()
+            peer_clock()
+            lib.sparknet_timer_start(st)
+            a_ms = run_rounds(rounds)
+            t_ms = lib.sparknet_timer_stop_ms(st)
+            barrier()
+            _, w_ms, x_ms = peer_clock()
+            v = torch.tensor([t_ms, a_ms, w_ms, x_ms], device="cuda", dtype=torch.float64)
+            if world > 1:
+                dist.all_reduce(v, op=dist.ReduceOp.MAX)
+            sweep.append({"tau": t, "rounds": rounds, "ms_per_round": float(v[0]) / rounds,
+                          "averaging_ms_per_round": float(v[1]) / rounds, "averaging_share": float(v[1]) / float(v[0]),
+                          "wait_for_slowest_replica_ms": float(v[2]), "exchange_ms": float(v[3]),
+                          "exchange_share": float(v[3]) * rounds / float(v[0]),
+                          "images_per_sec": args.gpus * batch * t * rounds / (float(v[0]) * 1e-3)})
+    if hasattr(averager, "check"):
+        averager.check()                                # every exchange completed (no replica timed out)
 
     # ---- (3) per-layer device timing of one iteration -> roofline of the dominant kernels ---------
     L = net.numLayers
@@ -335,10 +378,17 @@ def main():
                             "is copied back to a pinned host ring (4 bytes, asynchronous)"},
             "gpu_launches": int(launches), "clocks": clk,
             "averaging": {"rounds": n_rounds, "ms_per_round": avg_ms / n_rounds, "share_of_round": avg_ms / ms if ms else None,
-                          "method": averager.method},
+                          "method": averager.method,
+                          # ms_per_round is stream time from the end of this replica's last iteration to the end of the
+                          # exchange: it contains the wait for the slowest replica.  The kernel's own clock splits it:
+                          "wait_for_slowest_replica_ms": exchange_value.get("wait_ms"),
+                          "exchange_ms": exchange_value.get("exchange_ms"),
+                          "exchange_share_of_round": (exchange_value.get("exchange_ms", 0.0) * n_rounds / ms) if ms else None},
             "roofline": roofline, "roofline_hbm": roofline_hbm, "layer_ms_fwd_bwd": layer_ms,
             "published_context": {"caffenet_k40_native_caffe_images_per_sec": 193,
                                   "source": "caffe/docs/performance_hardware.md:19 (other hardware, 1 GPU, no averaging)"}}
+    if sweep:
+        line["tau_sweep"] = sweep
     if rank == 0 and not args.no_cpu_baseline and args.gpus == 1:
         r = cpu_reference_run(args.workload, 1, 0, budget_s=20.0)
         line["cpu_baseline"] = {"value": r["value"], "unit": "images/s", "cores": r["cores"], "kind": "port",

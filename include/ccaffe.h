@@ -158,6 +158,12 @@ int sparknet_average_replicas_device(const void* const* replicas, int n, long co
  * replicas with NCCL on that stream first). */
 int sparknet_average_replicas_async(const void* const* replicas, int n, long count, void* out);
 
+/* solver_step records the steady-state iteration into a CUDA graph and replays it (the first iteration of every
+ * call runs eagerly).  mode 1 on, 0 off, -1 = SPARKNET_GRAPH environment variable (default on); returns the previous
+ * mode.  sparknet_graph_replays = iterations that ran as replays so far. */
+int sparknet_set_graph_mode(caffenet_state* state, int mode);
+long sparknet_graph_replays(caffenet_state* state);
+
 /* Weight averaging over peer memory — replaces the driver's collect / reduce(WeightCollection.add) /
  * scalarDivide / broadcast / setWeights round (src/main/scala/apps/CifarApp.scala:92-99,133-134;
  * src/main/scala/libs/Net.scala:14-47,132-172; src/main/java/libs/JavaNDArray.java:84-117) for the replicas
@@ -167,12 +173,15 @@ int sparknet_average_replicas_async(const void* const* replicas, int n, long cou
  *   sparknet_peer_export         writes this replica's two handles (weight arena, flag block)
  *   sparknet_peer_attach         takes all replicas' handles (nranks x handle_bytes each, rank order)
  *   sparknet_average_peers       one round, enqueued on the compute stream; all replicas must call it
- *   sparknet_peer_status         synchronises; 0 = all rounds completed, 1 = a peer did not arrive in time */
+ *   sparknet_peer_status         synchronises; 0 = all rounds completed, 1 = a peer did not arrive in time
+ *   sparknet_peer_timing         device-side clock of the rounds since its last call: mean ms waiting for the slowest
+ *                                replica, mean ms of the exchange proper (all ready -> all stored); returns #rounds */
 int sparknet_peer_handle_bytes(void);
 int sparknet_peer_export(caffenet_state* state, void* arena_handle, void* flags_handle);
 int sparknet_peer_attach(caffenet_state* state, int rank, int nranks, const void* arena_handles, const void* flags_handles);
 int sparknet_average_peers(caffenet_state* state);
 int sparknet_peer_status(caffenet_state* state);
+int sparknet_peer_timing(caffenet_state* state, float* wait_ms, float* exchange_ms);
 /* Test hook: the same kernel and flag protocol with n replicas on ONE GPU (n streams, small grids).  in / out are
  * host arrays [n][count]; every replica's arena is returned after `rounds` exchanges.  0 = ok, 1 = time-out. */
 int sparknet_test_average_peers(int n, long count, const float* in, float* out, int rounds);

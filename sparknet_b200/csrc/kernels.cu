@@ -126,8 +126,10 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
   return c;
 }
 __global__ void dropout_fwd_kernel(size_t n, const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ mask,
-                                   uint32_t thres, float scale, bool draw, uint64_t seed, uint64_t offset) {
+                                   uint32_t thres, float scale, bool draw, uint64_t seed, uint64_t offset,
+                                   const unsigned long long* __restrict__ offset_dev) {
   const size_t n4 = (n + 3) / 4;
+  if (offset_dev) offset = *offset_dev;          // per-iteration value published on the device (replayed graphs)
   for (size_t q = blockIdx.x * (size_t)blockDim.x + threadIdx.x; q < n4; q += (size_t)gridDim.x * blockDim.x) {
     uint32_t r[4];
     if (draw) {
@@ -148,9 +150,9 @@ __global__ void dropout_fwd_kernel(size_t n, const float* __restrict__ x, float*
   }
 }
 void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* mask, float ratio, float scale, bool draw,
-                 uint64_t seed, uint64_t offset) {
+                 uint64_t seed, uint64_t offset, const unsigned long long* offset_dev) {
   const uint32_t thres = (uint32_t)((double)0xFFFFFFFFu * ratio);   // dropout_layer.cpp:18 uint_thres_
-  dropout_fwd_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, s>>>(n, x, y, mask, thres, scale, draw, seed, offset);
+  dropout_fwd_kernel<<<grid_for((n + 3) / 4, 256), 256, 0, s>>>(n, x, y, mask, thres, scale, draw, seed, offset, offset_dev);
   count_launch();
 }
 __global__ void dropout_bwd_kernel(size_t n, const float* __restrict__ dy, const uint8_t* __restrict__ mask,
@@ -948,7 +950,8 @@ __device__ __forceinline__ float round_tf32(float x) {
   return __uint_as_float(r);
 }
 __global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ h, float4* __restrict__ shadow,
-                                  const SgdChunk* __restrict__ table, float rate, float mu) {
+                                  const SgdChunk* __restrict__ table, float rate, float mu, const float* __restrict__ rate_dev) {
+  if (rate_dev) rate = *rate_dev;                // this iteration's learning rate, published on the device (replayed graphs)
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     const SgdChunk ck = table[i >> 8];           // 1024 floats = 256 float4
     const float local_rate = __fmul_rn(rate, ck.lr_mult);   // sgd_solver.cpp:210-211
@@ -968,9 +971,17 @@ __global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __r
   }
 }
 void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, float* shadow, const SgdChunk* chunk_table, float rate,
-                float momentum) {
+                float momentum, const float* rate_dev) {
   if (n % 1024) fatal("sgd_update: arena length %zu is not a multiple of 1024", n);
-  sgd_update_kernel<<<grid_for(n / 4, 256), 256, 0, s>>>(n / 4, (float4*)w, (float4*)g, (float4*)h, (float4*)shadow, chunk_table, rate, momentum);
+  sgd_update_kernel<<<grid_for(n / 4, 256), 256, 0, s>>>(n / 4, (float4*)w, (float4*)g, (float4*)h, (float4*)shadow, chunk_table, rate, momentum, rate_dev);
+  count_launch();
+}
+
+// Per-iteration scalars that a replayed CUDA graph cannot take as kernel arguments (learning rate, dropout counters):
+// one tiny launch OUTSIDE the graph writes them into device memory, the kernels inside read them from there.
+__global__ void publish_step_scalars_kernel(StepScalars* dst, StepScalars v) { *dst = v; }
+void publish_step_scalars(cudaStream_t s, StepScalars* dst, const StepScalars& v) {
+  publish_step_scalars_kernel<<<1, 1, 0, s>>>(dst, v);
   count_launch();
 }
 
@@ -1035,7 +1046,10 @@ __device__ __forceinline__ unsigned long long global_ns() {
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
   return t;
 }
-// flags layout per GPU: [0..7] ready, [8..15] done, [16] finished-block counter, [17] error
+// flags layout per GPU (32 words): [0..7] ready, [8..15] done, [16] finished-block counter, [17] error,
+// [20..21] entry time of the current round, [22..23] time all replicas were ready, then three u64 sums over the
+// rounds so far: [24..25] ns spent waiting for the slowest replica, [26..27] ns from "all ready" to "all done"
+// (the exchange proper), [28..29] rounds
 __device__ bool wait_flags(const unsigned* mine, int base, int n, unsigned epoch, unsigned long long timeout_ns) {
   const unsigned long long t0 = global_ns();
   for (int p = 0; p < n; ++p) {
@@ -1052,12 +1066,15 @@ __global__ void __launch_bounds__(512) average_peers_kernel(PeerTable t, int ran
   unsigned* mine = t.flags[rank];
   __shared__ int ok;
   if (threadIdx.x == 0) {
+    unsigned long long* stamps = reinterpret_cast<unsigned long long*>(mine + 20);
     if (blockIdx.x == 0) {
+      stamps[0] = global_ns();
       __threadfence_system();
       for (int p = 0; p < N; ++p) st_flag(t.flags[p] + rank, epoch);
     }
     ok = wait_flags(mine, 0, N, epoch, timeout_ns) ? 1 : 0;
     if (!ok) mine[17] = 1u;
+    if (blockIdx.x == 0) stamps[1] = global_ns();
   }
   __syncthreads();
   if (ok) {
@@ -1099,6 +1116,11 @@ __global__ void __launch_bounds__(512) average_peers_kernel(PeerTable t, int ran
       __threadfence_system();
       for (int p = 0; p < N; ++p) st_flag(t.flags[p] + 8 + rank, epoch);
       if (!wait_flags(mine, 8, N, epoch, timeout_ns)) mine[17] = 1u;
+      unsigned long long* stamps = reinterpret_cast<unsigned long long*>(mine + 20);
+      const unsigned long long t2 = global_ns();
+      stamps[2] += stamps[1] - stamps[0];
+      stamps[3] += t2 - stamps[1];
+      stamps[4] += 1ull;
     }
   }
 }

@@ -89,7 +89,7 @@ void relu_bwd(cudaStream_t s, size_t n, const float* dy, const float* x_or_y, fl
 // mask: one byte per element (1 = keep).  If `draw` the kernel draws it (Philox4x32-10 keyed by
 // seed/offset); otherwise it uses the mask as given (injected by tests).
 void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* mask, float ratio, float scale,
-                 bool draw, uint64_t seed, uint64_t offset);
+                 bool draw, uint64_t seed, uint64_t offset, const unsigned long long* offset_dev = nullptr);
 void dropout_bwd(cudaStream_t s, size_t n, const float* dy, const uint8_t* mask, float* dx, float scale);
 
 struct LrnGeom { int N, C, H, W, size; float alpha, beta, k; };
@@ -118,7 +118,16 @@ void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db
 struct SgdChunk { float lr_mult, decay; };     // per-chunk lr_mult and local_decay (= weight_decay * decay_mult)
 // shadow (nullable): receives the tf32-rounded new weights, same layout as w
 void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, float* shadow, const SgdChunk* chunk_table, float rate,
-                float momentum);
+                float momentum, const float* rate_dev = nullptr);
+// Scalars that change every iteration, kept in device memory so that a captured iteration can be replayed
+// (Solver::step): the learning rate and the Philox counters of up to kMaxDropout dropout layers.
+struct StepScalars {
+  static constexpr int kMaxDropout = 6;
+  float rate;
+  unsigned int n_dropout;
+  unsigned long long dropout_offset[kMaxDropout];
+};
+void publish_step_scalars(cudaStream_t s, StepScalars* dst, const StepScalars& v);
 
 void fill(cudaStream_t s, size_t n, float* p, float v);
 void split_add(cudaStream_t s, size_t n, const float* a, const float* b, float* out);

@@ -679,6 +679,8 @@ struct DropoutLayer : Layer {
   size_t n = 0;
   bool injected = false;
   uint64_t seed = 0, offset = 0;
+  const unsigned long long* offset_slot = nullptr;   // inside Solver::step: the counter is read from device memory
+  void advance() { offset += (n + 3) / 4; }
   using Layer::Layer;
   ~DropoutLayer() override { if (mask) cudaFree(mask); }
   const char* type() const override { return "Dropout"; }
@@ -694,8 +696,8 @@ struct DropoutLayer : Layer {
     const float* x = bottom[0]->data->gpu();
     float* y = top[0]->data->mutable_gpu();
     if (phase == cp::TRAIN) {
-      dropout_fwd(S(), n, x, y, mask, ratio, scale, !injected, seed, offset);
-      offset += (n + 3) / 4;
+      dropout_fwd(S(), n, x, y, mask, ratio, scale, !injected, seed, offset, offset_slot);
+      advance();
     } else if (x != y) {
       SN_CUDA(cudaMemcpyAsync(y, x, n * sizeof(float), cudaMemcpyDeviceToDevice, S()));
     }
@@ -1154,8 +1156,10 @@ Solver::Solver(const cp::SolverParameter& p) : param(p) {
     SN_CUDA(cudaMalloc(&chunk_table, table.size() * sizeof(SgdChunk)));
     SN_CUDA(cudaMemcpy(chunk_table, table.data(), table.size() * sizeof(SgdChunk), cudaMemcpyHostToDevice));
   }
-  SN_CUDA(cudaMalloc(&loss_hist, kLossHist * sizeof(float)));
-  SN_CUDA(cudaMemset(loss_hist, 0, kLossHist * sizeof(float)));
+  SN_CUDA(cudaMalloc(&loss_hist, (kLossHist + 1) * sizeof(float)));      // last slot: the loss of a replayed iteration
+  SN_CUDA(cudaMemset(loss_hist, 0, (kLossHist + 1) * sizeof(float)));
+  SN_CUDA(cudaMalloc(&scalars_dev, sizeof(StepScalars)));
+  SN_CUDA(cudaMemset(scalars_dev, 0, sizeof(StepScalars)));
   SN_CUDA(cudaMallocHost(&loss_hist_host, kLossHist * sizeof(float)));
   memset(loss_hist_host, 0, kLossHist * sizeof(float));
 }
@@ -1166,6 +1170,18 @@ Solver::~Solver() {
   if (chunk_table) cudaFree(chunk_table);
   if (loss_hist) cudaFree(loss_hist);
   if (loss_hist_host) cudaFreeHost(loss_hist_host);
+  drop_graphs();
+  if (scalars_dev) cudaFree(scalars_dev);
+}
+// Configuration epoch: bumped by every ABI call that can change WHICH kernels an iteration launches or with what
+// arguments (precision, resident inputs, injected masks, development switches, callbacks); recordings of an older
+// epoch are discarded.
+static uint64_t g_config_epoch = 1;
+void bump_config_epoch() { ++g_config_epoch; }
+void Solver::drop_graphs() {
+  for (GraphEntry& g : graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
+  graphs.clear();
+  eager_iters = 0;
 }
 float Solver::get_learning_rate() {   // sgd_solver.cpp:27-63, same expression types
   const string& pol = param.lr_policy;
@@ -1207,23 +1223,91 @@ void Solver::step(int iters) {
         for (JavaDataLayer* d : feeds) d->prefetch_fill(k);      // data callback, then label callback: one pair per iteration
     });
   }
+  // ---- CUDA-graph replay (see runtime.hpp Solver::GraphEntry) ----
+  int D = 0;                                                   // leading JavaData layers run eagerly every iteration
+  while (D < L && dynamic_cast<JavaDataLayer*>(net->layers[(size_t)D].get())) ++D;
+  std::vector<DropoutLayer*> drops;
+  for (auto& l : net->layers)
+    if (DropoutLayer* d = dynamic_cast<DropoutLayer*>(l.get())) drops.push_back(d);
+  bool use_graph = graph_mode >= 0 ? graph_mode == 1 : !(getenv("SPARKNET_GRAPH") && atoi(getenv("SPARKNET_GRAPH")) == 0);
+  if (param.display || (int)feeds.size() != D || (int)drops.size() > StepScalars::kMaxDropout || !net->arena_floats) use_graph = false;
+  if (graphs_epoch != g_config_epoch) { drop_graphs(); graphs_epoch = g_config_epoch; }
+  for (size_t i = 0; i < drops.size(); ++i) drops[i]->offset_slot = &scalars_dev->dropout_offset[i];
+  const int first_iter = iter;
+  cudaStream_t cs = ctx().compute;
   while (iter < stop_iter) {
-    net->loss_log = loss_hist + (iter % kLossHist);
-    net->forward_from_to(0, L - 1);
-    net->backward_from_to(L - 1, 0);
-    if (param.display && iter % param.display == 0) {
-      const float loss = net->total_loss();
-      fprintf(stderr, "Iteration %d, loss = %g, lr = %g\n", iter, loss, get_learning_rate());
+    for (int i = 0; i < D; ++i) net->layers[(size_t)i]->forward(net->bottom_vecs[(size_t)i], net->top_vecs[(size_t)i]);
+    // this iteration's scalars -> device memory (one tiny launch, skipped while nothing changed)
+    StepScalars sc{};
+    sc.rate = get_learning_rate();
+    sc.n_dropout = (unsigned)drops.size();
+    for (size_t i = 0; i < drops.size(); ++i) sc.dropout_offset[i] = drops[i]->offset;
+    if (!scalars_published || memcmp(&sc, &scalars_last, sizeof(sc)) != 0) {
+      publish_step_scalars(cs, scalars_dev, sc);
+      scalars_last = sc;
+      scalars_published = true;
     }
-    const float rate = get_learning_rate();
-    if (net->arena_floats) sgd_update(ctx().compute, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum);
+    const float rate = sc.rate;
+    GraphEntry* entry = nullptr;
+    bool replay = use_graph && iter != first_iter && eager_iters >= 2;
+    if (replay) {
+      std::vector<const void*> key;
+      for (int i = 0; i < D; ++i) key.push_back(net->top_vecs[(size_t)i][0]->data->dev);
+      for (GraphEntry& g : graphs) if (g.key == key) entry = &g;
+      if (!entry) {
+        if (graphs.size() >= 64) drop_graphs();                // input buffers keep changing: start over
+        // record: the host walks the layers exactly as in an eager iteration, the launches go into the graph
+        const long l0 = ctx().launches;
+        cudaGraph_t graph = nullptr;
+        SN_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed));
+        net->loss_log = loss_hist + kLossHist;
+        net->forward_from_to(D, L - 1);
+        net->backward_from_to(L - 1, 0);
+        sgd_update(cs, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum, &scalars_dev->rate);
+        cudaError_t e = cudaStreamEndCapture(cs, &graph);
+        GraphEntry g;
+        if (e == cudaSuccess && graph) {
+          e = cudaGraphInstantiate(&g.exec, graph, 0);
+          cudaGraphDestroy(graph);
+        }
+        if (e != cudaSuccess || !g.exec) {
+          cudaGetLastError();
+          fprintf(stderr, "sparknet: recording the iteration into a CUDA graph failed (%s); continuing without graphs\n", cudaGetErrorString(e));
+          use_graph = false; graph_mode = 0; replay = false;
+        } else {
+          g.key = key;
+          g.launches = ctx().launches - l0;
+          ctx().launches = l0;                                 // nothing ran yet; the replay below counts them
+          graphs.push_back(std::move(g));
+          entry = &graphs.back();
+          for (DropoutLayer* d : drops) d->offset -= (d->n + 3) / 4;   // the recording pass advanced them; the replay does it below
+        }
+      }
+    }
+    if (replay && entry) {
+      SN_CUDA(cudaGraphLaunch(entry->exec, cs));
+      ctx().launches += entry->launches;
+      ++graph_replays;
+      for (DropoutLayer* d : drops) d->advance();
+      SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + kLossHist, sizeof(float), cudaMemcpyDeviceToHost, cs));
+    } else {
+      net->loss_log = loss_hist + (iter % kLossHist);
+      net->forward_from_to(D, L - 1);
+      net->backward_from_to(L - 1, 0);
+      if (param.display && iter % param.display == 0) {
+        const float loss = net->total_loss();
+        fprintf(stderr, "Iteration %d, loss = %g, lr = %g\n", iter, loss, rate);
+      }
+      if (net->arena_floats) sgd_update(cs, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum, &scalars_dev->rate);
+      // this iteration's loss goes to the pinned host ring too: 4 bytes, asynchronous, read after the caller's next sync
+      SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost, cs));
+      ++eager_iters;
+    }
     for (Blob* b : net->learnable_params) ++b->data->gen;    // weights changed on the device
     net->mark_shadows_current();                              // ... and sgd_update rounded them into the shadow arena
-    // this iteration's loss goes to the pinned host ring too: 4 bytes, asynchronous, read after the caller's next sync
-    SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost,
-                            ctx().compute));
     ++iter;
   }
+  for (DropoutLayer* d : drops) d->offset_slot = nullptr;
   if (prefetch) {
     helper.join();
     for (JavaDataLayer* d : feeds) d->pf = nullptr;

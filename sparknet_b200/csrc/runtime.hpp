@@ -161,6 +161,24 @@ struct Solver {
   float* loss_hist_host = nullptr;      // pinned mirror: every iteration copies its loss here asynchronously (4 bytes D2H per step)
   static constexpr int kLossHist = 4096;
   float smoothed_loss = 0.f;
+  // Steady-state iterations are captured once into a CUDA graph and replayed.  The first iteration of
+  // every solver_step call runs eagerly (it picks up whatever the caller changed through the ABI in between: weights
+  // written through get_data pointers, host-side heads, stale shadows), later ones replay the graph recorded for the
+  // current input buffers.  Per-iteration scalars live in `scalars_dev` (see kernels.hpp StepScalars).
+  struct GraphEntry {
+    std::vector<const void*> key;       // device pointers of the data layers' tops the recording reads
+    cudaGraphExec_t exec = nullptr;
+    long launches = 0;                  // kernel launches inside (bookkeeping for sparknet_kernel_launches)
+  };
+  std::vector<GraphEntry> graphs;
+  StepScalars* scalars_dev = nullptr;
+  StepScalars scalars_last{};
+  bool scalars_published = false;
+  int graph_mode = -1;                  // -1: SPARKNET_GRAPH environment variable (default on), 0 off, 1 on
+  int eager_iters = 0;                  // eager iterations since the graphs were last dropped (capture needs >= 2)
+  uint64_t graphs_epoch = 0;            // value of the configuration epoch the recordings belong to
+  long graph_replays = 0;
+  void drop_graphs();
   explicit Solver(const cp::SolverParameter& p);
   ~Solver();
   float get_learning_rate();

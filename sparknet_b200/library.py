@@ -82,11 +82,14 @@ _EXTENSIONS = {
     "sparknet_last_average_ms": (c_float, [c_void_p]),
     "sparknet_average_replicas_device": (c_int, [POINTER(c_void_p), c_int, ctypes.c_long, c_void_p]),
     "sparknet_average_replicas_async": (c_int, [POINTER(c_void_p), c_int, ctypes.c_long, c_void_p]),
+    "sparknet_set_graph_mode": (c_int, [c_void_p, c_int]),
+    "sparknet_graph_replays": (ctypes.c_long, [c_void_p]),
     "sparknet_peer_handle_bytes": (c_int, []),
     "sparknet_peer_export": (c_int, [c_void_p, c_void_p, c_void_p]),
     "sparknet_peer_attach": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
     "sparknet_average_peers": (c_int, [c_void_p]),
     "sparknet_peer_status": (c_int, [c_void_p]),
+    "sparknet_peer_timing": (c_int, [c_void_p, POINTER(c_float), POINTER(c_float)]),
     "sparknet_test_average_peers": (c_int, [c_int, ctypes.c_long, POINTER(c_float), POINTER(c_float), c_int]),
     "sparknet_timer_start": (None, [c_void_p]),
     "sparknet_timer_stop_ms": (c_float, [c_void_p]),

@@ -136,6 +136,15 @@ class PeerAverager:
         self.ev1.synchronize()
         return float(self.ev0.elapsed_time(self.ev1))
 
+    def timing(self):
+        """(rounds, mean ms waiting for the slowest replica, mean ms of the exchange proper) since the last call,
+        from the kernel's own clock (include/ccaffe.h sparknet_peer_timing)."""
+        if self.world == 1:
+            return 0, 0.0, 0.0
+        w, x = ctypes.c_float(0), ctypes.c_float(0)
+        n = self.lib.sparknet_peer_timing(self.net.state, ctypes.byref(w), ctypes.byref(x))
+        return n, float(w.value), float(x.value)
+
     def check(self) -> None:
         assert self.world == 1 or self.lib.sparknet_peer_status(self.net.state) == 0, \
             "a replica did not arrive at an averaging round within the time-out"

@@ -262,6 +262,58 @@ def test_averaging_kernel_is_bit_exact_rank_ordered(oracle, product, nrep):
     assert got.tobytes() == want.tobytes()                           # memcmp, incl. -0.0 and denormals
 
 
+@pytest.mark.parametrize("name,batch,precision", [("lenet", 16, 0), ("cifar10_quick", 10, 1), ("cifar10_full", 10, 1),
+                                                  ("caffenet", 2, 1)])
+def test_graph_replay_is_bit_identical_to_eager_iterations(product, name, batch, precision):
+    """solver_step replays a recorded CUDA graph for the steady-state iterations (no per-iteration host
+    work beyond the data callbacks).  Same kernels, same order, same arguments: weights, momentum history and the loss
+    of every iteration must be bit-identical to eager launches — across several solver_step calls, with host writes to
+    the weights in between (setWeights through get_data pointers), an lr policy that changes every iteration (LeNet
+    'inv') and dropout counters (CaffeNet)."""
+    sol = zoo.solver_with_net(name, train_bs=batch, test_bs=batch, random_seed=1701, display=0)
+    imgs, labs = synthetic_batches(name, 4, batch)
+    runs = []
+    for mode in (0, 1):
+        p = CaffeNet.from_solver(sol, product)
+        product.sparknet_set_precision(p.state, precision)
+        assert product.sparknet_set_graph_mode(p.state, mode) == -1
+        p.setTrainData(MinibatchSource(imgs, labs))
+        if mode == 0:
+            w0 = p.getWeights()
+        p.setWeights(w0)
+        p.train(5)
+        w = p.getWeights()                                   # host reads ...
+        for ln in w.layerNames:
+            for a in w.allWeights[ln]:
+                a *= F(0.999)
+        p.setWeights(w)                                      # ... and writes between two calls
+        p.train(6)
+        p.train(1)
+        p.train(4)
+        n = int(product.sparknet_num_params(p.state))
+        flat = np.empty(n, dtype=F)
+        assert product.sparknet_get_weights_flat(p.state, fptr(flat), n) == 0
+        losses = np.empty(16, dtype=F)
+        assert product.sparknet_get_loss_history(p.state, fptr(losses), 16) == 16
+        hist, k, w = [], 0, p.getWeights()
+        for ln in w.layerNames:
+            for a in w.allWeights[ln]:
+                h = np.empty(a.size, dtype=F)
+                assert product.sparknet_get_history(p.state, k, fptr(h), a.size) == 0
+                hist.append(h)
+                k += 1
+        replays = int(product.sparknet_graph_replays(p.state))
+        runs.append((flat, losses, hist, replays))
+        p.close()
+    (w_e, l_e, h_e, r_e), (w_g, l_g, h_g, r_g) = runs
+    assert r_e == 0
+    assert r_g == (5 - 3) + (6 - 1) + 0 + (4 - 1)           # first call: two eager iterations before the first recording
+    assert np.isfinite(l_g).all()
+    assert l_g.tobytes() == l_e.tobytes()
+    assert w_g.tobytes() == w_e.tobytes()
+    assert len(h_e) == len(h_g) and all(a.tobytes() == b.tobytes() for a, b in zip(h_e, h_g))
+
+
 @pytest.mark.parametrize("nrep", [1, 2, 3, 5, 8])
 def test_peer_memory_exchange_kernel_is_bit_exact_rank_ordered(oracle, product, nrep):
     """The one-kernel exchange of the multi-GPU driver (kernels.cu average_peers_kernel: rank-ordered fold of the own
