@@ -713,6 +713,39 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits
     epi((int)(i / N), (int)(i % N), acc);
   }
 }
+// Many slices over a small output (first-layer backward-filter: 200 slices x 2400 elements): one thread per element
+// would walk `splits` dependent loads.  Here 8 lanes share an element: lane j sums slices j, j+8, ... in ascending
+// order, then the eight partial sums are combined in a fixed butterfly — still the same order on every run.
+template <class E>
+__global__ void tc_splitk_reduce_wide_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  const size_t total = (size_t)M * N;
+  const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const size_t i = t >> 3;
+  const int j = (int)(t & 7);
+  float acc = 0.f;
+  if (i < total) {
+    float a0 = 0.f, a1 = 0.f;
+    int z = j;
+    for (; z + 8 < splits; z += 16) { a0 += ws[(size_t)z * total + i]; a1 += ws[(size_t)(z + 8) * total + i]; }
+    if (z < splits) a0 += ws[(size_t)z * total + i];
+    acc = a0 + a1;
+  }
+  acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+  if (i < total && j == 0) epi((int)(i / N), (int)(i % N), acc);
+}
+template <class E>
+static void launch_splitk_reduce(cudaStream_t s, const float* ws, int splits, int M, int N, E epi) {
+  const size_t total = (size_t)M * N;
+  if (splits >= 16 && total * 8 <= (size_t)148 * 8 * 256) {
+    tc_splitk_reduce_wide_kernel<<<(int)((total * 8 + 255) / 256), 256, 0, s>>>(ws, splits, M, N, epi);
+    return;
+  }
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  tc_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ws, splits, M, N, epi);
+}
 
 // ------------------------------------------------------------------------------------------
 // host side
@@ -805,10 +838,7 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, true>;
     if (smem > attr_done_split) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done_split = smem; }
     kfn<<<grid, kTcThreads, smem, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
-    const size_t total = (size_t)M * N;
-    int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 8) blocks = 148 * 8;
-    tc_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(ws, (int)grid.z, M, N, reduce_epi);
+    launch_splitk_reduce(s, ws, (int)grid.z, M, N, reduce_epi);
     count_launch(2);
   }
   SN_CUDA(cudaGetLastError());
@@ -1307,10 +1337,7 @@ static int launch_static_bn(cudaStream_t s, AL al, BL bl, int M, int N, int R, i
     e = cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::kSmemBytes);
     if (e != cudaSuccess) return -20;
     kfn<<<grid, kTcThreads, Cfg::kSmemBytes, s>>>(dummy_tmap(), dummy_tmap(), al, bl, ep, M, N, R, len, n_mma, scratch);
-    const size_t total = (size_t)M * N;
-    int blocks = (int)((total + 255) / 256);
-    if (blocks > 148 * 8) blocks = 148 * 8;
-    tc_splitk_reduce_kernel<<<blocks, 256, 0, s>>>(scratch, (int)grid.z, M, N, re);
+    launch_splitk_reduce(s, scratch, (int)grid.z, M, N, re);
   }
   e = cudaGetLastError();
   if (e != cudaSuccess) {
