@@ -171,7 +171,8 @@ long sparknet_graph_replays(caffenet_state* state);
  * IEEE fp32, rank order — bit-exact against the reference's sequential sum.
  *   sparknet_peer_handle_bytes   size of one handle (a cudaIpcMemHandle_t, 64 bytes)
  *   sparknet_peer_export         writes this replica's two handles (weight arena, flag block)
- *   sparknet_peer_attach         takes all replicas' handles (nranks x handle_bytes each, rank order)
+ *   sparknet_peer_attach         takes all replicas' handles (nranks x handle_bytes each, rank order); -3 when a
+ *                                peer's memory cannot be mapped (no peer access / no IPC): the caller picks another path
  *   sparknet_average_peers       one round, enqueued on the compute stream; all replicas must call it
  *   sparknet_peer_status         synchronises; 0 = all rounds completed, 1 = a peer did not arrive in time
  *   sparknet_peer_timing         device-side clock of the rounds since its last call: mean ms waiting for the slowest

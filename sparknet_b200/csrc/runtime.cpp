@@ -1202,7 +1202,11 @@ void Solver::step(int iters) {
   const int stop_iter = iter + iters;
   const int L = (int)net->layers.size();
   // every learnable blob's device copy must be current before the fused update touches the arena
-  for (Blob* b : net->learnable_params) { b->data->mutable_gpu(); b->diff->mutable_gpu(); }
+  // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
+  for (Blob* b : net->learnable_params) {
+    if (b->data->head != Storage::AT_DEVICE) b->data->mutable_gpu();
+    b->diff->mutable_gpu();
+  }
   net->overwrite_param_diffs = true;     // Net::ClearParamDiffs (net.cpp:990-1008) folded into the wgrad epilogues
   // In-call prefetch of the data callbacks (see JavaDataLayer): worth a thread when several iterations follow
   std::vector<JavaDataLayer*> feeds;
@@ -1322,7 +1326,11 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
   std::vector<cudaEvent_t> ev((size_t)(2 * L + 3));
   for (auto& e : ev) SN_CUDA(cudaEventCreate(&e));
   cudaStream_t s = ctx().compute;
-  for (Blob* b : net->learnable_params) { b->data->mutable_gpu(); b->diff->mutable_gpu(); }
+  // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
+  for (Blob* b : net->learnable_params) {
+    if (b->data->head != Storage::AT_DEVICE) b->data->mutable_gpu();
+    b->diff->mutable_gpu();
+  }
   net->overwrite_param_diffs = true;
   net->loss_log = loss_hist + (iter % kLossHist);
   for (int i = 0; i < L; ++i) {

@@ -104,8 +104,11 @@ class PeerAverager:
         flags_h = np.ascontiguousarray(allh[:, hb:])
         rc = lib.sparknet_peer_attach(net.state, rank, world, ctypes.c_void_p(arena_h.ctypes.data),
                                       ctypes.c_void_p(flags_h.ctypes.data))
-        assert rc == 0, rc
-        dist.barrier()
+        ok = torch.tensor([1 if rc == 0 else 0], device="cuda")
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)              # every replica must have mapped every other one
+        self.attached = int(ok) == 1
+        if not self.attached:
+            return
         ptr, cnt = ctypes.c_void_p(), ctypes.c_long()
         assert lib.sparknet_param_arena(net.state, ctypes.byref(ptr), ctypes.byref(cnt)) == 0
         self.n = int(cnt.value)
@@ -153,7 +156,19 @@ class PeerAverager:
 def make_averager(lib, net, rank: int, world: int):
     """The multi-GPU driver's choice: peer-memory kernel unless SPARKNET_AVG=nccl."""
     import os
-    return (Averager if os.environ.get("SPARKNET_AVG", "peer") == "nccl" else PeerAverager)(lib, net, rank, world)
+    import sys
+    if os.environ.get("SPARKNET_AVG", "peer") == "nccl":
+        return Averager(lib, net, rank, world)
+    avg = PeerAverager(lib, net, rank, world)
+    if world > 1 and not avg.attached:
+        # GPUs without peer access to each other (or no CUDA IPC in this container): the exchange kernel cannot
+        # run; the NCCL all-gather + fold kernel computes the same bits.  Said loudly, and recorded in `method`.
+        if rank == 0:
+            print("sparknet: peer-memory mapping failed on at least one replica; averaging through NCCL all-gather + "
+                  "fold kernel instead", file=sys.stderr, flush=True)
+        avg = Averager(lib, net, rank, world)
+        avg.method += " (peer-memory mapping unavailable on this box)"
+    return avg
 
 
 def sequential_average(weight_lists):
