@@ -92,8 +92,15 @@ void Storage::ensure_dev() {
 void Storage::ensure_host() {
   if (!host) SN_CUDA(cudaMallocHost(&host, std::max<size_t>(count, 1) * sizeof(float)));
 }
+// Anything that reads or writes a Storage OUTSIDE Solver::step (get_data, forward(), averaging, weight IO ...)
+// advances this counter; a solver_step call that finds it unchanged since the previous call returned knows that
+// host-side state and device contents are exactly as that call left them (Solver::step replays from iteration one).
+static uint64_t g_outside_touch = 0;
+static bool g_in_step = false;
+static inline void note_touch() { if (!g_in_step) ++g_outside_touch; }
 const float* Storage::gpu() {
   Context& c = ctx();
+  if (head == UNINIT || head == AT_HOST) note_touch();
   switch (head) {
     case UNINIT:
       ensure_dev();
@@ -110,6 +117,7 @@ const float* Storage::gpu() {
   return dev;
 }
 float* Storage::mutable_gpu() {
+  note_touch();
   gpu();
   head = AT_DEVICE;
   ++gen;
@@ -117,6 +125,7 @@ float* Storage::mutable_gpu() {
 }
 float* Storage::mutable_cpu() {
   Context& c = ctx();
+  note_touch();
   ensure_host();
   switch (head) {
     case UNINIT:
@@ -310,7 +319,10 @@ struct JavaDataLayer : Layer {
       pf->cv.wait(lk, [&] { return pf_filled > pf_enqueued; });
     } else {
       SN_CUDA(cudaEventSynchronize(h2d_done[p]));   // pinned[p] free again (no-op the first time)
+      const bool in_step = g_in_step;
+      g_in_step = false;                            // a callback that reaches back into the ABI (get_data ...) counts as outside
       cb((void*)pinned[p], shape[0], (int)shape.size() - 1, java_shape.data());
+      g_in_step = in_step;
     }
     if (consumed_valid[p]) SN_CUDA(cudaStreamWaitEvent(c.copy, consumed[p], 0));
     SN_CUDA(cudaMemcpyAsync(devbuf[p], pinned[p], count * sizeof(float), cudaMemcpyHostToDevice, c.copy));
@@ -1201,6 +1213,10 @@ float Solver::get_learning_rate() {   // sgd_solver.cpp:27-63, same expression t
 void Solver::step(int iters) {
   const int stop_iter = iter + iters;
   const int L = (int)net->layers.size();
+  // nothing touched any blob since the previous call returned: iteration one may replay too
+  uint64_t touch_seen = step_calls > 0 ? touch_at_exit : ~0ull;
+  ++step_calls;
+  g_in_step = true;
   // every learnable blob's device copy must be current before the fused update touches the arena
   // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
   for (Blob* b : net->learnable_params) {
@@ -1234,10 +1250,9 @@ void Solver::step(int iters) {
   for (auto& l : net->layers)
     if (DropoutLayer* d = dynamic_cast<DropoutLayer*>(l.get())) drops.push_back(d);
   bool use_graph = graph_mode >= 0 ? graph_mode == 1 : !(getenv("SPARKNET_GRAPH") && atoi(getenv("SPARKNET_GRAPH")) == 0);
-  if (param.display || (int)feeds.size() != D || (int)drops.size() > StepScalars::kMaxDropout || !net->arena_floats) use_graph = false;
+  if (param.display || prefetch || (int)feeds.size() != D || (int)drops.size() > StepScalars::kMaxDropout || !net->arena_floats) use_graph = false;
   if (graphs_epoch != g_config_epoch) { drop_graphs(); graphs_epoch = g_config_epoch; }
   for (size_t i = 0; i < drops.size(); ++i) drops[i]->offset_slot = &scalars_dev->dropout_offset[i];
-  const int first_iter = iter;
   cudaStream_t cs = ctx().compute;
   while (iter < stop_iter) {
     for (int i = 0; i < D; ++i) net->layers[(size_t)i]->forward(net->bottom_vecs[(size_t)i], net->top_vecs[(size_t)i]);
@@ -1253,7 +1268,11 @@ void Solver::step(int iters) {
     }
     const float rate = sc.rate;
     GraphEntry* entry = nullptr;
-    bool replay = use_graph && iter != first_iter && eager_iters >= 2;
+    // eager whenever something outside this loop touched a blob since the last iteration (always true for the first
+    // iteration after get_data / setWeights / forward() / averaging ...; a data callback that calls back into the ABI)
+    const bool dirty = g_outside_touch != touch_seen;
+    touch_seen = g_outside_touch;
+    bool replay = use_graph && !dirty && eager_iters >= 2;
     if (replay) {
       std::vector<const void*> key;
       for (int i = 0; i < D; ++i) key.push_back(net->top_vecs[(size_t)i][0]->data->dev);
@@ -1318,6 +1337,8 @@ void Solver::step(int iters) {
   }
   net->overwrite_param_diffs = false;
   net->loss_log = nullptr;
+  g_in_step = false;
+  touch_at_exit = g_outside_touch;
 }
 // One training iteration with CUDA events around every layer's forward and backward and around the
 // update (the per-layer timing of `caffe time`, caffe/tools/caffe.cpp:290-375, on the device).
