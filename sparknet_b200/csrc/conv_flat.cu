@@ -70,6 +70,8 @@ struct WinArgs {
 struct WinEpi {
   float* dst; const float* bias; int Hv, Wv, Ctot, Cgrp, relu; FastDiv dGp, dWp;
   int ld; size_t split_stride;
+  const float* gate;        // backward-data only: same shape as dst; dst = (gate > 0) ? value : 0  (the backward of an in-place
+                            // ReLU below this layer, relu_layer.cu:35-41, applied while the gradient is written)
 };
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2 along x) runs every MMA with M = 256: each CTA keeps its
@@ -188,7 +190,14 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
           p = ep.dst + ((((size_t)img * ep.Ctot + chan0 + n0 + c0) * ep.Hv + h) * ep.Wv + w);
         }
         tmem_ld_wait();
-        if (ok) {
+        if (ok && ep.gate) {
+          const float* gp = ep.gate + (p - ep.dst);
+          float gv[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) gv[j] = __ldg(gp + (size_t)j * plane);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) p[(size_t)j * plane] = __uint_as_float(v[j]) * (gv[j] > 0.f ? 1.f : 0.f);   // relu_g() of kernels.cu
+        } else if (ok) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             float acc = __uint_as_float(v[j]) + bias[j];
@@ -614,11 +623,11 @@ void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const f
   const CUtensorMap tmB = tc_make_tmap(wf, (uint64_t)kp, (uint64_t)g.Cout, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - (g.ph * f.Wp + g.pw), pl.MT, pl.n_mma, slots / 32, Cg, slots, Cg, Og,
             pl.box_rows, pl.nbox, pl.nstage, nullptr, 2, 1, slots / 32, 0};
-  WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0};
+  WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0, nullptr};
   launch_window(s, tmA, tmB, a, ep, pl, Og, g.group);
 }
 // `dyflat`: packed top gradient (tc_flat_pack, output side); `wt`: tc_flat_pack_filter(dgrad = true)
-void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx) {
+void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx, const float* relu_gate) {
   const FlatGeom f = tc_flat_geom(g);
   const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Ptot = g.N * f.Gp, slots = slots_of(Og), kp = T * slots;
   const int span = (g.kh - 1) * f.Wp + g.kw - 1;
@@ -628,7 +637,7 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
   const CUtensorMap tmB = tc_make_tmap(wt, (uint64_t)kp, (uint64_t)g.C, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - ((g.kh - 1 - g.ph) * f.Wp + (g.kw - 1 - g.pw)), pl.MT, pl.n_mma, slots / 32, Og, slots,
             Og, Cg, pl.box_rows, pl.nbox, pl.nstage, nullptr, 2, 1, slots / 32, 0};
-  WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0};
+  WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0, relu_gate};
   launch_window(s, tmA, tmB, a, ep, pl, Cg, g.group);
 }
 
@@ -685,7 +694,7 @@ void tcw_matmul(cudaStream_t s, int M, int N, int K, const float* A, const float
   float* dst = out;
   size_t stride = 0;
   if (splits > 1) { stride = (size_t)M * N; dst = get_workspace(stride * splits); }
-  WinEpi ep{dst, bias, 1, 1, N, N, relu ? 1 : 0, FastDiv(1), FastDiv(1), N, stride};
+  WinEpi ep{dst, bias, 1, 1, N, N, relu ? 1 : 0, FastDiv(1), FastDiv(1), N, stride, nullptr};
   launch_window(s, tmA, tmB, a, ep, pl, N, 1);
   if (splits > 1) {
     const size_t total = (size_t)M * N;

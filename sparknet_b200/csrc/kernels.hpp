@@ -52,7 +52,7 @@ void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, 
 void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
 // window kernels (conv_flat.cu): same packed operands, one TMA load of the grid rows per channel block serves every tap
 void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
-void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
+void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx, const float* relu_gate = nullptr);
 bool tcw_supported(const ConvGeom& g);
 bool tcw_wgrad_supported(const ConvGeom& g);
 void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);

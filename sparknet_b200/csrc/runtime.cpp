@@ -360,6 +360,7 @@ struct JavaDataLayer : Layer {
 struct ConvolutionLayer : Layer {
   ConvGeom g;
   bool bias_term = true, fuse_relu = false;
+  bool gate_relu = false;     // the bottom is the output of an in-place ReLU whose backward is applied while this layer writes dx
   using Layer::Layer;
   const char* type() const override { return "Convolution"; }
   void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
@@ -496,7 +497,11 @@ struct ConvolutionLayer : Layer {
       if (!dws) SN_CUDA(cudaMalloc(&dws, (size_t)gs.Cout * gs.C * gs.kh * gs.kw * sizeof(float)));
       tcw_conv_wgrad(S(), gs, packed_input(bottom[0]), dyflat, dws, false);
       tcw_s2d_unpack_wgrad(S(), g, dws, blobs[0]->diff->mutable_gpu(), acc);
-      if (pd[0]) tc_conv_dgrad(S(), g, dy, blobs[0]->data->gpu(), bottom[0]->diff->mutable_gpu());
+      if (pd[0]) {
+        float* dx = bottom[0]->diff->mutable_gpu();
+        tc_conv_dgrad(S(), g, dy, blobs[0]->data->gpu(), dx);
+        if (gate_relu) relu_bwd(S(), bottom[0]->count(), dx, bottom[0]->data->gpu(), dx, 0.f);
+      }
       return;
     }
     if (flat_w || flat_d) {
@@ -517,10 +522,12 @@ struct ConvolutionLayer : Layer {
     if (pd[0]) {
       const float* w = blobs[0]->data->gpu();
       float* dx = bottom[0]->diff->mutable_gpu();
-      if (flat_d && use_window()) tcw_conv_dgrad(S(), g, dyflat, packed_filter(true), dx);
+      const float* gate = gate_relu ? bottom[0]->data->gpu() : nullptr;       // y of the in-place ReLU below (y > 0 <=> x > 0)
+      if (flat_d && use_window()) { tcw_conv_dgrad(S(), g, dyflat, packed_filter(true), dx, gate); gate = nullptr; }
       else if (flat_d) tc_conv_dgrad_flat(S(), g, dyflat, packed_filter(true), dx);
       else if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
       else ffma_conv_dgrad(S(), g, dy, w, dx);
+      if (gate) relu_bwd(S(), bottom[0]->count(), dx, gate, dx, 0.f);          // paths without a gating epilogue
     }
   }
 };
@@ -1056,6 +1063,15 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
         for (Blob* t : top_vecs[(size_t)lj]) if (t == blob) rewritten = true;      // another in-place layer on the same blob
       }
       if (consumers != 1 || rewritten) continue;
+      if (ConvolutionLayer* cl = dynamic_cast<ConvolutionLayer*>(layers[(size_t)consumer].get())) {
+        // ... or a convolution: its backward-data epilogue gates the gradient (conv_flat.cu WinEpi::gate).  SPARKNET_FUSE_RELU_CONV=0 turns it off.
+        const char* ec = getenv("SPARKNET_FUSE_RELU_CONV");
+        if (ec && atoi(ec) == 0) continue;
+        if (bottom_vecs[(size_t)consumer].size() != 1) continue;
+        cl->gate_relu = true;
+        r->bwd_fused_by_consumer = true;
+        continue;
+      }
       PoolingLayer* pl = dynamic_cast<PoolingLayer*>(layers[(size_t)consumer].get());
       if (!pl || pl->method != 0) continue;
       pl->gate_relu = true;

@@ -155,6 +155,41 @@ def test_relu_backward_folded_into_max_pool_backward(oracle, product, monkeypatc
         assert_mostly_close(b, a, 1e-4, f"param diff {j}")
 
 
+@pytest.mark.parametrize("precision", [0, 1])
+@pytest.mark.parametrize("shape,group", [((3, 32, 13, 13), 1), ((2, 32, 13, 13), 2), ((2, 16, 9, 11), 1)])
+def test_relu_backward_folded_into_convolution_backward_data(oracle, product, monkeypatch, shape, group, precision):
+    """conv -> in-place ReLU -> conv, the CaffeNet conv3/relu3/conv4 pattern.  With SPARKNET_FUSE_RELU_CONV=1 (default) the
+    second convolution's backward-data epilogue applies dx = dy * (y > 0) (relu_layer.cu:35-41) while it writes the
+    gradient and the ReLU layer's own backward is skipped: BIT-identical to the unfused product in both precision modes
+    (window kernels in TF32, gather / FFMA kernels with a separate gating pass otherwise), and within tolerance of the oracle."""
+    x = np.random.default_rng(19).standard_normal(shape).astype(F)
+    layers = [conv_layer("conva", "data", 64, kernel_size=[3], pad=[1], weight_filler=gaussian(0.1), bias_filler=gaussian(0.1)),
+              ReLULayer("relu", ["conva"]),
+              conv_layer("convb", "conva", 32, kernel_size=[3], pad=[1], group=group, weight_filler=gaussian(0.1), bias_filler=gaussian(0.1))]
+    monkeypatch.setenv("SPARKNET_FUSE_RELU_CONV", "1")
+    r = run_pair(oracle, product, {"data": x}, layers, "convb", ["conva", "convb"], precision=precision)
+    monkeypatch.setenv("SPARKNET_FUSE_RELU_CONV", "0")
+    o, fused = r["nets"]
+    u = LayerNet(product, {"data": x}, layers)
+    product.sparknet_set_precision(u.state, precision)
+    for wl in ("conva", "convb"):
+        u.set_weights(wl, o.weights(wl))
+    u.forward()
+    u.zero_param_diffs()
+    u.set_diff("convb", np.random.default_rng(3).standard_normal(r["fwd"][0]["convb"].shape).astype(F))
+    ub = u.backward()
+    for k in ("conva", "data"):
+        assert np.array_equal(r["bwd"][1][k], ub[k]), k
+    for wl in ("conva", "convb"):
+        for a, b in zip(r["wdiff"][wl][1], u.weights(wl, True)):
+            assert np.array_equal(a, b), wl
+    tol = 1e-4 if precision == 0 else 3 * TOL
+    assert_mostly_close(r["bwd"][1]["conva"], r["bwd"][0]["conva"], tol, "diff behind the ReLU")
+    assert_mostly_close(r["bwd"][1]["data"], r["bwd"][0]["data"], tol, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["conva"])):
+        assert_mostly_close(b, a, tol, f"param diff {j}")
+
+
 def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
     """The TMA-fed operands read a tf32-rounded copy of the weights; it must track setWeights and SGD."""
     sol = zoo.solver_with_net("lenet", train_bs=16, test_bs=16, random_seed=1701, display=0)
