@@ -183,11 +183,13 @@ def test_relu_backward_folded_into_convolution_backward_data(oracle, product, mo
     for wl in ("conva", "convb"):
         for a, b in zip(r["wdiff"][wl][1], u.weights(wl, True)):
             assert np.array_equal(a, b), wl
-    tol = 1e-4 if precision == 0 else 3 * TOL
-    assert_mostly_close(r["bwd"][1]["conva"], r["bwd"][0]["conva"], tol, "diff behind the ReLU")
-    assert_mostly_close(r["bwd"][1]["data"], r["bwd"][0]["data"], tol, "bottom diff")
+    # against the oracle: in TF32 a pre-activation within rounding noise of zero may open a different gate than the
+    # oracle's fp32 forward did, which changes a neighbourhood of the gradient: a bounded fraction may disagree there
+    tol, bad = (1e-4, 5e-4) if precision == 0 else (3 * TOL, 0.05)
+    assert_mostly_close(r["bwd"][1]["conva"], r["bwd"][0]["conva"], tol, "diff behind the ReLU", max_bad_frac=bad)
+    assert_mostly_close(r["bwd"][1]["data"], r["bwd"][0]["data"], tol, "bottom diff", max_bad_frac=bad)
     for j, (a, b) in enumerate(zip(*r["wdiff"]["conva"])):
-        assert_mostly_close(b, a, tol, f"param diff {j}")
+        assert_mostly_close(b, a, tol, f"param diff {j}", max_bad_frac=bad)
 
 
 def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
