@@ -1069,6 +1069,62 @@ void tcw_s2d_pack_filter(cudaStream_t st, const ConvGeom& g, const float* w, flo
   count_launch();
   SN_CUDA(cudaGetLastError());
 }
+// All stale filter copies of a net in ONE launch (Solver::step, start of an iteration): the weights of every layer
+// change with every SGD update, and eight 5-microsecond pack kernels per CaffeNet iteration are pure launch latency.
+// mode 0 / 1: tc_flat_pack_filter(dgrad = mode) layout; mode 2: the folded filter of s2d_pack_filter_kernel.
+__global__ void filter_pack_batch_kernel(const FilterPackBatch b) {
+  const FilterPackJob& j = b.job[blockIdx.y];
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < j.total; i += (size_t)gridDim.x * blockDim.x) {
+    float v = 0.f;
+    if (j.mode == 2) {
+      const int Cout = j.p[0], C = j.p[1], kh = j.p[2], kw = j.p[3], s = j.p[4], khs = j.p[5], kws = j.p[6], slots = j.p[7];
+      (void)Cout;
+      const int slot = (int)(i % slots);
+      const size_t r = i / slots;
+      const int tap = (int)(r % (khs * kws)), co = (int)(r / (khs * kws));
+      if (slot < C * s * s) {
+        const int dx = slot % s, dy = (slot / s) % s, c = slot / (s * s), ky = s * (tap / kws) + dy, kx = s * (tap % kws) + dx;
+        if (ky < kh && kx < kw) v = j.w[(((size_t)co * C + c) * kh + ky) * kw + kx];
+      }
+    } else {
+      const int Cg = j.p[0], Og = j.p[1], T = j.p[2], dgrad = j.mode;
+      const int red = dgrad ? Og : Cg;
+      const int slots = (red + 31) / 32 * 32, kp = T * slots;
+      const int row = (int)(i / kp), k = (int)(i - (size_t)row * kp), tap = k / slots, ch = k - tap * slots;
+      if (ch < red) {
+        if (!dgrad) v = j.w[((size_t)row * Cg + ch) * T + tap];
+        else { const int grp = row / Cg, c = row - grp * Cg; v = j.w[((size_t)(grp * Og + ch) * Cg + c) * T + (T - 1 - tap)]; }
+      }
+    }
+    j.dst[i] = to_tf32_exact(v);
+  }
+}
+FilterPackJob tcw_filter_pack_job(const ConvGeom& g, int mode, const float* w, float* dst) {
+  FilterPackJob j{};
+  j.w = w; j.dst = dst; j.mode = mode;
+  if (mode == 2) {
+    const ConvGeom e = tcw_s2d_geom(g);
+    const int slots = slots_of(e.C);
+    j.total = (size_t)g.Cout * e.kh * e.kw * slots;
+    const int p[8] = {g.Cout, g.C, g.kh, g.kw, g.sh, e.kh, e.kw, slots};
+    for (int i = 0; i < 8; ++i) j.p[i] = p[i];
+  } else {
+    j.total = tc_flat_filter_floats(g, mode == 1);
+    j.p[0] = g.Cg(); j.p[1] = g.Og(); j.p[2] = g.kh * g.kw;
+  }
+  return j;
+}
+void tcw_filter_pack_batch(cudaStream_t st, const FilterPackBatch& b) {
+  if (b.n <= 0) return;
+  size_t most = 0;
+  for (int i = 0; i < b.n; ++i) most = std::max(most, b.job[i].total);
+  int blocks = (int)((most + 255) / 256);
+  const int cap = std::max(148 * 4 / b.n, 32);
+  if (blocks > cap) blocks = cap;
+  filter_pack_batch_kernel<<<dim3(blocks, b.n), 256, 0, st>>>(b);
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
 // dw[co][c][ky][kx] (+)= dws[co][(c,dy,dx)][tap']  (the folded filter gradient, layout of tcw_conv_wgrad's output)
 __global__ void s2d_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int kh, int kw, int s, int khs,
                                         int kws, int accumulate) {

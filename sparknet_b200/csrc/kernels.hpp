@@ -61,6 +61,12 @@ bool tcw_s2d_supported(const ConvGeom& g);
 ConvGeom tcw_s2d_geom(const ConvGeom& g);
 void tcw_s2d_pack_input(cudaStream_t s, const ConvGeom& g, const float* x, float* xflat);
 void tcw_s2d_pack_filter(cudaStream_t s, const ConvGeom& g, const float* w, float* wf);
+// Several filter copies in one launch (conv_flat.cu filter_pack_batch_kernel): mode 0 / 1 = tc_flat_pack_filter(dgrad = mode),
+// mode 2 = tcw_s2d_pack_filter.
+struct FilterPackJob { const float* w; float* dst; size_t total; int mode; int p[8]; };
+struct FilterPackBatch { static constexpr int kMax = 16; FilterPackJob job[kMax]; int n; };
+FilterPackJob tcw_filter_pack_job(const ConvGeom& g, int mode, const float* w, float* dst);
+void tcw_filter_pack_batch(cudaStream_t s, const FilterPackBatch& b);
 void tcw_s2d_unpack_wgrad(cudaStream_t s, const ConvGeom& g, const float* dws, float* dw, bool accumulate);
 // out[m][n] = sum_k A[m][k] * B(n,k) (+ bias[n], ReLU) on the window kernel; A [M][K] tf32-rounded, B [N][K] or (b_mn) [K][N]
 bool tcw_matmul_supported(int M, int N, int K, const float* A, const float* B, bool b_mn, const float* out);

@@ -481,6 +481,22 @@ struct ConvolutionLayer : Layer {
     }
     return wflat[i];
   }
+  // Solver::step, start of an iteration: the stale filter copies this layer is about to need go into the net-wide batch
+  // (one launch for all layers); packed_filter() then finds them current.  Anything missed here is packed lazily as before.
+  void queue_filter_packs(FilterPackBatch& b, bool propagate_down) {
+    if (net->precision != PREC_TF32) return;
+    Storage* st = blobs[0]->data.get();
+    auto add = [&](bool dgrad, int mode) {
+      const int i = dgrad ? 1 : 0;
+      if (b.n >= FilterPackBatch::kMax || (wflat[i] && wflat_gen[i] == st->gen)) return;
+      if (!wflat[i]) SN_CUDA(cudaMalloc(&wflat[i], tc_flat_filter_floats(fg(), dgrad) * sizeof(float)));
+      b.job[b.n++] = tcw_filter_pack_job(g, mode, st->gpu(), wflat[i]);
+      wflat_gen[i] = st->gen;
+    };
+    if (use_s2d()) { add(false, 2); return; }
+    if (use_flat(1)) add(false, 0);
+    if (use_flat(4) && propagate_down) add(true, 1);
+  }
   ~ConvolutionLayer() override {
     cudaFree(xflat); cudaFree(dyflat); cudaFree(wflat[0]); cudaFree(wflat[1]); cudaFree(dws);
   }
@@ -1119,6 +1135,13 @@ void Net::mark_shadows_current() {
   for (auto& l : layers)
     if (l->w_shadow_in_arena && !l->blobs.empty()) l->w_shadow_gen = l->blobs[0]->data->gen;
 }
+void Net::prepack_filters() {
+  FilterPackBatch b{};
+  for (size_t i = 0; i < layers.size(); ++i)
+    if (ConvolutionLayer* c = dynamic_cast<ConvolutionLayer*>(layers[i].get()))
+      c->queue_filter_packs(b, layer_need_backward[i] && bottom_need_backward[i][0]);
+  tcw_filter_pack_batch(ctx().compute, b);
+}
 void Net::forward_from_to(int start, int end) {
   for (int i = start; i <= end; ++i) layers[(size_t)i]->forward(bottom_vecs[(size_t)i], top_vecs[(size_t)i]);
 }
@@ -1300,6 +1323,7 @@ void Solver::step(int iters) {
         cudaGraph_t graph = nullptr;
         SN_CUDA(cudaStreamBeginCapture(cs, cudaStreamCaptureModeRelaxed));
         net->loss_log = loss_hist + kLossHist;
+        net->prepack_filters();
         net->forward_from_to(D, L - 1);
         net->backward_from_to(L - 1, 0);
         sgd_update(cs, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum, &scalars_dev->rate);
@@ -1331,6 +1355,7 @@ void Solver::step(int iters) {
       SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + kLossHist, sizeof(float), cudaMemcpyDeviceToHost, cs));
     } else {
       net->loss_log = loss_hist + (iter % kLossHist);
+      net->prepack_filters();
       net->forward_from_to(D, L - 1);
       net->backward_from_to(L - 1, 0);
       if (param.display && iter % param.display == 0) {

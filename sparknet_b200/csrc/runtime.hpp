@@ -145,6 +145,7 @@ struct Net {
   Net(const cp::NetParameter& param, int phase, uint64_t seed);
   ~Net();
   void mark_shadows_current();
+  void prepack_filters();               // all stale tf32 filter copies of the convolution layers in one launch (Solver::step)
   void forward_from_to(int start, int end);
   void backward_from_to(int start, int end);
   void share_trained_layers_with(const Net& other);
