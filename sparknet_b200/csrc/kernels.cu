@@ -420,6 +420,63 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_kernel(PoolGeom g, uin
     }
   }
 }
+// Strip form of the same 3x3 / stride 2 backward: one thread owns the two input columns (2b, 2b+1) of a plane and walks
+// down the rows two at a time, keeping the pooled row above (a-1) in registers.  Per 2x2 block that is two new (mask, dy,
+// gate) triples instead of four and no integer division (one per thread, not one per block): the block form above is
+// bound by instruction issue, not by memory.  Same windows, same (ph, pw) order of the additions: identical results.
+__global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_strip_kernel(PoolGeom g, uint32_t total, FastDiv dB, int A, const float* __restrict__ dy,
+                                                                       const int* __restrict__ mask, const float* __restrict__ gate,
+                                                                       float* __restrict__ dx) {
+  const int P = g.PH * g.PW, HW = g.H * g.W;
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    uint32_t plane, b;
+    dB.divmod(idx, plane, b);
+    const int w0 = 2 * (int)b;
+    const int* mp = mask + (size_t)plane * P;
+    const float* gp = dy + (size_t)plane * P;
+    const float* tp = gate ? gate + (size_t)plane * P : nullptr;
+    const bool okl = (int)b - 1 >= 0, okr = (int)b < g.PW;      // window columns b-1 and b exist
+    const bool has_w1 = w0 + 1 < g.W;
+    float* dp = dx + (size_t)plane * HW + w0;
+    int m0l = -2, m0r = -2;                                      // pooled row a-1 (none above the first)
+    float v0l = 0.f, v0r = 0.f;
+    // pooled row a, loaded one step ahead
+    auto load_row = [&](int a, int& ml, int& mr, float& vl, float& vr) {
+      ml = mr = -2; vl = vr = 0.f;
+      if (a < g.PH) {
+        const int o = a * g.PW + (int)b;
+        if (okl) { ml = __ldg(mp + o - 1); vl = __ldg(gp + o - 1); if (tp && !(__ldg(tp + o - 1) > 0.f)) vl = 0.f; }
+        if (okr) { mr = __ldg(mp + o); vr = __ldg(gp + o); if (tp && !(__ldg(tp + o) > 0.f)) vr = 0.f; }
+      }
+    };
+    int m1l, m1r; float v1l, v1r;
+    load_row(0, m1l, m1r, v1l, v1r);
+    for (int a = 0; a < A; ++a) {
+      int m2l, m2r; float v2l, v2r;
+      load_row(a + 1, m2l, m2r, v2l, v2r);                       // next step's loads are in flight during this step's stores
+      const int h0 = 2 * a, me00 = h0 * g.W + w0;
+      float acc;
+      acc = (m0l == me00 ? v0l : 0.f);                            // (2a, 2b): windows (a-1,b-1), (a-1,b), (a,b-1), (a,b)
+      acc += (m0r == me00 ? v0r : 0.f);
+      acc += (m1l == me00 ? v1l : 0.f);
+      acc += (m1r == me00 ? v1r : 0.f);
+      dp[me00 - w0] = acc;
+      if (has_w1) {                                               // (2a, 2b+1): windows (a-1,b), (a,b)
+        acc = (m0r == me00 + 1 ? v0r : 0.f);
+        acc += (m1r == me00 + 1 ? v1r : 0.f);
+        dp[me00 - w0 + 1] = acc;
+      }
+      if (h0 + 1 < g.H) {
+        acc = (m1l == me00 + g.W ? v1l : 0.f);                    // (2a+1, 2b): windows (a,b-1), (a,b)
+        acc += (m1r == me00 + g.W ? v1r : 0.f);
+        dp[me00 - w0 + g.W] = acc;
+        if (has_w1) dp[me00 - w0 + g.W + 1] = (m1r == me00 + g.W + 1 ? v1r : 0.f);   // (2a+1, 2b+1): window (a,b)
+      }
+      m0l = m1l; m0r = m1r; v0l = v1l; v0r = v1r;
+      m1l = m2l; m1r = m2r; v1l = v2l; v1r = v2r;
+    }
+  }
+}
 __global__ void pool_gate_kernel(size_t n, const float* __restrict__ dy, const float* __restrict__ gate, float* __restrict__ out) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = gate[i] > 0.f ? dy[i] : 0.f;
@@ -430,8 +487,13 @@ void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int*
   const bool fixed = g.ph == 0 && g.pw == 0 && total_in < (1ull << 31);
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
     const int A = (g.H + 1) / 2, B = (g.W + 1) / 2;
-    const size_t total = (size_t)g.N * g.C * A * B;
-    pool_max_bwd_3x3s2_kernel<<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)B), FastDiv((uint32_t)A), dy, mask, gate, dx);
+    const size_t total = (size_t)g.N * g.C * A * B, strips = (size_t)g.N * g.C * B;
+    const char* e = getenv("SPARKNET_POOL_STRIP");      // 0: block form only, 2: strip form always (tests), default: by size
+    const int strip_mode = e ? atoi(e) : 1;
+    if (strip_mode == 2 || (strip_mode == 1 && strips >= (size_t)148 * 2048))   // enough strips to fill the GPU: half the instructions per element
+      pool_max_bwd_3x3s2_strip_kernel<<<grid_for(strips, 256, 32), 256, 0, s>>>(g, (uint32_t)strips, FastDiv((uint32_t)B), A, dy, mask, gate, dx);
+    else
+      pool_max_bwd_3x3s2_kernel<<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)B), FastDiv((uint32_t)A), dy, mask, gate, dx);
   } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
     pool_max_bwd_fixed_kernel<2, 2, 2, 2><<<grid_for(total_in, 256, 32), 256, 0, s>>>(g, (uint32_t)total_in, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx);
   } else if (smem <= 40 * 1024) {

@@ -123,7 +123,8 @@ def test_inner_product_tma_and_gather_paths_tf32(oracle, product, monkeypatch, s
 
 
 @pytest.mark.parametrize("shape,kernel,stride", [((3, 16, 27, 27), 3, 2), ((2, 16, 32, 30), 3, 2), ((2, 16, 12, 12), 2, 2)])
-def test_relu_backward_folded_into_max_pool_backward(oracle, product, monkeypatch, shape, kernel, stride):
+@pytest.mark.parametrize("strip", ["0", "2"])
+def test_relu_backward_folded_into_max_pool_backward(oracle, product, monkeypatch, shape, kernel, stride, strip):
     """conv -> in-place ReLU -> MAX pool -> LRN, the CaffeNet pattern.  With SPARKNET_FUSE_RELU_POOL=1 (default) the pool's
     backward applies the ReLU gate and the ReLU layer's own backward is skipped: the result must be BIT-identical to the
     unfused product (same forward, same gates), and match the oracle."""
@@ -132,6 +133,7 @@ def test_relu_backward_folded_into_max_pool_backward(oracle, product, monkeypatc
               ReLULayer("relu", ["conv"]), PoolingLayer("pool", ["conv"], "MAX", kernel, stride),
               LRNLayer("norm", ["pool"], 5, 1e-4, 0.75)]
     # fp32 FFMA mode: the forward passes agree to ~1e-6, so oracle and product open the same gates
+    monkeypatch.setenv("SPARKNET_POOL_STRIP", strip)     # both forms of the 3x3 / stride-2 backward kernel apply the gate
     monkeypatch.setenv("SPARKNET_FUSE_RELU_POOL", "1")
     r = run_pair(oracle, product, {"data": x}, layers, "norm", "conv", precision=0)
     # the unfused product on the same weights and the same top gradient (the switch is read when a net is built)
