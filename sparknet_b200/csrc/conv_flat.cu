@@ -1024,6 +1024,20 @@ __global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__
   __syncthreads();
   const int Cs = C * s * s;
   float* out = dst + ((size_t)lead + (size_t)n * Gp + (size_t)hs * Wp) * Cs;
+  if (s == 4 && (((uintptr_t)out) & 15) == 0) {
+    // the four dx of one (position, c, dy) are contiguous in the staged row AND in the output: float4 in, float4 out,
+    // one division per four elements (the scalar loop below is bound by its index arithmetic, not by memory)
+    const int R = Cs / 4;                              // (c, dy) pairs
+    float4* out4 = reinterpret_cast<float4*>(out);
+    for (int i4 = threadIdx.x; i4 < Ws * R; i4 += blockDim.x) {
+      uint32_t ws, r;
+      dCs.divmod((uint32_t)i4 * 4u, ws, r);            // i = 4 * i4 = ws * Cs + 4 * r
+      r >>= 2;
+      const float4 v = *reinterpret_cast<const float4*>(rows + r * Wpad + ws * 4);
+      out4[i4] = make_float4(to_tf32_exact(v.x), to_tf32_exact(v.y), to_tf32_exact(v.z), to_tf32_exact(v.w));
+    }
+    return;
+  }
   for (int i = threadIdx.x; i < Ws * Cs; i += blockDim.x) {
     uint32_t ws, ch, r, dx;
     dCs.divmod((uint32_t)i, ws, ch);

@@ -991,6 +991,43 @@ __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict_
   for (int i = 0; i < rows; ++i) acc += dy[(size_t)i * cols + j];
   db[j] = accumulate ? db[j] + acc : acc;
 }
+// InnerProduct backward on the TMA path needs the top gradient twice: rounded to tf32 as the tensor-core operand and
+// summed over the batch rows as the bias gradient (inner_product_layer.cpp:100-104 caffe_cpu_gemv).  One pass does both:
+// block = 32 float4 columns x 8 row groups, each thread walks rows rg, rg + 8, ..., the eight partial sums are added
+// in row-group order (fixed order, no atomics).  cols % 4 == 0.
+__device__ __forceinline__ float round_tf32_rna(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+__global__ void __launch_bounds__(256) ip_round_bias_kernel(int rows, int cols4, const float4* __restrict__ dy, float4* __restrict__ dy_r,
+                                                            float* __restrict__ db, int accumulate) {
+  __shared__ float4 part[8][32];
+  const int cx = threadIdx.x & 31, rg = threadIdx.x >> 5, c4 = blockIdx.x * 32 + cx;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (c4 < cols4) {
+    for (int r = rg; r < rows; r += 8) {
+      const float4 v = dy[(size_t)r * cols4 + c4];
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+      dy_r[(size_t)r * cols4 + c4] = make_float4(round_tf32_rna(v.x), round_tf32_rna(v.y), round_tf32_rna(v.z), round_tf32_rna(v.w));
+    }
+  }
+  part[rg][cx] = acc;
+  __syncthreads();
+  if (rg == 0 && c4 < cols4 && db) {
+    float4 t = part[0][cx];
+#pragma unroll
+    for (int k = 1; k < 8; ++k) { const float4 u = part[k][cx]; t.x += u.x; t.y += u.y; t.z += u.z; t.w += u.w; }
+    float4* out = reinterpret_cast<float4*>(db) + c4;
+    if (accumulate) { const float4 o = *out; t.x += o.x; t.y += o.y; t.z += o.z; t.w += o.w; }
+    *out = t;
+  }
+}
+void ip_round_bias(cudaStream_t s, int rows, int cols, const float* dy, float* dy_r, float* db, bool accumulate) {
+  const int cols4 = cols / 4;
+  ip_round_bias_kernel<<<(cols4 + 31) / 32, 256, 0, s>>>(rows, cols4, (const float4*)dy, (float4*)dy_r, db, accumulate ? 1 : 0);
+  count_launch();
+}
 void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db, bool accumulate) {
   ip_bias_grad_kernel<<<(cols + 127) / 128, 128, 0, s>>>(rows, cols, dy, db, accumulate ? 1 : 0);
   count_launch();

@@ -118,6 +118,8 @@ void accuracy_top1(cudaStream_t s, int rows, int classes, const float* x, const 
 void conv_bias_grad(cudaStream_t s, int N, int C, int HW, const float* dy, float* db, bool accumulate);
 // db[j] (+)= sum_i dY[i][j]                                   (inner_product_layer.cpp:104-109)
 void ip_bias_grad(cudaStream_t s, int rows, int cols, const float* dy, float* db, bool accumulate);
+// dy_r = tf32(dy) and (db nullable) db (+)= column sums of dy, one pass; cols % 4 == 0, 16-byte aligned pointers
+void ip_round_bias(cudaStream_t s, int rows, int cols, const float* dy, float* dy_r, float* db, bool accumulate);
 
 // fused SGD step over the whole parameter arena (sgd_solver.cpp:145-239 + blob.cpp:154-162):
 //   g += decay*w ; h = momentum*h + rate*g ; g = h ; w -= h       per 1024-element chunk table

@@ -616,9 +616,17 @@ struct InnerProductLayer : Layer {
     const float* x = bottom[0]->data->gpu();
     const bool tma_w = tf32 && use_tma() && param_propagate_down[0] && tcw_matmul_wgrad_supported(M, N, K, dy, x, blobs[0]->diff->gpu());
     const bool tma_d = tf32 && use_tma() && pd[0] && tcw_matmul_supported(M, K, N, dy, blobs[0]->data->gpu(), true, bottom[0]->diff->gpu());
+    bool bias_done = false;
     if (tma_w || tma_d) {
       if (!dy_r) SN_CUDA(cudaMalloc(&dy_r, (size_t)M * N * sizeof(float)));
-      tc_round_to_tf32(S(), (size_t)M * N, dy, dy_r);
+      const bool want_db = bias_term && param_propagate_down[1];
+      float* db = want_db ? blobs[1]->diff->mutable_gpu() : nullptr;
+      if (N % 4 == 0 && ((uintptr_t)dy & 15) == 0 && (!db || ((uintptr_t)db & 15) == 0)) {
+        ip_round_bias(S(), M, N, dy, dy_r, db, acc);      // rounding pass and bias gradient share one read of dy
+        bias_done = want_db;
+      } else {
+        tc_round_to_tf32(S(), (size_t)M * N, dy, dy_r);
+      }
     }
     if (param_propagate_down[0]) {
       float* dw = blobs[0]->diff->mutable_gpu();
@@ -626,7 +634,7 @@ struct InnerProductLayer : Layer {
       else if (tf32) tc_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
       else ffma_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
     }
-    if (bias_term && param_propagate_down[1]) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
+    if (bias_term && param_propagate_down[1] && !bias_done) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
     if (pd[0]) {
       float* dx = bottom[0]->diff->mutable_gpu();
       if (tma_d) tcw_matmul(S(), M, K, N, dy_r, weights_tf32(), true, nullptr, false, dx);
