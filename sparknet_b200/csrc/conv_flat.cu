@@ -64,6 +64,9 @@ struct WinArgs {
   int m_units, n_tiles, total_tiles;   // m unit = MT*128 rows per CTA, one per CTA of the cluster
   int tpg;                  // taps per pipeline stage: one barrier hand-shake serves tpg filter chunks (a stage = tpg * b_bytes)
   int acc_stages;           // 2 when two accumulator sets fit in TMEM (MT * n_mma <= 256): the epilogue of tile k overlaps the MMAs of tile k+1
+  int b_resident;           // the launch has ONE filter tile (one group, one column tile, no split) and all its chunks fit in the
+                            // stage buffers (nstage == ncb * ceil(T / tpg)): they are loaded for the cluster's first tile and stay;
+                            // later tiles stream only their windows (AlexNet conv1: 83 KB of filter per tile left the L2 -> SM path)
 };
 // m = grid position, n = channel in group; NCHW destination with Hv x Wv valid positions per cell.
 // ld > 0 selects the matrix epilogue instead: dst[split][m][ld] row-major (bias / ReLU only when splits == 1).
@@ -251,8 +254,10 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         for (int tap0 = 0; tap0 < a.T; tap0 += a.tpg) {
           const int ng = min(a.tpg, a.T - tap0);                   // filter chunks in this stage
           tw = (stamp && mi == 0) ? clock64() : 0;
-          mbar_wait(&b_full[s], sphase);
-          tc_fence_after_sync();
+          if (!a.b_resident || ti == 0) {                           // resident filter: the chunks of the first tile stay valid
+            mbar_wait(&b_full[s], sphase);
+            tc_fence_after_sync();
+          }
           if (stamp && mi == 0) wait_b += clock64() - tw;
           // The 128-byte swizzle is a function of the absolute shared-memory address (bits 4-6 ^= bits 7-9), for the
           // TMA write and for the MMA read alike, so a descriptor may start at any row of the window: the
@@ -272,11 +277,11 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
             }
             const bool last_tap = tap0 + ng == a.T, last = last_tap && cb == cb_end - 1;
             if (CG == 2) {
-              mma_commit_pair(&b_empty[s]);
+              if (!a.b_resident) mma_commit_pair(&b_empty[s]);
               if (last_tap) mma_commit_pair(&win_empty[wb]);
               if (last) mma_commit_pair(&tmem_full[buf]);
             } else {
-              mma_commit(&b_empty[s]);
+              if (!a.b_resident) mma_commit(&b_empty[s]);
               if (last_tap) mma_commit(&win_empty[wb]);
               if (last) mma_commit(&tmem_full[buf]);
             }
@@ -312,6 +317,10 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
         }
         for (int tap0 = 0; tap0 < a.T; tap0 += a.tpg) {
           const int ng = min(a.tpg, a.T - tap0);
+          if (a.b_resident && t != cluster_id) {                    // already in shared memory since this cluster's first tile
+            if (++s == a.nstage) { s = 0; sphase ^= 1u; }
+            continue;
+          }
           mbar_wait(&b_empty[s], sphase ^ 1u);
           if (rank == 0) mbar_arrive_expect_tx(&b_full[s], b_bytes * CG * ng);
           for (int g = 0; g < ng; ++g) {
@@ -572,7 +581,30 @@ static void launch_window(cudaStream_t s, const CUtensorMap& tmA, const CUtensor
     aa.nstage = nst > kWMaxStages ? kWMaxStages : nst;
     smem_bytes = win_total + (size_t)aa.nstage * best_g * b_bytes + 1024;
   }
+  aa.b_resident = 0;
+  {
+    static const int allow = getenv("SPARKNET_B_RESIDENT") ? atoi(getenv("SPARKNET_B_RESIDENT")) : 1;
+    const size_t b_bytes = (size_t)a.n_mma * 128 / pl.cg, win_total = (size_t)a.nwin * a.nbox * a.box_rows * 128;
+    if (allow && aa.n_tiles * groups * a.splits == 1 && !a.b_mn && aa.total_tiles > 148 / pl.cg) {
+      // taps per stage g: all ncb * ceil(T / g) stages must exist at once (<= kWMaxStages barriers) and fit beside the windows
+      int best = 0;
+      size_t best_bytes = 0;
+      for (int g = 1; g <= a.T; ++g) {
+        const int nst = a.ncb * ((a.T + g - 1) / g);
+        const size_t bytes = (size_t)nst * g * b_bytes;
+        if (nst > kWMaxStages || win_total + bytes + 2048 > kWSmemLimit) continue;
+        if (!best || bytes <= best_bytes) { best = g; best_bytes = bytes; }
+      }
+      if (best) {
+        aa.b_resident = 1;
+        aa.tpg = best;
+        aa.nstage = a.ncb * ((a.T + best - 1) / best);
+        smem_bytes = win_total + best_bytes + 1024;
+      }
+    }
+  }
   static const bool plan_debug = getenv("SPARKNET_PLAN_DEBUG") != nullptr;
+  if (plan_debug && aa.b_resident) fprintf(stderr, "window plan: filter resident in shared memory (%d stages of %d taps)\n", aa.nstage, aa.tpg);
   if (plan_debug)
     fprintf(stderr, "window plan: rows %d N %d T %d ncb %d -> MT %d n_mma %d cg %d stages %d tiles %d acc_stages %d splits %d\n", a.Ptot, N, a.T,
             a.ncb, a.MT, a.n_mma, pl.cg, aa.nstage, aa.total_tiles, aa.acc_stages, a.splits);
