@@ -1138,15 +1138,17 @@ __global__ void filter_pack_batch_kernel(const FilterPackBatch b) {
       const int slots = (red + 31) / 32 * 32, kp = T * slots;
       const int row = (int)(i / kp), k = (int)(i - (size_t)row * kp), tap = k / slots, ch = k - tap * slots;
       if (ch < red) {
-        if (!dgrad) v = j.w[((size_t)row * Cg + ch) * T + tap];
+        const int Csrc = j.p[3] > 0 ? j.p[3] : Cg;      // channel-padded first layers: the stored filter has Csrc < Cg channels
+        if (!dgrad) v = ch < Csrc ? j.w[((size_t)row * Csrc + ch) * T + tap] : 0.f;
         else { const int grp = row / Cg, c = row - grp * Cg; v = j.w[((size_t)(grp * Og + ch) * Cg + c) * T + (T - 1 - tap)]; }
       }
     }
     j.dst[i] = to_tf32_exact(v);
   }
 }
-FilterPackJob tcw_filter_pack_job(const ConvGeom& g, int mode, const float* w, float* dst) {
+FilterPackJob tcw_filter_pack_job(const ConvGeom& g, int mode, const float* w, float* dst, int src_cg) {
   FilterPackJob j{};
+  j.p[3] = mode == 0 ? src_cg : 0;
   j.w = w; j.dst = dst; j.mode = mode;
   if (mode == 2) {
     const ConvGeom e = tcw_s2d_geom(g);
@@ -1168,6 +1170,21 @@ void tcw_filter_pack_batch(cudaStream_t st, const FilterPackBatch& b) {
   const int cap = std::max(148 * 4 / b.n, 32);
   if (blocks > cap) blocks = cap;
   filter_pack_batch_kernel<<<dim3(blocks, b.n), 256, 0, st>>>(b);
+  count_launch();
+  SN_CUDA(cudaGetLastError());
+}
+// Channel-padded first layers (C < 16 padded to 16 on the flat grid): dw[co][c][tap] (+)= dws[co][c][tap] for the real channels
+__global__ void cpad_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int Cpad, int T, int accumulate) {
+  const int total = Cout * C * T;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int r = i % (C * T), co = i / (C * T);
+    const float v = dws[(size_t)co * Cpad * T + r];
+    dw[i] = accumulate ? dw[i] + v : v;
+  }
+}
+void tcw_cpad_unpack_wgrad(cudaStream_t st, const ConvGeom& g, int Cpad, const float* dws, float* dw, bool accumulate) {
+  const int total = g.Cout * g.C * g.kh * g.kw;
+  cpad_unpack_wgrad_kernel<<<(total + 255) / 256, 256, 0, st>>>(dws, dw, g.Cout, g.C, Cpad, g.kh * g.kw, accumulate ? 1 : 0);
   count_launch();
   SN_CUDA(cudaGetLastError());
 }

@@ -981,11 +981,13 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
 // in image order.  The top gradient is therefore read from HBM once for both purposes.
 template <bool BIAS>
 __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
-                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span) {
+                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span, int Csrc) {
+  // Csrc <= C: the source tensor has Csrc channels, the packed rows C (the rest are written as zeros: channel padding of
+  // first layers with fewer than 16 input channels)
   __shared__ float tile[32][129];
   const int HW = H * W, c0 = blockIdx.x * 32, n = blockIdx.y;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-  const float* sp = src + ((size_t)n * C + c0) * HW;
+  const float* sp = src + ((size_t)n * Csrc + c0) * HW;
   float* dp = dst + ((size_t)lead + (size_t)n * Gp) * C + c0 + tx;
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};
   const int p_begin = blockIdx.z * span, p_end = min(HW, p_begin + span);     // this block's share of the image's pixels
@@ -996,7 +998,7 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
         const int j = ty + 8 * k, p = p0 + tx + 32 * q;
-        v[k][q] = (c0 + j < C && p < p_end) ? sp[(size_t)j * HW + p] : 0.f;
+        v[k][q] = (c0 + j < Csrc && p < p_end) ? sp[(size_t)j * HW + p] : 0.f;
       }
 #pragma unroll
     for (int k = 0; k < 4; ++k)
@@ -1038,8 +1040,9 @@ __global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ p
   if (lane == 0) db[c] = accumulate ? db[c] + t : t;
 }
 // db (nullable): bias gradient, summed here when the packed tensor is the top gradient
-void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db, bool accumulate) {
+void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db, bool accumulate, int src_channels) {
   const int C = output_side ? g.Cout : g.C, H = output_side ? g.Ho : g.H, W = output_side ? g.Wo : g.W;
+  const int Csrc = src_channels > 0 ? src_channels : C;
   const FlatGeom f = tc_flat_geom(g);
   const int HW = H * W;
   int Z = (HW + 1023) / 1024;                          // large planes: several blocks per (image, channel block)
@@ -1049,18 +1052,18 @@ void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const flo
   dim3 grid((C + 31) / 32, g.N, Z);
   if (db) {
     float* part = get_workspace((size_t)C * g.N * Z);
-    flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span);
+    flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, Csrc);
     bias_grad_final_kernel<<<(C * 32 + 127) / 128, 128, 0, s>>>(C, g.N * Z, part, db, accumulate ? 1 : 0);
     count_launch(2);
   } else {
-    flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span);
+    flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, Csrc);
     count_launch();
   }
   SN_CUDA(cudaGetLastError());
 }
 // dst[row][tap*slots + ch]: fwd   (dgrad = 0): row = co (all groups), ch = c in group,  value W[co][c][tap]
 //                           dgrad (dgrad = 1): row = grp*Cg + c,      ch = co in group, value W[grp*Og + co][c][T-1-tap]
-__global__ void flat_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ dst, int Cg, int Og, int T, int groups, int dgrad) {
+__global__ void flat_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ dst, int Cg, int Og, int T, int groups, int dgrad, int Csrc) {
   const int red = dgrad ? Og : Cg, rows = dgrad ? Cg * groups : Og * groups;
   const int slots = (red + 31) / 32 * 32, kp = T * slots;
   const size_t total = (size_t)rows * kp;
@@ -1068,17 +1071,17 @@ __global__ void flat_pack_filter_kernel(const float* __restrict__ w, float* __re
     const int row = (int)(i / kp), k = (int)(i - (size_t)row * kp), tap = k / slots, ch = k - tap * slots;
     float v = 0.f;
     if (ch < red) {
-      if (!dgrad) v = w[((size_t)row * Cg + ch) * T + tap];
+      if (!dgrad) v = ch < Csrc ? w[((size_t)row * Csrc + ch) * T + tap] : 0.f;   // Csrc < Cg: zero slots for padded channels
       else { const int grp = row / Cg, c = row - grp * Cg; v = w[((size_t)(grp * Og + ch) * Cg + c) * T + (T - 1 - tap)]; }
     }
     dst[i] = to_tf32_exact(v);
   }
 }
-void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst) {
+void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst, int src_cg) {
   const size_t total = tc_flat_filter_floats(g, dgrad);
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  flat_pack_filter_kernel<<<blocks, 256, 0, s>>>(w, dst, g.Cg(), g.Og(), g.kh * g.kw, g.group, dgrad ? 1 : 0);
+  flat_pack_filter_kernel<<<blocks, 256, 0, s>>>(w, dst, g.Cg(), g.Og(), g.kh * g.kw, g.group, dgrad ? 1 : 0, (src_cg > 0 && !dgrad) ? src_cg : g.Cg());
   count_launch();
   SN_CUDA(cudaGetLastError());
 }

@@ -45,8 +45,9 @@ FlatGeom tc_flat_geom(const ConvGeom& g);
 size_t tc_flat_rows(const ConvGeom& g);                                // grid rows of a packed tensor (x channels = floats)
 size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad);
 // dst zeroed once by the owner; db (nullable) = bias gradient summed in the same pass over the top gradient
-void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db = nullptr, bool accumulate = false);
-void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst);
+void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db = nullptr,
+                  bool accumulate = false, int src_channels = 0);   // src_channels < g.C: the remaining packed channels are zeros
+void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst, int src_cg = 0);   // src_cg < g.Cg() (forward layout): zero slots
 void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
 void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
 void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
@@ -65,7 +66,8 @@ void tcw_s2d_pack_filter(cudaStream_t s, const ConvGeom& g, const float* w, floa
 // mode 2 = tcw_s2d_pack_filter.
 struct FilterPackJob { const float* w; float* dst; size_t total; int mode; int p[8]; };
 struct FilterPackBatch { static constexpr int kMax = 16; FilterPackJob job[kMax]; int n; };
-FilterPackJob tcw_filter_pack_job(const ConvGeom& g, int mode, const float* w, float* dst);
+FilterPackJob tcw_filter_pack_job(const ConvGeom& g, int mode, const float* w, float* dst, int src_cg = 0);
+void tcw_cpad_unpack_wgrad(cudaStream_t s, const ConvGeom& g, int Cpad, const float* dws, float* dw, bool accumulate);
 void tcw_filter_pack_batch(cudaStream_t s, const FilterPackBatch& b);
 void tcw_s2d_unpack_wgrad(cudaStream_t s, const ConvGeom& g, const float* dws, float* dw, bool accumulate);
 // out[m][n] = sum_k A[m][k] * B(n,k) (+ bias[n], ReLU) on the window kernel; A [M][K] tf32-rounded, B [N][K] or (b_mn) [K][N]

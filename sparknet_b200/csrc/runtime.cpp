@@ -442,14 +442,24 @@ struct ConvolutionLayer : Layer {
   ConvGeom gs;
   int s2d_ok = -1;
   float* dws = nullptr;                               // filter gradient in the folded layout
+  // s2d_ok: 1 = space to depth (stride folded away), 2 = channel padding: a stride-1 first layer with fewer than 16 input
+  // channels (cifar conv1: C = 3) runs on the window kernels over a grid whose rows carry 16 channels, 13 of them zero —
+  // the wasted MMAs are microseconds, the gather kernels it replaces were 40 % of a cifar10_quick iteration.
   bool use_s2d() {
     if (s2d_ok < 0) {
       const char* e = getenv("SPARKNET_CONV_S2D");
       s2d_ok = (tcw_s2d_supported(g) && !(e && atoi(e) == 0)) ? 1 : 0;
       if (s2d_ok) gs = tcw_s2d_geom(g);
+      const char* ep = getenv("SPARKNET_CONV_CPAD");
+      if (!s2d_ok && !(ep && atoi(ep) == 0) && g.sh == 1 && g.sw == 1 && g.group == 1 && g.C < 16 && g.Cout % 16 == 0) {
+        ConvGeom gp = g;
+        gp.C = 16;
+        if (tcw_supported(gp) && tcw_wgrad_supported(gp)) { gs = gp; s2d_ok = 2; }
+      }
     }
     return s2d_ok != 0;
   }
+  bool cpad() { return use_s2d() && s2d_ok == 2; }
   const ConvGeom& fg() { return use_s2d() ? gs : g; } // geometry of the flat grid in use
   float* flat_alloc(int channels) {
     float* p = nullptr;
@@ -462,7 +472,8 @@ struct ConvolutionLayer : Layer {
     const float* x = bottom->data->gpu();
     if (!xflat) xflat = flat_alloc(fg().C);
     if (xflat_src != bottom->data.get() || xflat_gen != bottom->data->gen) {
-      if (use_s2d()) tcw_s2d_pack_input(S(), g, x, xflat);
+      if (cpad()) tc_flat_pack(S(), gs, false, x, xflat, nullptr, false, g.C);
+      else if (use_s2d()) tcw_s2d_pack_input(S(), g, x, xflat);
       else tc_flat_pack(S(), g, false, x, xflat);
       xflat_src = bottom->data.get();
       xflat_gen = bottom->data->gen;
@@ -475,7 +486,8 @@ struct ConvolutionLayer : Layer {
     const int i = dgrad ? 1 : 0;
     if (!wflat[i]) SN_CUDA(cudaMalloc(&wflat[i], tc_flat_filter_floats(fg(), dgrad) * sizeof(float)));
     if (wflat_gen[i] != st->gen) {
-      if (use_s2d()) tcw_s2d_pack_filter(S(), g, w, wflat[i]);
+      if (cpad()) tc_flat_pack_filter(S(), gs, false, w, wflat[i], g.C);
+      else if (use_s2d()) tcw_s2d_pack_filter(S(), g, w, wflat[i]);
       else tc_flat_pack_filter(S(), g, dgrad, w, wflat[i]);
       wflat_gen[i] = st->gen;
     }
@@ -493,6 +505,14 @@ struct ConvolutionLayer : Layer {
       b.job[b.n++] = tcw_filter_pack_job(g, mode, st->gpu(), wflat[i]);
       wflat_gen[i] = st->gen;
     };
+    if (cpad()) {
+      if (b.n < FilterPackBatch::kMax && !(wflat[0] && wflat_gen[0] == st->gen)) {
+        if (!wflat[0]) SN_CUDA(cudaMalloc(&wflat[0], tc_flat_filter_floats(gs, false) * sizeof(float)));
+        b.job[b.n++] = tcw_filter_pack_job(gs, 0, st->gpu(), wflat[0], g.C);
+        wflat_gen[0] = st->gen;
+      }
+      return;
+    }
     if (use_s2d()) { add(false, 2); return; }
     if (use_flat(1)) add(false, 0);
     if (use_flat(4) && propagate_down) add(true, 1);
@@ -512,7 +532,8 @@ struct ConvolutionLayer : Layer {
       tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
       if (!dws) SN_CUDA(cudaMalloc(&dws, (size_t)gs.Cout * gs.C * gs.kh * gs.kw * sizeof(float)));
       tcw_conv_wgrad(S(), gs, packed_input(bottom[0]), dyflat, dws, false);
-      tcw_s2d_unpack_wgrad(S(), g, dws, blobs[0]->diff->mutable_gpu(), acc);
+      if (cpad()) tcw_cpad_unpack_wgrad(S(), g, gs.C, dws, blobs[0]->diff->mutable_gpu(), acc);
+      else tcw_s2d_unpack_wgrad(S(), g, dws, blobs[0]->diff->mutable_gpu(), acc);
       if (pd[0]) {
         float* dx = bottom[0]->diff->mutable_gpu();
         tc_conv_dgrad(S(), g, dy, blobs[0]->data->gpu(), dx);

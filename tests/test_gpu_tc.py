@@ -54,6 +54,29 @@ def test_convolution_flat_grid_and_gather_paths_tf32(oracle, product, monkeypatc
         assert_close(a, b, TOL, f"param diff {j}")
 
 
+# stride-1 first layers with fewer than 16 input channels run on the window kernels over a channel-padded grid (runtime.cpp
+# ConvolutionLayer::use_s2d kind 2); SPARKNET_CONV_CPAD=0 keeps them on the gather kernels
+CPAD_CASES = [
+    ((4, 3, 32, 32), 32, dict(kernel_size=[5], pad=[2])),                           # cifar conv1
+    ((7, 1, 12, 9), 16, dict(kernel_size=[3])),                                    # one channel, no padding
+    ((3, 8, 10, 10), 48, dict(kernel_h=3, kernel_w=5, pad_h=1, pad_w=2)),          # rectangular
+    ((50, 3, 32, 32), 32, dict(kernel_size=[5], pad=[2])),                          # many tiles: persistent CTAs, resident filter
+]
+
+
+@pytest.mark.parametrize("cpad", ["1", "0"])
+@pytest.mark.parametrize("shape,num_output,kw", CPAD_CASES)
+def test_convolution_channel_padded_first_layer_tf32(oracle, product, monkeypatch, shape, num_output, kw, cpad):
+    monkeypatch.setenv("SPARKNET_CONV_CPAD", cpad)
+    x = np.random.default_rng(78).standard_normal(shape).astype(F)
+    l = conv_layer("conv", "data", num_output, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5), **kw)
+    r = run_pair(oracle, product, {"data": x}, [l], "conv", "conv", precision=1)
+    assert_close(r["fwd"][0]["conv"], r["fwd"][1]["conv"], TOL, "top")
+    assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL, "bottom diff")
+    for j, (a, b) in enumerate(zip(*r["wdiff"]["conv"])):
+        assert_close(a, b, TOL, f"param diff {j}")
+
+
 # strided, unpadded layers whose folded channel count C*s*s is a multiple of 16 run as stride-1 window convolutions on
 # the space-to-depth grid (csrc/conv_flat.cu); SPARKNET_CONV_S2D=0 keeps them on the gather kernels
 S2D_CASES = [
