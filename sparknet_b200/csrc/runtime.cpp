@@ -442,16 +442,18 @@ struct ConvolutionLayer : Layer {
   ConvGeom gs;
   int s2d_ok = -1;
   float* dws = nullptr;                               // filter gradient in the folded layout
-  // s2d_ok: 1 = space to depth (stride folded away), 2 = channel padding: a stride-1 first layer with fewer than 16 input
-  // channels (cifar conv1: C = 3) runs on the window kernels over a grid whose rows carry 16 channels, 13 of them zero —
-  // the wasted MMAs are microseconds, the gather kernels it replaces were 40 % of a cifar10_quick iteration.
+  // s2d_ok: 1 = space to depth (stride folded away), 2 = channel padding (opt-in, SPARKNET_CONV_CPAD=1): a stride-1 first
+  // layer with fewer than 16 input channels (cifar conv1: C = 3) runs on the window kernels over a grid whose rows carry
+  // 16 channels, 13 of them zero.  Correct (tests/test_gpu_tc.py) but not faster on B200 at cifar sizes: forward 44 us
+  // either way, backward 105 us against 73 us on the gather kernels (pack + window + slice reduction + unpack are four
+  // latency-bound launches), so the gather kernels stay the default.
   bool use_s2d() {
     if (s2d_ok < 0) {
       const char* e = getenv("SPARKNET_CONV_S2D");
       s2d_ok = (tcw_s2d_supported(g) && !(e && atoi(e) == 0)) ? 1 : 0;
       if (s2d_ok) gs = tcw_s2d_geom(g);
       const char* ep = getenv("SPARKNET_CONV_CPAD");
-      if (!s2d_ok && !(ep && atoi(ep) == 0) && g.sh == 1 && g.sw == 1 && g.group == 1 && g.C < 16 && g.Cout % 16 == 0) {
+      if (!s2d_ok && ep && atoi(ep) == 1 && g.sh == 1 && g.sw == 1 && g.group == 1 && g.C < 16 && g.Cout % 16 == 0) {
         ConvGeom gp = g;
         gp.C = 16;
         if (tcw_supported(gp) && tcw_wgrad_supported(gp)) { gs = gp; s2d_ok = 2; }

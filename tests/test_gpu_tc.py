@@ -54,8 +54,8 @@ def test_convolution_flat_grid_and_gather_paths_tf32(oracle, product, monkeypatc
         assert_close(a, b, TOL, f"param diff {j}")
 
 
-# stride-1 first layers with fewer than 16 input channels run on the window kernels over a channel-padded grid (runtime.cpp
-# ConvolutionLayer::use_s2d kind 2); SPARKNET_CONV_CPAD=0 keeps them on the gather kernels
+# stride-1 first layers with fewer than 16 input channels CAN run on the window kernels over a channel-padded grid (runtime.cpp
+# ConvolutionLayer::use_s2d kind 2, SPARKNET_CONV_CPAD=1); the default keeps them on the gather kernels, which are faster there
 CPAD_CASES = [
     ((4, 3, 32, 32), 32, dict(kernel_size=[5], pad=[2])),                           # cifar conv1
     ((7, 1, 12, 9), 16, dict(kernel_size=[3])),                                    # one channel, no padding
