@@ -477,6 +477,78 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_strip_kernel(PoolGeom 
     }
   }
 }
+// Row form of the same backward: a group of G = 8 / 16 / 32 lanes owns one plane (G >= ceil(W / 2)), lane b the input
+// columns (2b, 2b+1), and the group walks down the plane two input rows per step.  Per step a lane loads ONE pooled
+// element (mask, dy, gate of window (a, b)) — the left neighbour's comes by shuffle, the row above stays in registers —
+// and the two finished input rows leave through shuffles so that every store instruction writes a contiguous run of the
+// row (the block and strip forms write every other float per instruction).  Same windows, same order of additions.
+template <int G>
+__global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g, uint32_t planes, int A, const float* __restrict__ dy,
+                                                                     const int* __restrict__ mask, const float* __restrict__ gate,
+                                                                     float* __restrict__ dx) {
+  const int P = g.PH * g.PW, HW = g.H * g.W;
+  const int lane = threadIdx.x & 31, b = lane & (G - 1);
+  const uint32_t groups_per_block = 256 / G;
+  const uint32_t first = blockIdx.x * groups_per_block + threadIdx.x / G, stride = gridDim.x * groups_per_block;
+  const int w0 = 2 * b;
+  const bool okw = b < g.PW;                            // window column b exists
+  for (uint32_t plane0 = first; plane0 - (plane0 % (32 / G)) < planes; plane0 += stride) {   // whole warps stay in the loop (shuffles)
+    const bool live = plane0 < planes;
+    const uint32_t plane = live ? plane0 : planes - 1;
+    const int* mp = mask + (size_t)plane * P;
+    const float* gp = dy + (size_t)plane * P;
+    const float* tp = gate ? gate + (size_t)plane * P : nullptr;
+    float* dp = dx + (size_t)plane * HW;
+    int m0l = -2, m0r = -2;
+    float v0l = 0.f, v0r = 0.f;
+    auto load_row = [&](int a, int& mr, float& vr) {
+      mr = -2; vr = 0.f;
+      if (a < g.PH && okw) {
+        const int o = a * g.PW + b;
+        mr = __ldg(mp + o); vr = __ldg(gp + o);
+        if (tp && !(__ldg(tp + o) > 0.f)) vr = 0.f;
+      }
+    };
+    int m1r; float v1r;
+    load_row(0, m1r, v1r);
+    for (int a = 0; a < A; ++a) {
+      int m2r; float v2r;
+      load_row(a + 1, m2r, v2r);
+      // window (a, b-1) lives in the lane to the left
+      int m1l = __shfl_up_sync(0xffffffffu, m1r, 1, G);
+      float v1l = __shfl_up_sync(0xffffffffu, v1r, 1, G);
+      if (b == 0) { m1l = -2; v1l = 0.f; }
+      const int h0 = 2 * a, me00 = h0 * g.W + w0;
+      float x00, x01, x10, x11;
+      x00 = (m0l == me00 ? v0l : 0.f);                       // (2a, 2b): windows (a-1,b-1), (a-1,b), (a,b-1), (a,b)
+      x00 += (m0r == me00 ? v0r : 0.f);
+      x00 += (m1l == me00 ? v1l : 0.f);
+      x00 += (m1r == me00 ? v1r : 0.f);
+      x01 = (m0r == me00 + 1 ? v0r : 0.f);                   // (2a, 2b+1): windows (a-1,b), (a,b)
+      x01 += (m1r == me00 + 1 ? v1r : 0.f);
+      x10 = (m1l == me00 + g.W ? v1l : 0.f);                 // (2a+1, 2b): windows (a,b-1), (a,b)
+      x10 += (m1r == me00 + g.W ? v1r : 0.f);
+      x11 = (m1r == me00 + g.W + 1 ? v1r : 0.f);             // (2a+1, 2b+1): window (a,b)
+      // column c of a row sits in lane c >> 1, component c & 1: lane j stores columns j and G + j
+      const int src0 = b >> 1, src1 = (G >> 1) + (b >> 1);
+      const bool odd = b & 1;
+#pragma unroll
+      for (int r = 0; r < 2; ++r) {
+        const float e = r ? x10 : x00, o = r ? x11 : x01;
+        const float lo_e = __shfl_sync(0xffffffffu, e, src0, G), lo_o = __shfl_sync(0xffffffffu, o, src0, G);
+        const float hi_e = __shfl_sync(0xffffffffu, e, src1, G), hi_o = __shfl_sync(0xffffffffu, o, src1, G);
+        const int h = h0 + r;
+        if (live && h < g.H) {
+          float* row = dp + h * g.W;
+          if (b < g.W) row[b] = odd ? lo_o : lo_e;
+          if (G + b < g.W) row[G + b] = odd ? hi_o : hi_e;
+        }
+      }
+      m0l = m1l; m0r = m1r; v0l = v1l; v0r = v1r;
+      m1r = m2r; v1r = v2r;
+    }
+  }
+}
 __global__ void pool_gate_kernel(size_t n, const float* __restrict__ dy, const float* __restrict__ gate, float* __restrict__ out) {
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     out[i] = gate[i] > 0.f ? dy[i] : 0.f;
@@ -488,9 +560,15 @@ void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int*
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
     const int A = (g.H + 1) / 2, B = (g.W + 1) / 2;
     const size_t total = (size_t)g.N * g.C * A * B, strips = (size_t)g.N * g.C * B;
-    const char* e = getenv("SPARKNET_POOL_STRIP");      // 0: block form only, 2: strip form always (tests), default: by size
+    const char* e = getenv("SPARKNET_POOL_STRIP");      // 0: block form only, 2: strip form always, 3: row form always (tests), default: by size
     const int strip_mode = e ? atoi(e) : 1;
-    if (strip_mode == 2 || (strip_mode == 1 && strips >= (size_t)148 * 2048))   // enough strips to fill the GPU: half the instructions per element
+    const uint32_t planes = (uint32_t)(g.N * g.C);
+    if ((strip_mode == 3 || (strip_mode == 1 && strips >= (size_t)148 * 2048)) && B <= 32) {
+      // large layers: the row form (coalesced stores, one load per window)
+      if (B > 16) pool_max_bwd_3x3s2_row_kernel<32><<<grid_for((size_t)planes * 32, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx);
+      else if (B > 8) pool_max_bwd_3x3s2_row_kernel<16><<<grid_for((size_t)planes * 16, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx);
+      else pool_max_bwd_3x3s2_row_kernel<8><<<grid_for((size_t)planes * 8, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx);
+    } else if (strip_mode == 2 || (strip_mode == 1 && strips >= (size_t)148 * 2048))   // the strip form: half the instructions per element
       pool_max_bwd_3x3s2_strip_kernel<<<grid_for(strips, 256, 32), 256, 0, s>>>(g, (uint32_t)strips, FastDiv((uint32_t)B), A, dy, mask, gate, dx);
     else
       pool_max_bwd_3x3s2_kernel<<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)B), FastDiv((uint32_t)A), dy, mask, gate, dx);

@@ -169,10 +169,11 @@ def test_pooling_fwd_bwd_and_mask(oracle, product, shape, pp, method):
         assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], TOL_FFMA, "bottom diff")
 
 
-@pytest.mark.parametrize("shape", [(3, 32, 32, 32), (2, 96, 55, 55), (2, 256, 13, 13), (2, 8, 27, 27), (1, 3, 6, 5)])
+@pytest.mark.parametrize("shape", [(3, 32, 32, 32), (2, 96, 55, 55), (2, 256, 13, 13), (2, 8, 27, 27), (1, 3, 6, 5), (1, 5, 64, 63), (3, 7, 9, 16)])
 def test_max_pool_3x3s2_backward_strip_and_block_forms_agree(oracle, product, monkeypatch, shape):
-    """The 3x3 / stride-2 max-pool backward has two kernels (kernels.cu: a 2x2 block per thread, and a column strip per
-    thread that carries the pooled row above in registers; large layers take the strip form).  Both must give the
+    """The 3x3 / stride-2 max-pool backward has three kernels (kernels.cu: a 2x2 block per thread; a column strip per thread
+    that carries the pooled row above in registers; a lane group per plane with shuffled, contiguous stores — large layers
+    take the last).  All must give the
     oracle's bottom diff (pooling_layer.cpp:253-270: every input sums the top diffs of the windows whose argmax it is,
     ties planted) and be BIT-identical to each other."""
     rng = np.random.default_rng(33)
@@ -181,12 +182,12 @@ def test_max_pool_3x3s2_backward_strip_and_block_forms_agree(oracle, product, mo
     l = Msg("LayerParameter", name="pool", type="Pooling", bottom=["data"], top=["pool"])
     l.pooling_param = Msg("PoolingParameter", pool=0, kernel_size=3, stride=2)
     out = {}
-    for mode in ("0", "2"):
+    for mode in ("0", "2", "3"):                               # block, strip, row form
         monkeypatch.setenv("SPARKNET_POOL_STRIP", mode)
         r = run_pair(oracle, product, {"data": x}, [l], "pool")
         assert_close(r["bwd"][0]["data"], r["bwd"][1]["data"], 1e-6, "bottom diff, mode " + mode)
         out[mode] = r["bwd"][1]["data"]
-    assert np.array_equal(out["0"], out["2"])
+    assert np.array_equal(out["0"], out["2"]) and np.array_equal(out["0"], out["3"])
 
 
 def test_pool_literals_on_device(product):

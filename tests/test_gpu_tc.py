@@ -146,7 +146,7 @@ def test_inner_product_tma_and_gather_paths_tf32(oracle, product, monkeypatch, s
 
 
 @pytest.mark.parametrize("shape,kernel,stride", [((3, 16, 27, 27), 3, 2), ((2, 16, 32, 30), 3, 2), ((2, 16, 12, 12), 2, 2)])
-@pytest.mark.parametrize("strip", ["0", "2"])
+@pytest.mark.parametrize("strip", ["0", "2", "3"])
 def test_relu_backward_folded_into_max_pool_backward(oracle, product, monkeypatch, shape, kernel, stride, strip):
     """conv -> in-place ReLU -> MAX pool -> LRN, the CaffeNet pattern.  With SPARKNET_FUSE_RELU_POOL=1 (default) the pool's
     backward applies the ReLU gate and the ReLU layer's own backward is skipped: the result must be BIT-identical to the

@@ -28,16 +28,14 @@ def elts(c, h, w=None):
 
 # name: (fwd bytes, bwd bytes, note)
 BW = {
-    # max pool: fwd reads x, writes y + int32 mask; bwd reads dy + mask, writes dx (and, with ReLU folded in, reads y of the ReLU)
-    "pool1": (E * (elts(96, 55) + 2 * elts(96, 27)), E * (2 * elts(96, 27) + 2 * elts(96, 55)), "bwd includes relu1's backward (reads its output)"),
-    "pool2": (E * (elts(256, 27) + 2 * elts(256, 13)), E * (2 * elts(256, 13) + 2 * elts(256, 27)), "bwd includes relu2's backward"),
-    "pool5": (E * (elts(256, 13) + 2 * elts(256, 6)), E * (2 * elts(256, 6) + 2 * elts(256, 13)), "bwd includes relu5's backward"),
+    # max pool: fwd reads x, writes y + int32 mask; bwd reads dy + mask (+ the POOLED output as the gate of the ReLU folded
+    # in: the element that won a window is > 0 exactly when the pooled value is), writes dx
+    "pool1": (E * (elts(96, 55) + 2 * elts(96, 27)), E * (3 * elts(96, 27) + elts(96, 55)), "bwd includes relu1's backward (gate = pooled output)"),
+    "pool2": (E * (elts(256, 27) + 2 * elts(256, 13)), E * (3 * elts(256, 13) + elts(256, 27)), "bwd includes relu2's backward"),
+    "pool5": (E * (elts(256, 13) + 2 * elts(256, 6)), E * (3 * elts(256, 6) + elts(256, 13)), "bwd includes relu5's backward"),
     # LRN across channels without a stored scale tensor: fwd reads x writes y; bwd reads x, y, dy writes dx
     "norm1": (E * 2 * elts(96, 27), E * 4 * elts(96, 27), "no scale tensor kept"),
     "norm2": (E * 2 * elts(256, 13), E * 4 * elts(256, 13), "no scale tensor kept"),
-    # stand-alone ReLU backward (relu3 / relu4 sit between two convolutions): reads dy and y, writes dx
-    "relu3": (0, E * 3 * elts(384, 13), "forward fused into conv3's epilogue"),
-    "relu4": (0, E * 3 * elts(384, 13), "forward fused into conv4's epilogue"),
     # dropout: fwd reads x writes y + byte mask; bwd reads dy + mask writes dx
     "drop6": (N * 4096 * (2 * E + 1), N * 4096 * (2 * E + 1), ""),
     "drop7": (N * 4096 * (2 * E + 1), N * 4096 * (2 * E + 1), ""),
