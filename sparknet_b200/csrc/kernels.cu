@@ -509,43 +509,53 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g,
         if (tp && !(__ldg(tp + o) > 0.f)) vr = 0.f;
       }
     };
-    int m1r; float v1r;
-    load_row(0, m1r, v1r);
-    for (int a = 0; a < A; ++a) {
-      int m2r; float v2r;
-      load_row(a + 1, m2r, v2r);
-      // window (a, b-1) lives in the lane to the left
-      int m1l = __shfl_up_sync(0xffffffffu, m1r, 1, G);
-      float v1l = __shfl_up_sync(0xffffffffu, v1r, 1, G);
-      if (b == 0) { m1l = -2; v1l = 0.f; }
-      const int h0 = 2 * a, me00 = h0 * g.W + w0;
-      float x00, x01, x10, x11;
-      x00 = (m0l == me00 ? v0l : 0.f);                       // (2a, 2b): windows (a-1,b-1), (a-1,b), (a,b-1), (a,b)
-      x00 += (m0r == me00 ? v0r : 0.f);
-      x00 += (m1l == me00 ? v1l : 0.f);
-      x00 += (m1r == me00 ? v1r : 0.f);
-      x01 = (m0r == me00 + 1 ? v0r : 0.f);                   // (2a, 2b+1): windows (a-1,b), (a,b)
-      x01 += (m1r == me00 + 1 ? v1r : 0.f);
-      x10 = (m1l == me00 + g.W ? v1l : 0.f);                 // (2a+1, 2b): windows (a,b-1), (a,b)
-      x10 += (m1r == me00 + g.W ? v1r : 0.f);
-      x11 = (m1r == me00 + g.W + 1 ? v1r : 0.f);             // (2a+1, 2b+1): window (a,b)
-      // column c of a row sits in lane c >> 1, component c & 1: lane j stores columns j and G + j
-      const int src0 = b >> 1, src1 = (G >> 1) + (b >> 1);
-      const bool odd = b & 1;
+    // pooled rows are fetched kDepth steps ahead: a warp's walk down the plane is a chain of memory round trips, and one
+    // row of three 4-byte loads per lane per round trip leaves the memory system idle
+    constexpr int kDepth = 4;
+    int mq[kDepth + 1]; float vq[kDepth + 1];
+    load_row(0, mq[0], vq[0]);
+    for (int a0 = 0; a0 < A; a0 += kDepth) {
 #pragma unroll
-      for (int r = 0; r < 2; ++r) {
-        const float e = r ? x10 : x00, o = r ? x11 : x01;
-        const float lo_e = __shfl_sync(0xffffffffu, e, src0, G), lo_o = __shfl_sync(0xffffffffu, o, src0, G);
-        const float hi_e = __shfl_sync(0xffffffffu, e, src1, G), hi_o = __shfl_sync(0xffffffffu, o, src1, G);
-        const int h = h0 + r;
-        if (live && h < g.H) {
-          float* row = dp + h * g.W;
-          if (b < g.W) row[b] = odd ? lo_o : lo_e;
-          if (G + b < g.W) row[G + b] = odd ? hi_o : hi_e;
+      for (int k = 1; k <= kDepth; ++k) load_row(a0 + k, mq[k], vq[k]);
+#pragma unroll
+      for (int k = 0; k < kDepth; ++k) {
+        const int a = a0 + k;
+        if (a >= A) break;                                       // uniform across the warp
+        const int m1r = mq[k];
+        const float v1r = vq[k];
+        // window (a, b-1) lives in the lane to the left
+        int m1l = __shfl_up_sync(0xffffffffu, m1r, 1, G);
+        float v1l = __shfl_up_sync(0xffffffffu, v1r, 1, G);
+        if (b == 0) { m1l = -2; v1l = 0.f; }
+        const int h0 = 2 * a, me00 = h0 * g.W + w0;
+        float x00, x01, x10, x11;
+        x00 = (m0l == me00 ? v0l : 0.f);                       // (2a, 2b): windows (a-1,b-1), (a-1,b), (a,b-1), (a,b)
+        x00 += (m0r == me00 ? v0r : 0.f);
+        x00 += (m1l == me00 ? v1l : 0.f);
+        x00 += (m1r == me00 ? v1r : 0.f);
+        x01 = (m0r == me00 + 1 ? v0r : 0.f);                   // (2a, 2b+1): windows (a-1,b), (a,b)
+        x01 += (m1r == me00 + 1 ? v1r : 0.f);
+        x10 = (m1l == me00 + g.W ? v1l : 0.f);                 // (2a+1, 2b): windows (a,b-1), (a,b)
+        x10 += (m1r == me00 + g.W ? v1r : 0.f);
+        x11 = (m1r == me00 + g.W + 1 ? v1r : 0.f);             // (2a+1, 2b+1): window (a,b)
+        // column c of a row sits in lane c >> 1, component c & 1: lane j stores columns j and G + j
+        const int src0 = b >> 1, src1 = (G >> 1) + (b >> 1);
+        const bool odd = b & 1;
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          const float e = r ? x10 : x00, o = r ? x11 : x01;
+          const float lo_e = __shfl_sync(0xffffffffu, e, src0, G), lo_o = __shfl_sync(0xffffffffu, o, src0, G);
+          const float hi_e = __shfl_sync(0xffffffffu, e, src1, G), hi_o = __shfl_sync(0xffffffffu, o, src1, G);
+          const int h = h0 + r;
+          if (live && h < g.H) {
+            float* row = dp + h * g.W;
+            if (b < g.W) row[b] = odd ? lo_o : lo_e;
+            if (G + b < g.W) row[G + b] = odd ? hi_o : hi_e;
+          }
         }
+        m0l = m1l; m0r = m1r; v0l = v1l; v0r = v1r;
       }
-      m0l = m1l; m0r = m1r; v0l = v1l; v0r = v1r;
-      m1r = m2r; v1r = v2r;
+      mq[0] = mq[kDepth]; vq[0] = vq[kDepth];
     }
   }
 }
