@@ -208,13 +208,18 @@ def test_relu_backward_folded_into_convolution_backward_data(oracle, product, mo
     for wl in ("conva", "convb"):
         for a, b in zip(r["wdiff"][wl][1], u.weights(wl, True)):
             assert np.array_equal(a, b), wl
-    # against the oracle: in TF32 a pre-activation within rounding noise of zero may open a different gate than the
-    # oracle's fp32 forward did, which changes a neighbourhood of the gradient: a bounded fraction may disagree there
-    tol, bad = (1e-4, 5e-4) if precision == 0 else (3 * TOL, 0.2)         # small blobs (64 bias gradients): a few flips are a large fraction
-    assert_mostly_close(r["bwd"][1]["conva"], r["bwd"][0]["conva"], tol, "diff behind the ReLU", max_bad_frac=bad)
-    assert_mostly_close(r["bwd"][1]["data"], r["bwd"][0]["data"], tol, "bottom diff", max_bad_frac=bad)
-    for j, (a, b) in enumerate(zip(*r["wdiff"]["conva"])):
-        assert_mostly_close(b, a, tol, f"param diff {j}", max_bad_frac=bad)
+    # against the oracle.  fp32 FFMA mode: same gates, tight.  TF32: a pre-activation within rounding noise of zero may
+    # open a different gate than the oracle's fp32 forward did, and ONE flipped gate moves a bias-gradient sum of ~500
+    # random-sign terms by several percent, so only the relative L2 error is bounded there (bit-identity with the
+    # unfused product above is the strict check of the fusion itself).
+    pairs = [(r["bwd"][1]["conva"], r["bwd"][0]["conva"], "diff behind the ReLU"), (r["bwd"][1]["data"], r["bwd"][0]["data"], "bottom diff")]
+    pairs += [(b, a, f"param diff {j}") for j, (a, b) in enumerate(zip(*r["wdiff"]["conva"]))]
+    for got, want, what in pairs:
+        if precision == 0:
+            assert_mostly_close(got, want, 1e-4, what)
+        else:
+            l2 = float(np.linalg.norm(got.astype(np.float64) - want) / max(np.linalg.norm(want.astype(np.float64)), 1e-30))
+            assert l2 <= 5e-2, (what, l2)
 
 
 def test_weight_shadow_follows_host_writes_and_updates(oracle, product):
