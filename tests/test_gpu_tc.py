@@ -68,6 +68,7 @@ CPAD_CASES = [
 @pytest.mark.parametrize("shape,num_output,kw", CPAD_CASES)
 def test_convolution_channel_padded_first_layer_tf32(oracle, product, monkeypatch, shape, num_output, kw, cpad):
     monkeypatch.setenv("SPARKNET_CONV_CPAD", cpad)
+    oracle.oracle_seed(4243)
     x = np.random.default_rng(78).standard_normal(shape).astype(F)
     l = conv_layer("conv", "data", num_output, weight_filler=gaussian(0.05), bias_filler=gaussian(0.5), **kw)
     r = run_pair(oracle, product, {"data": x}, [l], "conv", "conv", precision=1)
@@ -192,6 +193,7 @@ def test_relu_backward_folded_into_convolution_backward_data(oracle, product, mo
               ReLULayer("relu", ["conva"]),
               conv_layer("convb", "conva", 32, kernel_size=[3], pad=[1], group=group, weight_filler=gaussian(0.1), bias_filler=gaussian(0.1))]
     monkeypatch.setenv("SPARKNET_FUSE_RELU_CONV", "1")
+    oracle.oracle_seed(4242)                            # the oracle draws the filters: same draw on every run
     r = run_pair(oracle, product, {"data": x}, layers, "convb", ["conva", "convb"], precision=precision)
     monkeypatch.setenv("SPARKNET_FUSE_RELU_CONV", "0")
     o, fused = r["nets"]
