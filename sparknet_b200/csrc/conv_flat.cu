@@ -749,8 +749,10 @@ void tcw_matmul(cudaStream_t s, int M, int N, int K, const float* A, const float
 // wgrad_reduce_kernel sums them in slice order into dW's (co, c, tap) layout: deterministic, no atomics.
 // ------------------------------------------------------------------------------------------
 struct WgArgs {
-  int Ptot_chunks;          // number of 32-row chunks of the reduction
+  int Ptot_chunks;          // number of R*32-row chunks of the reduction
   int chunks_per_split;
+  int R;                    // 32-row top-gradient tiles per pipeline stage: they share ONE input window of R*32 + span rows, so the
+                            // span rows (116 for AlexNet conv1's folded 3x3) cross the L2 -> SM path once per R tiles instead of per tile
   int Wp, kw, T;
   int nt, n_groups_t;       // taps per CTA, number of tap groups
   int m_tiles, n_tiles, n_mma, nblk;      // 128-row tiles of Og, channel tiles of Cg (n_mma wide, nblk = ceil(n_mma / 32) boxes)
@@ -781,7 +783,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
   const int nchunks = max(kc_end - kc_begin, 0);
 
   uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-  const uint32_t a_bytes = 4u * 4096u, blk_bytes = (uint32_t)a.KR * 128u, b_bytes = (uint32_t)a.nblk * blk_bytes;
+  const uint32_t a_bytes = (uint32_t)a.R * 4u * 4096u, blk_bytes = (uint32_t)a.KR * 128u, b_bytes = (uint32_t)a.nblk * blk_bytes;
   const uint32_t stage_bytes = a_bytes + b_bytes;                          // multiple of 1024 (KR % 8 == 0)
 
   if (tid == 0) {
@@ -852,11 +854,15 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
           const uint32_t a_addr = smem_u32(smem) + (uint32_t)s * stage_bytes, b_addr = a_addr + a_bytes;
           const uint32_t a_lo = (a_addr >> 4) | a_lo_flags, b_lo0 = (b_addr >> 4) | b_lo_flags;
 #pragma unroll 1
-          for (int k = 0; k < mine; ++k) {
-            const uint32_t b_lo = b_lo0 + shift8[k];
-            const uint32_t d = tmem_base + (uint32_t)((mi + k * issuers) * a.n_mma);
+          for (int r = 0; r < a.R; ++r) {                          // tile r: top-gradient rows 32r.., window rows 32r + shift..
+            const uint32_t a_lo_r = a_lo + (uint32_t)r * (16384u >> 4), b_lo_r = b_lo0 + (uint32_t)r * 32u * 8u;
+#pragma unroll 1
+            for (int k = 0; k < mine; ++k) {
+              const uint32_t b_lo = b_lo_r + shift8[k];
+              const uint32_t d = tmem_base + (uint32_t)((mi + k * issuers) * a.n_mma);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) mma_tf32_lohi(d, a_lo + 64u * j, b_lo + 64u * j, a_hi, idesc, (kc | j) != 0 ? 1u : 0u);
+              for (int j = 0; j < 4; ++j) mma_tf32_lohi(d, a_lo_r + 64u * j, b_lo + 64u * j, a_hi, idesc, (kc | r | j) != 0 ? 1u : 0u);
+            }
           }
           mma_commit(&empty[s]);
           if (kc == nchunks - 1) mma_commit(&tmem_full);
@@ -872,12 +878,13 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
       uint32_t phase = 0;
       const int a_chan = grp * a.Og + m0, b_chan = grp * a.Cg + n0;
       for (int kc = 0; kc < nchunks; ++kc) {
-        const int q0 = (kc_begin + kc) * 32;
+        const int q0 = (kc_begin + kc) * 32 * a.R;
         mbar_wait(&empty[s], phase ^ 1u);
         uint8_t* a_tile = smem + (size_t)s * stage_bytes;
         uint8_t* b_tile = a_tile + a_bytes;
         mbar_arrive_expect_tx(&full[s], stage_bytes);
-        for (int i = 0; i < 4; ++i) tma_load_2d(a_tile + i * 4096, &tmDY, &full[s], a_chan + 32 * i, a.lead + q0);
+        for (int r = 0; r < a.R; ++r)
+          for (int i = 0; i < 4; ++i) tma_load_2d(a_tile + r * 16384 + i * 4096, &tmDY, &full[s], a_chan + 32 * i, a.lead + q0 + 32 * r);
         for (int j = 0; j < a.nblk; ++j)
           tma_load_2d(b_tile + (size_t)j * blk_bytes, &tmX, &full[s], b_chan + 32 * j, a.lead + q0 + sh0 - a.pad_off);
         if (++s == a.nstage) { s = 0; phase ^= 1u; }
@@ -903,7 +910,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, si
   }
 }
 
-struct WgPlan { int n_mma, nt, KR, nstage, splits, chunks_per_split; size_t smem; bool ok; };
+struct WgPlan { int n_mma, nt, KR, nstage, splits, chunks_per_split; size_t smem; bool ok; int R; };
 static int span_of_taps(int t0, int nt, int kw, int Wp) {
   const int t1 = t0 + nt - 1;
   return (t1 / kw) * Wp + t1 % kw - ((t0 / kw) * Wp + t0 % kw);
@@ -932,27 +939,35 @@ static WgPlan plan_wgrad_impl(int Ptot, int Og, int Cg, int groups, int T, int k
     const int n_groups_t = (T + nt_max - 1) / nt_max, nt = (T + n_groups_t - 1) / n_groups_t;
     int span = 0;
     for (int t0 = 0; t0 < T; t0 += nt) { const int sp = span_of_taps(t0, nt < T - t0 ? nt : T - t0, kw, Wp); if (sp > span) span = sp; }
-    const int KR = (32 + span + 7) / 8 * 8;
-    if (KR > 256) continue;
-    const int nblk = (n_mma + 31) / 32;
-    const size_t stage = 16384 + (size_t)nblk * KR * 128;
-    if (3 * stage + 2048 > kWSmemLimit) continue;
-    int nstage = (int)((kWSmemLimit - 2048) / stage);
-    if (nstage > kWMaxStages) nstage = kWMaxStages;
-    const long long tiles = (long long)m_tiles * n_tiles * n_groups_t * groups;
-    int splits = (int)(148 / tiles);
-    if (splits < 1) splits = 1;
-    if (splits > chunks / 8) splits = chunks / 8 > 0 ? chunks / 8 : 1;
-    const int cps = (chunks + splits - 1) / splits;
-    splits = (chunks + cps - 1) / cps;
-    const long long waves = (tiles * splits + 147) / 148;
-    const double mma_clk = nt * 4.0 * (n_mma / 2.0 > 44.0 ? n_mma / 2.0 : 44.0);
-    const double l2_clk = (double)stage / 25.0;
-    const double per_chunk = mma_clk > l2_clk ? mma_clk : l2_clk;
-    const double cost = (double)waves * (cps * per_chunk + 128.0 * nt * n_mma * 4 / 30.0 + 5000.0);
-    if (!best.ok || cost < best_cost) {
-      best = WgPlan{n_mma, nt, KR, nstage, splits, cps, (size_t)nstage * stage + 1024, true};
-      best_cost = cost;
+    static const int forced_R = getenv("SPARKNET_WGRAD_R") ? atoi(getenv("SPARKNET_WGRAD_R")) : 0;
+    for (int R = 1; R <= 4; R *= 2) {                                  // top-gradient tiles per stage (they share one input window)
+      if (forced_R && R != forced_R) continue;
+      if (R > 1 && span == 0) break;                                   // nothing to share (one tap, inner products)
+      const int KR = (32 * R + span + 7) / 8 * 8;
+      if (KR > 256) continue;
+      const int nblk = (n_mma + 31) / 32;
+      const size_t stage = (size_t)R * 16384 + (size_t)nblk * KR * 128;
+      if ((R == 1 ? 3 : 2) * stage + 2048 > kWSmemLimit) continue;
+      int nstage = (int)((kWSmemLimit - 2048) / stage);
+      if (nstage > kWMaxStages) nstage = kWMaxStages;
+      const int chunksR = (chunks + R - 1) / R;                        // chunks of R * 32 rows
+      const long long tiles = (long long)m_tiles * n_tiles * n_groups_t * groups;
+      int splits = (int)(148 / tiles);
+      if (splits < 1) splits = 1;
+      const int min_cps = 8 / R > 1 ? 8 / R : 1;
+      if (splits > chunksR / min_cps) splits = chunksR / min_cps > 0 ? chunksR / min_cps : 1;
+      const int cps = (chunksR + splits - 1) / splits;
+      splits = (chunksR + cps - 1) / cps;
+      const long long waves = (tiles * splits + 147) / 148;
+      const double mma_clk = R * nt * 4.0 * (n_mma / 2.0 > 44.0 ? n_mma / 2.0 : 44.0);
+      const double l2_clk = (double)stage / 25.0;
+      double per_chunk = mma_clk > l2_clk ? mma_clk : l2_clk;
+      if (nstage < 3) per_chunk *= 1.1;                                // two buffers hide less of the load latency
+      const double cost = (double)waves * (cps * per_chunk + 128.0 * nt * n_mma * 4 / 30.0 + 5000.0);
+      if (!best.ok || cost < best_cost) {
+        best = WgPlan{n_mma, nt, KR, nstage, splits, cps, (size_t)nstage * stage + 1024, true, R};
+        best_cost = cost;
+      }
     }
   }
   return best;
@@ -975,7 +990,8 @@ static void wgrad_core(cudaStream_t s, const float* xflat, int x_chan, const flo
     attr_done = true;
   }
   WgArgs a;
-  a.Ptot_chunks = (Ptot + 31) / 32;
+  a.R = pl.R;
+  a.Ptot_chunks = ((Ptot + 31) / 32 + pl.R - 1) / pl.R;
   a.chunks_per_split = pl.chunks_per_split;
   a.Wp = Wp; a.kw = kw; a.T = T;
   a.nt = pl.nt; a.n_groups_t = (T + pl.nt - 1) / pl.nt;
@@ -991,6 +1007,10 @@ static void wgrad_core(cudaStream_t s, const float* xflat, int x_chan, const flo
   const CUtensorMap tmDY = tc_make_tmap(dyflat, (uint64_t)dy_chan, rows_total, (uint64_t)dy_chan * 4, 32, true);
   const CUtensorMap tmX = tc_make_tmap(xflat, (uint64_t)x_chan, rows_total, (uint64_t)x_chan * 4, (uint32_t)pl.KR, true);
   dim3 grid(a.m_tiles * a.n_tiles * a.n_groups_t * groups, pl.splits, 1);
+  static const bool plan_debug = getenv("SPARKNET_PLAN_DEBUG") != nullptr;
+  if (plan_debug)
+    fprintf(stderr, "wgrad plan: rows %d Og %d Cg %d T %d -> n_mma %d taps/CTA %d tiles/stage %d window rows %d stages %d splits %d grid %u x %u\n", Ptot, Og,
+            Cg, T, pl.n_mma, pl.nt, pl.R, pl.KR, pl.nstage, pl.splits, grid.x, grid.y);
   wgrad_window_kernel<<<grid, kWThreads, pl.smem, s>>>(tmDY, tmX, a);
   count_launch();
   if (!direct) {
