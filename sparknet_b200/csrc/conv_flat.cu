@@ -963,6 +963,8 @@ static WgPlan plan_wgrad_impl(int Ptot, int Og, int Cg, int groups, int T, int k
       const double l2_clk = (double)stage / 25.0;
       double per_chunk = mma_clk > l2_clk ? mma_clk : l2_clk;
       if (nstage < 3) per_chunk *= 1.1;                                // two buffers hide less of the load latency
+      if (R > 1 && span >= 32) per_chunk *= 0.95;                      // measured (AlexNet conv2, span 56-66): the shared window pays
+                                                                       // 20 us even where this model calls the chunk MMA-bound
       const double cost = (double)waves * (cps * per_chunk + 128.0 * nt * n_mma * 4 / 30.0 + 5000.0);
       if (!best.ok || cost < best_cost) {
         best = WgPlan{n_mma, nt, KR, nstage, splits, cps, (size_t)nstage * stage + 1024, true, R};
