@@ -101,9 +101,9 @@ __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, i
 
 // Number of reduction slices: as many CTAs as fit in two waves of 148 SMs (never a partial third wave),
 // each slice >= 512 long.
-int splitk_slices(int tiles, int R) {
+int splitk_slices(int tiles, int R, int ctas_per_sm) {
   if (tiles >= 148 || R < 2048) return 1;
-  int want = (2 * 148) / tiles;
+  int want = (ctas_per_sm * 148) / tiles;
   int maxs = R / 512;
   int s = want < maxs ? want : maxs;
   return s < 1 ? 1 : s;

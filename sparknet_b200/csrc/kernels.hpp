@@ -27,7 +27,7 @@ void ffma_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* x, const fl
 void ffma_ip_fwd(cudaStream_t s, int batch, int out, int K, const float* x, const float* w, const float* bias, float* y, bool relu);
 void ffma_ip_dgrad(cudaStream_t s, int batch, int out, int K, const float* dy, const float* w, float* dx);
 void ffma_ip_wgrad(cudaStream_t s, int batch, int out, int K, const float* x, const float* dy, float* dw, bool accumulate);
-int splitk_slices(int tiles, int R);
+int splitk_slices(int tiles, int R, int ctas_per_sm = 2);   // slices of the reduction so that tiles * slices fills the GPU
 
 // ---- TF32 tcgen05 contractions (gemm_tc.cu) --------------------------------------------------
 bool tc_available();
