@@ -817,7 +817,9 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
                       int M, int N, int R, int n_mma) {
   typedef TcCfg<BN> Cfg;
   dim3 grid((M + TBM - 1) / TBM, (N + n_mma - 1) / n_mma, 1);
-  static const int split_waves = getenv("SPARKNET_TC_SPLIT_WAVES") ? atoi(getenv("SPARKNET_TC_SPLIT_WAVES")) : 2;
+  // one CTA of this kernel per SM: 148 slices are one wave (cifar conv1 backward-filter, 102400 reduction rows: 200 slices ran
+  // as 148 + 52, 72.7 -> 58.4 us with 148)
+  static const int split_waves = getenv("SPARKNET_TC_SPLIT_WAVES") ? atoi(getenv("SPARKNET_TC_SPLIT_WAVES")) : 1;
   const int splits = splitk_slices((int)(grid.x * grid.y), R, split_waves);
   static size_t attr_done_split = 0, attr_done = 0;          // largest dynamic smem size opted in so far
   constexpr size_t kMaxSmem = 227 * 1024;
@@ -980,11 +982,8 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
 // and walks its pixels; with BIAS it also sums every value it reads per channel (the bias gradient of this image,
 // conv_layer.cpp:52-55: gemv against the all-ones multiplier) into part[c][n], which bias_grad_final_kernel adds up
 // in image order.  The top gradient is therefore read from HBM once for both purposes.
-#ifndef SN_FLAT_PACK_MIN_BLOCKS
-#define SN_FLAT_PACK_MIN_BLOCKS 6     // <= 40 registers: six blocks (1536 threads) per SM instead of four
-#endif
 template <bool BIAS>
-__global__ void __launch_bounds__(256, SN_FLAT_PACK_MIN_BLOCKS) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
+__global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
                                                          int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span, int Csrc) {
   // Csrc <= C: the source tensor has Csrc channels, the packed rows C (the rest are written as zeros: channel padding of
   // first layers with fewer than 16 input channels)
