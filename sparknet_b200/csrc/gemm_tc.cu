@@ -1322,7 +1322,7 @@ static int launch_static_bn(cudaStream_t s, AL al, BL bl, int M, int N, int R, i
   TEpiRowMajor ep{D, N, M, N, 0};
   EpiRowMajor re{D, N, M, N, 0};
   dim3 grid((M + TBM - 1) / TBM, (N + n_mma - 1) / n_mma, 1);
-  const int splits = splitk_slices((int)(grid.x * grid.y), R);
+  const int splits = splitk_slices((int)(grid.x * grid.y), R, 1);   // as launch_bn: one CTA per SM, one wave
   cudaError_t e;
   if (splits == 1) {                                    // no scratch needed at all
     auto kfn = gemm_tc_kernel<AL, BL, TEpiRowMajor, BN, false>;
