@@ -751,6 +751,7 @@ void tcw_matmul(cudaStream_t s, int M, int N, int K, const float* A, const float
 struct WgArgs {
   int Ptot_chunks;          // number of R*32-row chunks of the reduction
   int chunks_per_split;
+  int tmem_cols;            // TMEM columns to allocate: nt * n_mma rounded up to a power of two (>= 32)
   int R;                    // 32-row top-gradient tiles per pipeline stage: they share ONE input window of R*32 + span rows, so the
                             // span rows (116 for AlexNet conv1's folded 3x3) cross the L2 -> SM path once per R tiles instead of per tile
   int Wp, kw, T;
@@ -794,7 +795,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
     tma_prefetch_desc(&tmDY);
     tma_prefetch_desc(&tmX);
   }
-  if (warp == kWEpiWarps) tmem_alloc<512>(&tmem_base_smem);
+  if (warp == kWEpiWarps) tmem_alloc_cols(&tmem_base_smem, (uint32_t)a.tmem_cols);
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
@@ -893,7 +894,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
   }
   tc_fence_before_sync();
   __syncthreads();
-  if (warp == kWEpiWarps) tmem_dealloc<512>(tmem_base);
+  if (warp == kWEpiWarps) tmem_dealloc_cols(tmem_base, (uint32_t)a.tmem_cols);
 }
 
 // dw[(co, c, tap)] (+)= sum over slices of ws[slice][(co, tap, c)], slices in ascending order
@@ -1002,6 +1003,20 @@ static void wgrad_core(cudaStream_t s, const float* xflat, int x_chan, const flo
   a.Og = Og; a.Cg = Cg;
   a.lead = lead; a.pad_off = pad_off;
   a.KR = pl.KR; a.nstage = pl.nstage;
+  a.tmem_cols = 32;
+  while (a.tmem_cols < pl.nt * pl.n_mma) a.tmem_cols *= 2;
+  size_t smem_bytes = pl.smem;
+  {
+    // Short reductions (inner products: 8 chunks per CTA) are dominated by each CTA's prologue and epilogue, not by its
+    // main loop: two stages and half of the TMEM let TWO CTAs share an SM, one loading while the other drains.
+    static const int allow2 = getenv("SPARKNET_WGRAD_2CTA") ? atoi(getenv("SPARKNET_WGRAD_2CTA")) : 1;
+    const size_t stage = (pl.smem - 1024) / (size_t)pl.nstage;
+    if (allow2 && pl.chunks_per_split <= 16 && a.tmem_cols <= 256 && 2 * stage + 1024 <= 110 * 1024) {
+      a.nstage = (int)((110 * 1024 - 1024) / stage);
+      if (a.nstage > pl.nstage) a.nstage = pl.nstage;
+      smem_bytes = (size_t)a.nstage * stage + 1024;
+    }
+  }
   a.split_stride = (size_t)Og * groups * T * Cg;
   // one tap, one slice, plain store: the slice layout [co][tap][c] IS dW, so the kernel writes it directly
   const bool direct = T == 1 && pl.splits == 1 && !accumulate;
@@ -1013,7 +1028,7 @@ static void wgrad_core(cudaStream_t s, const float* xflat, int x_chan, const flo
   if (plan_debug)
     fprintf(stderr, "wgrad plan: rows %d Og %d Cg %d T %d -> n_mma %d taps/CTA %d tiles/stage %d window rows %d stages %d splits %d grid %u x %u\n", Ptot, Og,
             Cg, T, pl.n_mma, pl.nt, pl.R, pl.KR, pl.nstage, pl.splits, grid.x, grid.y);
-  wgrad_window_kernel<<<grid, kWThreads, pl.smem, s>>>(tmDY, tmX, a);
+  wgrad_window_kernel<<<grid, kWThreads, smem_bytes, s>>>(tmDY, tmX, a);
   count_launch();
   if (!direct) {
     int blocks = (int)((a.split_stride + 255) / 256);
