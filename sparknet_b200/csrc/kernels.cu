@@ -719,8 +719,12 @@ __device__ __forceinline__ float lrn_pow_neg(float sc, float beta, bool is075, f
   if (inv_sc) *inv_sc = __fdividef(1.f, sc);
   return __powf(sc, -beta);
 }
-constexpr int kLrnCH = 16;
-template <int SIZE>
+// channels per thread: 16 by default (SPARKNET_LRN_CH = 8 / 16 / 32 selects another instantiation)
+static int lrn_chunk() {
+  static const int ch = getenv("SPARKNET_LRN_CH") ? atoi(getenv("SPARKNET_LRN_CH")) : 16;
+  return ch == 8 || ch == 32 ? ch : 16;
+}
+template <int SIZE, int CH>
 __global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x, float* __restrict__ y) {
   constexpr int PRE = (SIZE - 1) / 2;
   const int HW = g.H * g.W;
@@ -730,17 +734,17 @@ __global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, in
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int pix = (int)(idx % HW);
     const int ck = (int)((idx / HW) % chunks), n = (int)(idx / ((size_t)HW * chunks));
-    const int c0 = ck * kLrnCH;
+    const int c0 = ck * CH;
     const float* xp = x + ((size_t)n * g.C) * HW + pix;
-    float v[kLrnCH + 2 * PRE];
+    float v[CH + 2 * PRE];
 #pragma unroll
-    for (int j = 0; j < kLrnCH + 2 * PRE; ++j) {
+    for (int j = 0; j < CH + 2 * PRE; ++j) {
       const int c = c0 - PRE + j;
       v[j] = (c >= 0 && c < g.C) ? xp[(size_t)c * HW] : 0.f;
     }
     float* yp = y + ((size_t)n * g.C) * HW + pix;
 #pragma unroll
-    for (int j = 0; j < kLrnCH; ++j) {
+    for (int j = 0; j < CH; ++j) {
       if (c0 + j < g.C) {
         float acc = 0.f;
 #pragma unroll
@@ -753,10 +757,12 @@ __global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, in
 }
 void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, float* scale) {
   if (g.size == 5 || g.size == 3) {
-    const int chunks = (g.C + kLrnCH - 1) / kLrnCH;
+    const int CHn = lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
     const size_t total = (size_t)g.N * chunks * g.H * g.W;
-    if (g.size == 5) lrn_across_fwd_chunk_kernel<5><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y);
-    else lrn_across_fwd_chunk_kernel<3><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y);
+#define SN_LRN_F(SZ, CHV) lrn_across_fwd_chunk_kernel<SZ, CHV><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y)
+    if (g.size == 5) { if (CHn == 8) SN_LRN_F(5, 8); else if (CHn == 32) SN_LRN_F(5, 32); else SN_LRN_F(5, 16); }
+    else { if (CHn == 8) SN_LRN_F(3, 8); else if (CHn == 32) SN_LRN_F(3, 32); else SN_LRN_F(3, 16); }
+#undef SN_LRN_F
     count_launch();
     return;
   }
@@ -796,7 +802,7 @@ __global__ void lrn_across_bwd_kernel(LrnGeom g, int nthreads, const float* __re
 // Chunked backward (local_size 3 or 5), reference LRNComputeDiff (lrn_layer.cu:122-177) / CrossChannelBackward_cpu
 // (lrn_layer.cpp:180-232):   dx_c = dy_c * scale_c^-beta - (2 alpha beta / n) * x_c * sum_{|j-c| <= pre} dy_j * y_j / scale_j
 // with scale and y recomputed from x (halo 2*pre).  Reads x and dy, writes dx: 12 B per element.
-template <int SIZE>
+template <int SIZE, int CH>
 __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x,
                                                                    const float* __restrict__ dy, float* __restrict__ dx) {
   constexpr int PRE = (SIZE - 1) / 2;
@@ -808,21 +814,21 @@ __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, in
   for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
     const int pix = (int)(idx % HW);
     const int ck = (int)((idx / HW) % chunks), n = (int)(idx / ((size_t)HW * chunks));
-    const int c0 = ck * kLrnCH;
+    const int c0 = ck * CH;
     const size_t base = ((size_t)n * g.C) * HW + pix;
-    float v[kLrnCH + 4 * PRE], r[kLrnCH + 2 * PRE], p[kLrnCH + 2 * PRE];
+    float v[CH + 4 * PRE], r[CH + 2 * PRE], p[CH + 2 * PRE];
 #pragma unroll
-    for (int j = 0; j < kLrnCH + 4 * PRE; ++j) {
+    for (int j = 0; j < CH + 4 * PRE; ++j) {
       const int c = c0 - 2 * PRE + j;
       v[j] = (c >= 0 && c < g.C) ? x[base + (size_t)c * HW] : 0.f;
     }
 #pragma unroll
-    for (int j = 0; j < kLrnCH + 2 * PRE; ++j) {
+    for (int j = 0; j < CH + 2 * PRE; ++j) {
       const int c = c0 - PRE + j;
       r[j] = (c >= 0 && c < g.C) ? dy[base + (size_t)c * HW] : 0.f;          // r holds dy for now
     }
 #pragma unroll
-    for (int j = 0; j < kLrnCH + 2 * PRE; ++j) {                             // channel c0 - PRE + j
+    for (int j = 0; j < CH + 2 * PRE; ++j) {                             // channel c0 - PRE + j
       float acc = 0.f;
 #pragma unroll
       for (int t = 0; t < SIZE; ++t) acc += v[j + t] * v[j + t];
@@ -833,7 +839,7 @@ __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, in
       r[j] = r[j] * (v[j + PRE] * pw) * inv;                                  // dy * y / scale; the raw dy is re-read below
     }
 #pragma unroll
-    for (int j = 0; j < kLrnCH; ++j) {
+    for (int j = 0; j < CH; ++j) {
       const int c = c0 + j;
       if (c < g.C) {
         float acc = 0.f;
@@ -848,10 +854,12 @@ __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, in
 void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* y, const float* scale,
                     const float* dy, float* dx) {
   if (g.size == 5 || g.size == 3) {
-    const int chunks = (g.C + kLrnCH - 1) / kLrnCH;
+    const int CHn = lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
     const size_t total = (size_t)g.N * chunks * g.H * g.W;
-    if (g.size == 5) lrn_across_bwd_chunk_kernel<5><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, dy, dx);
-    else lrn_across_bwd_chunk_kernel<3><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, dy, dx);
+#define SN_LRN_B(SZ, CHV) lrn_across_bwd_chunk_kernel<SZ, CHV><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, dy, dx)
+    if (g.size == 5) { if (CHn == 8) SN_LRN_B(5, 8); else if (CHn == 32) SN_LRN_B(5, 32); else SN_LRN_B(5, 16); }
+    else { if (CHn == 8) SN_LRN_B(3, 8); else if (CHn == 32) SN_LRN_B(3, 32); else SN_LRN_B(3, 16); }
+#undef SN_LRN_B
     count_launch();
     return;
   }
