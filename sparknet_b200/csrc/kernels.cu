@@ -482,7 +482,7 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_strip_kernel(PoolGeom 
 // element (mask, dy, gate of window (a, b)) — the left neighbour's comes by shuffle, the row above stays in registers —
 // and the two finished input rows leave through shuffles so that every store instruction writes a contiguous run of the
 // row (the block and strip forms write every other float per instruction).  Same windows, same order of additions.
-template <int G>
+template <int G, int DEPTH>
 __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g, uint32_t planes, int A, const float* __restrict__ dy,
                                                                      const int* __restrict__ mask, const float* __restrict__ gate,
                                                                      float* __restrict__ dx) {
@@ -509,21 +509,20 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g,
         if (tp && !(__ldg(tp + o) > 0.f)) vr = 0.f;
       }
     };
-    // pooled rows are fetched kDepth steps ahead.  Measured on B200 (CaffeNet pool1 / pool2 / pool5 backward): depth 1
-    // 131 / 88 / 24.5 us, depth 4 162 / 98 / 26.7 us (64 registers instead of 44 cost more occupancy than the deeper
-    // prefetch wins), so one step ahead it is.
-    constexpr int kDepth = 1;
-    int mq[kDepth + 1]; float vq[kDepth + 1];
-    load_row(0, mq[0], vq[0]);
-    for (int a0 = 0; a0 < A; a0 += kDepth) {
+    // pooled rows are fetched kDepth steps ahead through a rotating set of registers: slot k holds row a0 + k and is
+    // refilled with row a0 + k + kDepth as soon as step a0 + k has read it
+    constexpr int kDepth = DEPTH;
+    int mq[kDepth]; float vq[kDepth];
 #pragma unroll
-      for (int k = 1; k <= kDepth; ++k) load_row(a0 + k, mq[k], vq[k]);
+    for (int k = 0; k < kDepth; ++k) load_row(k, mq[k], vq[k]);
+    for (int a0 = 0; a0 < A; a0 += kDepth) {
 #pragma unroll
       for (int k = 0; k < kDepth; ++k) {
         const int a = a0 + k;
         if (a >= A) break;                                       // uniform across the warp
         const int m1r = mq[k];
         const float v1r = vq[k];
+        load_row(a + kDepth, mq[k], vq[k]);
         // window (a, b-1) lives in the lane to the left
         int m1l = __shfl_up_sync(0xffffffffu, m1r, 1, G);
         float v1l = __shfl_up_sync(0xffffffffu, v1r, 1, G);
@@ -556,7 +555,6 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g,
         }
         m0l = m1l; m0r = m1r; v0l = v1l; v0r = v1r;
       }
-      mq[0] = mq[kDepth]; vq[0] = vq[kDepth];
     }
   }
 }
@@ -576,9 +574,14 @@ void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int*
     const uint32_t planes = (uint32_t)(g.N * g.C);
     if ((strip_mode == 3 || (strip_mode == 1 && strips >= (size_t)148 * 2048)) && B <= 32) {
       // large layers: the row form (coalesced stores, one load per window)
-      if (B > 16) pool_max_bwd_3x3s2_row_kernel<32><<<grid_for((size_t)planes * 32, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx);
-      else if (B > 8) pool_max_bwd_3x3s2_row_kernel<16><<<grid_for((size_t)planes * 16, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx);
-      else pool_max_bwd_3x3s2_row_kernel<8><<<grid_for((size_t)planes * 8, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx);
+      static const int depth = getenv("SPARKNET_POOL_DEPTH") ? atoi(getenv("SPARKNET_POOL_DEPTH")) : 1;
+#define SN_POOL_ROW(GV, DV) pool_max_bwd_3x3s2_row_kernel<GV, DV><<<grid_for((size_t)planes * GV, 256, 32), 256, 0, s>>>(g, planes, A, dy, mask, gate, dx)
+#define SN_POOL_ROW_D(GV) do { if (depth == 2) SN_POOL_ROW(GV, 2); else if (depth == 3) SN_POOL_ROW(GV, 3); else SN_POOL_ROW(GV, 1); } while (0)
+      if (B > 16) SN_POOL_ROW_D(32);
+      else if (B > 8) SN_POOL_ROW_D(16);
+      else SN_POOL_ROW_D(8);
+#undef SN_POOL_ROW_D
+#undef SN_POOL_ROW
     } else if (strip_mode == 2 || (strip_mode == 1 && strips >= (size_t)148 * 2048))   // the strip form: half the instructions per element
       pool_max_bwd_3x3s2_strip_kernel<<<grid_for(strips, 256, 32), 256, 0, s>>>(g, (uint32_t)strips, FastDiv((uint32_t)B), A, dy, mask, gate, dx);
     else
