@@ -510,7 +510,9 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g,
       }
     };
     // pooled rows are fetched kDepth steps ahead through a rotating set of registers: slot k holds row a0 + k and is
-    // refilled with row a0 + k + kDepth as soon as step a0 + k has read it
+    // refilled with row a0 + k + kDepth as soon as step a0 + k has read it.  Measured on B200 (CaffeNet pool1 / pool2 /
+    // pool5 backward): depth 1 132 / 88 / 25 us, depth 2 154 / 91 / 27 us, depth 3 168 / 101 / 28 us — the kernel is not
+    // waiting on memory latency, the extra registers only cost occupancy; depth 1 is the default (SPARKNET_POOL_DEPTH).
     constexpr int kDepth = DEPTH;
     int mq[kDepth]; float vq[kDepth];
 #pragma unroll
