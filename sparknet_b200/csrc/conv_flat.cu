@@ -1204,7 +1204,7 @@ void tcw_filter_pack_batch(cudaStream_t st, const FilterPackBatch& b) {
   size_t most = 0;
   for (int i = 0; i < b.n; ++i) most = std::max(most, b.job[i].total);
   int blocks = (int)((most + 255) / 256);
-  const int cap = std::max(148 * 4 / b.n, 32);
+  const int cap = std::max(148 * 16 / b.n, 32);       // ~2400 blocks in all: the largest copy (conv3 backward-data, 0.9 M floats) gets ~4 elements per thread
   if (blocks > cap) blocks = cap;
   filter_pack_batch_kernel<<<dim3(blocks, b.n), 256, 0, st>>>(b);
   count_launch();
