@@ -1108,7 +1108,18 @@ __global__ void __launch_bounds__(256) ip_round_bias_kernel(int rows, int cols4,
   const int cx = threadIdx.x & 31, rg = threadIdx.x >> 5, c4 = blockIdx.x * 32 + cx;
   float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
   if (c4 < cols4) {
-    for (int r = rg; r < rows; r += 8) {
+    int r = rg;
+    for (; r + 24 < rows; r += 32) {                  // four rows in flight per thread: the walk is a chain of memory round trips
+      float4 v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = dy[(size_t)(r + 8 * k) * cols4 + c4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        acc.x += v[k].x; acc.y += v[k].y; acc.z += v[k].z; acc.w += v[k].w;
+        dy_r[(size_t)(r + 8 * k) * cols4 + c4] = make_float4(round_tf32_rna(v[k].x), round_tf32_rna(v[k].y), round_tf32_rna(v[k].z), round_tf32_rna(v[k].w));
+      }
+    }
+    for (; r < rows; r += 8) {
       const float4 v = dy[(size_t)r * cols4 + c4];
       acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
       dy_r[(size_t)r * cols4 + c4] = make_float4(round_tf32_rna(v.x), round_tf32_rna(v.y), round_tf32_rna(v.z), round_tf32_rna(v.w));
