@@ -911,6 +911,33 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, si
   }
 }
 
+// Many slices over a small filter (conv1: 147 slices x 41 k elements): one thread per element would walk `splits`
+// dependent round trips.  Eight lanes share an element: lane j sums slices j, j + 8, ... in ascending order, then the eight
+// partial sums meet in a fixed butterfly (same order on every run).
+__global__ void wgrad_reduce_wide_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
+                                         int accumulate) {
+  const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+  const size_t i = t >> 3;
+  const int j = (int)(t & 7);
+  float acc = 0.f;
+  if (i < split_stride) {
+    float a0 = 0.f, a1 = 0.f;
+    int z = j;
+    for (; z + 8 < splits; z += 16) { a0 += ws[(size_t)z * split_stride + i]; a1 += ws[(size_t)(z + 8) * split_stride + i]; }
+    if (z < splits) a0 += ws[(size_t)z * split_stride + i];
+    acc = a0 + a1;
+  }
+  acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+  acc += __shfl_xor_sync(0xffffffffu, acc, 4);
+  if (i < split_stride && j == 0) {
+    const size_t co = i / ((size_t)T * Cg);
+    const int rem = (int)(i - co * (size_t)T * Cg), tap = rem / Cg, c = rem - tap * Cg;
+    float* p = dw + (co * Cg + c) * T + tap;
+    *p = accumulate ? *p + acc : acc;
+  }
+}
+
 struct WgPlan { int n_mma, nt, KR, nstage, splits, chunks_per_split; size_t smem; bool ok; int R; };
 static int span_of_taps(int t0, int nt, int kw, int Wp) {
   const int t1 = t0 + nt - 1;
@@ -1033,7 +1060,10 @@ static void wgrad_core(cudaStream_t s, const float* xflat, int x_chan, const flo
   if (!direct) {
     int blocks = (int)((a.split_stride + 255) / 256);
     if (blocks > 148 * 8) blocks = 148 * 8;
-    wgrad_reduce_kernel<<<blocks, 256, 0, s>>>(a.ws, pl.splits, a.split_stride, T, Cg, dw, accumulate ? 1 : 0);
+    if (pl.splits >= 32 && a.split_stride * 8 <= (size_t)148 * 8 * 256)
+      wgrad_reduce_wide_kernel<<<(int)((a.split_stride * 8 + 255) / 256), 256, 0, s>>>(a.ws, pl.splits, a.split_stride, T, Cg, dw, accumulate ? 1 : 0);
+    else
+      wgrad_reduce_kernel<<<blocks, 256, 0, s>>>(a.ws, pl.splits, a.split_stride, T, Cg, dw, accumulate ? 1 : 0);
     count_launch();
   }
   SN_CUDA(cudaGetLastError());
