@@ -31,7 +31,7 @@ def test_non_zero_ranks_of_the_reference_arm_exit_quietly():
 def test_committed_bench_line_carries_the_contract_keys_and_feeds_the_roofline_table():
     """The last GPU bench line committed under profiles/ has every key the driver reads, and tools/roofline_table.py
     turns its per-layer event times into the per-layer roofline table (fractions of the peaks the line itself names)."""
-    path = os.path.join(ROOT, "profiles", "r1_bench_caffenet_tf32_v32.json")
+    path = os.path.join(ROOT, "profiles", "r1_bench_caffenet_tf32_v33.json")
     d = json.loads(open(path).read().strip().splitlines()[-1])
     for k in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling", "vs_baseline",
               "dtype", "data", "config", "e2e", "gpu_launches", "clocks", "roofline", "cpu_baseline"):
