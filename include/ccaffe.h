@@ -117,6 +117,9 @@ int sparknet_snapshot(caffenet_state* state, const char* model_filename, const c
 /* memcpy on `threads` host threads, for data callbacks that fill the library's pinned staging buffer (no reference
  * counterpart: the JVM callback of Net.scala:194-221 copies element by element). */
 void sparknet_host_copy(void* dst, const void* src, long bytes, int threads);
+/* n bytes -> n floats on `threads` host threads (signed Java bytes or 0..255): the widening the reference's callback
+ * does per image (src/main/java/libs/ByteImage.java:86-104), for fp32 callbacks whose pixels are held as bytes. */
+void sparknet_host_widen(void* dst, const void* src, long n, int is_signed, int threads);
 /* Make Dropout layer `layer_idx` of the train net use `mask` (count values, 0 = drop, non-zero = keep)
  * instead of drawing one; NULL restores drawing.  0 ok, -1 bad index, -2 not Dropout, -3 bad count. */
 int sparknet_inject_dropout_mask(caffenet_state* state, int layer_idx, const unsigned* mask, int count);
@@ -135,6 +138,33 @@ int sparknet_get_pool_mask(caffenet_state* state, int layer_idx, int* out, long 
 int sparknet_set_resident_inputs(caffenet_state* state, int n);
 /* Number of kernels launched by this process so far. */
 long sparknet_kernel_launches(caffenet_state* state);
+/* Byte-pixel data callback.  The reference keeps images as Java bytes and widens them to float on the host inside its
+ * callback (src/main/java/libs/ByteImage.java:86-104 cropInto; src/main/scala/libs/Net.scala:194-221 makeImageCallback;
+ * mean subtraction src/main/scala/apps/ImageNetApp.scala:158-175).  With this entry the callback (same type, same call
+ * pattern and pairing as set_train_data_callback, libccaffe/ccaffe.h:33) fills batch*C*H*W BYTES in NCHW order and the
+ * device widens them into the layer's fp32 blob: x = ((float)b - mean[..]) * scale, b read as a signed Java byte
+ * (is_signed != 0) or as 0..255; mean = NULL, C*H*W values (mean image) or C values (per channel), copied by the call.
+ * The blob is bit-identical to what the fp32 callback path holds for the same pixels.  Returns 0, -1 bad layer index,
+ * -2 not a JavaData layer.  set_train_data_callback on the same layer switches back to fp32 buffers. */
+int sparknet_set_train_data_callback_bytes(caffenet_state* state, int layer_idx, java_callback_t callback, int is_signed,
+                                           const float* mean, int mean_count, float scale);
+/* Host-side cost of the input path since the previous call: out[0] = callbacks run, out[1] = mean ms inside a callback,
+ * out[2] = mean ms the solver thread waited for a pinned staging buffer before a callback. */
+int sparknet_input_stats(caffenet_state* state, double* out3);
+/* Net::ForwardFromTo / BackwardFromTo (caffe/src/caffe/net.cpp:565-581, 635-645), which libccaffe/ccaffe.h does not
+ * expose: forward over layers [start, end]; backward from layer `start` down to layer `end`.  0 ok, -1 bad range. */
+int sparknet_forward_range(caffenet_state* state, int start, int end);
+int sparknet_backward_range(caffenet_state* state, int start, int end);
+/* Grow the per-process scratch workspace (split-reduction slices, bias partials) to at least nfloats now; returns its
+ * size in floats.  Growing reallocates, so iterations recorded for replay are recorded again afterwards. */
+long sparknet_reserve_workspace(long nfloats);
+/* Bulk copies between the weight arena and its pinned host mirror so far.  All get_weight_blob handles of a net share
+ * one mirror: the first get_data after device-side updates moves the whole arena in ONE device-to-host copy (the other
+ * blobs' get_data calls then copy nothing), and the next device use after host writes is ONE host-to-device copy —
+ * what keeps Net.scala:132-172 getWeights / setWeights cheap for the unchanged JVM driver. */
+void sparknet_param_copy_counts(caffenet_state* state, long* d2h, long* h2d);
+/* NUMA placement of this process: writes "gpu_node=<n> pinned=<0|1> cpus=<count>" into buf. */
+int sparknet_numa_info(char* buf, int n);
 /* Test hook for the tensor-core GEMM core: D[M][N] = A x B^T, host pointers.  a_mn/b_mn: 0 = operand
  * stored [rows][R], 1 = stored [R][rows]; tma_a: feed A through TMA. */
 int sparknet_test_tc_gemm(int a_mn, int b_mn, int tma_a, int M, int N, int R, const float* A, const float* B, float* D);

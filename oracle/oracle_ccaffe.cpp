@@ -1366,6 +1366,17 @@ void set_mode_gpu() {}   // the oracle is the CPU path; accepted so one harness 
 void set_device(int) {}
 
 // ---- oracle/test extensions (same names as the product's sparknet_* superset where they overlap) ----
+// Net::ForwardFromTo / BackwardFromTo (src/caffe/net.cpp:565-581, 635-645)
+int sparknet_forward_range(caffenet_state* s, int start, int end) {
+  if (start < 0 || end >= (int)s->net->layers.size() || start > end) return -1;
+  s->net->forward_from_to(start, end);
+  return 0;
+}
+int sparknet_backward_range(caffenet_state* s, int start, int end) {
+  if (end < 0 || start >= (int)s->net->layers.size() || start < end) return -1;
+  s->net->backward_from_to(start, end);
+  return 0;
+}
 int sparknet_get_iter(caffenet_state* s) { return s->solver ? s->solver->iter : -1; }
 float sparknet_last_loss(caffenet_state* s) { return s->solver ? s->solver->last_loss : 0.f; }
 float sparknet_smoothed_loss(caffenet_state* s) { return s->solver ? s->solver->smoothed_loss : 0.f; }

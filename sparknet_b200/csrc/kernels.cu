@@ -70,6 +70,48 @@ void axpy(cudaStream_t s, size_t n, float a, const float* x, float* y) {
 }
 
 // ------------------------------------------------------------------------------------------
+// Byte pixels to fp32 — the device side of the byte-input path (runtime.cpp JavaDataLayer).  The reference widens on
+// the host inside its data callback (ByteImage.java:86-104: float = (signed) byte; ImageNetApp.scala:158-175 then
+// subtracts the mean image in fp32); the same two fp32 operations here, so the blob is bit-identical to the fp32
+// callback path.  5 B per element: 1 read + 4 written.
+// ------------------------------------------------------------------------------------------
+template <bool SIGNED>
+__global__ void __launch_bounds__(256) widen_bytes_kernel(size_t n, const uint4* __restrict__ src16, const uint8_t* __restrict__ src,
+                                                          const float* __restrict__ mean, FastDiv ddiv, FastDiv dper, float scale,
+                                                          float4* __restrict__ dst4, float* __restrict__ dst, int vec) {
+  const size_t n16 = vec ? n >> 4 : 0;                       // unaligned buffers: every element through the scalar tail loop
+  auto one = [&](uint32_t byte, size_t i) -> float {
+    float v = SIGNED ? (float)(int)(signed char)byte : (float)byte;
+    if (mean) {
+      const uint32_t q = ddiv.div((uint32_t)i);
+      v = __fsub_rn(v, __ldg(mean + (q - dper.div(q) * dper.d)));
+    }
+    return scale == 1.f ? v : __fmul_rn(v, scale);
+  };
+  for (size_t g = blockIdx.x * (size_t)blockDim.x + threadIdx.x; g < n16; g += (size_t)gridDim.x * blockDim.x) {
+    const uint4 b = __ldg(src16 + g);
+    const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const size_t i = (g << 4) + (size_t)(k << 2);
+      dst4[(g << 2) + k] = make_float4(one(w[k] & 0xffu, i), one((w[k] >> 8) & 0xffu, i + 1), one((w[k] >> 16) & 0xffu, i + 2), one(w[k] >> 24, i + 3));
+    }
+  }
+  for (size_t i = (n16 << 4) + blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = one(src[i], i);
+}
+void widen_bytes(cudaStream_t s, size_t n, const uint8_t* src, bool is_signed, const float* mean, int mean_div, int mean_period,
+                 float scale, float* dst) {
+  if (!n) return;
+  if (n >= (1ull << 31)) fatal("widen_bytes: %zu elements exceed the 32-bit index range of the mean lookup", n);
+  const int vec = (((uintptr_t)src | (uintptr_t)dst) & 15) == 0 ? 1 : 0;
+  const FastDiv ddiv((uint32_t)std::max(mean_div, 1)), dper((uint32_t)std::max(mean_period, 1));
+  const int grid = grid_for(vec ? n / 16 + 1 : n, 256, 16);
+  if (is_signed) widen_bytes_kernel<true><<<grid, 256, 0, s>>>(n, (const uint4*)src, src, mean, ddiv, dper, scale, (float4*)dst, dst, vec);
+  else widen_bytes_kernel<false><<<grid, 256, 0, s>>>(n, (const uint4*)src, src, mean, ddiv, dper, scale, (float4*)dst, dst, vec);
+  count_launch();
+}
+
+// ------------------------------------------------------------------------------------------
 // ReLU — reference ReLUForward/ReLUBackward caffe/src/caffe/layers/relu_layer.cu:9-14,35-41
 // (CPU form relu_layer.cpp:16-17,32-33).  fwd 8 B/elt, bwd 12 B/elt.
 // ------------------------------------------------------------------------------------------
@@ -171,56 +213,177 @@ void dropout_bwd(cudaStream_t s, size_t n, const float* dy, const uint8_t* mask,
 // Tie rule: strict '>' scanning h then w (first maximum wins), start value -FLT_MAX, mask = h*W+w.
 // AVE divisor = window area clipped to H+pad / W+pad (counts the padding), true division.
 // ------------------------------------------------------------------------------------------
-__global__ void pool_max_fwd_kernel(PoolGeom g, size_t total, const float* __restrict__ x, float* __restrict__ y,
-                                    int* __restrict__ mask) {
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    const int pw = (int)(idx % g.PW), ph = (int)((idx / g.PW) % g.PH);
-    const size_t plane = idx / ((size_t)g.PW * g.PH);
-    int hs = ph * g.sh - g.ph, ws = pw * g.sw - g.pw;
-    const int he = min(hs + g.kh, g.H), we = min(ws + g.kw, g.W);
-    hs = max(hs, 0); ws = max(ws, 0);
-    const float* xp = x + plane * (size_t)(g.H * g.W);
-    float best = -FLT_MAX;
-    int bi = -1;
-    for (int h = hs; h < he; ++h)
-      for (int w = ws; w < we; ++w) {
-        const float v = __ldg(xp + h * g.W + w);
-        if (v > best) { best = v; bi = h * g.W + w; }
-      }
-    y[idx] = best;
-    mask[idx] = bi;
+// ---- tile kernels: every window shape the fixed-shape kernels below do not cover, and both directions of AVE ----
+// A work unit is a CONTIGUOUS span of the input tensor: either `ppb` whole (n, c) planes (small planes: several per unit,
+// so a CTA always has a few thousand elements to chew on) or, for planes too large for shared memory, the input rows that
+// one band of output rows needs.  The span is staged in shared memory with 16-byte loads (ragged head / tail by scalar
+// loads; the staging keeps the span's 16-byte phase so both sides of the copy are aligned), every window is then scanned
+// there in the reference's order (h outer, w inner, strict '>' for MAX, plain fp32 sum for AVE), and the results of a
+// unit — also contiguous in memory — leave as 16-byte stores where the destination phase allows.  Global traffic is the
+// algorithmic 4*in + 4*out (+ 4*out mask) bytes; strided window reads never leave the SM.
+struct PoolTile {
+  int ppb;             // planes per unit (> 1 only when bands == 1)
+  int band;            // rows per unit: output rows (forward) / input rows (backward)
+  int bands;           // units per plane group
+  unsigned units;
+  int vec;             // 1: source and destination pointers are 16-byte aligned
+};
+// sm[(goff & 3) + i] = src[goff + i], i < len
+__device__ __forceinline__ void pool_stage_span(float* __restrict__ sm, const float* __restrict__ src, size_t goff, int len, bool vec) {
+  const int lead = (int)(goff & 3);
+  const float* base = src + (goff - lead);                  // 16-byte aligned when src is
+  const int total = lead + len;
+  if (vec) {
+    const int n4 = total >> 2;                              // whole float4s inside [base, base + total): never past the span's end
+    const float4* b4 = reinterpret_cast<const float4*>(base);
+    float4* s4 = reinterpret_cast<float4*>(sm);
+    for (int k = threadIdx.x; k < n4; k += blockDim.x) s4[k] = __ldg(b4 + k);
+    for (int i = (n4 << 2) + threadIdx.x; i < total; i += blockDim.x) sm[i] = __ldg(base + i);
+  } else {
+    for (int i = lead + threadIdx.x; i < total; i += blockDim.x) sm[i] = __ldg(base + i);
   }
 }
-// Plane-per-CTA form: the input plane is staged in shared memory with linear, coalesced loads; every pooled
-// element then scans its window there (same scan order and strict '>' as above).  Global traffic is the algorithmic
-// 4*in + 8*out bytes; the strided window reads never leave the SM.
-__global__ void __launch_bounds__(256) pool_max_fwd_plane_kernel(PoolGeom g, FastDiv dPW, const float* __restrict__ x, float* __restrict__ y,
-                                                                 int* __restrict__ mask) {
-  extern __shared__ float sm_plane[];
+// Results of a unit: element j of `n` goes to dst[off + j].  Threads own groups of four elements aligned to the
+// DESTINATION's 16-byte phase; `f(j)` computes one element.
+template <class T4, class T, class F>
+__device__ __forceinline__ void pool_store_span(T* __restrict__ dst, size_t off, int n, bool vec, F f) {
+  const int lead = (int)(off & 3);
+  T* base = dst + (off - lead);
+  const int groups = (lead + n + 3) >> 2;
+  for (int k = threadIdx.x; k < groups; k += blockDim.x) {
+    const int j0 = (k << 2) - lead;
+    if (vec && j0 >= 0 && j0 + 3 < n) {
+      T4 v;
+      v.x = f(j0); v.y = f(j0 + 1); v.z = f(j0 + 2); v.w = f(j0 + 3);
+      reinterpret_cast<T4*>(base)[k] = v;
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        if (j0 + e >= 0 && j0 + e < n) base[(k << 2) + e] = f(j0 + e);
+    }
+  }
+}
+// forward: MAX writes (value, argmax), AVE the window mean with the padded-area divisor (pooling_layer.cpp:179-212)
+template <bool AVE>
+__global__ void __launch_bounds__(256) pool_fwd_tile_kernel(PoolGeom g, PoolTile t, FastDiv dPW, FastDiv dPH, const float* __restrict__ x,
+                                                            float* __restrict__ y, int* __restrict__ mask) {
+  extern __shared__ __align__(16) float sm_pool[];
   const int HW = g.H * g.W, P = g.PH * g.PW;
-  for (size_t plane = blockIdx.x; plane < (size_t)g.N * g.C; plane += gridDim.x) {
-    const float* xp = x + plane * (size_t)HW;
-    for (int i = threadIdx.x; i < HW; i += blockDim.x) sm_plane[i] = xp[i];
+  const unsigned planes = (unsigned)(g.N * g.C);
+  for (unsigned u = blockIdx.x; u < t.units; u += gridDim.x) {
+    const unsigned pg = u / (unsigned)t.bands, b = u - pg * (unsigned)t.bands;
+    const unsigned p0 = pg * (unsigned)t.ppb;
+    const int np = (int)min((unsigned)t.ppb, planes - p0);
+    const int r0 = (int)b * t.band, r1 = min(r0 + t.band, g.PH);
+    int hs0 = 0, rows_in = g.H;
+    if (t.bands > 1) {                                       // one plane, the input rows of output rows [r0, r1)
+      hs0 = max(r0 * g.sh - g.ph, 0);
+      rows_in = max(min((r1 - 1) * g.sh - g.ph + g.kh, g.H) - hs0, 0);
+    }
+    const size_t goff = (size_t)p0 * HW + (size_t)hs0 * g.W;
+    const int len = t.bands > 1 ? rows_in * g.W : np * HW;
+    __syncthreads();                                         // the previous unit's readers are done with the tile
+    pool_stage_span(sm_pool, x, goff, len, t.vec != 0);
     __syncthreads();
-    for (int j = threadIdx.x; j < P; j += blockDim.x) {
-      uint32_t ph, pw;
-      dPW.divmod((uint32_t)j, ph, pw);
-      int hs = (int)ph * g.sh - g.ph, ws = (int)pw * g.sw - g.pw;
+    const float* tile = sm_pool + (goff & 3) - hs0 * g.W;   // tile[pl * HW + h * W + w]
+    const int nout = np * (r1 - r0) * g.PW;
+    const size_t yoff = (size_t)p0 * P + (size_t)r0 * g.PW;
+    auto window = [&](int j, int& arg) -> float {
+      uint32_t q, pw, pl, r;
+      dPW.divmod((uint32_t)j, q, pw);
+      if (t.bands > 1) { pl = 0; r = q; } else dPH.divmod(q, pl, r);
+      const int ph = r0 + (int)r;
+      int hs = ph * g.sh - g.ph, ws = (int)pw * g.sw - g.pw;
+      const float* tp = tile + (int)pl * HW;
+      if (AVE) {
+        int he = min(hs + g.kh, g.H + g.ph), we = min(ws + g.kw, g.W + g.pw);
+        const int pool_size = (he - hs) * (we - ws);
+        hs = max(hs, 0); ws = max(ws, 0); he = min(he, g.H); we = min(we, g.W);
+        float acc = 0.f;
+        for (int h = hs; h < he; ++h)
+          for (int w = ws; w < we; ++w) acc += tp[h * g.W + w];
+        return __fdiv_rn(acc, (float)pool_size);
+      }
       const int he = min(hs + g.kh, g.H), we = min(ws + g.kw, g.W);
       hs = max(hs, 0); ws = max(ws, 0);
       float best = -FLT_MAX;
       int bi = -1;
       for (int h = hs; h < he; ++h)
         for (int w = ws; w < we; ++w) {
-          const float v = sm_plane[h * g.W + w];
+          const float v = tp[h * g.W + w];
           if (v > best) { best = v; bi = h * g.W + w; }
         }
-      y[plane * P + j] = best;
-      mask[plane * P + j] = bi;
+      arg = bi;
+      return best;
+    };
+    if (AVE) {
+      pool_store_span<float4>(y, yoff, nout, t.vec != 0, [&](int j) { int a; return window(j, a); });
+    } else {
+      // value and argmax index come from one scan; both leave as 16-byte stores (same group walk as pool_store_span)
+      const int lead = (int)(yoff & 3), groups = (lead + nout + 3) >> 2;
+      for (int k0 = 0; k0 < groups; k0 += blockDim.x) {
+        const int k = k0 + threadIdx.x;
+        if (k < groups) {
+          const int j0 = (k << 2) - lead;
+          float v[4]; int a[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) { a[e] = -1; v[e] = (j0 + e >= 0 && j0 + e < nout) ? window(j0 + e, a[e]) : 0.f; }
+          float* yb = y + (yoff - lead);
+          int* mb = mask + (yoff - lead);
+          if (t.vec && j0 >= 0 && j0 + 3 < nout) {
+            reinterpret_cast<float4*>(yb)[k] = make_float4(v[0], v[1], v[2], v[3]);
+            reinterpret_cast<int4*>(mb)[k] = make_int4(a[0], a[1], a[2], a[3]);
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e)
+              if (j0 + e >= 0 && j0 + e < nout) { yb[(k << 2) + e] = v[e]; mb[(k << 2) + e] = a[e]; }
+          }
+        }
+      }
     }
-    __syncthreads();
   }
 }
+static constexpr int kPoolTileFloats = 6144;                 // staged span per unit: 24 KB, eight CTAs per SM
+static constexpr int kPoolTileMaxFloats = 50 * 1024;         // opt-in ceiling (200 KB of the 227 KB an SM has)
+// rows_for(band) = rows of the staged tensor a band needs; row_floats = floats per staged row
+template <class RowsFor>
+static PoolTile plan_pool_tile(size_t planes, int plane_floats, int row_floats, int out_rows, RowsFor rows_for, size_t* smem_floats,
+                               int work_per_plane) {
+  PoolTile t{};
+  if (plane_floats <= kPoolTileFloats) {
+    size_t ppb = std::max<size_t>(1, (size_t)kPoolTileFloats / (size_t)plane_floats);
+    ppb = std::min(ppb, std::max<size_t>(1, planes / (size_t)(kSMs * 4)));       // small layers: keep every SM busy
+    ppb = std::min(ppb, std::max<size_t>(1, (size_t)32768 / (size_t)std::max(work_per_plane, 1)));
+    t.ppb = (int)ppb; t.band = out_rows; t.bands = 1;
+    *smem_floats = (size_t)t.ppb * plane_floats + 4;
+  } else {
+    int band = out_rows;
+    while (band > 1 && (size_t)rows_for(band) * row_floats > (size_t)kPoolTileFloats) band = (band + 1) / 2;
+    if ((size_t)rows_for(band) * row_floats > (size_t)kPoolTileMaxFloats)
+      fatal("pooling: a window band of %d rows x %d floats does not fit in shared memory", rows_for(band), row_floats);
+    t.ppb = 1; t.band = band; t.bands = (out_rows + band - 1) / band;
+    *smem_floats = (size_t)rows_for(band) * row_floats + 4;
+  }
+  t.units = (unsigned)(((planes + t.ppb - 1) / t.ppb) * (size_t)t.bands);
+  return t;
+}
+template <class K>
+static void pool_tile_smem_attr(K kernel, size_t bytes) {
+  if (bytes > 48 * 1024) SN_CUDA(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+}
+template <bool AVE>
+static void pool_fwd_tile(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask) {
+  size_t smf = 0;
+  const size_t planes = (size_t)g.N * g.C;
+  PoolTile t = plan_pool_tile(planes, g.H * g.W, g.W, g.PH, [&](int band) { return std::min((band - 1) * g.sh + g.kh, g.H); }, &smf,
+                              g.PH * g.PW * g.kh * g.kw / 4);
+  t.vec = (((uintptr_t)x | (uintptr_t)y | (uintptr_t)mask) & 15) == 0 ? 1 : 0;
+  const size_t bytes = (smf * sizeof(float) + 15) / 16 * 16;
+  pool_tile_smem_attr(pool_fwd_tile_kernel<AVE>, bytes);
+  const int blocks = (int)std::min<size_t>(t.units, (size_t)kSMs * 8);
+  pool_fwd_tile_kernel<AVE><<<blocks, 256, bytes, s>>>(g, t, FastDiv((uint32_t)g.PW), FastDiv((uint32_t)g.PH), x, y, mask);
+}
+
 // Thread-per-output form for the window shapes of the four nets (compile-time kernel size and stride, no padding):
 // 32-bit index arithmetic with multiply-shift division, all window loads issued before the compare chain.  Window
 // elements are read straight from global memory: neighbouring outputs share them through the L1, HBM sees them once.
@@ -251,56 +414,36 @@ __global__ void __launch_bounds__(256) pool_max_fwd_fixed_kernel(PoolGeom g, uin
   }
 }
 void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask) {
-  const size_t total = (size_t)g.N * g.C * g.PH * g.PW, smem = (size_t)g.H * g.W * sizeof(float);
+  const size_t total = (size_t)g.N * g.C * g.PH * g.PW;
   const bool fixed = g.ph == 0 && g.pw == 0 && total < (1ull << 31) && (size_t)g.N * g.C * g.H * g.W < (1ull << 31);
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
     pool_max_fwd_fixed_kernel<3, 3, 2, 2><<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)g.PW), FastDiv((uint32_t)g.PH), x, y, mask);
   } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
     pool_max_fwd_fixed_kernel<2, 2, 2, 2><<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)g.PW), FastDiv((uint32_t)g.PH), x, y, mask);
-  } else if (smem <= 40 * 1024 && g.H * g.W >= 64) {
-    const size_t planes = (size_t)g.N * g.C;
-    const int blocks = (int)std::min<size_t>(planes, (size_t)kSMs * 16);
-    pool_max_fwd_plane_kernel<<<blocks, 256, smem, s>>>(g, FastDiv((uint32_t)g.PW), x, y, mask);
   } else {
-    pool_max_fwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, x, y, mask);
+    pool_fwd_tile<false>(s, g, x, y, mask);
   }
   count_launch();
 }
-// gather form: every input element sums the top diffs of the windows whose argmax it is
-__global__ void pool_max_bwd_kernel(PoolGeom g, size_t total, const float* __restrict__ dy, const int* __restrict__ mask,
-                                    float* __restrict__ dx) {
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    const int w = (int)(idx % g.W), h = (int)((idx / g.W) % g.H);
-    const size_t plane = idx / ((size_t)g.W * g.H);
-    const int phs = (h + g.ph < g.kh) ? 0 : (h + g.ph - g.kh) / g.sh + 1;
-    const int phe = min((h + g.ph) / g.sh + 1, g.PH);
-    const int pws = (w + g.pw < g.kw) ? 0 : (w + g.pw - g.kw) / g.sw + 1;
-    const int pwe = min((w + g.pw) / g.sw + 1, g.PW);
-    const size_t off = plane * (size_t)(g.PH * g.PW);
-    const int me = h * g.W + w;
-    float acc = 0.f;
-    for (int ph = phs; ph < phe; ++ph)
-      for (int pw = pws; pw < pwe; ++pw)
-        if (__ldg(mask + off + ph * g.PW + pw) == me) acc += __ldg(dy + off + ph * g.PW + pw);
-    dx[idx] = acc;
-  }
-}
-// Plane-per-CTA form: the pooled plane's (dy, mask) pair is staged in shared memory with coalesced loads, the
-// window range of every input row / column is tabulated once per CTA (no integer division per element), and the
-// plane is then written linearly: every input element checks the <= ceil(k/s)^2 windows that cover it, in the
-// reference's (ph, pw) order.  Global traffic is exactly the algorithmic 8*out + 4*in bytes.
-// `gate` (nullable) = the pooled OUTPUT values: when the pooling input is the output of an in-place ReLU whose
-// backward would run next (relu_layer.cpp:26-36: dx = dy * (y > 0)), that test is applied here — the element that
-// won a window is > 0 exactly when the pooled value is — and the separate 12 B/element ReLU pass disappears.
-__global__ void __launch_bounds__(256) pool_max_bwd_plane_kernel(PoolGeom g, FastDiv dW, const float* __restrict__ dy,
-                                                                 const int* __restrict__ mask, const float* __restrict__ gate,
-                                                                 float* __restrict__ dx) {
-  extern __shared__ float sm_pool[];
+// backward, gather form (pooling_layer.cpp:253-270 MAX, :272-292 AVE scatter the top diffs window by window in (ph, pw)
+// order; here every input element adds the windows that cover it in that same order, so the fp32 sums are identical).
+// A unit stages the pooled rows (dy, and the argmax indices for MAX) that its input rows can receive from; the window
+// ranges of every input row / column and the AVE divisors' row / column extents are tabulated once per CTA.
+// `gate` (nullable, MAX) = the pooled OUTPUT values: when the pooling input is the output of an in-place ReLU whose
+// backward would run next (relu_layer.cpp:26-36: dx = dy * (y > 0)), that test is applied while staging — the element
+// that won a window is > 0 exactly when the pooled value is — and the separate 12 B/element ReLU pass disappears.
+template <bool AVE>
+__global__ void __launch_bounds__(256) pool_bwd_tile_kernel(PoolGeom g, PoolTile t, FastDiv dW, FastDiv dH, const float* __restrict__ dy,
+                                                            const int* __restrict__ mask, const float* __restrict__ gate,
+                                                            float* __restrict__ dx, int span_floats) {
+  extern __shared__ __align__(16) float sm_pool[];
   const int P = g.PH * g.PW, HW = g.H * g.W;
   float* sdy = sm_pool;
-  int* smask = (int*)(sm_pool + P);
-  int* rowr = smask + P;                           // packed (first window | one-past-last window << 16) per input row
+  int* smask = reinterpret_cast<int*>(sm_pool + span_floats);
+  int* rowr = smask + (AVE ? 0 : span_floats);              // packed (first window | one-past-last window << 16) per input row
   int* colr = rowr + g.H;
+  int* rext = colr + g.W;                                    // AVE: clipped-to-padding window extent per pooled row / column
+  int* cext = rext + g.PH;
   for (int h = threadIdx.x; h < g.H; h += blockDim.x) {
     const int phs = (h + g.ph < g.kh) ? 0 : (h + g.ph - g.kh) / g.sh + 1, phe = min((h + g.ph) / g.sh + 1, g.PH);
     rowr[h] = phs | (phe << 16);
@@ -309,28 +452,70 @@ __global__ void __launch_bounds__(256) pool_max_bwd_plane_kernel(PoolGeom g, Fas
     const int pws = (w + g.pw < g.kw) ? 0 : (w + g.pw - g.kw) / g.sw + 1, pwe = min((w + g.pw) / g.sw + 1, g.PW);
     colr[w] = pws | (pwe << 16);
   }
-  for (size_t plane = blockIdx.x; plane < (size_t)g.N * g.C; plane += gridDim.x) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < P; i += blockDim.x) {
-      float v = dy[plane * P + i];
-      if (gate && !(gate[plane * P + i] > 0.f)) v = 0.f;
-      sdy[i] = v;
-      smask[i] = mask[plane * P + i];
+  if (AVE) {
+    for (int p = threadIdx.x; p < g.PH; p += blockDim.x) { const int hs = p * g.sh - g.ph; rext[p] = min(hs + g.kh, g.H + g.ph) - hs; }
+    for (int p = threadIdx.x; p < g.PW; p += blockDim.x) { const int ws = p * g.sw - g.pw; cext[p] = min(ws + g.kw, g.W + g.pw) - ws; }
+  }
+  const unsigned planes = (unsigned)(g.N * g.C);
+  for (unsigned u = blockIdx.x; u < t.units; u += gridDim.x) {
+    const unsigned pg = u / (unsigned)t.bands, b = u - pg * (unsigned)t.bands;
+    const unsigned p0 = pg * (unsigned)t.ppb;
+    const int np = (int)min((unsigned)t.ppb, planes - p0);
+    const int h0 = (int)b * t.band, h1 = min(h0 + t.band, g.H);
+    __syncthreads();                                         // tables written / previous unit's readers done
+    int ps0 = 0, prows = g.PH;
+    if (t.bands > 1) {
+      ps0 = rowr[h0] & 0xffff;
+      prows = max((rowr[h1 - 1] >> 16) - ps0, 0);
+    }
+    const size_t goff = (size_t)p0 * P + (size_t)ps0 * g.PW;
+    const int len = t.bands > 1 ? prows * g.PW : np * P;
+    pool_stage_span(sdy, dy, goff, len, t.vec != 0);
+    if (!AVE) pool_stage_span(reinterpret_cast<float*>(smask), reinterpret_cast<const float*>(mask), goff, len, t.vec != 0);
+    if (!AVE && gate) {
+      __syncthreads();
+      const int lead = (int)(goff & 3);
+      for (int i = threadIdx.x; i < len; i += blockDim.x)
+        if (!(__ldg(gate + goff + i) > 0.f)) sdy[lead + i] = 0.f;
     }
     __syncthreads();
-    float* dxp = dx + plane * (size_t)HW;
-    for (int me = threadIdx.x; me < HW; me += blockDim.x) {
-      uint32_t h, w;
-      dW.divmod((uint32_t)me, h, w);
+    const float* tdy = sdy + (goff & 3) - ps0 * g.PW;       // tdy[pl * P + ph * PW + pw]
+    const int* tmask = smask + (goff & 3) - ps0 * g.PW;
+    const int nin = np * (h1 - h0) * g.W;
+    const size_t xoff = (size_t)p0 * HW + (size_t)h0 * g.W;
+    pool_store_span<float4>(dx, xoff, nin, t.vec != 0, [&](int j) -> float {
+      uint32_t q, w, pl, r;
+      dW.divmod((uint32_t)j, q, w);
+      if (t.bands > 1) { pl = 0; r = q; } else dH.divmod(q, pl, r);
+      const int h = h0 + (int)r;
       const int rr = rowr[h], cr = colr[w];
       const int phs = rr & 0xffff, phe = rr >> 16, pws = cr & 0xffff, pwe = cr >> 16;
+      const int me = h * g.W + (int)w;
+      const float* dp = tdy + (int)pl * P;
+      const int* mp = tmask + (int)pl * P;
       float acc = 0.f;
       for (int ph = phs; ph < phe; ++ph)
-        for (int pw = pws; pw < pwe; ++pw)
-          if (smask[ph * g.PW + pw] == me) acc += sdy[ph * g.PW + pw];
-      dxp[me] = acc;
-    }
+        for (int pw = pws; pw < pwe; ++pw) {
+          if (AVE) acc += __fdiv_rn(dp[ph * g.PW + pw], (float)(rext[ph] * cext[pw]));
+          else if (mp[ph * g.PW + pw] == me) acc += dp[ph * g.PW + pw];
+        }
+      return acc;
+    });
   }
+}
+template <bool AVE>
+static void pool_bwd_tile(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, const float* gate, float* dx) {
+  size_t span = 0;
+  const size_t planes = (size_t)g.N * g.C;
+  // pooled rows that a band of `band` input rows can receive from
+  auto rows_for = [&](int band) { return std::min((band - 1) / g.sh + (g.kh + g.sh - 1) / g.sh + 1, g.PH); };
+  PoolTile t = plan_pool_tile(planes, g.PH * g.PW, g.PW, g.H, rows_for, &span, g.H * g.W);
+  t.vec = (((uintptr_t)dy | (uintptr_t)dx | (AVE ? 0 : (uintptr_t)mask)) & 15) == 0 ? 1 : 0;
+  span = (span + 3) / 4 * 4;
+  const size_t bytes = (span * (AVE ? 1 : 2) + (size_t)(g.H + g.W + g.PH + g.PW)) * sizeof(float);
+  pool_tile_smem_attr(pool_bwd_tile_kernel<AVE>, bytes);
+  const int blocks = (int)std::min<size_t>(t.units, (size_t)kSMs * 8);
+  pool_bwd_tile_kernel<AVE><<<blocks, 256, bytes, s>>>(g, t, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx, (int)span);
 }
 // Thread-per-input-element gather for the same fixed window shapes: at most ceil(K/S)^2 = 4 candidate windows, tested
 // in the reference's (ph, pw) order; 32-bit index arithmetic, divisions by compile-time strides.
@@ -560,12 +745,7 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g,
     }
   }
 }
-__global__ void pool_gate_kernel(size_t n, const float* __restrict__ dy, const float* __restrict__ gate, float* __restrict__ out) {
-  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-    out[i] = gate[i] > 0.f ? dy[i] : 0.f;
-}
 void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx, const float* gate) {
-  const size_t smem = (size_t)g.PH * g.PW * 8 + (size_t)(g.H + g.W) * 4;
   const size_t total_in = (size_t)g.N * g.C * g.H * g.W;
   const bool fixed = g.ph == 0 && g.pw == 0 && total_in < (1ull << 31);
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
@@ -590,120 +770,27 @@ void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int*
       pool_max_bwd_3x3s2_kernel<<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)B), FastDiv((uint32_t)A), dy, mask, gate, dx);
   } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
     pool_max_bwd_fixed_kernel<2, 2, 2, 2><<<grid_for(total_in, 256, 32), 256, 0, s>>>(g, (uint32_t)total_in, FastDiv((uint32_t)g.W), FastDiv((uint32_t)g.H), dy, mask, gate, dx);
-  } else if (smem <= 40 * 1024) {
-    const size_t planes = (size_t)g.N * g.C;
-    const int blocks = (int)std::min<size_t>(planes, (size_t)kSMs * 16);
-    pool_max_bwd_plane_kernel<<<blocks, 256, smem, s>>>(g, FastDiv((uint32_t)g.W), dy, mask, gate, dx);
   } else {
-    const size_t total = (size_t)g.N * g.C * g.H * g.W;
-    if (gate) {                                    // large planes: gate into the workspace first
-      const size_t n = (size_t)g.N * g.C * g.PH * g.PW;
-      float* tmp = get_workspace(n);
-      pool_gate_kernel<<<grid_for(n, 256), 256, 0, s>>>(n, dy, gate, tmp);
-      count_launch();
-      dy = tmp;
-    }
-    pool_max_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, mask, dx);
+    pool_bwd_tile<false>(s, g, dy, mask, gate, dx);
   }
   count_launch();
-}
-__global__ void pool_ave_fwd_kernel(PoolGeom g, size_t total, const float* __restrict__ x, float* __restrict__ y) {
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    const int pw = (int)(idx % g.PW), ph = (int)((idx / g.PW) % g.PH);
-    const size_t plane = idx / ((size_t)g.PW * g.PH);
-    int hs = ph * g.sh - g.ph, ws = pw * g.sw - g.pw;
-    int he = min(hs + g.kh, g.H + g.ph), we = min(ws + g.kw, g.W + g.pw);
-    const int pool_size = (he - hs) * (we - ws);
-    hs = max(hs, 0); ws = max(ws, 0); he = min(he, g.H); we = min(we, g.W);
-    const float* xp = x + plane * (size_t)(g.H * g.W);
-    float acc = 0.f;
-    for (int h = hs; h < he; ++h)
-      for (int w = ws; w < we; ++w) acc += __ldg(xp + h * g.W + w);
-    y[idx] = __fdiv_rn(acc, (float)pool_size);
-  }
 }
 void pool_ave_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y) {
-  const size_t total = (size_t)g.N * g.C * g.PH * g.PW;
-  pool_ave_fwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, x, y);
+  pool_fwd_tile<true>(s, g, x, y, nullptr);
   count_launch();
 }
-__global__ void pool_ave_bwd_kernel(PoolGeom g, size_t total, const float* __restrict__ dy, float* __restrict__ dx) {
-  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
-    const int w = (int)(idx % g.W) + g.pw, h = (int)((idx / g.W) % g.H) + g.ph;
-    const size_t plane = idx / ((size_t)g.W * g.H);
-    const int phs = (h < g.kh) ? 0 : (h - g.kh) / g.sh + 1, phe = min(h / g.sh + 1, g.PH);
-    const int pws = (w < g.kw) ? 0 : (w - g.kw) / g.sw + 1, pwe = min(w / g.sw + 1, g.PW);
-    const size_t off = plane * (size_t)(g.PH * g.PW);
-    float acc = 0.f;
-    for (int ph = phs; ph < phe; ++ph)
-      for (int pw = pws; pw < pwe; ++pw) {
-        const int hs = ph * g.sh - g.ph, ws = pw * g.sw - g.pw;
-        const int he = min(hs + g.kh, g.H + g.ph), we = min(ws + g.kw, g.W + g.pw);
-        acc += __fdiv_rn(__ldg(dy + off + ph * g.PW + pw), (float)((he - hs) * (we - ws)));
-      }
-    dx[idx] = acc;
-  }
-}
 void pool_ave_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, float* dx) {
-  const size_t total = (size_t)g.N * g.C * g.H * g.W;
-  pool_ave_bwd_kernel<<<grid_for(total, 256, 16), 256, 0, s>>>(g, total, dy, dx);
+  pool_bwd_tile<true>(s, g, dy, nullptr, nullptr, dx);
   count_launch();
 }
 
 // ------------------------------------------------------------------------------------------
 // LRN across channels — reference LRNFillScale / LRNComputeOutput / LRNComputeDiff
 // caffe/src/caffe/layers/lrn_layer.cu:9-52,72-77,122-177 (CPU: lrn_layer.cpp:108-152,180-232).
-// One thread per (n,h,w) walks the channels with a running window; consecutive threads are
-// consecutive w, so every step is a coalesced row access.  fwd 12 B/elt (x, scale, y), bwd 20 B/elt.
+// Consecutive threads are consecutive pixels, so every channel step is a coalesced row access.
+// Algorithmic bytes: fwd 12 B/elt (x, scale, y), bwd 20 B/elt; moved here: 8 / 12 (no scale tensor).
 // ------------------------------------------------------------------------------------------
-__global__ void lrn_across_fwd_kernel(LrnGeom g, int nthreads, const float* __restrict__ x, float* __restrict__ y,
-                                      float* __restrict__ scale) {
-  const int HW = g.H * g.W;
-  const int pre = (g.size - 1) / 2, post = g.size - pre - 1;
-  const float aos = g.alpha / g.size;
-  const float nbeta = -g.beta;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nthreads; idx += gridDim.x * blockDim.x) {
-    const int pix = idx % HW, n = idx / HW;
-    const size_t off = (size_t)n * g.C * HW + pix;
-    const float* xi = x + off;
-    float* yi = y + off;
-    float* si = scale + off;
-    int head = 0;
-    float accum = 0.f;
-    while (head < post && head < g.C) {
-      const float v = xi[(size_t)head * HW];
-      accum += v * v;
-      ++head;
-    }
-    while (head < g.C) {
-      const float v = xi[(size_t)head * HW];
-      accum += v * v;
-      if (head - g.size >= 0) {
-        const float t = xi[(size_t)(head - g.size) * HW];
-        accum -= t * t;
-      }
-      const int c = head - post;
-      const float sc = g.k + accum * aos;
-      si[(size_t)c * HW] = sc;
-      yi[(size_t)c * HW] = xi[(size_t)c * HW] * powf(sc, nbeta);
-      ++head;
-    }
-    while (head < g.C + post) {
-      if (head - g.size >= 0) {
-        const float t = xi[(size_t)(head - g.size) * HW];
-        accum -= t * t;
-      }
-      const int c = head - post;
-      if (c >= 0 && c < g.C) {
-        const float sc = g.k + accum * aos;
-        si[(size_t)c * HW] = sc;
-        yi[(size_t)c * HW] = xi[(size_t)c * HW] * powf(sc, nbeta);
-      }
-      ++head;
-    }
-  }
-}
-// Chunked form (local_size 3 or 5): one thread owns CH consecutive channels of one pixel, loads them plus the halo in
+// Chunked form (odd local_size up to 11): one thread owns CH consecutive channels of one pixel, loads them plus the halo in
 // one batch (independent loads in flight instead of a serial walk over all C channels), and sums each window directly:
 //   scale_c = k + alpha/n * sum_{|j-c| <= pre} x_j^2 ,   y_c = x_c * scale_c^-beta .
 // Nothing but y is written: the backward kernel recomputes scale from x (cheaper than 8 B/element of scale traffic),
@@ -760,51 +847,24 @@ __global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, in
     }
   }
 }
-void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, float* scale) {
-  if (g.size == 5 || g.size == 3) {
-    const int CHn = lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
-    const size_t total = (size_t)g.N * chunks * g.H * g.W;
+static void lrn_size_check(const LrnGeom& g) {
+  if (g.size != 3 && g.size != 5 && g.size != 7 && g.size != 9 && g.size != 11)
+    fatal("LRN ACROSS_CHANNELS: local_size %d is not on the supported path (odd sizes 3..11)", g.size);
+}
+void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y) {
+  lrn_size_check(g);
+  const int CHn = g.size > 5 ? 16 : lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
+  const size_t total = (size_t)g.N * chunks * g.H * g.W;
 #define SN_LRN_F(SZ, CHV) lrn_across_fwd_chunk_kernel<SZ, CHV><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y)
-    if (g.size == 5) { if (CHn == 8) SN_LRN_F(5, 8); else if (CHn == 32) SN_LRN_F(5, 32); else SN_LRN_F(5, 16); }
-    else { if (CHn == 8) SN_LRN_F(3, 8); else if (CHn == 32) SN_LRN_F(3, 32); else SN_LRN_F(3, 16); }
+  if (g.size == 5) { if (CHn == 8) SN_LRN_F(5, 8); else if (CHn == 32) SN_LRN_F(5, 32); else SN_LRN_F(5, 16); }
+  else if (g.size == 3) { if (CHn == 8) SN_LRN_F(3, 8); else if (CHn == 32) SN_LRN_F(3, 32); else SN_LRN_F(3, 16); }
+  else if (g.size == 7) SN_LRN_F(7, 16);
+  else if (g.size == 9) SN_LRN_F(9, 16);
+  else SN_LRN_F(11, 16);
 #undef SN_LRN_F
-    count_launch();
-    return;
-  }
-  const int nthreads = g.N * g.H * g.W;
-  lrn_across_fwd_kernel<<<grid_for(nthreads, 128, 16), 128, 0, s>>>(g, nthreads, x, y, scale);
   count_launch();
 }
-__global__ void lrn_across_bwd_kernel(LrnGeom g, int nthreads, const float* __restrict__ x, const float* __restrict__ y,
-                                      const float* __restrict__ scale, const float* __restrict__ dy,
-                                      float* __restrict__ dx) {
-  const int HW = g.H * g.W;
-  const int pre = g.size - (g.size + 1) / 2, post = g.size - pre - 1;
-  const float cache_ratio = 2.f * g.alpha * g.beta / g.size;
-  const float nbeta = -g.beta;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < nthreads; idx += gridDim.x * blockDim.x) {
-    const int pix = idx % HW, n = idx / HW;
-    const size_t off = (size_t)n * g.C * HW + pix;
-    const float *xi = x + off, *yi = y + off, *si = scale + off, *gi = dy + off;
-    float* di = dx + off;
-    int head = 0;
-    float accum = 0.f;
-    while (head < post && head < g.C) {
-      accum += gi[(size_t)head * HW] * yi[(size_t)head * HW] / si[(size_t)head * HW];
-      ++head;
-    }
-    while (head < g.C + post) {
-      if (head < g.C) accum += gi[(size_t)head * HW] * yi[(size_t)head * HW] / si[(size_t)head * HW];
-      if (head - g.size >= 0)
-        accum -= gi[(size_t)(head - g.size) * HW] * yi[(size_t)(head - g.size) * HW] / si[(size_t)(head - g.size) * HW];
-      const int c = head - post;
-      if (c >= 0 && c < g.C)
-        di[(size_t)c * HW] = gi[(size_t)c * HW] * powf(si[(size_t)c * HW], nbeta) - cache_ratio * xi[(size_t)c * HW] * accum;
-      ++head;
-    }
-  }
-}
-// Chunked backward (local_size 3 or 5), reference LRNComputeDiff (lrn_layer.cu:122-177) / CrossChannelBackward_cpu
+// Chunked backward, reference LRNComputeDiff (lrn_layer.cu:122-177) / CrossChannelBackward_cpu
 // (lrn_layer.cpp:180-232):   dx_c = dy_c * scale_c^-beta - (2 alpha beta / n) * x_c * sum_{|j-c| <= pre} dy_j * y_j / scale_j
 // with scale and y recomputed from x (halo 2*pre).  Reads x and dy, writes dx: 12 B per element.
 template <int SIZE, int CH>
@@ -856,20 +916,17 @@ __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, in
     }
   }
 }
-void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* y, const float* scale,
-                    const float* dy, float* dx) {
-  if (g.size == 5 || g.size == 3) {
-    const int CHn = lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
-    const size_t total = (size_t)g.N * chunks * g.H * g.W;
+void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx) {
+  lrn_size_check(g);
+  const int CHn = g.size > 5 ? 16 : lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
+  const size_t total = (size_t)g.N * chunks * g.H * g.W;
 #define SN_LRN_B(SZ, CHV) lrn_across_bwd_chunk_kernel<SZ, CHV><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, dy, dx)
-    if (g.size == 5) { if (CHn == 8) SN_LRN_B(5, 8); else if (CHn == 32) SN_LRN_B(5, 32); else SN_LRN_B(5, 16); }
-    else { if (CHn == 8) SN_LRN_B(3, 8); else if (CHn == 32) SN_LRN_B(3, 32); else SN_LRN_B(3, 16); }
+  if (g.size == 5) { if (CHn == 8) SN_LRN_B(5, 8); else if (CHn == 32) SN_LRN_B(5, 32); else SN_LRN_B(5, 16); }
+  else if (g.size == 3) { if (CHn == 8) SN_LRN_B(3, 8); else if (CHn == 32) SN_LRN_B(3, 32); else SN_LRN_B(3, 16); }
+  else if (g.size == 7) SN_LRN_B(7, 16);
+  else if (g.size == 9) SN_LRN_B(9, 16);
+  else SN_LRN_B(11, 16);
 #undef SN_LRN_B
-    count_launch();
-    return;
-  }
-  const int nthreads = g.N * g.H * g.W;
-  lrn_across_bwd_kernel<<<grid_for(nthreads, 128, 16), 128, 0, s>>>(g, nthreads, x, y, scale, dy, dx);
   count_launch();
 }
 

@@ -101,9 +101,9 @@ void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* ma
 void dropout_bwd(cudaStream_t s, size_t n, const float* dy, const uint8_t* mask, float* dx, float scale);
 
 struct LrnGeom { int N, C, H, W, size; float alpha, beta, k; };
-void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, float* scale);
-void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* y, const float* scale,
-                    const float* dy, float* dx);
+// across channels, odd local_size 3..11; nothing but y is kept: the backward pass recomputes the scale from x
+void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y);
+void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx);
 void lrn_within_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y);
 void lrn_within_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx);
 
@@ -139,6 +139,10 @@ struct StepScalars {
 };
 void publish_step_scalars(cudaStream_t s, StepScalars* dst, const StepScalars& v);
 
+// byte pixels -> fp32 (JavaData byte input): dst[i] = ((float)src[i] - mean[(i / mean_div) % mean_period]) * scale, src read as
+// signed (Java byte) or unsigned; mean nullable; 16 bytes in, four 16-byte stores out per thread and step
+void widen_bytes(cudaStream_t s, size_t n, const uint8_t* src, bool is_signed, const float* mean, int mean_div, int mean_period,
+                 float scale, float* dst);
 void fill(cudaStream_t s, size_t n, float* p, float v);
 void split_add(cudaStream_t s, size_t n, const float* a, const float* b, float* out);
 void axpy(cudaStream_t s, size_t n, float a, const float* x, float* y);

@@ -10,9 +10,12 @@
 #include <random>
 #include <sstream>
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
 #include <mutex>
 #include <thread>
+#include <sched.h>
+#include <ctype.h>
 
 namespace sn {
 
@@ -47,16 +50,57 @@ Context& ctx() {
   if (!c.initialised) c.init();
   return c;
 }
+// Keep the thread that drives this GPU (and the copy threads / pinned buffers it creates) on the GPU's NUMA node: the
+// input path moves every minibatch through host memory twice (callback write, DMA read).  Only when the process may
+// run on several nodes and the GPU's node is one of them; SPARKNET_NUMA_PIN=0 turns it off.
+static void numa_pin(Context& c) {
+  char bus[32] = {0};
+  if (cudaDeviceGetPCIBusId(bus, (int)sizeof(bus), c.device) != cudaSuccess) { cudaGetLastError(); return; }
+  for (char* p = bus; *p; ++p) *p = (char)tolower(*p);
+  char path[128];
+  snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/numa_node", bus);
+  FILE* f = fopen(path, "r");
+  if (!f) return;
+  int node = -1;
+  if (fscanf(f, "%d", &node) != 1) node = -1;
+  fclose(f);
+  c.numa_node = node;
+  const char* e = getenv("SPARKNET_NUMA_PIN");
+  if (node < 0 || (e && atoi(e) == 0)) return;
+  snprintf(path, sizeof(path), "/sys/devices/system/node/node%d/cpulist", node);
+  f = fopen(path, "r");
+  if (!f) return;
+  char list[4096] = {0};
+  const bool ok = fgets(list, sizeof(list), f) != nullptr;
+  fclose(f);
+  if (!ok) return;
+  cpu_set_t node_cpus, cur, both;
+  CPU_ZERO(&node_cpus);
+  for (char* p = list; *p && *p != '\n';) {                 // "0-31,64-95"
+    char* end = nullptr;
+    long a = strtol(p, &end, 10), b = a;
+    if (end == p) break;
+    if (*end == '-') { p = end + 1; b = strtol(p, &end, 10); }
+    for (long k = a; k <= b && k < CPU_SETSIZE; ++k) CPU_SET((int)k, &node_cpus);
+    p = (*end == ',') ? end + 1 : end;
+  }
+  if (sched_getaffinity(0, sizeof(cur), &cur) != 0) return;
+  CPU_AND(&both, &cur, &node_cpus);
+  if (CPU_COUNT(&both) == 0 || CPU_COUNT(&both) == CPU_COUNT(&cur)) return;   // not allowed there / already confined to it
+  if (sched_setaffinity(0, sizeof(both), &both) == 0) c.numa_pinned = true;
+}
 void Context::init() {
   int n = 0;
   cudaError_t e = cudaGetDeviceCount(&n);
   if (e != cudaSuccess || n == 0)
     fatal("no CUDA device available (%s). This library has no CPU path.", cudaGetErrorString(e));
   SN_CUDA(cudaSetDevice(device));
+  numa_pin(*this);
   SN_CUDA(cudaStreamCreateWithFlags(&compute, cudaStreamNonBlocking));
   SN_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
   initialised = true;
 }
+void bump_config_epoch();
 float* get_workspace(size_t nfloats) {
   Context& c = ctx();
   if (nfloats > c.workspace_floats) {
@@ -65,6 +109,9 @@ float* get_workspace(size_t nfloats) {
     size_t want = std::max(nfloats, c.workspace_floats * 2);
     SN_CUDA(cudaMalloc(&c.workspace, want * sizeof(float)));
     c.workspace_floats = want;
+    // recorded iterations (Solver::step) carry the old pointer in their split-reduction and bias-partial launches:
+    // they must be recorded again
+    bump_config_epoch();
   }
   return c.workspace;
 }
@@ -81,7 +128,7 @@ float* alloc_guarded(size_t count, float** raw) {
 }
 Storage::~Storage() {
   if (dev_raw && owns_dev) cudaFree(dev_raw);
-  if (host) cudaFreeHost(host);
+  if (host && owns_host) cudaFreeHost(host);
 }
 void Storage::ensure_dev() {
   if (!dev) {
@@ -132,6 +179,7 @@ float* Storage::mutable_cpu() {
       memset(host, 0, count * sizeof(float));
       break;
     case AT_DEVICE:
+      if (arena) { arena->download(); break; }   // the whole arena in one copy: the other weight blobs become SYNCED
       SN_CUDA(cudaMemcpyAsync(host, dev, count * sizeof(float), cudaMemcpyDeviceToHost, c.compute));
       SN_CUDA(cudaStreamSynchronize(c.compute));
       break;
@@ -144,6 +192,45 @@ float* Storage::mutable_cpu() {
   head = AT_HOST;
   ++gen;
   return host;
+}
+// Contiguous runs of members whose `from` copy is current or identical (from-side heads and SYNCED) move in one copy
+// each; a member whose OTHER side is newer ends a run (copying over it would lose data).
+void ParamArena::download() {
+  Context& c = ctx();
+  size_t i = 0;
+  const size_t n = members.size();
+  while (i < n) {
+    if (members[i]->head != Storage::AT_DEVICE && members[i]->head != Storage::SYNCED) { ++i; continue; }
+    size_t j = i;
+    bool need = false;
+    while (j < n && (members[j]->head == Storage::AT_DEVICE || members[j]->head == Storage::SYNCED)) { need |= members[j]->head == Storage::AT_DEVICE; ++j; }
+    if (need) {
+      const size_t lo = offsets[i], hi = j < n ? offsets[j] : floats;
+      SN_CUDA(cudaMemcpyAsync(host + lo, dev + lo, (hi - lo) * sizeof(float), cudaMemcpyDeviceToHost, c.compute));
+      ++c.param_d2h_copies;
+      for (size_t k = i; k < j; ++k) members[k]->head = Storage::SYNCED;
+    }
+    i = j;
+  }
+  SN_CUDA(cudaStreamSynchronize(c.compute));
+}
+void ParamArena::upload() {
+  Context& c = ctx();
+  size_t i = 0;
+  const size_t n = members.size();
+  while (i < n) {
+    if (members[i]->head != Storage::AT_HOST && members[i]->head != Storage::SYNCED) { ++i; continue; }
+    size_t j = i;
+    bool need = false;
+    while (j < n && (members[j]->head == Storage::AT_HOST || members[j]->head == Storage::SYNCED)) { need |= members[j]->head == Storage::AT_HOST; ++j; }
+    if (need) {
+      const size_t lo = offsets[i], hi = j < n ? offsets[j] : floats;
+      SN_CUDA(cudaMemcpyAsync(dev + lo, host + lo, (hi - lo) * sizeof(float), cudaMemcpyHostToDevice, c.compute));
+      ++c.param_h2d_copies;
+      for (size_t k = i; k < j; ++k) members[k]->head = Storage::SYNCED;
+    }
+    i = j;
+  }
 }
 void Blob::reshape(const std::vector<int>& s) {
   shape = s;
@@ -195,8 +282,9 @@ const float* Layer::weights_tf32() {
   Storage* st = blobs[0]->data.get();
   const float* w = st->gpu();
   if (!w_shadow) {
-    if (net && net->arena_s && w >= net->arena_w && w < net->arena_w + net->arena_floats) {
-      w_shadow = net->arena_s + (w - net->arena_w);
+    const Net* owner = net && net->shares_with ? net->shares_with : net;   // adopted weights: their net's shadow arena
+    if (owner && owner->arena_s && w >= owner->arena_w && w < owner->arena_w + owner->arena_floats) {
+      w_shadow = owner->arena_s + (w - owner->arena_w);
       w_shadow_in_arena = true;
     } else {
       SN_CUDA(cudaMalloc(&w_shadow, st->count * sizeof(float)));
@@ -250,6 +338,39 @@ struct JavaDataLayer : Layer {
   // them inside the solver_step call (SURVEY 8b "Prefetching is allowed only inside those bounds").
   //   filled   batches whose callback has returned (helper -> caller)
   //   enqueued batches whose H2D copy has been enqueued and whose h2d_done event is recorded (caller -> helper)
+  // Byte-pixel input (sparknet_set_train_data_callback_bytes): the callback fills batch*C*H*W BYTES — what the reference
+  // holds before its callback widens them on the host (ByteImage.java:86 cropInto: `buffer[i] = red[...]`, a signed Java
+  // byte to float; Net.scala:194-221) — a quarter of the host traffic and of the H2D copy; the device widens them into
+  // the same fp32 NCHW blob: x = ((float)b - mean[(i / mean_div) % mean_period]) * scale.
+  int byte_mode = 0;                            // 0 fp32 callback, 1 signed bytes (Java), 2 unsigned bytes
+  uint8_t* pinned_b[2] = {nullptr, nullptr};
+  uint8_t* dev_b[2] = {nullptr, nullptr};
+  float* mean_dev = nullptr;
+  int mean_div = 1, mean_period = 0;
+  float byte_scale = 1.f;
+  void set_byte_mode(int mode, const float* mean, int mean_count, float scale) {
+    if (mode == 0) { byte_mode = 0; return; }
+    for (int i = 0; i < 2; ++i) {
+      if (!pinned_b[i]) SN_CUDA(cudaMallocHost(&pinned_b[i], count));
+      if (!dev_b[i]) SN_CUDA(cudaMalloc(&dev_b[i], (count + 15) / 16 * 16));
+    }
+    if (mean_dev) { SN_CUDA(cudaStreamSynchronize(ctx().compute)); cudaFree(mean_dev); mean_dev = nullptr; }
+    mean_period = 0; mean_div = 1;
+    if (mean && mean_count > 0) {
+      const size_t per_image = count / (size_t)shape[0];
+      const size_t hw = shape.size() >= 3 ? per_image / (size_t)shape[1] : 1;
+      if ((size_t)mean_count == per_image) { mean_div = 1; mean_period = mean_count; }            // mean image (C*H*W)
+      else if (shape.size() >= 3 && mean_count == shape[1]) { mean_div = (int)hw; mean_period = mean_count; }   // per channel
+      else fatal("byte input: the mean must have C*H*W = %zu or C = %d values, got %d", per_image, shape.size() >= 2 ? shape[1] : 1, mean_count);
+      SN_CUDA(cudaMalloc(&mean_dev, (size_t)mean_count * sizeof(float)));
+      SN_CUDA(cudaMemcpy(mean_dev, mean, (size_t)mean_count * sizeof(float), cudaMemcpyHostToDevice));
+    }
+    byte_scale = scale;
+    byte_mode = mode;
+  }
+  // host-side cost of the input path since the last sparknet_input_stats call
+  double cb_ns = 0, wait_ns = 0;
+  long cb_calls = 0;
   struct PrefetchSync { std::mutex m; std::condition_variable cv; };
   PrefetchSync* pf = nullptr;                   // non-null while a prefetch thread serves this layer
   long pf_filled = 0, pf_enqueued = 0;
@@ -262,7 +383,7 @@ struct JavaDataLayer : Layer {
       pf->cv.wait(lk, [&] { return pf_enqueued + 2 > k; });       // batch k-2 (same slot) has been enqueued
     }
     SN_CUDA(cudaEventSynchronize(h2d_done[slot]));                // ... and its copy has left the pinned buffer
-    cb((void*)pinned[slot], shape[0], (int)shape.size() - 1, java_shape.data());
+    cb(byte_mode ? (void*)pinned_b[slot] : (void*)pinned[slot], shape[0], (int)shape.size() - 1, java_shape.data());
     {
       std::lock_guard<std::mutex> lk(pf->m);
       pf_filled = k + 1;
@@ -273,10 +394,13 @@ struct JavaDataLayer : Layer {
   ~JavaDataLayer() override {
     for (int i = 0; i < 2; ++i) {
       if (pinned[i]) cudaFreeHost(pinned[i]);
+      if (pinned_b[i]) cudaFreeHost(pinned_b[i]);
+      if (dev_b[i]) cudaFree(dev_b[i]);
       if (devraw[i]) cudaFree(devraw[i]);
       if (count) { cudaEventDestroy(h2d_done[i]); cudaEventDestroy(consumed[i]); }
     }
     if (pool_raw) cudaFree(pool_raw);
+    if (mean_dev) cudaFree(mean_dev);
   }
   const char* type() const override { return "JavaData"; }
   void setup(const vector<Blob*>&, const vector<Blob*>& top) override {
@@ -318,16 +442,24 @@ struct JavaDataLayer : Layer {
       std::unique_lock<std::mutex> lk(pf->m);
       pf->cv.wait(lk, [&] { return pf_filled > pf_enqueued; });
     } else {
+      const auto t0 = std::chrono::steady_clock::now();
       SN_CUDA(cudaEventSynchronize(h2d_done[p]));   // pinned[p] free again (no-op the first time)
+      const auto t1 = std::chrono::steady_clock::now();
       const bool in_step = g_in_step;
       g_in_step = false;                            // a callback that reaches back into the ABI (get_data ...) counts as outside
-      cb((void*)pinned[p], shape[0], (int)shape.size() - 1, java_shape.data());
+      cb(byte_mode ? (void*)pinned_b[p] : (void*)pinned[p], shape[0], (int)shape.size() - 1, java_shape.data());
       g_in_step = in_step;
+      const auto t2 = std::chrono::steady_clock::now();
+      wait_ns += std::chrono::duration<double, std::nano>(t1 - t0).count();
+      cb_ns += std::chrono::duration<double, std::nano>(t2 - t1).count();
+      ++cb_calls;
     }
     if (consumed_valid[p]) SN_CUDA(cudaStreamWaitEvent(c.copy, consumed[p], 0));
-    SN_CUDA(cudaMemcpyAsync(devbuf[p], pinned[p], count * sizeof(float), cudaMemcpyHostToDevice, c.copy));
+    if (byte_mode) SN_CUDA(cudaMemcpyAsync(dev_b[p], pinned_b[p], count, cudaMemcpyHostToDevice, c.copy));
+    else SN_CUDA(cudaMemcpyAsync(devbuf[p], pinned[p], count * sizeof(float), cudaMemcpyHostToDevice, c.copy));
     SN_CUDA(cudaEventRecord(h2d_done[p], c.copy));
     SN_CUDA(cudaStreamWaitEvent(c.compute, h2d_done[p], 0));
+    if (byte_mode) widen_bytes(c.compute, count, dev_b[p], byte_mode == 1, mean_dev, mean_div, mean_period, byte_scale, devbuf[p]);
     st->dev = devbuf[p];
     st->head = Storage::AT_DEVICE;
     ++st->gen;
@@ -347,8 +479,14 @@ struct JavaDataLayer : Layer {
     pool = alloc_guarded((size_t)n * count, &pool_raw);
   }
   void fill_resident_slot(int i) {
-    cb((void*)pinned[0], shape[0], (int)shape.size() - 1, java_shape.data());
-    SN_CUDA(cudaMemcpy(pool + (size_t)i * count, pinned[0], count * sizeof(float), cudaMemcpyHostToDevice));
+    cb(byte_mode ? (void*)pinned_b[0] : (void*)pinned[0], shape[0], (int)shape.size() - 1, java_shape.data());
+    if (byte_mode) {
+      SN_CUDA(cudaMemcpy(dev_b[0], pinned_b[0], count, cudaMemcpyHostToDevice));
+      widen_bytes(ctx().compute, count, dev_b[0], byte_mode == 1, mean_dev, mean_div, mean_period, byte_scale, pool + (size_t)i * count);
+      SN_CUDA(cudaStreamSynchronize(ctx().compute));
+    } else {
+      SN_CUDA(cudaMemcpy(pool + (size_t)i * count, pinned[0], count * sizeof(float), cudaMemcpyHostToDevice));
+    }
   }
 };
 
@@ -781,9 +919,7 @@ struct DropoutLayer : Layer {
 struct LRNLayer : Layer {
   LrnGeom g;
   int region = 0;
-  float* scale = nullptr;
   using Layer::Layer;
-  ~LRNLayer() override { if (scale) cudaFree(scale); }
   const char* type() const override { return "LRN"; }
   void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const cp::LRNParameter& p = lp.lrn_param;
@@ -793,19 +929,18 @@ struct LRNLayer : Layer {
     SN_CHECK(bottom[0]->shape.size() == 4, "LRN %s: input must have 4 axes", lp.name.c_str());
     g.N = bottom[0]->num(); g.C = bottom[0]->channels(); g.H = bottom[0]->height(); g.W = bottom[0]->width();
     top[0]->reshape(bottom[0]->shape);
-    if (region == 0 && !scale) SN_CUDA(cudaMalloc(&scale, bottom[0]->count() * sizeof(float)));
   }
   void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const float* x = bottom[0]->data->gpu();
     float* y = top[0]->data->mutable_gpu();
-    if (region == 0) lrn_across_fwd(S(), g, x, y, scale); else lrn_within_fwd(S(), g, x, y);
+    if (region == 0) lrn_across_fwd(S(), g, x, y); else lrn_within_fwd(S(), g, x, y);
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     if (!pd[0]) return;
     const float* dy = top[0]->diff->gpu();
     const float* x = bottom[0]->data->gpu();
     float* dx = bottom[0]->diff->mutable_gpu();
-    if (region == 0) lrn_across_bwd(S(), g, x, top[0]->data->gpu(), scale, dy, dx);
+    if (region == 0) lrn_across_bwd(S(), g, x, dy, dx);
     else lrn_within_bwd(S(), g, x, dy, dx);
   }
 };
@@ -979,7 +1114,7 @@ static vector<cp::LayerParameter> insert_splits(const vector<cp::LayerParameter>
 // Net — reference caffe/src/caffe/net.cpp:40-284 (Init), 385-562 (Append*), 565-581, 635-645,
 // 737-766 (ShareTrainedLayersWith)
 // ------------------------------------------------------------------------------------------
-Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_), rng_seed(seed) {
+Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed, const Net* share_from) : phase(phase_), rng_seed(seed), shares_with(share_from) {
   cp::NetState st = in.state;
   st.phase = phase_;
   vector<cp::LayerParameter> param = insert_splits(cp::filter_net(in, st));
@@ -996,6 +1131,11 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
     std::shared_ptr<Layer> layer = create_layer(lp);
     layer->phase = lp.phase;
     layer->net = this;
+    if (share_from) {                                  // adopt the other net's parameters before setup(): no allocation, no filler
+      for (size_t k = 0; k < share_from->layers.size(); ++k)
+        if (share_from->layer_names[k] == lp.name && !share_from->layers[k]->blobs.empty()) layer->blobs = share_from->layers[k]->blobs;
+    }
+    const bool adopted = !layer->blobs.empty();
     layers.push_back(layer);
     layer_names.push_back(lp.name);
     bool need_backward = false;
@@ -1039,6 +1179,7 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
       const bool pnb = spec.lr_mult != 0.f;
       need_backward |= pnb;
       layer->param_propagate_down[(size_t)p] = pnb;
+      if (adopted) continue;                           // owned, placed and updated by the net they were adopted from
       learnable_params.push_back(layer->blobs[(size_t)p].get());
       params_lr.push_back(spec.lr_mult);
       params_decay.push_back(spec.decay_mult);
@@ -1141,6 +1282,12 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
     SN_CUDA(cudaMalloc(&arena_s, arena_floats * sizeof(float)));
     SN_CUDA(cudaMemset(arena_s, 0, arena_floats * sizeof(float)));
     owns_arena = true;
+    // pinned mirror of the weight arena: the fillers' host copies move into it, every weight blob's host pointer
+    // (what get_data hands out) points into it from now on
+    param_arena.dev = arena_w;
+    param_arena.floats = arena_floats;
+    SN_CUDA(cudaMallocHost(&param_arena.host, arena_floats * sizeof(float)));
+    memset(param_arena.host, 0, arena_floats * sizeof(float));
     for (size_t i = 0; i < learnable_params.size(); ++i) {
       Blob* b = learnable_params[i];
       SN_CHECK(b->data->dev == nullptr && b->diff->dev == nullptr, "param blob touched before arena placement");
@@ -1149,16 +1296,35 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed) : phase(phase_),
       b->diff->dev = arena_g + param_offsets[i];
       b->diff->owns_dev = false;
       b->diff->head = Storage::AT_DEVICE;   // zeroed above
+      Storage* st = b->data.get();
+      float* slot = param_arena.host + param_offsets[i];
+      if (st->host) {
+        memcpy(slot, st->host, st->count * sizeof(float));
+        if (st->owns_host) SN_CUDA(cudaFreeHost(st->host));
+      }
+      st->host = slot;
+      st->owns_host = false;
+      st->arena = &param_arena;
+      param_arena.members.push_back(st);
+      param_arena.offsets.push_back(param_offsets[i]);
     }
   }
 }
+void Net::params_to_device() {
+  if (shares_with) { const_cast<Net*>(shares_with)->params_to_device(); return; }
+  if (param_arena.host) param_arena.upload();
+}
 Net::~Net() {
+  // weight blobs may outlive this net in a net that adopted them (they are destroyed with it, right after):
+  // detach them from the arena and its mirror before both go away
+  for (Storage* st : param_arena.members) { st->arena = nullptr; st->host = nullptr; st->dev = nullptr; }
   layers.clear();
   blobs.clear();
   if (owns_arena) {
     cudaFree(arena_w);
     cudaFree(arena_g);
     cudaFree(arena_s);
+    if (param_arena.host) cudaFreeHost(param_arena.host);
   }
 }
 // after sgd_update wrote the rounded weights into the shadow arena: layers whose shadow lives there need no re-rounding
@@ -1223,9 +1389,9 @@ Solver::Solver(const cp::SolverParameter& p) : param(p) {
   if (param.random_seed >= 0) host_rng().seed((uint32_t)param.random_seed);   // solver.cpp:52-54
   const cp::NetParameter& np = param.has_train_net_param ? param.train_net_param : param.net_param;
   net.reset(new Net(np, cp::TRAIN, seed));
-  if (param.has_net_param) test_net.reset(new Net(param.net_param, cp::TEST, seed + 1));
-  else if (!param.test_net_param.empty()) test_net.reset(new Net(param.test_net_param[0], cp::TEST, seed + 1));
-  if (test_net) test_net->share_trained_layers_with(*net);
+  // the TEST net adopts the TRAIN net's parameter blobs while it is built (net.cpp:737-766): no second set of arenas
+  if (param.has_net_param) test_net.reset(new Net(param.net_param, cp::TEST, seed + 1, net.get()));
+  else if (!param.test_net_param.empty()) test_net.reset(new Net(param.test_net_param[0], cp::TEST, seed + 1, net.get()));
   const size_t n = net->arena_floats;
   if (n) {
     SN_CUDA(cudaMalloc(&arena_h, n * sizeof(float)));
@@ -1287,8 +1453,10 @@ void Solver::step(int iters) {
   uint64_t touch_seen = step_calls > 0 ? touch_at_exit : ~0ull;
   ++step_calls;
   g_in_step = true;
-  // every learnable blob's device copy must be current before the fused update touches the arena
+  // every learnable blob's device copy must be current before the fused update touches the arena: host-written weights
+  // go up in one copy of the pinned arena mirror
   // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
+  net->params_to_device();
   for (Blob* b : net->learnable_params) {
     if (b->data->head != Storage::AT_DEVICE) b->data->mutable_gpu();
     b->diff->mutable_gpu();
@@ -1321,10 +1489,11 @@ void Solver::step(int iters) {
     if (DropoutLayer* d = dynamic_cast<DropoutLayer*>(l.get())) drops.push_back(d);
   bool use_graph = graph_mode >= 0 ? graph_mode == 1 : !(getenv("SPARKNET_GRAPH") && atoi(getenv("SPARKNET_GRAPH")) == 0);
   if (param.display || prefetch || (int)feeds.size() != D || (int)drops.size() > StepScalars::kMaxDropout || !net->arena_floats) use_graph = false;
-  if (graphs_epoch != g_config_epoch) { drop_graphs(); graphs_epoch = g_config_epoch; }
   for (size_t i = 0; i < drops.size(); ++i) drops[i]->offset_slot = &scalars_dev->dropout_offset[i];
   cudaStream_t cs = ctx().compute;
   while (iter < stop_iter) {
+    // recordings of an older configuration (or of an older scratch workspace, see get_workspace) are stale
+    if (graphs_epoch != g_config_epoch) { drop_graphs(); graphs_epoch = g_config_epoch; }
     for (int i = 0; i < D; ++i) net->layers[(size_t)i]->forward(net->bottom_vecs[(size_t)i], net->top_vecs[(size_t)i]);
     // this iteration's scalars -> device memory (one tiny launch, skipped while nothing changed)
     StepScalars sc{};
@@ -1420,6 +1589,7 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
   for (auto& e : ev) SN_CUDA(cudaEventCreate(&e));
   cudaStream_t s = ctx().compute;
   // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
+  net->params_to_device();
   for (Blob* b : net->learnable_params) {
     if (b->data->head != Storage::AT_DEVICE) b->data->mutable_gpu();
     b->diff->mutable_gpu();
@@ -1458,6 +1628,7 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
 }
 void Solver::test_and_store(int num_steps, std::vector<float>* score) {   // solver.cpp:413-444
   SN_CHECK(test_net != nullptr, "solver_test: the solver has no test net");
+  net->params_to_device();
   test_net->precision = net->precision;
   test_net->share_trained_layers_with(*net);
   const int L = (int)test_net->layers.size();

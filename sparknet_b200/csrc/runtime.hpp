@@ -34,6 +34,9 @@ struct Context {
   float* workspace = nullptr;
   size_t workspace_floats = 0;
   long launches = 0;
+  long param_d2h_copies = 0, param_h2d_copies = 0;   // bulk transfers between a parameter arena and its pinned mirror
+  int numa_node = -1;               // NUMA node of the GPU (sysfs), -1 unknown
+  bool numa_pinned = false;         // the calling thread was restricted to that node's CPUs at init
   void init();
 };
 Context& ctx();       // initialises the device context on first use
@@ -44,6 +47,7 @@ float* alloc_guarded(size_t count, float** raw);   // cudaMalloc with zeroed gua
 // Storage: one buffer with a device copy and a lazily created pinned host mirror.  State machine
 // of caffe/src/caffe/syncedmem.cpp:25-153 (UNINITIALIZED / HEAD_AT_CPU / HEAD_AT_GPU / SYNCED).
 // ------------------------------------------------------------------------------------------
+struct ParamArena;
 struct Storage {
   enum Head { UNINIT, AT_HOST, AT_DEVICE, SYNCED };
   size_t count = 0;
@@ -51,6 +55,8 @@ struct Storage {
   float* dev_raw = nullptr;      // owned allocation: dev = dev_raw + kGuardFloats
   float* host = nullptr;
   bool owns_dev = true;
+  bool owns_host = true;
+  ParamArena* arena = nullptr;   // set for weight blobs: dev / host point into the net's arena and its pinned mirror
   // Every activation buffer is surrounded by guard bands: the implicit-GEMM gathers read padded filter
   // taps unconditionally (the value is then discarded), which may touch a few rows before/after a tensor.
   static constexpr size_t kGuardFloats = 4096;
@@ -64,6 +70,20 @@ struct Storage {
   float* mutable_cpu();          // host copy current and authoritative (ccaffe.cpp:181-187 get_data/get_diff)
   void ensure_dev();
   void ensure_host();
+};
+
+// The weights of a net live in ONE device arena with ONE pinned host mirror of the same layout.  The JVM
+// driver reads / writes weights blob by blob through get_data (Net.scala:132-172); moving the arena as a whole makes that
+// one bulk D2H when the first blob is asked for after device-side updates (every other blob is then SYNCED and costs
+// nothing), and one bulk H2D before the next device use of host-written weights.
+struct ParamArena {
+  float* dev = nullptr;
+  float* host = nullptr;          // pinned, arena-sized
+  size_t floats = 0;
+  std::vector<Storage*> members;  // in offset order
+  std::vector<size_t> offsets;
+  void download();                // every AT_DEVICE member -> SYNCED, contiguous runs in one copy each; synchronises
+  void upload();                  // every AT_HOST member -> SYNCED, contiguous runs in one copy each; asynchronous (compute stream)
 };
 
 struct Blob {
@@ -141,9 +161,14 @@ struct Net {
   size_t arena_floats = 0;
   std::vector<size_t> param_offsets;
   bool owns_arena = false;
+  ParamArena param_arena;               // pinned host mirror of arena_w behind every get_weight_blob handle
+  const Net* shares_with = nullptr;     // TEST net of a solver: layers of the same name use the TRAIN net's blobs (no own arena)
 
-  Net(const cp::NetParameter& param, int phase, uint64_t seed);
+  // share_from (nullable): net.cpp:737-766 ShareTrainedLayersWith applied while building — same-named layers adopt the
+  // other net's parameter blobs instead of allocating and filling their own
+  Net(const cp::NetParameter& param, int phase, uint64_t seed, const Net* share_from = nullptr);
   ~Net();
+  void params_to_device();              // host-written weights -> device in as few copies as possible
   void mark_shadows_current();
   void prepack_filters();               // all stale tf32 filter copies of the convolution layers in one launch (Solver::step)
   void forward_from_to(int start, int end);

@@ -99,6 +99,14 @@ _EXTENSIONS = {
     "sparknet_snapshot": (c_int, [c_void_p, c_char_p, c_char_p]),
     "sparknet_get_history": (c_int, [c_void_p, c_int, POINTER(c_float), ctypes.c_long]),
     "sparknet_get_pool_mask": (c_int, [c_void_p, c_int, POINTER(c_int), ctypes.c_long]),
+    "sparknet_set_train_data_callback_bytes": (c_int, [c_void_p, c_int, java_callback_t, c_int, POINTER(c_float), c_int, c_float]),
+    "sparknet_input_stats": (c_int, [c_void_p, POINTER(ctypes.c_double)]),
+    "sparknet_forward_range": (c_int, [c_void_p, c_int, c_int]),
+    "sparknet_backward_range": (c_int, [c_void_p, c_int, c_int]),
+    "sparknet_reserve_workspace": (ctypes.c_long, [ctypes.c_long]),
+    "sparknet_param_copy_counts": (None, [c_void_p, POINTER(ctypes.c_long), POINTER(ctypes.c_long)]),
+    "sparknet_numa_info": (c_int, [c_char_p, c_int]),
+    "sparknet_host_widen": (None, [c_void_p, c_void_p, ctypes.c_long, c_int, c_int]),
     # oracle-only helpers
     "oracle_pool_mask": (POINTER(c_int), [c_void_p, c_int]),
     "oracle_history": (POINTER(c_float), [c_void_p, c_int]),
