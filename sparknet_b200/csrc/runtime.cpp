@@ -193,45 +193,34 @@ float* Storage::mutable_cpu() {
   ++gen;
   return host;
 }
-// Contiguous runs of members whose `from` copy is current or identical (from-side heads and SYNCED) move in one copy
-// each; a member whose OTHER side is newer ends a run (copying over it would lose data).
+// Members whose `from` side is newest move; a run of them — with SYNCED members in between, whose bytes are the same on
+// both sides — is one copy.  A member whose OTHER side is newer ends a run (copying over it would lose data).
+static void arena_move(ParamArena& a, Storage::Head from, bool to_host) {
+  Context& c = ctx();
+  const size_t n = a.members.size();
+  size_t i = 0;
+  while (i < n) {
+    if (a.members[i]->head != from && a.members[i]->head != Storage::SYNCED) { ++i; continue; }
+    size_t j = i, first = n, last = n;
+    while (j < n && (a.members[j]->head == from || a.members[j]->head == Storage::SYNCED)) {
+      if (a.members[j]->head == from) { if (first == n) first = j; last = j; }
+      ++j;
+    }
+    if (first != n) {                               // [first, last]: SYNCED members in between ride along (same bytes both sides)
+      const size_t lo = a.offsets[first], hi = a.offsets[last] + a.members[last]->count;
+      if (to_host) SN_CUDA(cudaMemcpyAsync(a.host + lo, a.dev + lo, (hi - lo) * sizeof(float), cudaMemcpyDeviceToHost, c.compute));
+      else SN_CUDA(cudaMemcpyAsync(a.dev + lo, a.host + lo, (hi - lo) * sizeof(float), cudaMemcpyHostToDevice, c.compute));
+      ++(to_host ? c.param_d2h_copies : c.param_h2d_copies);
+      for (size_t k = first; k <= last; ++k) a.members[k]->head = Storage::SYNCED;
+    }
+    i = j;
+  }
+}
 void ParamArena::download() {
-  Context& c = ctx();
-  size_t i = 0;
-  const size_t n = members.size();
-  while (i < n) {
-    if (members[i]->head != Storage::AT_DEVICE && members[i]->head != Storage::SYNCED) { ++i; continue; }
-    size_t j = i;
-    bool need = false;
-    while (j < n && (members[j]->head == Storage::AT_DEVICE || members[j]->head == Storage::SYNCED)) { need |= members[j]->head == Storage::AT_DEVICE; ++j; }
-    if (need) {
-      const size_t lo = offsets[i], hi = j < n ? offsets[j] : floats;
-      SN_CUDA(cudaMemcpyAsync(host + lo, dev + lo, (hi - lo) * sizeof(float), cudaMemcpyDeviceToHost, c.compute));
-      ++c.param_d2h_copies;
-      for (size_t k = i; k < j; ++k) members[k]->head = Storage::SYNCED;
-    }
-    i = j;
-  }
-  SN_CUDA(cudaStreamSynchronize(c.compute));
+  arena_move(*this, Storage::AT_DEVICE, true);
+  SN_CUDA(cudaStreamSynchronize(ctx().compute));
 }
-void ParamArena::upload() {
-  Context& c = ctx();
-  size_t i = 0;
-  const size_t n = members.size();
-  while (i < n) {
-    if (members[i]->head != Storage::AT_HOST && members[i]->head != Storage::SYNCED) { ++i; continue; }
-    size_t j = i;
-    bool need = false;
-    while (j < n && (members[j]->head == Storage::AT_HOST || members[j]->head == Storage::SYNCED)) { need |= members[j]->head == Storage::AT_HOST; ++j; }
-    if (need) {
-      const size_t lo = offsets[i], hi = j < n ? offsets[j] : floats;
-      SN_CUDA(cudaMemcpyAsync(dev + lo, host + lo, (hi - lo) * sizeof(float), cudaMemcpyHostToDevice, c.compute));
-      ++c.param_h2d_copies;
-      for (size_t k = i; k < j; ++k) members[k]->head = Storage::SYNCED;
-    }
-    i = j;
-  }
-}
+void ParamArena::upload() { arena_move(*this, Storage::AT_HOST, false); }
 void Blob::reshape(const std::vector<int>& s) {
   shape = s;
   const size_t c = count();

@@ -104,6 +104,27 @@ class CaffeNet:
                 ctypes.memmove(data, batch.ctypes.data, batch.nbytes)
         return java_callback_t(invoke)
 
+    def _byte_image_cb(self, src: MinibatchSource):
+        """Callback of the byte-pixel path (sparknet_set_train_data_callback_bytes): the minibatches are int8 / uint8
+        NCHW arrays, as the reference's ByteImage holds them, and are copied as they are — the device widens them."""
+        def invoke(data, batch_size, num_dims, shape):
+            batch = src.next_image_minibatch()
+            assert batch.shape[0] == batch_size and batch.dtype.itemsize == 1
+            if self.copy_threads > 1 and batch.nbytes >= (1 << 22):
+                self.lib.sparknet_host_copy(data, batch.ctypes.data, batch.nbytes, self.copy_threads)
+            else:
+                ctypes.memmove(data, batch.ctypes.data, batch.nbytes)
+        return java_callback_t(invoke)
+
+    def _widening_image_cb(self, src: MinibatchSource, signed: bool):
+        """makeImageCallback as the reference runs it (Net.scala:194-221): the source holds bytes, the callback widens
+        them to float into the library's buffer (ByteImage.cropInto), here on `copy_threads` native threads."""
+        def invoke(data, batch_size, num_dims, shape):
+            batch = src.next_image_minibatch()
+            assert batch.shape[0] == batch_size and batch.dtype.itemsize == 1
+            self.lib.sparknet_host_widen(data, batch.ctypes.data, batch.size, 1 if signed else 0, max(1, self.copy_threads))
+        return java_callback_t(invoke)
+
     def _label_cb(self, src: MinibatchSource):                      # makeLabelCallback, Net.scala:223-233
         def invoke(data, batch_size, num_dims, shape):
             lab = src.next_label_minibatch()
@@ -113,6 +134,24 @@ class CaffeNet:
 
     def setTrainData(self, src: MinibatchSource) -> None:           # Net.scala:83-88
         self._callbacks["img_train"], self._callbacks["lab_train"] = self._image_cb(src), self._label_cb(src)
+        assert self.lib.set_train_data_callback(self.state, 0, self._callbacks["img_train"]) == 0
+        assert self.lib.set_train_data_callback(self.state, 1, self._callbacks["lab_train"]) == 0
+
+    def setTrainDataBytes(self, src: MinibatchSource, signed: bool = True, mean: Optional[np.ndarray] = None,
+                          scale: float = 1.0) -> None:
+        """setTrainData for byte pixels: `src` yields int8 (signed, the JVM's byte) or uint8 NCHW minibatches; the
+        library widens them on the device and subtracts `mean` (C*H*W or C float32 values) there."""
+        self._callbacks["img_train"], self._callbacks["lab_train"] = self._byte_image_cb(src), self._label_cb(src)
+        m = None if mean is None else np.ascontiguousarray(mean, dtype=np.float32).ravel()
+        self._callbacks["mean_train"] = m
+        mp = None if m is None else m.ctypes.data_as(ctypes.POINTER(ctypes.c_float))
+        assert self.lib.sparknet_set_train_data_callback_bytes(self.state, 0, self._callbacks["img_train"], 1 if signed else 0,
+                                                               mp, 0 if m is None else m.size, scale) == 0
+        assert self.lib.set_train_data_callback(self.state, 1, self._callbacks["lab_train"]) == 0
+
+    def setTrainDataWidening(self, src: MinibatchSource, signed: bool = True) -> None:
+        """The reference's own arrangement: byte pixels on the host, widened to float inside the fp32 callback."""
+        self._callbacks["img_train"], self._callbacks["lab_train"] = self._widening_image_cb(src, signed), self._label_cb(src)
         assert self.lib.set_train_data_callback(self.state, 0, self._callbacks["img_train"]) == 0
         assert self.lib.set_train_data_callback(self.state, 1, self._callbacks["lab_train"]) == 0
 

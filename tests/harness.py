@@ -32,6 +32,20 @@ def load_oracle():
     return load_library(ORACLE_SO, strict=False)
 
 
+def find_openblas():
+    """The OpenBLAS inside the scipy / numpy wheel and the name of its cblas_sgemm (32-bit-int interface only is usable
+    by oracle_use_blas).  The reference links OpenBLAS; the image has no other BLAS."""
+    import glob
+    import sys
+    for pat in ("scipy.libs/libscipy_openblas*.so", "numpy.libs/libscipy_openblas*.so"):
+        for sp in sys.path:
+            hits = glob.glob(os.path.join(sp, pat))
+            if hits:
+                sym = "scipy_cblas_sgemm64_" if "openblas64_" in os.path.basename(hits[0]) else "scipy_cblas_sgemm"
+                return hits[0], sym
+    return None, None
+
+
 def fptr(a: np.ndarray):
     assert a.dtype == np.float32 and a.flags["C_CONTIGUOUS"]
     return a.ctypes.data_as(ctypes.POINTER(ctypes.c_float))

@@ -1,0 +1,346 @@
+"""Parity at the sizes BASELINE.json quotes and in the mode bench.py times (TF32, tcgen05 kernels): LeNet batch 64,
+cifar10_quick / cifar10_full batch 100, CaffeNet batch 256.  The tile plans of the window kernels (persistent clusters,
+resident filters, reduction splits, two accumulator sets, two top-gradient tiles per stage) depend on batch x grid size,
+so the small-batch layer tests do not exercise what the benchmark runs.
+
+Three kinds of checks, all product (CUDA, through the C ABI) vs the CPU oracle on identical inputs and weights:
+
+1. `test_every_layer_fed_the_oracles_input`: the net is walked layer by layer on both libraries
+   (Net::ForwardFromTo / BackwardFromTo, net.cpp:565-581, 635-645); before every step the product's bottom blobs (and,
+   going backward, its top gradients) are overwritten with the ORACLE's, so each layer's error is its own and does not
+   compound.  north_star tolerance: 1e-3 relative per layer, forward and backward — held normwise (max|a-b| / max|b|)
+   AND per output channel (the same ratio over each channel / each filter / each output column on its own, so a
+   channel of small values cannot hide behind a large one).
+2. `test_free_running_net`: plain forward() + backward() of the whole net: every blob, loss, parameter gradients.
+   Errors compound over the depth and ReLU / max-pool gates that sit within TF32 rounding of zero flip, so the
+   thresholds are wider (stated at the assertions).
+3. Solver level: a 200-iteration loss trajectory in TF32 (the 1 % rule of north_star) and three CaffeNet iterations at
+   batch 256 with the `step` learning-rate policy stepping inside the run (sgd_solver.cpp:27-63).
+
+The oracle's sgemm is routed through the scipy wheel's OpenBLAS for these sizes (the reference itself links OpenBLAS;
+its summation order is unpinned either way, see the oracle's header); the naive k-ascending loops would take minutes.
+Every measured error is also written to gpurun_out/parity_baseline_sizes.json."""
+import ctypes
+import json
+import os
+
+import numpy as np
+import pytest
+
+from sparknet_b200 import zoo
+from sparknet_b200.layers import TRAIN
+from sparknet_b200.net import CaffeNet, MinibatchSource, WeightCollection
+from tests.harness import ROOT, find_openblas, fptr, rel_err, synthetic_batches
+
+pytestmark = pytest.mark.gpu
+F = np.float32
+TOL = 1e-3
+SIZES = [("lenet", 64), ("cifar10_quick", 100), ("cifar10_full", 100), ("caffenet", 256)]
+REPORT = {}
+
+
+@pytest.fixture(scope="module")
+def fast_oracle(oracle):
+    path, sym = find_openblas()
+    oracle.oracle_set_threads(os.cpu_count() or 1)
+    used = bool(path) and sym == "scipy_cblas_sgemm" and oracle.oracle_use_blas(path.encode(), sym.encode()) == 0
+    yield oracle
+    if used:
+        oracle.oracle_use_blas(None, None)
+    oracle.oracle_set_threads(1)
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "parity_baseline_sizes.json"), "w") as f:
+        json.dump(REPORT, f, indent=1, sort_keys=True)
+
+
+def channel_err(got, want, axis):
+    """max over slices along `axis` of max|got - want| / max|want|, both taken within the slice."""
+    got = np.asarray(got, dtype=np.float64)
+    want = np.asarray(want, dtype=np.float64)
+    if want.ndim < 2 or want.ndim <= axis or want.size == 0:
+        return rel_err(got, want)             # vectors (bias gradients): one slice per element would be an element-wise
+    red = tuple(i for i in range(want.ndim) if i != axis)                       # relative error of sums that cancel
+    num = np.max(np.abs(got - want), axis=red)
+    # a slice's own scale, floored at 1e-3 of the tensor's (a channel that ReLU left all but dead has no scale of its own)
+    den = np.maximum(np.max(np.abs(want), axis=red), 1e-3 * max(float(np.max(np.abs(want))), 1e-30))
+    return float(np.max(num / den))
+
+
+def train_layers(sol):
+    out = []
+    for l in sol.net_param.layer:
+        inc = getattr(l, "include", None)
+        if inc and all(r.phase != TRAIN for r in inc):
+            continue
+        out.append(l)
+    return out
+
+
+def blob_view(net, name, diff=False):
+    for i in range(net.lib.num_data_blobs(net.state)):
+        if net.lib.get_data_blob_name(net.state, i).decode() == name:
+            return net._view(net.lib.get_data_blob(net.state, i), diff)
+    raise KeyError(name)
+
+
+def weight_views(net, li, diff=False):
+    return [net._view(net.lib.get_weight_blob(net.state, li, j), diff) for j in range(net.layerNumBlobs[li])]
+
+
+def make_pair(oracle, product, name, batch, n_batches=1, **over):
+    sol = zoo.solver_with_net(name, train_bs=batch, test_bs=batch, random_seed=1701, display=0, **over)
+    o, p = CaffeNet.from_solver(sol, oracle), CaffeNet.from_solver(sol, product)
+    assert product.sparknet_set_precision(p.state, 1) == 1
+    imgs, labs = synthetic_batches(name, n_batches, batch)
+    o.setTrainData(MinibatchSource(imgs, labs))
+    p.setTrainData(MinibatchSource(imgs, labs))
+    p.setWeights(o.getWeights())
+    return sol, o, p
+
+
+def inject_masks(oracle, product, o, p, layers, seed=0):
+    rng = np.random.default_rng(seed)
+    for idx, l in enumerate(layers):
+        if l.type == "Dropout":
+            n = blob_view(o, l.top[0]).size
+            m = (rng.random(n) > 0.5).astype(np.uint32)
+            mp = m.ctypes.data_as(ctypes.POINTER(ctypes.c_uint))
+            assert oracle.sparknet_inject_dropout_mask(o.state, idx, mp, n) == 0
+            assert product.sparknet_inject_dropout_mask(p.state, idx, mp, n) == 0
+
+
+def is_inplace_relu(l):
+    return l.type == "ReLU" and list(l.bottom) == list(l.top)
+
+
+@pytest.mark.parametrize("name,batch", SIZES)
+def test_every_layer_fed_the_oracles_input(fast_oracle, product, name, batch):
+    oracle = fast_oracle
+    sol, o, p = make_pair(oracle, product, name, batch)
+    layers = train_layers(sol)
+    assert [l.name for l in layers] == o.layerNames == p.layerNames
+    inject_masks(oracle, product, o, p, layers)
+    L = len(layers)
+    report = REPORT.setdefault(f"layers/{name}_b{batch}", {})
+    failures = []
+
+    def check(what, got, want, axis, tol=TOL):
+        e, ec = rel_err(got, want), channel_err(got, want, axis)
+        report[what] = {"normwise": e, "per_channel": ec}
+        if not (e <= tol and ec <= tol):
+            failures.append(f"{what}: normwise {e:.2e}, per channel {ec:.2e} (tolerance {tol:g})")
+
+    # ---- forward: groups = a layer plus the in-place ReLUs that directly follow it (the product applies those in the
+    # producer's epilogue, the oracle as layers of their own; after the group both hold the same thing)
+    i = 0
+    while i < L:
+        j = i
+        while j + 1 < L and is_inplace_relu(layers[j + 1]) and layers[j + 1].bottom[0] in layers[i].top:
+            j += 1
+        for b in layers[i].bottom:
+            blob_view(p, b)[...] = blob_view(o, b)                          # the product sees the oracle's input
+        assert oracle.sparknet_forward_range(o.state, i, j) == 0
+        assert product.sparknet_forward_range(p.state, i, j) == 0
+        exact = layers[i].type in ("JavaData", "ReLU", "Dropout")
+        for t in layers[i].top:
+            got, want = blob_view(p, t).copy(), blob_view(o, t)
+            if exact:
+                assert np.array_equal(got, want), (layers[i].name, t)
+            else:
+                tol = 1e-5 if layers[i].type in ("Pooling", "LRN", "SoftmaxWithLoss") else TOL
+                check(f"fwd {layers[i].name} -> {t}", got, want, 1, tol)
+        i = j + 1
+    # ---- backward: groups = a layer plus the in-place ReLUs directly below it on its bottom blob (the product folds
+    # their backward into the consumer: max-pool backward / convolution backward-data epilogue)
+    for n in (o, p):
+        for li in range(L):
+            for w in weight_views(n, li, True):
+                w[...] = 0                                                    # raw backward() accumulates
+    i = L - 1
+    while i >= 0:
+        j = i
+        while j - 1 >= 0 and is_inplace_relu(layers[j - 1]) and layers[j - 1].top[0] in layers[i].bottom:
+            j -= 1
+        if layers[i].type != "JavaData":
+            for t in layers[i].top:
+                blob_view(p, t, True)[...] = blob_view(o, t, True)            # the oracle's top gradient ...
+                if layers[i].type not in ("SoftmaxWithLoss",):
+                    blob_view(p, t)[...] = blob_view(o, t)                    # ... and its forward values (gates, y of LRN)
+            for b in layers[i].bottom:
+                if not (j < i):                                               # (with a ReLU below, the bottom IS its output: keep
+                    blob_view(p, b)[...] = blob_view(o, b)                    #  what the forward walk left there on both sides)
+            assert oracle.sparknet_backward_range(o.state, i, j) == 0
+            assert product.sparknet_backward_range(p.state, i, j) == 0
+            bottoms = [b for b in layers[j].bottom if b != "label"]
+            has_param = p.layerNumBlobs[i] > 0
+            tol = TOL if has_param else 1e-5
+            if layers[i].type in ("ReLU", "Dropout"):
+                tol = 0.0
+            for b in bottoms:
+                if layers[j].type == "JavaData" or b == "data":
+                    continue
+                got, want = blob_view(p, b, True).copy(), blob_view(o, b, True)
+                if tol == 0.0:
+                    assert np.array_equal(got, want), (layers[i].name, b)
+                else:
+                    check(f"bwd {layers[i].name} -> d{b}", got, want, 1, tol)
+            for k, (g, w) in enumerate(zip(weight_views(p, i, True), weight_views(o, i, True))):
+                check(f"bwd {layers[i].name} param diff {k}", g.copy(), w, 0, TOL)
+        i = j - 1
+    o.close(); p.close()
+    assert not failures, "\n".join(failures)
+
+
+@pytest.mark.parametrize("name,batch", SIZES)
+def test_free_running_net(fast_oracle, product, name, batch):
+    """forward() + backward() of the whole net at the benchmark batch, TF32.  Forward: every blob within 3e-3 normwise
+    (1e-3 per contraction, compounding over up to eight of them) and the loss within 1e-3 relative.  Backward: gates
+    of pre-activations within TF32 rounding of zero open differently than in the oracle's fp32 forward, which moves a
+    gradient element by its full size; what is bounded is the fraction of such elements (2 %) and the relative L2
+    error of every blob's gradient and of every parameter gradient (5e-2), as in tests/test_gpu_tc.py."""
+    oracle = fast_oracle
+    sol, o, p = make_pair(oracle, product, name, batch)
+    layers = train_layers(sol)
+    inject_masks(oracle, product, o, p, layers)
+    report = REPORT.setdefault(f"net/{name}_b{batch}", {})
+    o.forward(); p.forward()
+    do, dp = o.getData(), p.getData()
+    assert list(do) == list(dp)
+    worst = 0.0
+    for k in do:
+        e = rel_err(dp[k], do[k])
+        report[f"fwd {k}"] = e
+        worst = max(worst, e)
+    lo, lp = float(do["loss"].ravel()[0]), float(dp["loss"].ravel()[0])
+    report["loss"] = [lo, lp]
+    assert np.isfinite(lp) and abs(lp - lo) <= 1e-3 * max(abs(lo), 1.0), (lo, lp)
+    assert worst <= 3e-3, {k: v for k, v in report.items() if k.startswith("fwd") and v > 3e-3}
+    del do, dp
+    o.backward(); p.backward()
+    l2 = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-30))
+    bad = {}
+    go, gp = o.getData(diff=True), p.getData(diff=True)
+    for k in go:
+        if k in ("data", "label", "loss"):
+            continue
+        e = l2(gp[k], go[k])
+        scale = max(float(np.max(np.abs(go[k]))), 1e-30)
+        frac = float(np.mean(np.abs(gp[k].astype(np.float64) - go[k]) > 1e-2 * scale))
+        report[f"bwd {k}"] = {"rel_l2": e, "frac_off_1e-2": frac}
+        if e > 5e-2 or frac > 2e-2:
+            bad[k] = (e, frac)
+    del go, gp
+    wo, wp = o.getWeightDiffs(), p.getWeightDiffs()
+    for ln in wo:
+        for j, (a, b) in enumerate(zip(wo[ln], wp[ln])):
+            e = l2(b, a)
+            report[f"param diff {ln}[{j}]"] = e
+            if e > 5e-2:
+                bad[f"{ln}[{j}]"] = e
+    o.close(); p.close()
+    assert not bad, bad
+
+
+def learnable_task(name, n_batches, batch, seed=1701):
+    """Synthetic data of the config's shape that can be learned: one fixed prototype per class plus noise, in the value
+    range of SURVEY.md 8(d) ([0,1) for LeNet, [-128,127) for cifar)."""
+    c, h, w, classes, _, _ = zoo.GEOMETRY[name]
+    rng = np.random.default_rng(seed)
+    proto = rng.random((classes, c, h, w), dtype=F)
+    imgs, labs = [], []
+    for _ in range(n_batches):
+        lab = rng.integers(0, classes, size=batch)
+        x = 0.6 * proto[lab] + 0.4 * rng.random((batch, c, h, w), dtype=F)
+        if name != "lenet":
+            x = x * F(255.0) - F(128.0)
+        imgs.append(np.ascontiguousarray(x, dtype=F))
+        labs.append(lab.astype(F))
+    return imgs, labs
+
+
+@pytest.mark.parametrize("name,batch", [("lenet", 64), ("cifar10_quick", 100)])
+def test_loss_trajectory_200_iterations_tf32(fast_oracle, product, name, batch):
+    """north_star: 'the training-loss trajectory over 200 iterations must stay within 1 %' — in the benchmarked mode
+    (TF32) at the benchmark batch.  (a) every iteration's loss within 1 % of the loss scale (the initial loss);
+    (b) within max(1 %, 3 x the oracle's own sensitivity) of the CURRENT loss, where the sensitivity is how far the
+    oracle moves from itself when its initial weights are perturbed by one TF32 rounding (2^-11 relative): SGD
+    amplifies any rounding noise once the loss has collapsed, TF32 or not."""
+    oracle = fast_oracle
+    sol = zoo.solver_with_net(name, train_bs=batch, test_bs=batch, random_seed=1701, display=0)
+    imgs, labs = learnable_task(name, 16, batch)
+    runs = {}
+    for key, lib, perturb in (("oracle", oracle, 0.0), ("oracle_eps", oracle, 2.0 ** -11), ("product", product, 0.0)):
+        n = CaffeNet.from_solver(sol, lib)
+        n.setTrainData(MinibatchSource(imgs, labs))
+        if key == "oracle":
+            w0 = n.getWeights()
+        else:
+            w = WeightCollection({k: [a.copy() for a in v] for k, v in w0.allWeights.items()}, w0.layerNames)
+            if perturb:
+                rng = np.random.default_rng(0)
+                for ln in w.layerNames:
+                    for a in w.allWeights[ln]:
+                        a *= (1 + perturb * rng.uniform(-1, 1, a.shape)).astype(F)
+            n.setWeights(w)
+        if lib is product:
+            assert product.sparknet_set_precision(n.state, 1) == 1
+            n.train(200)
+            l = np.empty(200, dtype=F)
+            assert product.sparknet_get_loss_history(n.state, fptr(l), 200) == 200
+        else:
+            l = []
+            for _ in range(200):
+                n.train(1)
+                l.append(lib.sparknet_last_loss(n.state))
+            l = np.array(l, dtype=F)
+        runs[key] = l.astype(np.float64)
+        n.close()
+    lo, le, lp = runs["oracle"], runs["oracle_eps"], runs["product"]
+    rel = lambda x: float(np.max(np.abs(x - lo) / np.maximum(np.abs(lo), 1e-3)))
+    a = float(np.max(np.abs(lp - lo)) / lo[0])
+    REPORT[f"trajectory/{name}_b{batch}"] = {"first": lo[0], "last": lo[-1], "last_product": lp[-1], "max_dev_over_initial": a,
+                                              "max_rel_dev": rel(lp), "oracle_self_rel_dev": rel(le)}
+    assert np.isfinite(lp).all()
+    if name == "lenet":
+        assert lo[-1] < 0.05 * lo[0], (lo[0], lo[-1])                  # the task is being learned
+    assert a < 0.01, a                                                 # (a)
+    assert rel(lp) < max(0.01, 3 * rel(le)), (rel(lp), rel(le))        # (b)
+
+
+def test_caffenet_three_solver_steps_with_the_step_policy(fast_oracle, product):
+    """Three solver iterations of CaffeNet at batch 256 in TF32 against the oracle, with `stepsize` 2 so that the `step`
+    learning-rate policy (sgd_solver.cpp:27-63: rate = base_lr * gamma^(iter / stepsize)) changes the rate at the third
+    iteration: weights, momentum history and the three losses.  The history after iteration 3 is
+    mu * h2 + lr3 * (g3 + wd * w): a wrong rate would be off by the factor gamma = 10.  Tolerances: weights move by
+    lr * gradient per step, so they agree far tighter than the gradients do; history / gradient-sized quantities are held
+    to a relative L2 error of 5e-2 (gate flips, see test_free_running_net)."""
+    oracle = fast_oracle
+    sol, o, p = make_pair(oracle, product, "caffenet", 256, n_batches=3, stepsize=2)
+    layers = train_layers(sol)
+    inject_masks(oracle, product, o, p, layers)
+    o.train(3); p.train(3)
+    assert product.sparknet_get_iter(p.state) == 3 == oracle.sparknet_get_iter(o.state)
+    lp = np.empty(3, dtype=F)
+    assert product.sparknet_get_loss_history(p.state, fptr(lp), 3) == 3
+    report = REPORT.setdefault("solver/caffenet_b256_3_steps", {})
+    report["losses_product"] = [float(x) for x in lp]
+    report["last_loss_oracle"] = float(oracle.sparknet_last_loss(o.state))
+    assert np.isfinite(lp).all()
+    assert abs(float(lp[2]) - report["last_loss_oracle"]) <= 2e-3 * abs(report["last_loss_oracle"])
+    wo, wp = o.getWeights(), p.getWeights()
+    l2 = lambda a, b: float(np.linalg.norm(a.astype(np.float64) - b) / max(np.linalg.norm(b.astype(np.float64)), 1e-30))
+    bad, k = {}, 0
+    for ln in wo.layerNames:
+        for j, (a, b) in enumerate(zip(wo.allWeights[ln], wp.allWeights[ln])):
+            ew = rel_err(b, a)
+            ho = np.ctypeslib.as_array(oracle.oracle_history(o.state, k), shape=(a.size,)).copy()
+            hp = np.empty(a.size, dtype=F)
+            assert product.sparknet_get_history(p.state, k, fptr(hp), hp.size) == 0
+            eh = l2(hp, ho)
+            report[f"{ln}[{j}]"] = {"weights_rel_err": ew, "history_rel_l2": eh}
+            if ew > 1e-3 or eh > 5e-2:
+                bad[f"{ln}[{j}]"] = (ew, eh)
+            k += 1
+    o.close(); p.close()
+    assert not bad, bad
