@@ -181,6 +181,9 @@ float sparknet_timer_stop_ms(caffenet_state* state);
 /* Run ONE training iteration with events around every layer (consumes one callback pair).  Fills
  * per-layer forward/backward milliseconds (n = capacity) and the update time; returns the layer count. */
 int sparknet_profile_step(caffenet_state* state, float* fwd_ms, float* bwd_ms, float* update_ms, int n);
+/* Kernels each layer launched (forward / backward) in the iteration sparknet_profile_step ran last; 0 = the layer's work
+ * rode in another layer's kernel.  Returns the layer count. */
+int sparknet_profile_launches(caffenet_state* state, int* fwd, int* bwd, int n);
 /* out[i] = (((r0[i] + r1[i]) + ...) / n in IEEE fp32, replica order; all pointers are device pointers
  * on the current device (single-GPU emulation of the cross-GPU exchange; the arithmetic is the same). */
 int sparknet_average_replicas_device(const void* const* replicas, int n, long count, void* out);

@@ -1585,14 +1585,20 @@ void Solver::step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_m
   }
   net->overwrite_param_diffs = true;
   net->loss_log = loss_hist + (iter % kLossHist);
+  profile_launches_fwd.assign((size_t)L, 0);
+  profile_launches_bwd.assign((size_t)L, 0);
   for (int i = 0; i < L; ++i) {
     SN_CUDA(cudaEventRecord(ev[(size_t)i], s));
+    const long l0 = ctx().launches;
     net->layers[(size_t)i]->forward(net->bottom_vecs[(size_t)i], net->top_vecs[(size_t)i]);
+    profile_launches_fwd[(size_t)i] = (int)(ctx().launches - l0);
   }
   for (int i = L - 1; i >= 0; --i) {
     SN_CUDA(cudaEventRecord(ev[(size_t)(L + (L - 1 - i))], s));
+    const long l0 = ctx().launches;
     if (net->layer_need_backward[(size_t)i])
       net->layers[(size_t)i]->backward(net->top_vecs[(size_t)i], net->bottom_need_backward[(size_t)i], net->bottom_vecs[(size_t)i]);
+    profile_launches_bwd[(size_t)i] = (int)(ctx().launches - l0);
   }
   SN_CUDA(cudaEventRecord(ev[(size_t)(2 * L)], s));
   const float rate = get_learning_rate();

@@ -212,6 +212,7 @@ struct Solver {
   float get_learning_rate();
   void step(int iters);
   void step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_ms, float* update_ms);
+  std::vector<int> profile_launches_fwd, profile_launches_bwd;   // kernels each layer launched in the last profiled iteration
   void test_and_store(int num_steps, std::vector<float>* score);
 };
 

@@ -95,6 +95,7 @@ _EXTENSIONS = {
     "sparknet_timer_stop_ms": (c_float, [c_void_p]),
     "sparknet_profile_step": (c_int, [c_void_p, POINTER(c_float), POINTER(c_float), POINTER(c_float), c_int]),
     "sparknet_get_loss_history": (c_int, [c_void_p, POINTER(c_float), c_int]),
+    "sparknet_profile_launches": (c_int, [c_void_p, POINTER(c_int), POINTER(c_int), c_int]),
     "sparknet_host_copy": (None, [c_void_p, c_void_p, ctypes.c_long, c_int]),
     "sparknet_snapshot": (c_int, [c_void_p, c_char_p, c_char_p]),
     "sparknet_get_history": (c_int, [c_void_p, c_int, POINTER(c_float), ctypes.c_long]),

@@ -65,8 +65,11 @@ class Averager:
             self.dist.broadcast(self.arena, src=0)
         self.stream.synchronize()
 
-    def average(self) -> float:
-        """Average the weights of all replicas in place; returns the device time in ms."""
+    def drain(self) -> float:
+        return 0.0
+
+    def average(self, sync: bool = True) -> float:
+        """Average the weights of all replicas in place; returns the device time in ms (always synchronous)."""
         if self.world == 1:
             return 0.0
         self._touch()
@@ -116,6 +119,7 @@ class PeerAverager:
         self.stream = torch.cuda.ExternalStream(lib.sparknet_compute_stream(net.state))
         self.ev0 = torch.cuda.Event(enable_timing=True)
         self.ev1 = torch.cuda.Event(enable_timing=True)
+        self._pending, self._spare = [], []
 
     def broadcast_from_rank0(self) -> None:
         """All replicas start from rank 0's weights (the driver's first broadcast, CifarApp.scala:92-99)."""
@@ -127,17 +131,42 @@ class PeerAverager:
             self.dist.broadcast(self.arena, src=0)
         self.stream.synchronize()
 
-    def average(self) -> float:
-        """Average the weights of all replicas in place; returns the device time in ms (includes waiting for the
-        slowest replica to arrive)."""
+    def average(self, sync: bool = True) -> float:
+        """Average the weights of all replicas in place.  sync=True (default): waits for the exchange, checks that no
+        replica timed out and returns the device time in ms (it includes waiting for the slowest replica to arrive).
+        sync=False: only enqueues the exchange — the host goes on to the next round's first data callback while it
+        runs; the time is collected by `drain()`."""
         if self.world == 1:
+            return 0.0
+        if not sync:
+            ev0 = self._spare.pop() if self._spare else self.torch.cuda.Event(enable_timing=True)
+            ev1 = self._spare.pop() if self._spare else self.torch.cuda.Event(enable_timing=True)
+            ev0.record(self.stream)
+            rc = self.lib.sparknet_average_peers(self.net.state)
+            assert rc == 0, rc
+            ev1.record(self.stream)
+            self._pending.append((ev0, ev1))
             return 0.0
         self.ev0.record(self.stream)
         rc = self.lib.sparknet_average_peers(self.net.state)
         assert rc == 0, rc
         self.ev1.record(self.stream)
         self.ev1.synchronize()
+        self.check()                                   # weights are undefined after a time-out: never train on
         return float(self.ev0.elapsed_time(self.ev1))
+
+    def drain(self) -> float:
+        """Wait for the exchanges enqueued with sync=False, check their status, return their summed device time in ms."""
+        if self.world == 1:
+            return 0.0
+        total = 0.0
+        for ev0, ev1 in self._pending:
+            ev1.synchronize()
+            total += float(ev0.elapsed_time(ev1))
+            self._spare += [ev0, ev1]
+        self._pending = []
+        self.check()
+        return total
 
     def timing(self):
         """(rounds, mean ms waiting for the slowest replica, mean ms of the exchange proper) since the last call,
@@ -225,3 +254,5 @@ def run_rounds(net, averager, tau: int, rounds: int) -> None:
     for _ in range(rounds):
         net.train(tau)
         averager.average()
+    if hasattr(averager, "check"):
+        averager.check()
