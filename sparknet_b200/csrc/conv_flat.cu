@@ -75,6 +75,10 @@ struct WinEpi {
   int ld; size_t split_stride;
   const float* gate;        // backward-data only: same shape as dst; dst = (gate > 0) ? value : 0  (the backward of an in-place
                             // ReLU below this layer, relu_layer.cu:35-41, applied while the gradient is written)
+  // forward only (nullable): the flat grid of the NEXT window convolution, which reads this layer's output.  The epilogue
+  // writes every value a second time there, rounded to tf32, channels-last (64 contiguous bytes per thread):
+  // flat[(flat_lead + img * flat_Gp + h * flat_Wp + w) * flat_C + channel] — the consumer's pack kernel has nothing left to do.
+  float* flat; int flat_lead, flat_Gp, flat_Wp, flat_C;
 };
 
 // CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2 along x) runs every MMA with M = 256: each CTA keeps its
@@ -201,11 +205,23 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
 #pragma unroll
           for (int j = 0; j < 16; ++j) p[(size_t)j * plane] = __uint_as_float(v[j]) * (gv[j] > 0.f ? 1.f : 0.f);   // relu_g() of kernels.cu
         } else if (ok) {
+          float o[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             float acc = __uint_as_float(v[j]) + bias[j];
             if (ep.relu) acc = fmaxf(acc, 0.f);
             p[(size_t)j * plane] = acc;
+            o[j] = acc;
+          }
+          if (ep.flat) {
+            uint32_t img, rem, h, w;
+            ep.dGp.divmod((uint32_t)m, img, rem);
+            ep.dWp.divmod(rem, h, w);
+            float4* f = reinterpret_cast<float4*>(ep.flat + ((size_t)ep.flat_lead + (size_t)img * ep.flat_Gp + (size_t)h * ep.flat_Wp + w) * ep.flat_C +
+                                                  chan0 + n0 + c0);
+#pragma unroll
+            for (int j = 0; j < 16; j += 4)
+              f[j >> 2] = make_float4(to_tf32_exact(o[j]), to_tf32_exact(o[j + 1]), to_tf32_exact(o[j + 2]), to_tf32_exact(o[j + 3]));
           }
         }
       }
@@ -645,7 +661,8 @@ bool tcw_supported(const ConvGeom& g) {
 }
 
 // `xflat`: packed input (tc_flat_pack, input side); `wf`: tc_flat_pack_filter(dgrad = false)
-void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu) {
+void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu,
+                  const FlatOut* next) {
   const FlatGeom f = tc_flat_geom(g);
   const int Cg = g.Cg(), Og = g.Og(), T = g.kh * g.kw, Ptot = g.N * f.Gp, slots = slots_of(Cg), kp = T * slots;
   const int span = (g.kh - 1) * f.Wp + g.kw - 1;
@@ -655,7 +672,11 @@ void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const f
   const CUtensorMap tmB = tc_make_tmap(wf, (uint64_t)kp, (uint64_t)g.Cout, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - (g.ph * f.Wp + g.pw), pl.MT, pl.n_mma, slots / 32, Cg, slots, Cg, Og,
             pl.box_rows, pl.nbox, pl.nstage, nullptr, 2, 1, slots / 32, 0};
-  WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0, nullptr};
+  WinEpi ep{y, bias, g.Ho, g.Wo, g.Cout, Og, relu ? 1 : 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0, nullptr, nullptr, 0, 0, 0, 0};
+  if (next && next->flat) {
+    if (next->C != g.Cout || (next->C % 4) != 0) fatal("window convolution: the consumer's flat grid has %d channels, this layer writes %d", next->C, g.Cout);
+    ep.flat = next->flat; ep.flat_lead = next->lead; ep.flat_Gp = next->Gp; ep.flat_Wp = next->Wp; ep.flat_C = next->C;
+  }
   launch_window(s, tmA, tmB, a, ep, pl, Og, g.group);
 }
 // `dyflat`: packed top gradient (tc_flat_pack, output side); `wt`: tc_flat_pack_filter(dgrad = true)
@@ -669,7 +690,7 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
   const CUtensorMap tmB = tc_make_tmap(wt, (uint64_t)kp, (uint64_t)g.C, (uint64_t)kp * 4, (uint32_t)(pl.n_mma / pl.cg), false);
   WinArgs a{Ptot, f.Wp, g.kw, T, f.lead - ((g.kh - 1 - g.ph) * f.Wp + (g.kw - 1 - g.pw)), pl.MT, pl.n_mma, slots / 32, Og, slots,
             Og, Cg, pl.box_rows, pl.nbox, pl.nstage, nullptr, 2, 1, slots / 32, 0};
-  WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0, relu_gate};
+  WinEpi ep{dx, nullptr, g.H, g.W, g.C, Cg, 0, FastDiv(f.Gp), FastDiv(f.Wp), 0, 0, relu_gate, nullptr, 0, 0, 0, 0};
   launch_window(s, tmA, tmB, a, ep, pl, Cg, g.group);
 }
 
@@ -726,7 +747,7 @@ void tcw_matmul(cudaStream_t s, int M, int N, int K, const float* A, const float
   float* dst = out;
   size_t stride = 0;
   if (splits > 1) { stride = (size_t)M * N; dst = get_workspace(stride * splits); }
-  WinEpi ep{dst, bias, 1, 1, N, N, relu ? 1 : 0, FastDiv(1), FastDiv(1), N, stride, nullptr};
+  WinEpi ep{dst, bias, 1, 1, N, N, relu ? 1 : 0, FastDiv(1), FastDiv(1), N, stride, nullptr, nullptr, 0, 0, 0, 0};
   launch_window(s, tmA, tmB, a, ep, pl, N, 1);
   if (splits > 1) {
     const size_t total = (size_t)M * N;

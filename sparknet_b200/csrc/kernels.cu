@@ -25,6 +25,11 @@ static inline int grid_for(size_t work_items, int block, int max_waves = 8) {
   return (int)b;
 }
 
+__device__ __forceinline__ float round_tf32_rna(float x) {      // cvt.rna.tf32.f32: what the packed tensor-core operands hold
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -817,7 +822,8 @@ static int lrn_chunk() {
   return ch == 8 || ch == 32 ? ch : 16;
 }
 template <int SIZE, int CH>
-__global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x, float* __restrict__ y) {
+__global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x, float* __restrict__ y,
+                                                                   FlatOut fo, FastDiv dW) {
   constexpr int PRE = (SIZE - 1) / 2;
   const int HW = g.H * g.W;
   const float aos = g.alpha / g.size;
@@ -835,15 +841,28 @@ __global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, in
       v[j] = (c >= 0 && c < g.C) ? xp[(size_t)c * HW] : 0.f;
     }
     float* yp = y + ((size_t)n * g.C) * HW + pix;
+    float o[CH];
 #pragma unroll
     for (int j = 0; j < CH; ++j) {
+      o[j] = 0.f;
       if (c0 + j < g.C) {
         float acc = 0.f;
 #pragma unroll
         for (int t = 0; t < SIZE; ++t) acc += v[j + t] * v[j + t];
         const float sc = g.k + acc * aos;
-        yp[(size_t)(c0 + j) * HW] = v[j + PRE] * lrn_pow_neg(sc, g.beta, is075);
+        o[j] = v[j + PRE] * lrn_pow_neg(sc, g.beta, is075);
+        yp[(size_t)(c0 + j) * HW] = o[j];
       }
+    }
+    if (fo.flat) {
+      // second copy for the window convolution that reads this blob: its flat grid, channels-last, rounded to tf32 — this
+      // thread's CH channels are contiguous there (the consumer's pack kernel then has nothing to do)
+      uint32_t h, w;
+      dW.divmod((uint32_t)pix, h, w);
+      float4* f = reinterpret_cast<float4*>(fo.flat + ((size_t)fo.lead + (size_t)n * fo.Gp + (size_t)h * fo.Wp + w) * fo.C + c0);
+#pragma unroll
+      for (int j = 0; j < CH; j += 4)
+        if (c0 + j + 3 < g.C) f[j >> 2] = make_float4(round_tf32_rna(o[j]), round_tf32_rna(o[j + 1]), round_tf32_rna(o[j + 2]), round_tf32_rna(o[j + 3]));
     }
   }
 }
@@ -851,11 +870,17 @@ static void lrn_size_check(const LrnGeom& g) {
   if (g.size != 3 && g.size != 5 && g.size != 7 && g.size != 9 && g.size != 11)
     fatal("LRN ACROSS_CHANNELS: local_size %d is not on the supported path (odd sizes 3..11)", g.size);
 }
-void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y) {
+void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, const FlatOut* next) {
   lrn_size_check(g);
   const int CHn = g.size > 5 ? 16 : lrn_chunk(), chunks = (g.C + CHn - 1) / CHn;
   const size_t total = (size_t)g.N * chunks * g.H * g.W;
-#define SN_LRN_F(SZ, CHV) lrn_across_fwd_chunk_kernel<SZ, CHV><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y)
+  FlatOut fo{nullptr, 0, 0, 0, 0};
+  if (next && next->flat) {
+    if (next->C != g.C || g.C % 4 != 0) fatal("lrn: the consumer's flat grid has %d channels, this layer writes %d", next->C, g.C);
+    fo = *next;
+  }
+  const FastDiv dW((uint32_t)g.W);
+#define SN_LRN_F(SZ, CHV) lrn_across_fwd_chunk_kernel<SZ, CHV><<<grid_for(total, 128, 32), 128, 0, s>>>(g, chunks, x, y, fo, dW)
   if (g.size == 5) { if (CHn == 8) SN_LRN_F(5, 8); else if (CHn == 32) SN_LRN_F(5, 32); else SN_LRN_F(5, 16); }
   else if (g.size == 3) { if (CHn == 8) SN_LRN_F(3, 8); else if (CHn == 32) SN_LRN_F(3, 32); else SN_LRN_F(3, 16); }
   else if (g.size == 7) SN_LRN_F(7, 16);
@@ -1154,11 +1179,6 @@ __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict_
 // summed over the batch rows as the bias gradient (inner_product_layer.cpp:100-104 caffe_cpu_gemv).  One pass does both:
 // block = 32 float4 columns x 8 row groups, each thread walks rows rg, rg + 8, ..., the eight partial sums are added
 // in row-group order (fixed order, no atomics).  cols % 4 == 0.
-__device__ __forceinline__ float round_tf32_rna(float x) {
-  uint32_t r;
-  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
-  return __uint_as_float(r);
-}
 __global__ void __launch_bounds__(256) ip_round_bias_kernel(int rows, int cols4, const float4* __restrict__ dy, float4* __restrict__ dy_r,
                                                             float* __restrict__ db, int accumulate) {
   __shared__ float4 part[8][32];

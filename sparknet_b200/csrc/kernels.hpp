@@ -47,12 +47,20 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad);
 // dst zeroed once by the owner; db (nullable) = bias gradient summed in the same pass over the top gradient
 void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db = nullptr,
                   bool accumulate = false, int src_channels = 0);   // src_channels < g.C: the remaining packed channels are zeros
+struct PoolGeom;
+// packed top gradient of convolution g = backward of the MAX pooling layer pg above it (+ the ReLU gate), in one pass
+void tc_flat_pack_pool_bwd(cudaStream_t s, const ConvGeom& g, const PoolGeom& pg, const float* pooled_dy, const int* mask, const float* gate,
+                           float* dx, float* dst, float* db, bool accumulate);
 void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst, int src_cg = 0);   // src_cg < g.Cg() (forward layout): zero slots
 void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
 void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);
 void tc_conv_wgrad_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* dyflat, float* dw, bool accumulate);
 // window kernels (conv_flat.cu): same packed operands, one TMA load of the grid rows per channel block serves every tap
-void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
+// A producer that also writes its output into the flat grid of the window convolution that reads it (tf32-rounded,
+// channels-last; bands untouched = zero): flat[(lead + img*Gp + h*Wp + w) * C + c].  Saves the consumer's pack launch.
+struct FlatOut { float* flat; int lead, Gp, Wp, C; };
+void tcw_conv_fwd(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu,
+                  const FlatOut* next = nullptr);
 void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx, const float* relu_gate = nullptr);
 bool tcw_supported(const ConvGeom& g);
 bool tcw_wgrad_supported(const ConvGeom& g);
@@ -102,7 +110,7 @@ void dropout_bwd(cudaStream_t s, size_t n, const float* dy, const uint8_t* mask,
 
 struct LrnGeom { int N, C, H, W, size; float alpha, beta, k; };
 // across channels, odd local_size 3..11; nothing but y is kept: the backward pass recomputes the scale from x
-void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y);
+void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, const FlatOut* next = nullptr);
 void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx);
 void lrn_within_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y);
 void lrn_within_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const float* dy, float* dx);

@@ -531,22 +531,61 @@ struct ConvolutionLayer : Layer {
     param_propagate_down.assign(blobs.size(), true);
     top[0]->reshape({g.N, g.Cout, g.Ho, g.Wo});
   }
+  // The window convolution that reads this layer's output (through nothing but an in-place ReLU this layer applies
+  // itself) gets its packed, tf32-rounded, channels-last input straight from this layer's epilogue: one pack launch and
+  // one pass over the tensor less per iteration.  Set by Net::Net; SPARKNET_FUSE_PACK=0 turns it off.
+  ConvolutionLayer* flat_consumer = nullptr;
+  bool takes_flat_input() { return net->precision == PREC_TF32 && !use_s2d() && use_flat(1); }
+  FlatOut flat_target() {
+    if (!xflat) xflat = flat_alloc(g.C);
+    const FlatGeom f = tc_flat_geom(g);
+    return FlatOut{xflat, f.lead, f.Gp, f.Wp, g.C};
+  }
+  void flat_written(Blob* src) { xflat_src = src->data.get(); xflat_gen = src->data->gen; }
   void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const float* x = bottom[0]->data->gpu();
     const float* b = bias_term ? blobs[1]->data->gpu() : nullptr;
     float* y = top[0]->data->mutable_gpu();
+    FlatOut fo{nullptr, 0, 0, 0, 0};
+    const bool feed_next = flat_consumer && flat_consumer->takes_flat_input();
+    if (feed_next) fo = flat_consumer->flat_target();
+    bool fed = false;
     if (net->precision == PREC_TF32 && use_s2d()) {
-      tcw_conv_fwd(S(), gs, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
+      tcw_conv_fwd(S(), gs, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu, feed_next ? &fo : nullptr);
+      fed = feed_next;
     } else if (net->precision == PREC_TF32 && use_flat(1)) {
-      if (use_window()) tcw_conv_fwd(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
+      if (use_window()) { tcw_conv_fwd(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu, feed_next ? &fo : nullptr); fed = feed_next; }
       else tc_conv_fwd_flat(S(), g, packed_input(bottom[0]), packed_filter(false), b, y, fuse_relu);
     } else if (net->precision == PREC_TF32) tc_conv_fwd(S(), g, x, weights_tf32(), b, y, fuse_relu);
     else ffma_conv_fwd(S(), g, x, blobs[0]->data->gpu(), b, y, fuse_relu);
+    if (fed) flat_consumer->flat_written(top[0]);
   }
   // ---- flat-grid operands (gemm_tc.cu "flat-grid convolution"): packed copies owned by the layer ----
   float *xflat = nullptr, *dyflat = nullptr, *wflat[2] = {nullptr, nullptr};
   uint64_t xflat_gen = ~0ull, wflat_gen[2] = {~0ull, ~0ull};
   const Storage* xflat_src = nullptr;
+  // the packed top gradient may already be current: the MAX pooling layer above wrote it while computing its backward
+  // (pack_dy_from_pool), together with this layer's bias gradient
+  uint64_t dyflat_gen = ~0ull;
+  const Storage* dyflat_src = nullptr;
+  bool need_dx = false;                               // bottom_need_backward of this layer (set by Net::Net)
+  bool dy_is_packed(Blob* top) const { return dyflat && dyflat_src == top->diff.get() && dyflat_gen == top->diff->gen; }
+  bool wants_packed_dy() {
+    if (net->precision != PREC_TF32) return false;
+    if (use_s2d()) return param_propagate_down[0];
+    return (use_flat(2) && param_propagate_down[0]) || (use_flat(4) && need_dx);
+  }
+  // pg: the pooling layer's geometry; pooled_dy / mask / gate: its top diff, argmax mask and (nullable) top data; dx: this
+  // layer's NCHW top diff, written too.  See gemm_tc.cu tc_flat_pack_pool_bwd.
+  void pack_dy_from_pool(const PoolGeom& pg, const float* pooled_dy, const int* mask, const float* gate, float* dx, Blob* top) {
+    const ConvGeom& pgm = use_s2d() ? gs : g;
+    if (!dyflat) dyflat = flat_alloc(pgm.Cout);
+    const bool want_db = bias_term && param_propagate_down[1];
+    tc_flat_pack_pool_bwd(S(), pgm, pg, pooled_dy, mask, gate, dx, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr,
+                          !net->overwrite_param_diffs);
+    dyflat_src = top->diff.get();
+    dyflat_gen = top->diff->gen;
+  }
   int flat_ok = -1;
   // SPARKNET_CONV_FLAT: bit 0 forward, bit 1 backward-filter, bit 2 backward-data (default 7; 0 = gather kernels only)
   bool use_flat(int bit) {
@@ -658,7 +697,7 @@ struct ConvolutionLayer : Layer {
     if (tf32 && use_s2d() && param_propagate_down[0]) {
       // folded layer: pack the top gradient on the folded grid (+ bias gradient), window backward-filter, unfold dW
       if (!dyflat) dyflat = flat_alloc(gs.Cout);
-      tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
+      if (!dy_is_packed(top[0])) tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
       if (!dws) SN_CUDA(cudaMalloc(&dws, (size_t)gs.Cout * gs.C * gs.kh * gs.kw * sizeof(float)));
       tcw_conv_wgrad(S(), gs, packed_input(bottom[0]), dyflat, dws, false);
       if (cpad()) tcw_cpad_unpack_wgrad(S(), g, gs.C, dws, blobs[0]->diff->mutable_gpu(), acc);
@@ -672,8 +711,8 @@ struct ConvolutionLayer : Layer {
     }
     if (flat_w || flat_d) {
       if (!dyflat) dyflat = flat_alloc(g.Cout);
-      // one pass over the top gradient packs it and sums the bias gradient
-      tc_flat_pack(S(), g, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
+      // one pass over the top gradient packs it and sums the bias gradient (unless the pooling layer above already did both)
+      if (!dy_is_packed(top[0])) tc_flat_pack(S(), g, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
     } else if (want_db) {
       conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
     }
@@ -800,6 +839,10 @@ struct PoolingLayer : Layer {
   int method = 0;
   int* mask = nullptr;
   bool gate_relu = false;     // the bottom is the output of an in-place ReLU whose backward is folded into this layer's
+  // MAX pooling right above a convolution (through nothing but that ReLU): this layer's backward also writes the
+  // convolution's packed top gradient and bias gradient (ConvolutionLayer::pack_dy_from_pool).  Set by Net::Net;
+  // SPARKNET_FUSE_POOL_PACK=0 turns it off.
+  ConvolutionLayer* dy_consumer = nullptr;
   using Layer::Layer;
   ~PoolingLayer() override { if (mask) cudaFree(mask); }
   const char* type() const override { return "Pooling"; }
@@ -837,7 +880,9 @@ struct PoolingLayer : Layer {
     if (!pd[0]) return;
     const float* dy = top[0]->diff->gpu();
     float* dx = bottom[0]->diff->mutable_gpu();
-    if (method == 0) pool_max_bwd(S(), g, dy, mask, dx, gate_relu ? top[0]->data->gpu() : nullptr);
+    if (method == 0 && dy_consumer && dy_consumer->wants_packed_dy())
+      dy_consumer->pack_dy_from_pool(g, dy, mask, gate_relu ? top[0]->data->gpu() : nullptr, dx, bottom[0]);
+    else if (method == 0) pool_max_bwd(S(), g, dy, mask, dx, gate_relu ? top[0]->data->gpu() : nullptr);
     else pool_ave_bwd(S(), g, dy, dx);
   }
 };
@@ -908,6 +953,7 @@ struct DropoutLayer : Layer {
 struct LRNLayer : Layer {
   LrnGeom g;
   int region = 0;
+  ConvolutionLayer* flat_consumer = nullptr;   // see ConvolutionLayer::flat_consumer
   using Layer::Layer;
   const char* type() const override { return "LRN"; }
   void setup(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
@@ -922,7 +968,15 @@ struct LRNLayer : Layer {
   void forward(const vector<Blob*>& bottom, const vector<Blob*>& top) override {
     const float* x = bottom[0]->data->gpu();
     float* y = top[0]->data->mutable_gpu();
-    if (region == 0) lrn_across_fwd(S(), g, x, y); else lrn_within_fwd(S(), g, x, y);
+    if (region == 0) {
+      FlatOut fo{nullptr, 0, 0, 0, 0};
+      const bool feed_next = flat_consumer && flat_consumer->takes_flat_input();
+      if (feed_next) fo = flat_consumer->flat_target();
+      lrn_across_fwd(S(), g, x, y, feed_next ? &fo : nullptr);
+      if (feed_next) flat_consumer->flat_written(top[0]);
+    } else {
+      lrn_within_fwd(S(), g, x, y);
+    }
   }
   void backward(const vector<Blob*>& top, const vector<bool>& pd, const vector<Blob*>& bottom) override {
     if (!pd[0]) return;
@@ -1253,6 +1307,63 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed, const Net* share
       if (!pl || pl->method != 0) continue;
       pl->gate_relu = true;
       r->bwd_fused_by_consumer = true;
+    }
+  }
+  // Producer-side packing: a window convolution whose input blob is computed by another convolution or an
+  // across-channel LRN (and rewritten by nothing but in-place ReLUs the producer applies itself) has its flat grid
+  // written by that producer.  SPARKNET_FUSE_PACK=0 turns it off.
+  {
+    const char* e = getenv("SPARKNET_FUSE_PACK");
+    const bool enabled = !(e && atoi(e) == 0);
+    for (int lj = 0; enabled && lj < L; ++lj) {
+      ConvolutionLayer* consumer = dynamic_cast<ConvolutionLayer*>(layers[(size_t)lj].get());
+      if (!consumer || bottom_vecs[(size_t)lj].size() != 1) continue;
+      Blob* xb = bottom_vecs[(size_t)lj][0];
+      int prod = -1;
+      bool clean = true;
+      for (int li = 0; li < lj; ++li)
+        for (Blob* t : top_vecs[(size_t)li]) {
+          if (t != xb) continue;
+          const bool inplace = !bottom_vecs[(size_t)li].empty() && bottom_vecs[(size_t)li][0] == xb;
+          if (!inplace) { prod = li; continue; }
+          ReLULayer* r = dynamic_cast<ReLULayer*>(layers[(size_t)li].get());
+          if (!(r && r->fused_by_producer)) clean = false;
+        }
+      if (prod < 0 || !clean) continue;
+      if (ConvolutionLayer* p = dynamic_cast<ConvolutionLayer*>(layers[(size_t)prod].get())) p->flat_consumer = consumer;
+      else if (LRNLayer* n = dynamic_cast<LRNLayer*>(layers[(size_t)prod].get())) { if (n->region == 0) n->flat_consumer = consumer; }
+    }
+  }
+  for (int li = 0; li < L; ++li)
+    if (ConvolutionLayer* c = dynamic_cast<ConvolutionLayer*>(layers[(size_t)li].get()))
+      c->need_dx = layer_need_backward[(size_t)li] && !bottom_need_backward[(size_t)li].empty() && bottom_need_backward[(size_t)li][0];
+  // Top-gradient packing by the pooling layer above: MAX pool whose bottom blob is computed by a convolution, read by
+  // nothing else and rewritten in between only by an in-place ReLU whose backward the pool applies itself.
+  {
+    const char* e = getenv("SPARKNET_FUSE_POOL_PACK");
+    const bool enabled = !(e && atoi(e) == 0);
+    for (int lj = 0; enabled && lj < L; ++lj) {
+      PoolingLayer* pool = dynamic_cast<PoolingLayer*>(layers[(size_t)lj].get());
+      if (!pool || pool->method != 0 || !layer_need_backward[(size_t)lj] || !bottom_need_backward[(size_t)lj][0]) continue;
+      Blob* xb = bottom_vecs[(size_t)lj][0];
+      int prod = -1, readers = 0;
+      bool clean = true;
+      for (int li = 0; li < L; ++li) {
+        if (li != lj)
+          for (Blob* b : bottom_vecs[(size_t)li]) {
+            const bool inplace = !top_vecs[(size_t)li].empty() && top_vecs[(size_t)li][0] == xb;
+            if (b == xb && !inplace) ++readers;
+          }
+        for (Blob* t : top_vecs[(size_t)li]) {
+          if (t != xb) continue;
+          const bool inplace = !bottom_vecs[(size_t)li].empty() && bottom_vecs[(size_t)li][0] == xb;
+          if (!inplace) { prod = li; continue; }
+          ReLULayer* r = dynamic_cast<ReLULayer*>(layers[(size_t)li].get());
+          if (!(r && r->bwd_fused_by_consumer && pool->gate_relu)) clean = false;
+        }
+      }
+      if (prod < 0 || prod > lj || !clean || readers != 0) continue;
+      if (ConvolutionLayer* p = dynamic_cast<ConvolutionLayer*>(layers[(size_t)prod].get())) pool->dy_consumer = p;
     }
   }
   // Parameter arena: one contiguous device allocation for all weights and one for all gradients;

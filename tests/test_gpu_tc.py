@@ -263,3 +263,44 @@ def test_nets_forward_tf32(oracle, product, name, batch):
     for k in do:
         assert rel_err(dp[k], do[k]) <= 3 * TOL, (k, rel_err(dp[k], do[k]))     # error compounds over the depth
     o.close(); p.close()
+
+
+@pytest.mark.parametrize("name,batch", [("caffenet", 3), ("cifar10_full", 10)])
+def test_producer_side_packing_is_bit_identical_to_the_pack_kernels(oracle, product, monkeypatch, name, batch):
+    """The packed (channels-last, tf32-rounded) operands of the window convolutions are written by the layers that
+    produce the tensors where that is possible — a convolution's or an across-channel LRN's forward writes the next
+    convolution's packed input (SPARKNET_FUSE_PACK), a MAX pooling layer's backward writes the packed top gradient and
+    the bias gradient of the convolution below it (SPARKNET_FUSE_POOL_PACK) — instead of separate pack kernels.  Same
+    values, same rounding, same summation order: every blob, every blob gradient and every parameter gradient must be
+    BIT-identical with the fusions on and off, and two solver steps must leave identical weights."""
+    sol = zoo.solver_with_net(name, train_bs=batch, test_bs=batch, random_seed=1701, display=0)
+    imgs, labs = synthetic_batches(name, 2, batch)
+    out = []
+    for fuse in ("0", "1"):
+        monkeypatch.setenv("SPARKNET_FUSE_PACK", fuse)
+        monkeypatch.setenv("SPARKNET_FUSE_POOL_PACK", fuse)
+        p = CaffeNet.from_solver(sol, product)
+        product.sparknet_set_precision(p.state, 1)
+        p.setTrainData(MinibatchSource(imgs, labs))
+        if fuse == "0":
+            w0 = p.getWeights()
+        p.setWeights(w0)
+        l0 = product.sparknet_kernel_launches(p.state)
+        p.forward(); p.backward()
+        launches = product.sparknet_kernel_launches(p.state) - l0
+        data, diff, wd = p.getData(), p.getData(diff=True), p.getWeightDiffs()
+        p.train(2)
+        n = int(product.sparknet_num_params(p.state))
+        flat = np.empty(n, dtype=F)
+        assert product.sparknet_get_weights_flat(p.state, fptr(flat), n) == 0
+        out.append((data, diff, wd, flat, launches))
+        p.close()
+    (d0, g0, w0d, f0, n0), (d1, g1, w1d, f1, n1) = out
+    assert n1 < n0 if name == "caffenet" else n1 <= n0         # fewer kernels: CaffeNet loses 7 pack / pooling launches per pass
+    for k in d0:
+        assert np.array_equal(d0[k], d1[k]), k
+        assert np.array_equal(g0[k], g1[k]), k
+    for ln in w0d:
+        for a, b in zip(w0d[ln], w1d[ln]):
+            assert np.array_equal(a, b), ln
+    assert np.array_equal(f0, f1)
