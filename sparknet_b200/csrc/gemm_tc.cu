@@ -821,14 +821,23 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
   // as 148 + 52, 72.7 -> 58.4 us with 148)
   static const int split_waves = getenv("SPARKNET_TC_SPLIT_WAVES") ? atoi(getenv("SPARKNET_TC_SPLIT_WAVES")) : 1;
   const int splits = splitk_slices((int)(grid.x * grid.y), R, split_waves);
-  static size_t attr_done_split = 0, attr_done = 0;          // largest dynamic smem size opted in so far
+  // largest dynamic shared-memory size opted in so far, per device (cudaFuncSetAttribute is per device) and under a lock:
+  // sparknet_tc_gemm_static_scratch may be called on any device from any thread and shares these instantiations
+  static size_t attr_split_dev[32] = {0}, attr_dev[32] = {0};
+  static std::mutex attr_mu;
+  int dev = 0;
+  SN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 32) fatal("tensor-core contraction: device index %d out of range", dev);
   constexpr size_t kMaxSmem = 227 * 1024;
   if (splits == 1) {
     const int len = (R + TBK - 1) / TBK * TBK;
     const size_t smem = Cfg::kSmemBytes + (size_t)len * KTabEntryBytes<AL>::value;
     if (smem > kMaxSmem) fatal("tensor-core contraction: reduction of %d needs %zu bytes of shared memory (> %zu)", R, smem, kMaxSmem);
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, false>;
-    if (smem > attr_done) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done = smem; }
+    {
+      std::lock_guard<std::mutex> lock(attr_mu);
+      if (smem > attr_dev[dev]) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_dev[dev] = smem; }
+    }
     kfn<<<grid, kTcThreads, smem, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, nullptr);
     count_launch();
   } else {
@@ -839,7 +848,10 @@ static void launch_bn(cudaStream_t s, const CUtensorMap& tmA, const CUtensorMap&
     const size_t smem = Cfg::kSmemBytes + (size_t)len * KTabEntryBytes<AL>::value;
     if (smem > kMaxSmem) fatal("tensor-core contraction: reduction slice of %d needs %zu bytes of shared memory (> %zu)", len, smem, kMaxSmem);
     auto kfn = gemm_tc_kernel<AL, BL, EP, BN, true>;
-    if (smem > attr_done_split) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_done_split = smem; }
+    {
+      std::lock_guard<std::mutex> lock(attr_mu);
+      if (smem > attr_split_dev[dev]) { SN_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr_split_dev[dev] = smem; }
+    }
     kfn<<<grid, kTcThreads, smem, s>>>(tmA, tmB, al, bl, ep, M, N, R, len, n_mma, ws);
     launch_splitk_reduce(s, ws, (int)grid.z, M, N, reduce_epi);
     count_launch(2);
@@ -982,21 +994,9 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
 // and walks its pixels; with BIAS it also sums every value it reads per channel (the bias gradient of this image,
 // conv_layer.cpp:52-55: gemv against the all-ones multiplier) into part[c][n], which bias_grad_final_kernel adds up
 // in image order.  The top gradient is therefore read from HBM once for both purposes.
-// POOL: the source is not a tensor in memory but the BACKWARD of a max pooling layer (plus the in-place ReLU below it)
-// computed on the fly: value(n, c, h, w) = sum of the pooled top diffs of the windows whose argmax is (h, w), in the
-// reference's (ph, pw) order (pooling_layer.cpp:253-270), zero where the pooled output is <= 0 (relu_layer.cpp:26-36).
-// The convolution below such a pool then gets its packed top gradient, its NCHW diff blob (`nchw`, what the pooling
-// layer's own backward kernel would have written) and its bias gradient from ONE pass, instead of a pooling-backward
-// kernel writing the gradient and a pack kernel reading it back.
-struct PoolSrc {
-  const float* dy; const int* mask; const float* gate;       // pooled planes [N*C][PH*PW]; gate nullable
-  float* nchw;                                                // nullable: the unpooled gradient in NCHW
-  int PH, PW, kh, kw, sh, sw, ph, pw;
-};
-template <bool BIAS, bool POOL>
+template <bool BIAS>
 __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
-                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span, int Csrc,
-                                                         PoolSrc ps) {
+                                                         int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span, int Csrc) {
   // Csrc <= C: the source tensor has Csrc channels, the packed rows C (the rest are written as zeros: channel padding of
   // first layers with fewer than 16 input channels)
   __shared__ float tile[32][129];
@@ -1006,48 +1006,15 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
   float* dp = dst + ((size_t)lead + (size_t)n * Gp) * C + c0 + tx;
   float bsum[4] = {0.f, 0.f, 0.f, 0.f};
   const int p_begin = blockIdx.z * span, p_end = min(HW, p_begin + span);     // this block's share of the image's pixels
-  const int P = POOL ? ps.PH * ps.PW : 0;
   for (int p0 = p_begin; p0 < p_end; p0 += 128) {
     float v[4][4];
-    if (POOL) {
-      // window ranges depend on the pixel only: once per q, shared by the four channels of this thread
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
 #pragma unroll
       for (int q = 0; q < 4; ++q) {
-        const int p = p0 + tx + 32 * q;
-        uint32_t h = 0, w = 0;
-        dW.divmod((uint32_t)min(p, HW - 1), h, w);
-        const int hh = (int)h + ps.ph, ww = (int)w + ps.pw;
-        const int phs = hh < ps.kh ? 0 : (hh - ps.kh) / ps.sh + 1, phe = min(hh / ps.sh + 1, ps.PH);
-        const int pws = ww < ps.kw ? 0 : (ww - ps.kw) / ps.sw + 1, pwe = min(ww / ps.sw + 1, ps.PW);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const int j = ty + 8 * k;
-          float acc = 0.f;
-          if (c0 + j < Csrc && p < p_end) {
-            const size_t base = ((size_t)n * Csrc + c0 + j) * P;
-            for (int a = phs; a < phe; ++a)
-              for (int b = pws; b < pwe; ++b) {
-                const size_t o = base + a * ps.PW + b;
-                if (__ldg(ps.mask + o) == p) {
-                  float d = __ldg(ps.dy + o);
-                  if (ps.gate && !(__ldg(ps.gate + o) > 0.f)) d = 0.f;
-                  acc += d;
-                }
-              }
-            if (ps.nchw) ps.nchw[((size_t)n * Csrc + c0 + j) * HW + p] = acc;
-          }
-          v[k][q] = acc;
-        }
+        const int j = ty + 8 * k, p = p0 + tx + 32 * q;
+        v[k][q] = (c0 + j < Csrc && p < p_end) ? sp[(size_t)j * HW + p] : 0.f;
       }
-    } else {
-#pragma unroll
-      for (int k = 0; k < 4; ++k)
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int j = ty + 8 * k, p = p0 + tx + 32 * q;
-          v[k][q] = (c0 + j < Csrc && p < p_end) ? sp[(size_t)j * HW + p] : 0.f;
-        }
-    }
 #pragma unroll
     for (int k = 0; k < 4; ++k)
 #pragma unroll
@@ -1100,38 +1067,11 @@ void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const flo
   dim3 grid((C + 31) / 32, g.N, Z);
   if (db) {
     float* part = get_workspace((size_t)C * g.N * Z);
-    flat_pack_kernel<true, false><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, Csrc, PoolSrc{});
+    flat_pack_kernel<true><<<grid, 256, 0, s>>>(src, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, Csrc);
     bias_grad_final_kernel<<<(C * 32 + 127) / 128, 128, 0, s>>>(C, g.N * Z, part, db, accumulate ? 1 : 0);
     count_launch(2);
   } else {
-    flat_pack_kernel<false, false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, Csrc, PoolSrc{});
-    count_launch();
-  }
-  SN_CUDA(cudaGetLastError());
-}
-// The packed top gradient of convolution `g` when that gradient is the backward of the MAX pooling layer `pg` above it
-// (pg.H x pg.W = g.Ho x g.Wo, pg.C = g.Cout): pooled top diffs / argmax mask / optional ReLU gate in, packed gradient +
-// NCHW gradient (dx, nullable) + bias gradient (db, nullable) out, one pass.  Same per-block summation order as
-// tc_flat_pack, so db is bit-identical to the two-kernel route.
-void tc_flat_pack_pool_bwd(cudaStream_t s, const ConvGeom& g, const PoolGeom& pg, const float* pooled_dy, const int* mask, const float* gate,
-                           float* dx, float* dst, float* db, bool accumulate) {
-  const int C = g.Cout, H = g.Ho, W = g.Wo;
-  if (pg.C != C || pg.H != H || pg.W != W || pg.N != g.N) fatal("tc_flat_pack_pool_bwd: pooling input %dx%dx%d does not match the convolution output %dx%dx%d", pg.C, pg.H, pg.W, C, H, W);
-  const FlatGeom f = tc_flat_geom(g);
-  const int HW = H * W;
-  int Z = (HW + 1023) / 1024;
-  if (Z > 4) Z = 4;
-  const int span = ((HW + Z - 1) / Z + 127) / 128 * 128;
-  Z = (HW + span - 1) / span;
-  dim3 grid((C + 31) / 32, g.N, Z);
-  const PoolSrc ps{pooled_dy, mask, gate, dx, pg.PH, pg.PW, pg.kh, pg.kw, pg.sh, pg.sw, pg.ph, pg.pw};
-  if (db) {
-    float* part = get_workspace((size_t)C * g.N * Z);
-    flat_pack_kernel<true, true><<<grid, 256, 0, s>>>(nullptr, dst, part, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, C, ps);
-    bias_grad_final_kernel<<<(C * 32 + 127) / 128, 128, 0, s>>>(C, g.N * Z, part, db, accumulate ? 1 : 0);
-    count_launch(2);
-  } else {
-    flat_pack_kernel<false, true><<<grid, 256, 0, s>>>(nullptr, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, C, ps);
+    flat_pack_kernel<false><<<grid, 256, 0, s>>>(src, dst, nullptr, g.N, C, H, W, f.Wp, f.Gp, f.lead, FastDiv(W), span, Csrc);
     count_launch();
   }
   SN_CUDA(cudaGetLastError());

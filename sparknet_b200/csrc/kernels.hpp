@@ -47,10 +47,6 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad);
 // dst zeroed once by the owner; db (nullable) = bias gradient summed in the same pass over the top gradient
 void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const float* src, float* dst, float* db = nullptr,
                   bool accumulate = false, int src_channels = 0);   // src_channels < g.C: the remaining packed channels are zeros
-struct PoolGeom;
-// packed top gradient of convolution g = backward of the MAX pooling layer pg above it (+ the ReLU gate), in one pass
-void tc_flat_pack_pool_bwd(cudaStream_t s, const ConvGeom& g, const PoolGeom& pg, const float* pooled_dy, const int* mask, const float* gate,
-                           float* dx, float* dst, float* db, bool accumulate);
 void tc_flat_pack_filter(cudaStream_t s, const ConvGeom& g, bool dgrad, const float* w, float* dst, int src_cg = 0);   // src_cg < g.Cg() (forward layout): zero slots
 void tc_conv_fwd_flat(cudaStream_t s, const ConvGeom& g, const float* xflat, const float* wf, const float* bias, float* y, bool relu);
 void tc_conv_dgrad_flat(cudaStream_t s, const ConvGeom& g, const float* dyflat, const float* wt, float* dx);

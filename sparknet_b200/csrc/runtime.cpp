@@ -564,28 +564,6 @@ struct ConvolutionLayer : Layer {
   float *xflat = nullptr, *dyflat = nullptr, *wflat[2] = {nullptr, nullptr};
   uint64_t xflat_gen = ~0ull, wflat_gen[2] = {~0ull, ~0ull};
   const Storage* xflat_src = nullptr;
-  // the packed top gradient may already be current: the MAX pooling layer above wrote it while computing its backward
-  // (pack_dy_from_pool), together with this layer's bias gradient
-  uint64_t dyflat_gen = ~0ull;
-  const Storage* dyflat_src = nullptr;
-  bool need_dx = false;                               // bottom_need_backward of this layer (set by Net::Net)
-  bool dy_is_packed(Blob* top) const { return dyflat && dyflat_src == top->diff.get() && dyflat_gen == top->diff->gen; }
-  bool wants_packed_dy() {
-    if (net->precision != PREC_TF32) return false;
-    if (use_s2d()) return param_propagate_down[0];
-    return (use_flat(2) && param_propagate_down[0]) || (use_flat(4) && need_dx);
-  }
-  // pg: the pooling layer's geometry; pooled_dy / mask / gate: its top diff, argmax mask and (nullable) top data; dx: this
-  // layer's NCHW top diff, written too.  See gemm_tc.cu tc_flat_pack_pool_bwd.
-  void pack_dy_from_pool(const PoolGeom& pg, const float* pooled_dy, const int* mask, const float* gate, float* dx, Blob* top) {
-    const ConvGeom& pgm = use_s2d() ? gs : g;
-    if (!dyflat) dyflat = flat_alloc(pgm.Cout);
-    const bool want_db = bias_term && param_propagate_down[1];
-    tc_flat_pack_pool_bwd(S(), pgm, pg, pooled_dy, mask, gate, dx, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr,
-                          !net->overwrite_param_diffs);
-    dyflat_src = top->diff.get();
-    dyflat_gen = top->diff->gen;
-  }
   int flat_ok = -1;
   // SPARKNET_CONV_FLAT: bit 0 forward, bit 1 backward-filter, bit 2 backward-data (default 7; 0 = gather kernels only)
   bool use_flat(int bit) {
@@ -697,7 +675,7 @@ struct ConvolutionLayer : Layer {
     if (tf32 && use_s2d() && param_propagate_down[0]) {
       // folded layer: pack the top gradient on the folded grid (+ bias gradient), window backward-filter, unfold dW
       if (!dyflat) dyflat = flat_alloc(gs.Cout);
-      if (!dy_is_packed(top[0])) tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
+      tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
       if (!dws) SN_CUDA(cudaMalloc(&dws, (size_t)gs.Cout * gs.C * gs.kh * gs.kw * sizeof(float)));
       tcw_conv_wgrad(S(), gs, packed_input(bottom[0]), dyflat, dws, false);
       if (cpad()) tcw_cpad_unpack_wgrad(S(), g, gs.C, dws, blobs[0]->diff->mutable_gpu(), acc);
@@ -711,8 +689,8 @@ struct ConvolutionLayer : Layer {
     }
     if (flat_w || flat_d) {
       if (!dyflat) dyflat = flat_alloc(g.Cout);
-      // one pass over the top gradient packs it and sums the bias gradient (unless the pooling layer above already did both)
-      if (!dy_is_packed(top[0])) tc_flat_pack(S(), g, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
+      // one pass over the top gradient packs it and sums the bias gradient
+      tc_flat_pack(S(), g, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
     } else if (want_db) {
       conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
     }
@@ -839,10 +817,6 @@ struct PoolingLayer : Layer {
   int method = 0;
   int* mask = nullptr;
   bool gate_relu = false;     // the bottom is the output of an in-place ReLU whose backward is folded into this layer's
-  // MAX pooling right above a convolution (through nothing but that ReLU): this layer's backward also writes the
-  // convolution's packed top gradient and bias gradient (ConvolutionLayer::pack_dy_from_pool).  Set by Net::Net;
-  // SPARKNET_FUSE_POOL_PACK=0 turns it off.
-  ConvolutionLayer* dy_consumer = nullptr;
   using Layer::Layer;
   ~PoolingLayer() override { if (mask) cudaFree(mask); }
   const char* type() const override { return "Pooling"; }
@@ -880,9 +854,7 @@ struct PoolingLayer : Layer {
     if (!pd[0]) return;
     const float* dy = top[0]->diff->gpu();
     float* dx = bottom[0]->diff->mutable_gpu();
-    if (method == 0 && dy_consumer && dy_consumer->wants_packed_dy())
-      dy_consumer->pack_dy_from_pool(g, dy, mask, gate_relu ? top[0]->data->gpu() : nullptr, dx, bottom[0]);
-    else if (method == 0) pool_max_bwd(S(), g, dy, mask, dx, gate_relu ? top[0]->data->gpu() : nullptr);
+    if (method == 0) pool_max_bwd(S(), g, dy, mask, dx, gate_relu ? top[0]->data->gpu() : nullptr);
     else pool_ave_bwd(S(), g, dy, dx);
   }
 };
@@ -1332,38 +1304,6 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed, const Net* share
       if (prod < 0 || !clean) continue;
       if (ConvolutionLayer* p = dynamic_cast<ConvolutionLayer*>(layers[(size_t)prod].get())) p->flat_consumer = consumer;
       else if (LRNLayer* n = dynamic_cast<LRNLayer*>(layers[(size_t)prod].get())) { if (n->region == 0) n->flat_consumer = consumer; }
-    }
-  }
-  for (int li = 0; li < L; ++li)
-    if (ConvolutionLayer* c = dynamic_cast<ConvolutionLayer*>(layers[(size_t)li].get()))
-      c->need_dx = layer_need_backward[(size_t)li] && !bottom_need_backward[(size_t)li].empty() && bottom_need_backward[(size_t)li][0];
-  // Top-gradient packing by the pooling layer above: MAX pool whose bottom blob is computed by a convolution, read by
-  // nothing else and rewritten in between only by an in-place ReLU whose backward the pool applies itself.
-  {
-    const char* e = getenv("SPARKNET_FUSE_POOL_PACK");
-    const bool enabled = !(e && atoi(e) == 0);
-    for (int lj = 0; enabled && lj < L; ++lj) {
-      PoolingLayer* pool = dynamic_cast<PoolingLayer*>(layers[(size_t)lj].get());
-      if (!pool || pool->method != 0 || !layer_need_backward[(size_t)lj] || !bottom_need_backward[(size_t)lj][0]) continue;
-      Blob* xb = bottom_vecs[(size_t)lj][0];
-      int prod = -1, readers = 0;
-      bool clean = true;
-      for (int li = 0; li < L; ++li) {
-        if (li != lj)
-          for (Blob* b : bottom_vecs[(size_t)li]) {
-            const bool inplace = !top_vecs[(size_t)li].empty() && top_vecs[(size_t)li][0] == xb;
-            if (b == xb && !inplace) ++readers;
-          }
-        for (Blob* t : top_vecs[(size_t)li]) {
-          if (t != xb) continue;
-          const bool inplace = !bottom_vecs[(size_t)li].empty() && bottom_vecs[(size_t)li][0] == xb;
-          if (!inplace) { prod = li; continue; }
-          ReLULayer* r = dynamic_cast<ReLULayer*>(layers[(size_t)li].get());
-          if (!(r && r->bwd_fused_by_consumer && pool->gate_relu)) clean = false;
-        }
-      }
-      if (prod < 0 || prod > lj || !clean || readers != 0) continue;
-      if (ConvolutionLayer* p = dynamic_cast<ConvolutionLayer*>(layers[(size_t)prod].get())) pool->dy_consumer = p;
     }
   }
   // Parameter arena: one contiguous device allocation for all weights and one for all gradients;
