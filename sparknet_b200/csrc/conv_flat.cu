@@ -1130,16 +1130,37 @@ ConvGeom tcw_s2d_geom(const ConvGeom& g) {
   if (e.W - e.kw + 1 < g.Wo) e.W = g.Wo + e.kw - 1;
   return e;
 }
-// one block per (image, folded row): s*C image rows in, W' positions x C*s*s channels out (contiguous)
+// one block per (image, folded row): s*C image rows in, W' positions x C*s*s channels out (contiguous).
+// BYTES: the source is the byte-pixel staging buffer of a JavaData layer (runtime.cpp JavaDataLayer, byte input): the
+// pixels are widened here, value = ((float)b - mean[(i / mean_div) % mean_period]) * scale with i the NCHW element index,
+// the same two fp32 operations as kernels.cu widen_bytes — the fp32 copy of the minibatch is then never written or read.
+struct ByteSrc { const uint8_t* b; int is_signed; const float* mean; FastDiv ddiv, dper; float scale; };
+template <bool BYTES>
 __global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__ x, float* __restrict__ dst, int C, int H, int W, int s,
-                                                        int Hs, int Ws, int Wp, int Gp, int lead, FastDiv dCs, FastDiv dS) {
+                                                        int Hs, int Ws, int Wp, int Gp, int lead, FastDiv dCs, FastDiv dS, ByteSrc bs) {
   extern __shared__ float rows[];                      // [C*s][Ws*s]
   const int hs = blockIdx.x, n = blockIdx.y, Wpad = Ws * s, nrows = C * s;
   const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
   for (int r = ty; r < nrows; r += 4) {
     const int c = r / s, dy = r - c * s, h = hs * s + dy;
-    const float* xp = x + (((size_t)n * C + c) * H + h) * W;
-    for (int w = tx; w < Wpad; w += 64) rows[r * Wpad + w] = (h < H && w < W) ? xp[w] : 0.f;
+    const size_t row0 = (((size_t)n * C + c) * H + h) * W;
+    for (int w = tx; w < Wpad; w += 64) {
+      float v = 0.f;
+      if (h < H && w < W) {
+        if (BYTES) {
+          const uint32_t i = (uint32_t)(row0 + w), raw = bs.b[i];
+          v = bs.is_signed ? (float)(int)(signed char)raw : (float)raw;
+          if (bs.mean) {
+            const uint32_t q = bs.ddiv.div(i);
+            v = __fsub_rn(v, __ldg(bs.mean + (q - bs.dper.div(q) * bs.dper.d)));
+          }
+          if (bs.scale != 1.f) v = __fmul_rn(v, bs.scale);
+        } else {
+          v = x[row0 + w];
+        }
+      }
+      rows[r * Wpad + w] = v;
+    }
   }
   __syncthreads();
   const int Cs = C * s * s;
@@ -1165,17 +1186,29 @@ __global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__
     out[i] = to_tf32_exact(rows[r * Wpad + ws * s + dx]);
   }
 }
-void tcw_s2d_pack_input(cudaStream_t st, const ConvGeom& g, const float* x, float* xflat) {
+static void s2d_pack_launch(cudaStream_t st, const ConvGeom& g, const float* x, const ByteSrc* bs, float* xflat) {
   const ConvGeom e = tcw_s2d_geom(g);
   const FlatGeom f = tc_flat_geom(e);
   const int s = g.sh, Hs = (g.H + s - 1) / s, Ws = (g.W + s - 1) / s;
   const size_t smem = (size_t)g.C * s * Ws * s * sizeof(float);
-  static size_t attr = 48 * 1024;
-  if (smem > attr) { SN_CUDA(cudaFuncSetAttribute(s2d_pack_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); attr = smem; }
-  s2d_pack_kernel<<<dim3(Hs, g.N), 256, smem, st>>>(x, xflat, g.C, g.H, g.W, s, Hs, Ws, f.Wp, f.Gp, f.lead, FastDiv((uint32_t)(g.C * s * s)),
-                                                    FastDiv((uint32_t)s));
+  static size_t attr[2] = {48 * 1024, 48 * 1024};
+  if (smem > attr[bs ? 1 : 0]) {
+    if (bs) SN_CUDA(cudaFuncSetAttribute(s2d_pack_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else SN_CUDA(cudaFuncSetAttribute(s2d_pack_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr[bs ? 1 : 0] = smem;
+  }
+  const FastDiv dCs((uint32_t)(g.C * s * s)), dS((uint32_t)s);
+  if (bs) s2d_pack_kernel<true><<<dim3(Hs, g.N), 256, smem, st>>>(nullptr, xflat, g.C, g.H, g.W, s, Hs, Ws, f.Wp, f.Gp, f.lead, dCs, dS, *bs);
+  else s2d_pack_kernel<false><<<dim3(Hs, g.N), 256, smem, st>>>(x, xflat, g.C, g.H, g.W, s, Hs, Ws, f.Wp, f.Gp, f.lead, dCs, dS, ByteSrc{});
   count_launch();
   SN_CUDA(cudaGetLastError());
+}
+void tcw_s2d_pack_input(cudaStream_t st, const ConvGeom& g, const float* x, float* xflat) { s2d_pack_launch(st, g, x, nullptr, xflat); }
+void tcw_s2d_pack_input_bytes(cudaStream_t st, const ConvGeom& g, const uint8_t* bytes, bool is_signed, const float* mean, int mean_div,
+                              int mean_period, float scale, float* xflat) {
+  if ((size_t)g.N * g.C * g.H * g.W >= (1ull << 31)) fatal("s2d pack from bytes: tensor exceeds the 32-bit index range of the mean lookup");
+  const ByteSrc bs{bytes, is_signed ? 1 : 0, mean, FastDiv((uint32_t)(mean_div > 0 ? mean_div : 1)), FastDiv((uint32_t)(mean_period > 0 ? mean_period : 1)), scale};
+  s2d_pack_launch(st, g, nullptr, &bs, xflat);
 }
 // wf[co][tap'][slot]: slot = (c*s + dy)*s + dx < C*s*s holds w[co][c][s*ky'+dy][s*kx'+dx] (0 beyond the filter), tf32-rounded
 __global__ void s2d_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ wf, int Cout, int C, int kh, int kw, int s, int khs,

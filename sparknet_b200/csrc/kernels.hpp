@@ -65,6 +65,9 @@ void tcw_conv_wgrad(cudaStream_t s, const ConvGeom& g, const float* xflat, const
 bool tcw_s2d_supported(const ConvGeom& g);
 ConvGeom tcw_s2d_geom(const ConvGeom& g);
 void tcw_s2d_pack_input(cudaStream_t s, const ConvGeom& g, const float* x, float* xflat);
+// the same from a byte-pixel staging buffer, widened on the fly: ((float)b - mean[(i / mean_div) % mean_period]) * scale
+void tcw_s2d_pack_input_bytes(cudaStream_t s, const ConvGeom& g, const uint8_t* bytes, bool is_signed, const float* mean, int mean_div,
+                              int mean_period, float scale, float* xflat);
 void tcw_s2d_pack_filter(cudaStream_t s, const ConvGeom& g, const float* w, float* wf);
 // Several filter copies in one launch (conv_flat.cu filter_pack_batch_kernel): mode 0 / 1 = tc_flat_pack_filter(dgrad = mode),
 // mode 2 = tcw_s2d_pack_filter.

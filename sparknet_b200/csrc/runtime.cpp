@@ -10,6 +10,7 @@
 #include <random>
 #include <sstream>
 #include <atomic>
+#include <functional>
 #include <chrono>
 #include <condition_variable>
 #include <mutex>
@@ -308,8 +309,21 @@ static cudaStream_t S() { return ctx().compute; }
 // overlaps the compute of iteration i.  Callback order and count are exactly the reference's
 // (one call per JavaData layer per forward pass, data before label).
 // ------------------------------------------------------------------------------------------
+// What a byte-input JavaData layer hands to the one convolution that reads its blob, so that the convolution's pack kernel
+// widens the pixels itself (conv_flat.cu s2d_pack_kernel<true>) and the fp32 minibatch is never materialised inside solver_step.
+struct ByteFeed { const uint8_t* bytes; bool is_signed; const float* mean; int mean_div, mean_period; float scale; const Storage* src; uint64_t gen; };
 struct JavaDataLayer : Layer {
   java_callback_t cb = nullptr;
+  std::function<bool()> consumer_takes_bytes;                  // set by Net::Net when a single convolution reads the top blob
+  std::function<void(const ByteFeed&)> consumer_feed;
+  bool fp32_stale = false;                                     // the fp32 blob does not hold the current minibatch yet (see materialize)
+  int stale_slot = 0;
+  // after solver_step: make the fp32 blob current again for whoever reads it next (get_data, forward(), tests)
+  void materialize() {
+    if (!fp32_stale) return;
+    widen_bytes(ctx().compute, count, dev_b[stale_slot], byte_mode == 1, mean_dev, mean_div, mean_period, byte_scale, devbuf[stale_slot]);
+    fp32_stale = false;
+  }
   vector<int> shape, java_shape;
   size_t count = 0;
   float* pinned[2] = {nullptr, nullptr};
@@ -448,10 +462,14 @@ struct JavaDataLayer : Layer {
     else SN_CUDA(cudaMemcpyAsync(devbuf[p], pinned[p], count * sizeof(float), cudaMemcpyHostToDevice, c.copy));
     SN_CUDA(cudaEventRecord(h2d_done[p], c.copy));
     SN_CUDA(cudaStreamWaitEvent(c.compute, h2d_done[p], 0));
-    if (byte_mode) widen_bytes(c.compute, count, dev_b[p], byte_mode == 1, mean_dev, mean_div, mean_period, byte_scale, devbuf[p]);
+    const bool lazy = byte_mode && g_in_step && consumer_takes_bytes && consumer_takes_bytes();
+    if (byte_mode && !lazy) widen_bytes(c.compute, count, dev_b[p], byte_mode == 1, mean_dev, mean_div, mean_period, byte_scale, devbuf[p]);
+    fp32_stale = lazy;
+    stale_slot = p;
     st->dev = devbuf[p];
     st->head = Storage::AT_DEVICE;
     ++st->gen;
+    if (lazy) consumer_feed(ByteFeed{dev_b[p], byte_mode == 1, mean_dev, mean_div, mean_period, byte_scale, st, st->gen});
     parity = q;
     if (pf) {
       { std::lock_guard<std::mutex> lk(pf->m); ++pf_enqueued; }
@@ -614,11 +632,17 @@ struct ConvolutionLayer : Layer {
     SN_CUDA(cudaMemsetAsync(p, 0, bytes, S()));      // the bands between images stay zero for good
     return p;
   }
+  // byte-pixel input handed over by the JavaData layer below (ByteFeed): valid for exactly that generation of the blob
+  ByteFeed byte_feed{};
+  bool takes_bytes() { return net->precision == PREC_TF32 && use_s2d() && !cpad(); }
   const float* packed_input(Blob* bottom) {
     const float* x = bottom->data->gpu();
     if (!xflat) xflat = flat_alloc(fg().C);
     if (xflat_src != bottom->data.get() || xflat_gen != bottom->data->gen) {
-      if (cpad()) tc_flat_pack(S(), gs, false, x, xflat, nullptr, false, g.C);
+      if (takes_bytes() && byte_feed.bytes && byte_feed.src == bottom->data.get() && byte_feed.gen == bottom->data->gen)
+        tcw_s2d_pack_input_bytes(S(), g, byte_feed.bytes, byte_feed.is_signed, byte_feed.mean, byte_feed.mean_div, byte_feed.mean_period,
+                                 byte_feed.scale, xflat);
+      else if (cpad()) tc_flat_pack(S(), gs, false, x, xflat, nullptr, false, g.C);
       else if (use_s2d()) tcw_s2d_pack_input(S(), g, x, xflat);
       else tc_flat_pack(S(), g, false, x, xflat);
       xflat_src = bottom->data.get();
@@ -1281,6 +1305,20 @@ Net::Net(const cp::NetParameter& in, int phase_, uint64_t seed, const Net* share
       r->bwd_fused_by_consumer = true;
     }
   }
+  // A JavaData layer whose blob is read by exactly one convolution can hand it byte pixels (JavaDataLayer byte input)
+  for (int li = 0; li < L; ++li) {
+    JavaDataLayer* jd = dynamic_cast<JavaDataLayer*>(layers[(size_t)li].get());
+    if (!jd) continue;
+    Blob* xb = top_vecs[(size_t)li][0];
+    ConvolutionLayer* only = nullptr;
+    int readers = 0;
+    for (int lj = li + 1; lj < L; ++lj)
+      for (Blob* b : bottom_vecs[(size_t)lj])
+        if (b == xb) { ++readers; only = dynamic_cast<ConvolutionLayer*>(layers[(size_t)lj].get()); }
+    if (readers != 1 || !only) continue;
+    jd->consumer_takes_bytes = [only] { return only->takes_bytes(); };
+    jd->consumer_feed = [only](const ByteFeed& f) { only->byte_feed = f; };
+  }
   // Producer-side packing: a window convolution whose input blob is computed by another convolution or an
   // across-channel LRN (and rewritten by nothing but in-place ReLUs the producer applies itself) has its flat grid
   // written by that producer.  SPARKNET_FUSE_PACK=0 turns it off.
@@ -1612,6 +1650,7 @@ void Solver::step(int iters) {
     ++iter;
   }
   for (DropoutLayer* d : drops) d->offset_slot = nullptr;
+  for (JavaDataLayer* d : feeds) d->materialize();              // byte input: the fp32 blob of the last minibatch, once per call
   if (prefetch) {
     helper.join();
     for (JavaDataLayer* d : feeds) d->pf = nullptr;
