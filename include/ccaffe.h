@@ -196,6 +196,9 @@ int sparknet_average_replicas_async(const void* const* replicas, int n, long cou
  * mode.  sparknet_graph_replays = iterations that ran as replays so far. */
 int sparknet_set_graph_mode(caffenet_state* state, int mode);
 long sparknet_graph_replays(caffenet_state* state);
+/* Kernel-to-kernel edges of the most recent recording that run as programmatic dependent launches (the next kernel's
+ * prologue overlaps the previous kernel's tail); 0 with SPARKNET_PDL=0. */
+int sparknet_graph_programmatic_edges(caffenet_state* state);
 
 /* Weight averaging over peer memory — replaces the driver's collect / reduce(WeightCollection.add) /
  * scalarDivide / broadcast / setWeights round (src/main/scala/apps/CifarApp.scala:92-99,133-134;

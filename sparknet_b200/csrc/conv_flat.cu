@@ -122,6 +122,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   if (CG == 2) cluster_sync_all();
   else __syncthreads();
   tc_fence_after_sync();
+  SN_GRID_DEP_WAIT();                        // barriers and TMEM are set up; everything below touches the operands / outputs
   const uint32_t tmem_base = tmem_base_smem;
   long long* stamp = a.stamps ? a.stamps + 8 * (size_t)blockIdx.x : nullptr;      // stamps describe the CTA's FIRST tile
   if (stamp && tid == 0) { stamp[0] = t_enter; stamp[1] = clock64(); }
@@ -704,6 +705,7 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
 // ------------------------------------------------------------------------------------------
 __global__ void mat_reduce_kernel(const float* __restrict__ ws, int splits, size_t total, int N, const float* __restrict__ bias, int relu,
                                   float* __restrict__ out) {
+  SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float acc = ws[i];
     for (int z = 1; z < splits; ++z) acc += ws[(size_t)z * total + i];
@@ -820,6 +822,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  SN_GRID_DEP_WAIT();                        // prologue done; operands and the workspace slice are touched from here on
   const uint32_t tmem_base = tmem_base_smem;
   const int sh0 = (t0 / a.kw) * a.Wp + t0 % a.kw;                          // row shift of the group's first tap
 
@@ -921,6 +924,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
 // dw[(co, c, tap)] (+)= sum over slices of ws[slice][(co, tap, c)], slices in ascending order
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
                                     int accumulate) {
+  SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < split_stride; i += (size_t)gridDim.x * blockDim.x) {
     // i walks the workspace layout (co, tap, c): coalesced reads
     const size_t co = i / ((size_t)T * Cg);
@@ -937,6 +941,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, si
 // partial sums meet in a fixed butterfly (same order on every run).
 __global__ void wgrad_reduce_wide_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
                                          int accumulate) {
+  SN_GRID_DEP_WAIT();
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const size_t i = t >> 3;
   const int j = (int)(t & 7);
@@ -1138,6 +1143,7 @@ struct ByteSrc { const uint8_t* b; int is_signed; const float* mean; FastDiv ddi
 template <bool BYTES>
 __global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__ x, float* __restrict__ dst, int C, int H, int W, int s,
                                                         int Hs, int Ws, int Wp, int Gp, int lead, FastDiv dCs, FastDiv dS, ByteSrc bs) {
+  SN_GRID_DEP_WAIT();
   extern __shared__ float rows[];                      // [C*s][Ws*s]
   const int hs = blockIdx.x, n = blockIdx.y, Wpad = Ws * s, nrows = C * s;
   const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
@@ -1213,6 +1219,7 @@ void tcw_s2d_pack_input_bytes(cudaStream_t st, const ConvGeom& g, const uint8_t*
 // wf[co][tap'][slot]: slot = (c*s + dy)*s + dx < C*s*s holds w[co][c][s*ky'+dy][s*kx'+dx] (0 beyond the filter), tf32-rounded
 __global__ void s2d_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ wf, int Cout, int C, int kh, int kw, int s, int khs,
                                        int kws, int slots) {
+  SN_GRID_DEP_WAIT();
   const size_t total = (size_t)Cout * khs * kws * slots;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int slot = (int)(i % slots);
@@ -1240,6 +1247,7 @@ void tcw_s2d_pack_filter(cudaStream_t st, const ConvGeom& g, const float* w, flo
 // change with every SGD update, and eight 5-microsecond pack kernels per CaffeNet iteration are pure launch latency.
 // mode 0 / 1: tc_flat_pack_filter(dgrad = mode) layout; mode 2: the folded filter of s2d_pack_filter_kernel.
 __global__ void filter_pack_batch_kernel(const FilterPackBatch b) {
+  SN_GRID_DEP_WAIT();
   const FilterPackJob& j = b.job[blockIdx.y];
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < j.total; i += (size_t)gridDim.x * blockDim.x) {
     float v = 0.f;
@@ -1296,6 +1304,7 @@ void tcw_filter_pack_batch(cudaStream_t st, const FilterPackBatch& b) {
 }
 // Channel-padded first layers (C < 16 padded to 16 on the flat grid): dw[co][c][tap] (+)= dws[co][c][tap] for the real channels
 __global__ void cpad_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int Cpad, int T, int accumulate) {
+  SN_GRID_DEP_WAIT();
   const int total = Cout * C * T;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int r = i % (C * T), co = i / (C * T);
@@ -1312,6 +1321,7 @@ void tcw_cpad_unpack_wgrad(cudaStream_t st, const ConvGeom& g, int Cpad, const f
 // dw[co][c][ky][kx] (+)= dws[co][(c,dy,dx)][tap']  (the folded filter gradient, layout of tcw_conv_wgrad's output)
 __global__ void s2d_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int kh, int kw, int s, int khs,
                                         int kws, int accumulate) {
+  SN_GRID_DEP_WAIT();
   const size_t total = (size_t)Cout * C * kh * kw;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     const int kx = (int)(i % kw), ky = (int)((i / kw) % kh), c = (int)((i / ((size_t)kw * kh)) % C), co = (int)(i / ((size_t)kw * kh * C));

@@ -20,6 +20,12 @@ struct ConvGeom {
   __host__ __device__ int Kdim() const { return Cg() * kh * kw; }   // reduction length of fwd
 };
 
+// Programmatic dependent launch: inside a recorded iteration (runtime.cpp Solver::step) consecutive kernels are joined by
+// programmatic edges, so a kernel's CTAs are scheduled — and run their prologue — while the previous kernel's last CTAs
+// drain.  Every kernel executes this before its first access to global memory: it returns once the previous kernel of
+// the stream has completed and its writes are visible (a no-op for a kernel launched the ordinary way).
+#define SN_GRID_DEP_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+
 // Division by a runtime constant via float reciprocal-free 32-bit magic (exact for the ranges used
 // here: numerators < 2^31, divisors < 2^16).  Falls back to '/' on the host.
 struct FastDiv {

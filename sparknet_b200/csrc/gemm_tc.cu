@@ -586,6 +586,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
+  SN_GRID_DEP_WAIT();                        // barriers, TMEM and the index tables (pure geometry) are set up; operands are read below
   const uint32_t tmem_base = tmem_base_smem;
 
   if (warp < NW) {
@@ -706,6 +707,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // deterministic slice reduction (ascending z) + the per-element epilogue of gemm_ops.cuh
 template <class E>
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float acc = ws[i];
@@ -718,6 +720,7 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits
 // order, then the eight partial sums are combined in a fixed butterfly — still the same order on every run.
 template <class E>
 __global__ void tc_splitk_reduce_wide_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const size_t i = t >> 3;
@@ -874,6 +877,7 @@ bool tc_available() { return true; }
 // Rounded (tf32, round-to-nearest) shadow copies of weight blobs for the TMA-fed operands.  Keyed by
 // the fp32 pointer; refreshed by tc_refresh_shadow whenever the runtime knows the weights changed.
 __global__ void round_tf32_kernel(size_t n, const float* __restrict__ src, float* __restrict__ dst) {
+  SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = to_tf32_exact(src[i]);
 }
 void tc_round_to_tf32(cudaStream_t s, size_t n, const float* src, float* dst) {
@@ -997,6 +1001,7 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
 template <bool BIAS>
 __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
                                                          int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span, int Csrc) {
+  SN_GRID_DEP_WAIT();
   // Csrc <= C: the source tensor has Csrc channels, the packed rows C (the rest are written as zeros: channel padding of
   // first layers with fewer than 16 input channels)
   __shared__ float tile[32][129];
@@ -1047,6 +1052,7 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
 }
 // one warp per channel: lane l adds partials l, l + 32, ... in ascending order, then a fixed butterfly: deterministic
 __global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
+  SN_GRID_DEP_WAIT();
   const int c = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
   float t = 0.f;
@@ -1079,6 +1085,7 @@ void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const flo
 // dst[row][tap*slots + ch]: fwd   (dgrad = 0): row = co (all groups), ch = c in group,  value W[co][c][tap]
 //                           dgrad (dgrad = 1): row = grp*Cg + c,      ch = co in group, value W[grp*Og + co][c][T-1-tap]
 __global__ void flat_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ dst, int Cg, int Og, int T, int groups, int dgrad, int Csrc) {
+  SN_GRID_DEP_WAIT();
   const int red = dgrad ? Og : Cg, rows = dgrad ? Cg * groups : Og * groups;
   const int slots = (red + 31) / 32 * 32, kp = T * slots;
   const size_t total = (size_t)rows * kp;

@@ -1504,6 +1504,43 @@ Solver::~Solver() {
 // epoch are discarded.
 static uint64_t g_config_epoch = 1;
 void bump_config_epoch() { ++g_config_epoch; }
+// Programmatic dependent launch inside a recorded iteration: every kernel-to-kernel edge of the captured graph becomes a
+// programmatic edge, so the next kernel's CTAs are scheduled, and run their prologue (barrier set-up, TMEM allocation,
+// descriptor prefetch: 8-12 us for a tcgen05 kernel), while the last CTAs of the previous kernel drain.  Correctness rests
+// on every kernel of this library executing griddepcontrol.wait before its first global-memory access (SN_GRID_DEP_WAIT):
+// the wait returns when the previous kernel has completed and flushed, and by induction so have all before it.  Edges that
+// touch a non-kernel node (memcpy, memset) stay full dependencies.  SPARKNET_PDL=0 leaves the graph as captured.
+static int make_edges_programmatic(cudaGraph_t graph) {
+  static const bool enabled = !(getenv("SPARKNET_PDL") && atoi(getenv("SPARKNET_PDL")) == 0);
+  if (!enabled) return 0;
+  size_t n = 0;
+  if (cudaGraphGetEdges_v2(graph, nullptr, nullptr, nullptr, &n) != cudaSuccess || n == 0) { cudaGetLastError(); return 0; }
+  std::vector<cudaGraphNode_t> from(n), to(n);
+  std::vector<cudaGraphEdgeData> ed(n);
+  if (cudaGraphGetEdges_v2(graph, from.data(), to.data(), ed.data(), &n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  // a kernel may have ONE programmatic predecessor; the captured iteration is a chain, anything else is left alone
+  std::map<cudaGraphNode_t, int> in_degree;
+  for (size_t i = 0; i < n; ++i) ++in_degree[to[i]];
+  int converted = 0;
+  for (size_t i = 0; i < n; ++i) {
+    cudaGraphNodeType tf, tt;
+    if (cudaGraphNodeGetType(from[i], &tf) != cudaSuccess || cudaGraphNodeGetType(to[i], &tt) != cudaSuccess) { cudaGetLastError(); continue; }
+    if (tf != cudaGraphNodeTypeKernel || tt != cudaGraphNodeTypeKernel || in_degree[to[i]] != 1) continue;
+    if (ed[i].type == cudaGraphDependencyTypeProgrammatic) continue;
+    cudaGraphEdgeData prog{};
+    prog.from_port = cudaGraphKernelNodePortProgrammatic;
+    prog.to_port = 0;
+    prog.type = cudaGraphDependencyTypeProgrammatic;
+    if (cudaGraphRemoveDependencies_v2(graph, &from[i], &to[i], &ed[i], 1) != cudaSuccess) { cudaGetLastError(); continue; }
+    if (cudaGraphAddDependencies_v2(graph, &from[i], &to[i], &prog, 1) != cudaSuccess) {
+      cudaGetLastError();
+      SN_CUDA(cudaGraphAddDependencies_v2(graph, &from[i], &to[i], &ed[i], 1));     // put the full dependency back
+      continue;
+    }
+    ++converted;
+  }
+  return converted;
+}
 void Solver::drop_graphs() {
   for (GraphEntry& g : graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
   graphs.clear();
@@ -1608,6 +1645,7 @@ void Solver::step(int iters) {
         cudaError_t e = cudaStreamEndCapture(cs, &graph);
         GraphEntry g;
         if (e == cudaSuccess && graph) {
+          programmatic_edges = make_edges_programmatic(graph);
           e = cudaGraphInstantiate(&g.exec, graph, 0);
           cudaGraphDestroy(graph);
         }

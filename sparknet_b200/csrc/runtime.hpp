@@ -204,6 +204,7 @@ struct Solver {
   int eager_iters = 0;                  // eager iterations since the graphs were last dropped (capture needs >= 2)
   uint64_t graphs_epoch = 0;            // value of the configuration epoch the recordings belong to
   long graph_replays = 0;
+  int programmatic_edges = 0;           // kernel-to-kernel edges of the last recording that became programmatic (PDL)
   long step_calls = 0;
   uint64_t touch_at_exit = 0;           // value of the outside-touch counter when the last step() returned
   void drop_graphs();

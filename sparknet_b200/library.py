@@ -84,6 +84,7 @@ _EXTENSIONS = {
     "sparknet_average_replicas_async": (c_int, [POINTER(c_void_p), c_int, ctypes.c_long, c_void_p]),
     "sparknet_set_graph_mode": (c_int, [c_void_p, c_int]),
     "sparknet_graph_replays": (ctypes.c_long, [c_void_p]),
+    "sparknet_graph_programmatic_edges": (c_int, [c_void_p]),
     "sparknet_peer_handle_bytes": (c_int, []),
     "sparknet_peer_export": (c_int, [c_void_p, c_void_p, c_void_p]),
     "sparknet_peer_attach": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p]),
