@@ -607,6 +607,7 @@ def main():
                     if bytes_pool else "solver_step through the reference's C ABI; fp32 minibatches copied into the pinned buffer"},
             "e2e_u8": e2e_u8, "numa": numa.value.decode(),
             "gpu_launches": int(launches), "clocks": clk,
+            "graph": {"replays": int(lib.sparknet_graph_replays(st)), "programmatic_edges": int(lib.sparknet_graph_programmatic_edges(st))},
             "averaging": {"rounds": n_rounds, "ms_per_round": avg_ms / n_rounds, "share_of_round": avg_ms / ms if ms else None,
                           "method": averager.method,
                           # ms_per_round is stream time from the end of this replica's last iteration to the end of the

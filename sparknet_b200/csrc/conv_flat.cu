@@ -91,6 +91,7 @@ conv_window_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constan
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t win_full[kWMaxStages], win_empty[kWMaxStages], b_full[kWMaxStages], b_empty[kWMaxStages], tmem_full[2], tmem_empty[2];
   __shared__ uint32_t tmem_base_smem;
+  SN_GRID_DEP_LAUNCH();
 
   const long long t_enter = clock64();
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -705,6 +706,7 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
 // ------------------------------------------------------------------------------------------
 __global__ void mat_reduce_kernel(const float* __restrict__ ws, int splits, size_t total, int N, const float* __restrict__ bias, int relu,
                                   float* __restrict__ out) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float acc = ws[i];
@@ -793,6 +795,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
   extern __shared__ uint8_t smem_raw[];
   __shared__ uint64_t full[kWMaxStages], empty[kWMaxStages], tmem_full;
   __shared__ uint32_t tmem_base_smem;
+  SN_GRID_DEP_LAUNCH();
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   // work item: (group, m tile, n tile, tap group)
@@ -924,6 +927,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
 // dw[(co, c, tap)] (+)= sum over slices of ws[slice][(co, tap, c)], slices in ascending order
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
                                     int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < split_stride; i += (size_t)gridDim.x * blockDim.x) {
     // i walks the workspace layout (co, tap, c): coalesced reads
@@ -941,6 +945,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, si
 // partial sums meet in a fixed butterfly (same order on every run).
 __global__ void wgrad_reduce_wide_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
                                          int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const size_t i = t >> 3;
@@ -1143,6 +1148,7 @@ struct ByteSrc { const uint8_t* b; int is_signed; const float* mean; FastDiv ddi
 template <bool BYTES>
 __global__ void __launch_bounds__(256) s2d_pack_kernel(const float* __restrict__ x, float* __restrict__ dst, int C, int H, int W, int s,
                                                         int Hs, int Ws, int Wp, int Gp, int lead, FastDiv dCs, FastDiv dS, ByteSrc bs) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   extern __shared__ float rows[];                      // [C*s][Ws*s]
   const int hs = blockIdx.x, n = blockIdx.y, Wpad = Ws * s, nrows = C * s;
@@ -1219,6 +1225,7 @@ void tcw_s2d_pack_input_bytes(cudaStream_t st, const ConvGeom& g, const uint8_t*
 // wf[co][tap'][slot]: slot = (c*s + dy)*s + dx < C*s*s holds w[co][c][s*ky'+dy][s*kx'+dx] (0 beyond the filter), tf32-rounded
 __global__ void s2d_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ wf, int Cout, int C, int kh, int kw, int s, int khs,
                                        int kws, int slots) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)Cout * khs * kws * slots;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -1247,6 +1254,7 @@ void tcw_s2d_pack_filter(cudaStream_t st, const ConvGeom& g, const float* w, flo
 // change with every SGD update, and eight 5-microsecond pack kernels per CaffeNet iteration are pure launch latency.
 // mode 0 / 1: tc_flat_pack_filter(dgrad = mode) layout; mode 2: the folded filter of s2d_pack_filter_kernel.
 __global__ void filter_pack_batch_kernel(const FilterPackBatch b) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const FilterPackJob& j = b.job[blockIdx.y];
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < j.total; i += (size_t)gridDim.x * blockDim.x) {
@@ -1304,6 +1312,7 @@ void tcw_filter_pack_batch(cudaStream_t st, const FilterPackBatch& b) {
 }
 // Channel-padded first layers (C < 16 padded to 16 on the flat grid): dw[co][c][tap] (+)= dws[co][c][tap] for the real channels
 __global__ void cpad_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int Cpad, int T, int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int total = Cout * C * T;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -1321,6 +1330,7 @@ void tcw_cpad_unpack_wgrad(cudaStream_t st, const ConvGeom& g, int Cpad, const f
 // dw[co][c][ky][kx] (+)= dws[co][(c,dy,dx)][tap']  (the folded filter gradient, layout of tcw_conv_wgrad's output)
 __global__ void s2d_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int kh, int kw, int s, int khs,
                                         int kws, int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)Cout * C * kh * kw;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {

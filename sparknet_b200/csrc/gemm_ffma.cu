@@ -18,6 +18,7 @@ constexpr int BM = 128, BN = 128, BK = 8, TM = 8, TN = 8, NT = 256;
 template <bool SPLIT, class A, class B, class E>
 __global__ void __launch_bounds__(NT) gemm_ffma_kernel(A a, B b, E epi, int M, int N, int R, int r_split_len,
                                                        float* __restrict__ ws) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   __shared__ float As[2][BK][BM + 4];
   __shared__ float Bs[2][BK][BN + 4];
@@ -92,6 +93,7 @@ __global__ void __launch_bounds__(NT) gemm_ffma_kernel(A a, B b, E epi, int M, i
 
 template <class E>
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {

@@ -25,6 +25,15 @@ struct ConvGeom {
 // drain.  Every kernel executes this before its first access to global memory: it returns once the previous kernel of
 // the stream has completed and its writes are visible (a no-op for a kernel launched the ordinary way).
 #define SN_GRID_DEP_WAIT() asm volatile("griddepcontrol.wait;" ::: "memory")
+// ... and this lets the NEXT kernel of a recorded iteration be scheduled as soon as every CTA of this one has started
+// (instead of when they have all exited): its CTAs take free slots and sit in their own wait, so the launch latency
+// between two kernels is off the critical path.  Only for launches that leave SMs free (fewer CTAs than the GPU has SMs —
+// the small nets: cifar10_quick / full -4 % per iteration); measured on CaffeNet, whose kernels fill the GPU, early
+// release of every kernel cost 1.8 % (3.73 -> 3.80 ms), so full-size launches release their successor when they exit.
+#define SN_GRID_DEP_LAUNCH()                                                                              \
+  do {                                                                                                    \
+    if (gridDim.x * gridDim.y * gridDim.z < 148u) asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); \
+  } while (0)
 
 // Division by a runtime constant via float reciprocal-free 32-bit magic (exact for the ranges used
 // here: numerators < 2^31, divisors < 2^16).  Falls back to '/' on the host.

@@ -553,6 +553,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   __shared__ uint64_t full_bar[TSTAGES], empty_bar[TSTAGES], tmem_full_bar;
   __shared__ uint32_t tmem_base_smem;
   __shared__ int4 row_table[256];                              // backward-filter: per-CTA row table
+  SN_GRID_DEP_LAUNCH();
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int m0 = blockIdx.x * TBM, n0 = blockIdx.y * n_mma;
@@ -707,6 +708,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // deterministic slice reduction (ascending z) + the per-element epilogue of gemm_ops.cuh
 template <class E>
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -720,6 +722,7 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits
 // order, then the eight partial sums are combined in a fixed butterfly — still the same order on every run.
 template <class E>
 __global__ void tc_splitk_reduce_wide_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -877,6 +880,7 @@ bool tc_available() { return true; }
 // Rounded (tf32, round-to-nearest) shadow copies of weight blobs for the TMA-fed operands.  Keyed by
 // the fp32 pointer; refreshed by tc_refresh_shadow whenever the runtime knows the weights changed.
 __global__ void round_tf32_kernel(size_t n, const float* __restrict__ src, float* __restrict__ dst) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = to_tf32_exact(src[i]);
 }
@@ -1001,6 +1005,7 @@ size_t tc_flat_filter_floats(const ConvGeom& g, bool dgrad) {
 template <bool BIAS>
 __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict__ src, float* __restrict__ dst, float* __restrict__ part,
                                                          int N, int C, int H, int W, int Wp, int Gp, int lead, FastDiv dW, int span, int Csrc) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   // Csrc <= C: the source tensor has Csrc channels, the packed rows C (the rest are written as zeros: channel padding of
   // first layers with fewer than 16 input channels)
@@ -1052,6 +1057,7 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
 }
 // one warp per channel: lane l adds partials l, l + 32, ... in ascending order, then a fixed butterfly: deterministic
 __global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int c = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;
@@ -1085,6 +1091,7 @@ void tc_flat_pack(cudaStream_t s, const ConvGeom& g, bool output_side, const flo
 // dst[row][tap*slots + ch]: fwd   (dgrad = 0): row = co (all groups), ch = c in group,  value W[co][c][tap]
 //                           dgrad (dgrad = 1): row = grp*Cg + c,      ch = co in group, value W[grp*Og + co][c][T-1-tap]
 __global__ void flat_pack_filter_kernel(const float* __restrict__ w, float* __restrict__ dst, int Cg, int Og, int T, int groups, int dgrad, int Csrc) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int red = dgrad ? Og : Cg, rows = dgrad ? Cg * groups : Og * groups;
   const int slots = (red + 31) / 32 * 32, kp = T * slots;

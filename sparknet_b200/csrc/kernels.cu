@@ -45,6 +45,7 @@ __device__ __forceinline__ float warp_max(float v) {
 // fill / axpy / split_add
 // ------------------------------------------------------------------------------------------
 __global__ void fill_kernel(size_t n4, size_t n, float4* __restrict__ p4, float* __restrict__ p, float v) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -59,6 +60,7 @@ void fill(cudaStream_t s, size_t n, float* p, float v) {
   count_launch();
 }
 __global__ void split_add_kernel(size_t n, const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ o) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     o[i] = a[i] + b[i];
@@ -68,6 +70,7 @@ void split_add(cudaStream_t s, size_t n, const float* a, const float* b, float* 
   count_launch();
 }
 __global__ void axpy_kernel(size_t n, float a, const float* __restrict__ x, float* __restrict__ y) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     y[i] = __fadd_rn(y[i], __fmul_rn(a, x[i]));
@@ -87,6 +90,7 @@ template <bool SIGNED>
 __global__ void __launch_bounds__(256) widen_bytes_kernel(size_t n, const uint4* __restrict__ src16, const uint8_t* __restrict__ src,
                                                           const float* __restrict__ mean, FastDiv ddiv, FastDiv dper, float scale,
                                                           float4* __restrict__ dst4, float* __restrict__ dst, int vec) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t n16 = vec ? n >> 4 : 0;                       // unaligned buffers: every element through the scalar tail loop
   auto one = [&](uint32_t byte, size_t i) -> float {
@@ -127,6 +131,7 @@ void widen_bytes(cudaStream_t s, size_t n, const uint8_t* src, bool is_signed, c
 __device__ __forceinline__ float relu1(float x, float slope) { return fmaxf(x, 0.f) + slope * fminf(x, 0.f); }
 __global__ void relu_fwd_kernel(size_t n4, size_t n, const float4* __restrict__ x4, float4* __restrict__ y4,
                                 const float* __restrict__ x, float* __restrict__ y, float slope) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t stride = (size_t)gridDim.x * blockDim.x, i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   for (size_t j = i; j < n4; j += stride) {
@@ -147,6 +152,7 @@ __device__ __forceinline__ float relu_g(float dy, float x, float slope) {
 __global__ void relu_bwd_kernel(size_t n4, size_t n, const float4* __restrict__ dy4, const float4* __restrict__ x4,
                                 float4* __restrict__ dx4, const float* __restrict__ dy, const float* __restrict__ x,
                                 float* __restrict__ dx, float slope) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t stride = (size_t)gridDim.x * blockDim.x, i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   for (size_t j = i; j < n4; j += stride) {
@@ -181,6 +187,7 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 __global__ void dropout_fwd_kernel(size_t n, const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ mask,
                                    uint32_t thres, float scale, bool draw, uint64_t seed, uint64_t offset,
                                    const unsigned long long* __restrict__ offset_dev) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const size_t n4 = (n + 3) / 4;
   if (offset_dev) offset = *offset_dev;          // per-iteration value published on the device (replayed graphs)
@@ -211,6 +218,7 @@ void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* ma
 }
 __global__ void dropout_bwd_kernel(size_t n, const float* __restrict__ dy, const uint8_t* __restrict__ mask,
                                    float* __restrict__ dx, float scale) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dx[i] = dy[i] * (float)mask[i] * scale;
@@ -280,6 +288,7 @@ __device__ __forceinline__ void pool_store_span(T* __restrict__ dst, size_t off,
 template <bool AVE>
 __global__ void __launch_bounds__(256) pool_fwd_tile_kernel(PoolGeom g, PoolTile t, FastDiv dPW, FastDiv dPH, const float* __restrict__ x,
                                                             float* __restrict__ y, int* __restrict__ mask) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   extern __shared__ __align__(16) float sm_pool[];
   const int HW = g.H * g.W, P = g.PH * g.PW;
@@ -404,6 +413,7 @@ static void pool_fwd_tile(cudaStream_t s, const PoolGeom& g, const float* x, flo
 template <int KH, int KW, int SH, int SW>
 __global__ void __launch_bounds__(256) pool_max_fwd_fixed_kernel(PoolGeom g, uint32_t total, FastDiv dPW, FastDiv dPH, const float* __restrict__ x,
                                                                  float* __restrict__ y, int* __restrict__ mask) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int HW = g.H * g.W;
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
@@ -451,6 +461,7 @@ template <bool AVE>
 __global__ void __launch_bounds__(256) pool_bwd_tile_kernel(PoolGeom g, PoolTile t, FastDiv dW, FastDiv dH, const float* __restrict__ dy,
                                                             const int* __restrict__ mask, const float* __restrict__ gate,
                                                             float* __restrict__ dx, int span_floats) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   extern __shared__ __align__(16) float sm_pool[];
   const int P = g.PH * g.PW, HW = g.H * g.W;
@@ -539,6 +550,7 @@ template <int KH, int KW, int SH, int SW>
 __global__ void __launch_bounds__(256) pool_max_bwd_fixed_kernel(PoolGeom g, uint32_t total, FastDiv dW, FastDiv dH, const float* __restrict__ dy,
                                                                  const int* __restrict__ mask, const float* __restrict__ gate,
                                                                  float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   constexpr int NH = (KH + SH - 1) / SH, NW = (KW + SW - 1) / SW;
   const int P = g.PH * g.PW;
@@ -577,6 +589,7 @@ __global__ void __launch_bounds__(256) pool_max_bwd_fixed_kernel(PoolGeom g, uin
 __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_kernel(PoolGeom g, uint32_t total, FastDiv dB, FastDiv dA, const float* __restrict__ dy,
                                                                  const int* __restrict__ mask, const float* __restrict__ gate,
                                                                  float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int P = g.PH * g.PW, HW = g.H * g.W;
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
@@ -630,6 +643,7 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_kernel(PoolGeom g, uin
 __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_strip_kernel(PoolGeom g, uint32_t total, FastDiv dB, int A, const float* __restrict__ dy,
                                                                        const int* __restrict__ mask, const float* __restrict__ gate,
                                                                        float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int P = g.PH * g.PW, HW = g.H * g.W;
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
@@ -690,6 +704,7 @@ template <int G, int DEPTH>
 __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g, uint32_t planes, int A, const float* __restrict__ dy,
                                                                      const int* __restrict__ mask, const float* __restrict__ gate,
                                                                      float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int P = g.PH * g.PW, HW = g.H * g.W;
   const int lane = threadIdx.x & 31, b = lane & (G - 1);
@@ -839,6 +854,7 @@ static int lrn_chunk() {
 template <int SIZE, int CH>
 __global__ void __launch_bounds__(128) lrn_across_fwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x, float* __restrict__ y,
                                                                    FlatOut fo, FastDiv dW) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   constexpr int PRE = (SIZE - 1) / 2;
   const int HW = g.H * g.W;
@@ -911,6 +927,7 @@ void lrn_across_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y, 
 template <int SIZE, int CH>
 __global__ void __launch_bounds__(128) lrn_across_bwd_chunk_kernel(LrnGeom g, int chunks, const float* __restrict__ x,
                                                                    const float* __restrict__ dy, float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   constexpr int PRE = (SIZE - 1) / 2;
   const int HW = g.H * g.W;
@@ -981,6 +998,7 @@ void lrn_across_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const floa
 // ------------------------------------------------------------------------------------------
 constexpr int kLrnWithinMaxPlane = 1024;
 __global__ void lrn_within_fwd_kernel(LrnGeom g, const float* __restrict__ x, float* __restrict__ y) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   __shared__ float xs[kLrnWithinMaxPlane];
   const int HW = g.H * g.W, pre = (g.size - 1) / 2;
@@ -1006,6 +1024,7 @@ void lrn_within_fwd(cudaStream_t s, const LrnGeom& g, const float* x, float* y) 
 }
 __global__ void lrn_within_bwd_kernel(LrnGeom g, const float* __restrict__ x, const float* __restrict__ dy,
                                       float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   __shared__ float xs[kLrnWithinMaxPlane], ps[kLrnWithinMaxPlane], qs[kLrnWithinMaxPlane];
   const int HW = g.H * g.W, pre = (g.size - 1) / 2;
@@ -1054,6 +1073,7 @@ void lrn_within_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const floa
 // ------------------------------------------------------------------------------------------
 __global__ void softmax_rows_kernel(int rows, int classes, const float* __restrict__ x, const float* __restrict__ label,
                                     float* __restrict__ prob, float* __restrict__ row_loss) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -1080,6 +1100,7 @@ __global__ void softmax_rows_kernel(int rows, int classes, const float* __restri
 // out[0] = (sum_i v[i]) / denom with a fixed-shape tree (deterministic)
 __global__ void reduce_rows_kernel(int n, const float* __restrict__ v, float denom, float* __restrict__ out,
                                    float* __restrict__ out2) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   __shared__ float sh[32];
   float acc = 0.f;
@@ -1106,6 +1127,7 @@ void softmax_loss_fwd(cudaStream_t s, int rows, int classes, const float* x, con
 }
 __global__ void softmax_loss_bwd_kernel(int rows, int classes, const float* __restrict__ prob, const float* __restrict__ label,
                                         const float* __restrict__ lw, float* __restrict__ dx) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const float scale = __fdiv_rn(lw[0], (float)rows);     // loss_weight / count   (softmax_loss_layer.cpp:110-116)
   const size_t total = (size_t)rows * classes;
@@ -1125,6 +1147,7 @@ void softmax_loss_bwd(cudaStream_t s, int rows, int classes, const float* prob, 
 // (value, index) pairs with std::greater, i.e. among equal values the larger index ranks first.
 __global__ void accuracy_rows_kernel(int rows, int classes, const float* __restrict__ x, const float* __restrict__ label,
                                      float* __restrict__ hit) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -1158,6 +1181,7 @@ void accuracy_top1(cudaStream_t s, int rows, int classes, const float* x, const 
 // fill the GPU: block (c, s) sums the images n = s, s+S, ...; a second tiny kernel adds the S partials of
 // each channel in ascending order.
 __global__ void conv_bias_grad_partial_kernel(int N, int C, int HW, int S, const float* __restrict__ dy, float* __restrict__ part) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   __shared__ float sh[32];
   const int c = blockIdx.x, s = blockIdx.y;
@@ -1176,6 +1200,7 @@ __global__ void conv_bias_grad_partial_kernel(int N, int C, int HW, int S, const
   }
 }
 __global__ void conv_bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -1194,6 +1219,7 @@ void conv_bias_grad(cudaStream_t s, int N, int C, int HW, const float* dy, float
   count_launch(2);
 }
 __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict__ dy, float* __restrict__ db, int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= cols) return;
@@ -1207,6 +1233,7 @@ __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict_
 // in row-group order (fixed order, no atomics).  cols % 4 == 0.
 __global__ void __launch_bounds__(256) ip_round_bias_kernel(int rows, int cols4, const float4* __restrict__ dy, float4* __restrict__ dy_r,
                                                             float* __restrict__ db, int accumulate) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   __shared__ float4 part[8][32];
   const int cx = threadIdx.x & 31, rg = threadIdx.x >> 5, c4 = blockIdx.x * 32 + cx;
@@ -1267,6 +1294,7 @@ __device__ __forceinline__ float round_tf32(float x) {
 }
 __global__ void sgd_update_kernel(size_t n4, float4* __restrict__ w, float4* __restrict__ g, float4* __restrict__ h, float4* __restrict__ shadow,
                                   const SgdChunk* __restrict__ table, float rate, float mu, const float* __restrict__ rate_dev) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   if (rate_dev) rate = *rate_dev;                // this iteration's learning rate, published on the device (replayed graphs)
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -1297,6 +1325,7 @@ void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, float* s
 // Per-iteration scalars that a replayed CUDA graph cannot take as kernel arguments (learning rate, dropout counters):
 // one tiny launch OUTSIDE the graph writes them into device memory, the kernels inside read them from there.
 __global__ void publish_step_scalars_kernel(StepScalars* dst, StepScalars v) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT(); *dst = v; }
 void publish_step_scalars(cudaStream_t s, StepScalars* dst, const StepScalars& v) {
   publish_step_scalars_kernel<<<1, 1, 0, s>>>(dst, v);
@@ -1309,6 +1338,7 @@ void publish_step_scalars(cudaStream_t s, StepScalars* dst, const StepScalars& v
 // one IEEE division by (float)N.
 // ------------------------------------------------------------------------------------------
 __global__ void average_replicas_kernel(const float* const* __restrict__ reps, int nrep, size_t n, float* __restrict__ out) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   const float denom = (float)nrep;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
@@ -1382,6 +1412,7 @@ __device__ bool wait_flags(const unsigned* mine, int base, int n, unsigned epoch
 template <int N>
 __global__ void __launch_bounds__(512) average_peers_kernel(PeerTable t, int rank, size_t count, unsigned epoch,
                                                             unsigned long long timeout_ns) {
+  SN_GRID_DEP_LAUNCH();
   SN_GRID_DEP_WAIT();
   unsigned* mine = t.flags[rank];
   __shared__ int ok;

@@ -1514,7 +1514,10 @@ static int make_edges_programmatic(cudaGraph_t graph) {
   static const bool enabled = !(getenv("SPARKNET_PDL") && atoi(getenv("SPARKNET_PDL")) == 0);
   if (!enabled) return 0;
   size_t n = 0;
-  if (cudaGraphGetEdges_v2(graph, nullptr, nullptr, nullptr, &n) != cudaSuccess || n == 0) { cudaGetLastError(); return 0; }
+  static const bool debug = getenv("SPARKNET_PDL_DEBUG") != nullptr;
+  cudaError_t e0 = cudaGraphGetEdges_v2(graph, nullptr, nullptr, nullptr, &n);
+  if (debug) fprintf(stderr, "sparknet pdl: %zu edges (%s)\n", n, cudaGetErrorString(e0));
+  if (e0 != cudaSuccess || n == 0) { cudaGetLastError(); return 0; }
   std::vector<cudaGraphNode_t> from(n), to(n);
   std::vector<cudaGraphEdgeData> ed(n);
   if (cudaGraphGetEdges_v2(graph, from.data(), to.data(), ed.data(), &n) != cudaSuccess) { cudaGetLastError(); return 0; }
@@ -1531,14 +1534,18 @@ static int make_edges_programmatic(cudaGraph_t graph) {
     prog.from_port = cudaGraphKernelNodePortProgrammatic;
     prog.to_port = 0;
     prog.type = cudaGraphDependencyTypeProgrammatic;
-    if (cudaGraphRemoveDependencies_v2(graph, &from[i], &to[i], &ed[i], 1) != cudaSuccess) { cudaGetLastError(); continue; }
-    if (cudaGraphAddDependencies_v2(graph, &from[i], &to[i], &prog, 1) != cudaSuccess) {
+    cudaError_t er = cudaGraphRemoveDependencies_v2(graph, &from[i], &to[i], &ed[i], 1);
+    if (er != cudaSuccess) { if (debug) fprintf(stderr, "sparknet pdl: remove edge %zu: %s\n", i, cudaGetErrorString(er)); cudaGetLastError(); continue; }
+    er = cudaGraphAddDependencies_v2(graph, &from[i], &to[i], &prog, 1);
+    if (er != cudaSuccess) {
+      if (debug) fprintf(stderr, "sparknet pdl: add programmatic edge %zu: %s\n", i, cudaGetErrorString(er));
       cudaGetLastError();
       SN_CUDA(cudaGraphAddDependencies_v2(graph, &from[i], &to[i], &ed[i], 1));     // put the full dependency back
       continue;
     }
     ++converted;
   }
+  if (debug) fprintf(stderr, "sparknet pdl: %d of %zu edges programmatic\n", converted, n);
   return converted;
 }
 void Solver::drop_graphs() {
