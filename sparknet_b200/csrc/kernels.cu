@@ -440,7 +440,8 @@ __global__ void __launch_bounds__(256) pool_max_fwd_fixed_kernel(PoolGeom g, uin
 }
 void pool_max_fwd(cudaStream_t s, const PoolGeom& g, const float* x, float* y, int* mask) {
   const size_t total = (size_t)g.N * g.C * g.PH * g.PW;
-  const bool fixed = g.ph == 0 && g.pw == 0 && total < (1ull << 31) && (size_t)g.N * g.C * g.H * g.W < (1ull << 31);
+  static const bool force_tile = getenv("SPARKNET_POOL_TILE") && atoi(getenv("SPARKNET_POOL_TILE")) == 1;   // experiments: every shape on the tile kernels
+  const bool fixed = !force_tile && g.ph == 0 && g.pw == 0 && total < (1ull << 31) && (size_t)g.N * g.C * g.H * g.W < (1ull << 31);
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
     pool_max_fwd_fixed_kernel<3, 3, 2, 2><<<grid_for(total, 256, 32), 256, 0, s>>>(g, (uint32_t)total, FastDiv((uint32_t)g.PW), FastDiv((uint32_t)g.PH), x, y, mask);
   } else if (fixed && g.kh == 2 && g.kw == 2 && g.sh == 2 && g.sw == 2) {
@@ -782,7 +783,8 @@ __global__ void __launch_bounds__(256) pool_max_bwd_3x3s2_row_kernel(PoolGeom g,
 }
 void pool_max_bwd(cudaStream_t s, const PoolGeom& g, const float* dy, const int* mask, float* dx, const float* gate) {
   const size_t total_in = (size_t)g.N * g.C * g.H * g.W;
-  const bool fixed = g.ph == 0 && g.pw == 0 && total_in < (1ull << 31);
+  static const bool force_tile = getenv("SPARKNET_POOL_TILE") && atoi(getenv("SPARKNET_POOL_TILE")) == 1;
+  const bool fixed = !force_tile && g.ph == 0 && g.pw == 0 && total_in < (1ull << 31);
   if (fixed && g.kh == 3 && g.kw == 3 && g.sh == 2 && g.sw == 2) {
     const int A = (g.H + 1) / 2, B = (g.W + 1) / 2;
     const size_t total = (size_t)g.N * g.C * A * B, strips = (size_t)g.N * g.C * B;
