@@ -265,6 +265,9 @@ def moved_bytes(layers, sizes, lf, lb):
             f, b = 8 * n_in, 12 * n_in
         elif t == "LRN":
             f, b = 8 * n_in, 12 * n_in                           # no scale tensor is kept
+            nxt = [m for m in layers[i + 1:] if l.top[0] in m.bottom]
+            if nxt and nxt[0].type == "Convolution" and getattr(l.lrn_param, "norm_region", 0) in (0, None):
+                f += 4 * n_in                                    # ... but the next convolution's packed input is written too
         elif t == "Dropout":
             f, b = 9 * n_in, 9 * n_in
         elif t == "SoftmaxWithLoss":

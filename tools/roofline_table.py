@@ -34,8 +34,10 @@ BW = {
     "pool2": (E * (elts(256, 27) + 2 * elts(256, 13)), E * (3 * elts(256, 13) + elts(256, 27)), "bwd includes relu2's backward"),
     "pool5": (E * (elts(256, 13) + 2 * elts(256, 6)), E * (3 * elts(256, 6) + elts(256, 13)), "bwd includes relu5's backward"),
     # LRN across channels without a stored scale tensor: fwd reads x writes y; bwd reads x, y, dy writes dx
-    "norm1": (E * 2 * elts(96, 27), E * 4 * elts(96, 27), "no scale tensor kept"),
-    "norm2": (E * 2 * elts(256, 13), E * 4 * elts(256, 13), "no scale tensor kept"),
+    # (round 2: the forward kernel also writes the next convolution's packed input, 4 B per element more;
+    #  the backward kernel recomputes y and reads x, dy only: 12 B per element)
+    "norm1": (E * 3 * elts(96, 27), E * 3 * elts(96, 27), "no scale tensor kept; forward also writes conv2's packed input"),
+    "norm2": (E * 3 * elts(256, 13), E * 3 * elts(256, 13), "no scale tensor kept; forward also writes conv3's packed input"),
     # dropout: fwd reads x writes y + byte mask; bwd reads dy + mask writes dx
     "drop6": (N * 4096 * (2 * E + 1), N * 4096 * (2 * E + 1), ""),
     "drop7": (N * 4096 * (2 * E + 1), N * 4096 * (2 * E + 1), ""),
