@@ -174,10 +174,13 @@ def cpu_reference_run(workload, steps, warmup, budget_s):
         net.close()
         return dt
 
-    cal = min(batch, 8)
-    t_img = run(cal, 1, 1) / cal                            # calibration: seconds per image
+    # calibration: seconds per iteration = a + b * images (the SGD update over the parameters does not depend on the batch)
+    b1, b2 = min(batch, 4), min(batch, 16)
+    t1, t2 = run(b1, 1, 1), run(b2, 1, 1)
+    per_img = max((t2 - t1) / max(b2 - b1, 1), 1e-9) if b2 > b1 else t1 / b1
+    fixed = max(t1 - per_img * b1, 0.0)
     total_steps = max(1, steps + warmup)
-    sample = int(max(1, min(batch, budget_s / max(t_img * total_steps, 1e-9))))
+    sample = int(max(1, min(batch, (budget_s / total_steps - fixed) / per_img)))
     dt = run(sample, warmup, steps)
     full = sample == batch
     return {"value": sample * steps / dt, "ms_per_step": dt / steps * 1e3, "cores": cores, "sample_batch": sample, "blas": blas,
