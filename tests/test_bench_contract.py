@@ -16,10 +16,7 @@ def test_reference_arm_prints_one_contract_line():
     assert len(lines) == 1
     d = json.loads(lines[0])
     assert d["impl"] == "reference" and d["unit"] == "images/s" and d["value"] > 0 and d["higher_is_better"] is True
-    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1
-    assert d["parity"]["ok"] is True and d["clocks"]["samples"] > 0 and not d["clocks"]["reasons"]
-    assert all(row["frac"] <= 1.0 for row in d["roofline_hbm"]["per_kernel"]) and 0 < d["roofline_hbm"]["frac"] <= 1.0
-    assert d["e2e_u8"]["h2d_bytes_per_step"] == 256 * (3 * 227 * 227) + 256 * 4 and d["cpu_baseline"]["value"] == d["value"]
+    assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["cores"] >= 1 and d["cpu_baseline"]["value"] == d["value"]
     assert d["e2e"] == {"value": d["value"], "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
     assert d["config"]["workload"].startswith("lenet") and d["steps"] == 2 and d["warmup"] == 1
 
