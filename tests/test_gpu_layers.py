@@ -142,6 +142,13 @@ POOL_CASES = [
     ((3, 32, 32, 32), dict(kernel_size=3, stride=2)),          # cifar pool1 (32 -> 16, ceil)
     ((2, 96, 55, 55), dict(kernel_size=3, stride=2)),          # CaffeNet pool1 (55 -> 27)
     ((2, 256, 13, 13), dict(kernel_size=3, stride=2)),         # CaffeNet pool5 (13 -> 6)
+    # the tile kernels' other regimes: planes too large for one shared-memory tile are cut into row bands ...
+    ((1, 3, 120, 100), dict(kernel_size=3, stride=2, pad=1)),  # 12000 floats per plane: bands, padded
+    ((2, 2, 90, 80), dict(kernel_size=5, stride=3)),           # window wider than the stride, ceil rule on both axes
+    ((1, 2, 70, 90), dict(kernel_h=70, kernel_w=90)),          # global pooling: one window = the whole plane
+    ((2, 3, 33, 35), dict(kernel_h=4, kernel_w=3, stride=1, pad=1)),   # stride 1: every input under up to 12 windows
+    ((3, 5, 7, 6), dict(kernel_size=2, stride=2, pad=1)),      # ... and many small planes per tile, odd sizes
+    ((1, 1, 200, 160), dict(kernel_size=2, stride=2, pad=1)),  # 2x2 / stride 2 WITH padding: not the fixed-shape kernel
 ]
 
 
@@ -220,6 +227,9 @@ def test_relu_fwd_bwd(oracle, product, shape):
     ((2, 256, 13, 13), 5, 1e-4, 0.75, False),                 # CaffeNet norm2
     ((3, 32, 16, 16), 3, 5e-5, 0.75, True),                   # cifar10_full norm1
     ((3, 32, 8, 8), 3, 5e-5, 0.75, True),                     # cifar10_full norm2
+    ((2, 20, 5, 6), 7, 1e-2, 0.75, False),                    # the chunk kernels' other window sizes (odd, up to 11) ...
+    ((2, 37, 4, 3), 9, 1e-2, 0.5, False),                     # ... with a channel count that is no multiple of the chunk
+    ((1, 11, 6, 6), 11, 1e-2, 1.25, False),                   # window as wide as the tensor is deep
 ])
 def test_lrn_fwd_bwd(oracle, product, shape, size, alpha, beta, within):
     x = (np.random.default_rng(1701).standard_normal(shape) * (30 if alpha < 1e-3 else 1)).astype(F)
