@@ -706,7 +706,7 @@ void tcw_conv_dgrad(cudaStream_t s, const ConvGeom& g, const float* dyflat, cons
 // ------------------------------------------------------------------------------------------
 __global__ void mat_reduce_kernel(const float* __restrict__ ws, int splits, size_t total, int N, const float* __restrict__ bias, int relu,
                                   float* __restrict__ out) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
     float acc = ws[i];
@@ -927,7 +927,7 @@ wgrad_window_kernel(const __grid_constant__ CUtensorMap tmDY, const __grid_const
 // dw[(co, c, tap)] (+)= sum over slices of ws[slice][(co, tap, c)], slices in ascending order
 __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
                                     int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < split_stride; i += (size_t)gridDim.x * blockDim.x) {
     // i walks the workspace layout (co, tap, c): coalesced reads
@@ -945,7 +945,7 @@ __global__ void wgrad_reduce_kernel(const float* __restrict__ ws, int splits, si
 // partial sums meet in a fixed butterfly (same order on every run).
 __global__ void wgrad_reduce_wide_kernel(const float* __restrict__ ws, int splits, size_t split_stride, int T, int Cg, float* __restrict__ dw,
                                          int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   const size_t i = t >> 3;
@@ -1254,7 +1254,7 @@ void tcw_s2d_pack_filter(cudaStream_t st, const ConvGeom& g, const float* w, flo
 // change with every SGD update, and eight 5-microsecond pack kernels per CaffeNet iteration are pure launch latency.
 // mode 0 / 1: tc_flat_pack_filter(dgrad = mode) layout; mode 2: the folded filter of s2d_pack_filter_kernel.
 __global__ void filter_pack_batch_kernel(const FilterPackBatch b) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const FilterPackJob& j = b.job[blockIdx.y];
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < j.total; i += (size_t)gridDim.x * blockDim.x) {
@@ -1312,7 +1312,7 @@ void tcw_filter_pack_batch(cudaStream_t st, const FilterPackBatch& b) {
 }
 // Channel-padded first layers (C < 16 padded to 16 on the flat grid): dw[co][c][tap] (+)= dws[co][c][tap] for the real channels
 __global__ void cpad_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int Cpad, int T, int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const int total = Cout * C * T;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -1330,7 +1330,7 @@ void tcw_cpad_unpack_wgrad(cudaStream_t st, const ConvGeom& g, int Cpad, const f
 // dw[co][c][ky][kx] (+)= dws[co][(c,dy,dx)][tap']  (the folded filter gradient, layout of tcw_conv_wgrad's output)
 __global__ void s2d_unpack_wgrad_kernel(const float* __restrict__ dws, float* __restrict__ dw, int Cout, int C, int kh, int kw, int s, int khs,
                                         int kws, int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)Cout * C * kh * kw;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {

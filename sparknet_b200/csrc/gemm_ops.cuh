@@ -35,6 +35,10 @@ struct ConvGeom {
     if (gridDim.x * gridDim.y * gridDim.z < 148u) asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); \
   } while (0)
 
+// Short helper kernels (slice reductions, rounding passes, bias-gradient partial sums ...: a few microseconds each) release
+// their successor at entry whatever their grid size.
+#define SN_GRID_DEP_LAUNCH_ALWAYS() asm volatile("griddepcontrol.launch_dependents;" ::: "memory")
+
 // Division by a runtime constant via float reciprocal-free 32-bit magic (exact for the ranges used
 // here: numerators < 2^31, divisors < 2^16).  Falls back to '/' on the host.
 struct FastDiv {

@@ -708,7 +708,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // deterministic slice reduction (ascending z) + the per-element epilogue of gemm_ops.cuh
 template <class E>
 __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -722,7 +722,7 @@ __global__ void tc_splitk_reduce_kernel(const float* __restrict__ ws, int splits
 // order, then the eight partial sums are combined in a fixed butterfly — still the same order on every run.
 template <class E>
 __global__ void tc_splitk_reduce_wide_kernel(const float* __restrict__ ws, int splits, int M, int N, E epi) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t total = (size_t)M * N;
   const size_t t = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -880,7 +880,7 @@ bool tc_available() { return true; }
 // Rounded (tf32, round-to-nearest) shadow copies of weight blobs for the TMA-fed operands.  Keyed by
 // the fp32 pointer; refreshed by tc_refresh_shadow whenever the runtime knows the weights changed.
 __global__ void round_tf32_kernel(size_t n, const float* __restrict__ src, float* __restrict__ dst) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = to_tf32_exact(src[i]);
 }
@@ -1057,7 +1057,7 @@ __global__ void __launch_bounds__(256) flat_pack_kernel(const float* __restrict_
 }
 // one warp per channel: lane l adds partials l, l + 32, ... in ascending order, then a fixed butterfly: deterministic
 __global__ void bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const int c = (int)((blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5), lane = threadIdx.x & 31;
   if (c >= C) return;

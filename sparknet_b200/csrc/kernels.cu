@@ -45,7 +45,7 @@ __device__ __forceinline__ float warp_max(float v) {
 // fill / axpy / split_add
 // ------------------------------------------------------------------------------------------
 __global__ void fill_kernel(size_t n4, size_t n, float4* __restrict__ p4, float* __restrict__ p, float v) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t stride = (size_t)gridDim.x * blockDim.x;
   size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -131,7 +131,7 @@ void widen_bytes(cudaStream_t s, size_t n, const uint8_t* src, bool is_signed, c
 __device__ __forceinline__ float relu1(float x, float slope) { return fmaxf(x, 0.f) + slope * fminf(x, 0.f); }
 __global__ void relu_fwd_kernel(size_t n4, size_t n, const float4* __restrict__ x4, float4* __restrict__ y4,
                                 const float* __restrict__ x, float* __restrict__ y, float slope) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t stride = (size_t)gridDim.x * blockDim.x, i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   for (size_t j = i; j < n4; j += stride) {
@@ -152,7 +152,7 @@ __device__ __forceinline__ float relu_g(float dy, float x, float slope) {
 __global__ void relu_bwd_kernel(size_t n4, size_t n, const float4* __restrict__ dy4, const float4* __restrict__ x4,
                                 float4* __restrict__ dx4, const float* __restrict__ dy, const float* __restrict__ x,
                                 float* __restrict__ dx, float slope) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t stride = (size_t)gridDim.x * blockDim.x, i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
   for (size_t j = i; j < n4; j += stride) {
@@ -187,7 +187,7 @@ __device__ __forceinline__ uint4 philox4x32_10(uint4 c, uint2 k) {
 __global__ void dropout_fwd_kernel(size_t n, const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ mask,
                                    uint32_t thres, float scale, bool draw, uint64_t seed, uint64_t offset,
                                    const unsigned long long* __restrict__ offset_dev) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const size_t n4 = (n + 3) / 4;
   if (offset_dev) offset = *offset_dev;          // per-iteration value published on the device (replayed graphs)
@@ -218,7 +218,7 @@ void dropout_fwd(cudaStream_t s, size_t n, const float* x, float* y, uint8_t* ma
 }
 __global__ void dropout_bwd_kernel(size_t n, const float* __restrict__ dy, const uint8_t* __restrict__ mask,
                                    float* __restrict__ dx, float scale) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
     dx[i] = dy[i] * (float)mask[i] * scale;
@@ -1075,7 +1075,7 @@ void lrn_within_bwd(cudaStream_t s, const LrnGeom& g, const float* x, const floa
 // ------------------------------------------------------------------------------------------
 __global__ void softmax_rows_kernel(int rows, int classes, const float* __restrict__ x, const float* __restrict__ label,
                                     float* __restrict__ prob, float* __restrict__ row_loss) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= rows) return;
@@ -1102,7 +1102,7 @@ __global__ void softmax_rows_kernel(int rows, int classes, const float* __restri
 // out[0] = (sum_i v[i]) / denom with a fixed-shape tree (deterministic)
 __global__ void reduce_rows_kernel(int n, const float* __restrict__ v, float denom, float* __restrict__ out,
                                    float* __restrict__ out2) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   __shared__ float sh[32];
   float acc = 0.f;
@@ -1129,7 +1129,7 @@ void softmax_loss_fwd(cudaStream_t s, int rows, int classes, const float* x, con
 }
 __global__ void softmax_loss_bwd_kernel(int rows, int classes, const float* __restrict__ prob, const float* __restrict__ label,
                                         const float* __restrict__ lw, float* __restrict__ dx) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const float scale = __fdiv_rn(lw[0], (float)rows);     // loss_weight / count   (softmax_loss_layer.cpp:110-116)
   const size_t total = (size_t)rows * classes;
@@ -1202,7 +1202,7 @@ __global__ void conv_bias_grad_partial_kernel(int N, int C, int HW, int S, const
   }
 }
 __global__ void conv_bias_grad_final_kernel(int C, int S, const float* __restrict__ part, float* __restrict__ db, int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= C) return;
@@ -1221,7 +1221,7 @@ void conv_bias_grad(cudaStream_t s, int N, int C, int HW, const float* dy, float
   count_launch(2);
 }
 __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict__ dy, float* __restrict__ db, int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   const int j = blockIdx.x * blockDim.x + threadIdx.x;
   if (j >= cols) return;
@@ -1235,7 +1235,7 @@ __global__ void ip_bias_grad_kernel(int rows, int cols, const float* __restrict_
 // in row-group order (fixed order, no atomics).  cols % 4 == 0.
 __global__ void __launch_bounds__(256) ip_round_bias_kernel(int rows, int cols4, const float4* __restrict__ dy, float4* __restrict__ dy_r,
                                                             float* __restrict__ db, int accumulate) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT();
   __shared__ float4 part[8][32];
   const int cx = threadIdx.x & 31, rg = threadIdx.x >> 5, c4 = blockIdx.x * 32 + cx;
@@ -1327,7 +1327,7 @@ void sgd_update(cudaStream_t s, size_t n, float* w, float* g, float* h, float* s
 // Per-iteration scalars that a replayed CUDA graph cannot take as kernel arguments (learning rate, dropout counters):
 // one tiny launch OUTSIDE the graph writes them into device memory, the kernels inside read them from there.
 __global__ void publish_step_scalars_kernel(StepScalars* dst, StepScalars v) {
-  SN_GRID_DEP_LAUNCH();
+  SN_GRID_DEP_LAUNCH_ALWAYS();
   SN_GRID_DEP_WAIT(); *dst = v; }
 void publish_step_scalars(cudaStream_t s, StepScalars* dst, const StepScalars& v) {
   publish_step_scalars_kernel<<<1, 1, 0, s>>>(dst, v);
