@@ -99,22 +99,53 @@ void Context::init() {
   numa_pin(*this);
   SN_CUDA(cudaStreamCreateWithFlags(&compute, cudaStreamNonBlocking));
   SN_CUDA(cudaStreamCreateWithFlags(&copy, cudaStreamNonBlocking));
+  SN_CUDA(cudaStreamCreateWithFlags(&side, cudaStreamNonBlocking));
+  SN_CUDA(cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming));
+  SN_CUDA(cudaEventCreateWithFlags(&ev_join, cudaEventDisableTiming));
   initialised = true;
 }
 void bump_config_epoch();
+static int g_ws_sel = 0;            // which scratch buffer get_workspace hands out: 1 while launches go to the side stream
 float* get_workspace(size_t nfloats) {
   Context& c = ctx();
-  if (nfloats > c.workspace_floats) {
+  const int k = g_ws_sel;
+  if (nfloats > c.workspace_floats[k]) {
     SN_CUDA(cudaStreamSynchronize(c.compute));
-    if (c.workspace) SN_CUDA(cudaFree(c.workspace));
-    size_t want = std::max(nfloats, c.workspace_floats * 2);
-    SN_CUDA(cudaMalloc(&c.workspace, want * sizeof(float)));
-    c.workspace_floats = want;
+    SN_CUDA(cudaStreamSynchronize(c.side));
+    if (c.workspace[k]) SN_CUDA(cudaFree(c.workspace[k]));
+    size_t want = std::max(nfloats, c.workspace_floats[k] * 2);
+    SN_CUDA(cudaMalloc(&c.workspace[k], want * sizeof(float)));
+    c.workspace_floats[k] = want;
     // recorded iterations (Solver::step) carry the old pointer in their split-reduction and bias-partial launches:
     // they must be recorded again
     bump_config_epoch();
   }
-  return c.workspace;
+  return c.workspace[k];
+}
+// Backward-filter on a side stream.  Inside solver_step the weight gradient of a layer is a leaf of the backward pass:
+// nothing reads it before the SGD update.  Its kernels (64 registers per thread, L2 / tensor bound) are queued on a second
+// stream that forks after the layer's top gradient is packed and joins in front of the update, so the compute stream goes
+// straight on to backward-data and to the pooling / LRN / pack kernels of the layers below (HBM bound, small CTAs), which
+// share the SMs with the backward-filter CTAs.  Own scratch buffer (the two streams' split-reduction slices and bias
+// partials are live at the same time).  SPARKNET_WGRAD_STREAM=0 keeps everything on the compute stream.
+static bool g_side_allowed = false;   // set by Solver::step around its iterations
+static cudaStream_t side_begin() {
+  Context& c = ctx();
+  static const bool enabled = !(getenv("SPARKNET_WGRAD_STREAM") && atoi(getenv("SPARKNET_WGRAD_STREAM")) == 0);
+  if (!enabled || !g_side_allowed) return c.compute;
+  SN_CUDA(cudaEventRecord(c.ev_fork, c.compute));
+  SN_CUDA(cudaStreamWaitEvent(c.side, c.ev_fork, 0));
+  c.side_used = true;
+  g_ws_sel = 1;
+  return c.side;
+}
+static void side_end() { g_ws_sel = 0; }
+static void side_join() {
+  Context& c = ctx();
+  if (!c.side_used) return;
+  SN_CUDA(cudaEventRecord(c.ev_join, c.side));
+  SN_CUDA(cudaStreamWaitEvent(c.compute, c.ev_join, 0));
+  c.side_used = false;
 }
 void count_launch(int n) { ctx().launches += n; }
 
@@ -701,9 +732,13 @@ struct ConvolutionLayer : Layer {
       if (!dyflat) dyflat = flat_alloc(gs.Cout);
       tc_flat_pack(S(), gs, true, dy, dyflat, want_db ? blobs[1]->diff->mutable_gpu() : nullptr, acc);
       if (!dws) SN_CUDA(cudaMalloc(&dws, (size_t)gs.Cout * gs.C * gs.kh * gs.kw * sizeof(float)));
-      tcw_conv_wgrad(S(), gs, packed_input(bottom[0]), dyflat, dws, false);
-      if (cpad()) tcw_cpad_unpack_wgrad(S(), g, gs.C, dws, blobs[0]->diff->mutable_gpu(), acc);
-      else tcw_s2d_unpack_wgrad(S(), g, dws, blobs[0]->diff->mutable_gpu(), acc);
+      const float* xin = packed_input(bottom[0]);                 // (current since the forward pass; before the fork if not)
+      float* dwp = blobs[0]->diff->mutable_gpu();
+      cudaStream_t ws = side_begin();
+      tcw_conv_wgrad(ws, gs, xin, dyflat, dws, false);
+      if (cpad()) tcw_cpad_unpack_wgrad(ws, g, gs.C, dws, dwp, acc);
+      else tcw_s2d_unpack_wgrad(ws, g, dws, dwp, acc);
+      side_end();
       if (pd[0]) {
         float* dx = bottom[0]->diff->mutable_gpu();
         tc_conv_dgrad(S(), g, dy, blobs[0]->data->gpu(), dx);
@@ -721,10 +756,13 @@ struct ConvolutionLayer : Layer {
     if (param_propagate_down[0]) {
       const float* x = bottom[0]->data->gpu();
       float* dw = blobs[0]->diff->mutable_gpu();
-      if (flat_w && use_window() && tcw_wgrad_supported(g)) tcw_conv_wgrad(S(), g, packed_input(bottom[0]), dyflat, dw, acc);
-      else if (flat_w) tc_conv_wgrad_flat(S(), g, packed_input(bottom[0]), dyflat, dw, acc);
-      else if (net->precision == PREC_TF32) tc_conv_wgrad(S(), g, x, dy, dw, acc);
-      else ffma_conv_wgrad(S(), g, x, dy, dw, acc);
+      const float* xin = flat_w ? packed_input(bottom[0]) : nullptr;
+      cudaStream_t ws = side_begin();
+      if (flat_w && use_window() && tcw_wgrad_supported(g)) tcw_conv_wgrad(ws, g, xin, dyflat, dw, acc);
+      else if (flat_w) tc_conv_wgrad_flat(ws, g, xin, dyflat, dw, acc);
+      else if (net->precision == PREC_TF32) tc_conv_wgrad(ws, g, x, dy, dw, acc);
+      else ffma_conv_wgrad(ws, g, x, dy, dw, acc);
+      side_end();
     }
     if (pd[0]) {
       const float* w = blobs[0]->data->gpu();
@@ -821,9 +859,12 @@ struct InnerProductLayer : Layer {
     }
     if (param_propagate_down[0]) {
       float* dw = blobs[0]->diff->mutable_gpu();
-      if (tma_w) tcw_matmul_wgrad(S(), M, N, K, dy_r, rounded_input(bottom[0]), dw, acc);
-      else if (tf32) tc_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
-      else ffma_ip_wgrad(S(), M, N, K, x, dy, dw, acc);
+      const float* xr = tma_w ? rounded_input(bottom[0]) : nullptr;
+      cudaStream_t ws = side_begin();
+      if (tma_w) tcw_matmul_wgrad(ws, M, N, K, dy_r, xr, dw, acc);
+      else if (tf32) tc_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
+      else ffma_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
+      side_end();
     }
     if (bias_term && param_propagate_down[1] && !bias_done) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
     if (pd[0]) {
@@ -1522,13 +1563,14 @@ static int make_edges_programmatic(cudaGraph_t graph) {
   std::vector<cudaGraphEdgeData> ed(n);
   if (cudaGraphGetEdges_v2(graph, from.data(), to.data(), ed.data(), &n) != cudaSuccess) { cudaGetLastError(); return 0; }
   // a kernel may have ONE programmatic predecessor; the captured iteration is a chain, anything else is left alone
-  std::map<cudaGraphNode_t, int> in_degree;
-  for (size_t i = 0; i < n; ++i) ++in_degree[to[i]];
+  // ... and a kernel with several successors (the fork to the backward-filter stream) keeps full dependencies
+  std::map<cudaGraphNode_t, int> in_degree, out_degree;
+  for (size_t i = 0; i < n; ++i) { ++in_degree[to[i]]; ++out_degree[from[i]]; }
   int converted = 0;
   for (size_t i = 0; i < n; ++i) {
     cudaGraphNodeType tf, tt;
     if (cudaGraphNodeGetType(from[i], &tf) != cudaSuccess || cudaGraphNodeGetType(to[i], &tt) != cudaSuccess) { cudaGetLastError(); continue; }
-    if (tf != cudaGraphNodeTypeKernel || tt != cudaGraphNodeTypeKernel || in_degree[to[i]] != 1) continue;
+    if (tf != cudaGraphNodeTypeKernel || tt != cudaGraphNodeTypeKernel || in_degree[to[i]] != 1 || out_degree[from[i]] != 1) continue;
     if (ed[i].type == cudaGraphDependencyTypeProgrammatic) continue;
     cudaGraphEdgeData prog{};
     prog.from_port = cudaGraphKernelNodePortProgrammatic;
@@ -1575,6 +1617,7 @@ void Solver::step(int iters) {
   uint64_t touch_seen = step_calls > 0 ? touch_at_exit : ~0ull;
   ++step_calls;
   g_in_step = true;
+  g_side_allowed = true;
   // every learnable blob's device copy must be current before the fused update touches the arena: host-written weights
   // go up in one copy of the pinned arena mirror
   // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
@@ -1648,6 +1691,7 @@ void Solver::step(int iters) {
         net->prepack_filters();
         net->forward_from_to(D, L - 1);
         net->backward_from_to(L - 1, 0);
+        side_join();                                           // the backward-filter stream rejoins before the update (and the end of the capture)
         sgd_update(cs, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum, &scalars_dev->rate);
         cudaError_t e = cudaStreamEndCapture(cs, &graph);
         GraphEntry g;
@@ -1681,6 +1725,7 @@ void Solver::step(int iters) {
       net->prepack_filters();
       net->forward_from_to(D, L - 1);
       net->backward_from_to(L - 1, 0);
+      side_join();
       if (param.display && iter % param.display == 0) {
         const float loss = net->total_loss();
         fprintf(stderr, "Iteration %d, loss = %g, lr = %g\n", iter, loss, rate);
@@ -1703,6 +1748,7 @@ void Solver::step(int iters) {
   net->overwrite_param_diffs = false;
   net->loss_log = nullptr;
   g_in_step = false;
+  g_side_allowed = false;
   touch_at_exit = g_outside_touch;
 }
 // One training iteration with CUDA events around every layer's forward and backward and around the

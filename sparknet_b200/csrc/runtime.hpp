@@ -31,8 +31,12 @@ struct Context {
   bool initialised = false;
   cudaStream_t compute = nullptr;   // all kernels
   cudaStream_t copy = nullptr;      // JavaData H2D staging
-  float* workspace = nullptr;
-  size_t workspace_floats = 0;
+  cudaStream_t side = nullptr;      // backward-filter kernels inside solver_step (see runtime.cpp side_begin)
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  bool side_used = false;           // work has been queued on `side` since the last join
+  // scratch: [0] for the compute stream, [1] for the side stream (they run concurrently)
+  float* workspace[2] = {nullptr, nullptr};
+  size_t workspace_floats[2] = {0, 0};
   long launches = 0;
   long param_d2h_copies = 0, param_h2d_copies = 0;   // bulk transfers between a parameter arena and its pinned mirror
   int numa_node = -1;               // NUMA node of the GPU (sysfs), -1 unknown
