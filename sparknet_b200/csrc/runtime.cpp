@@ -753,27 +753,37 @@ struct ConvolutionLayer : Layer {
     } else if (want_db) {
       conv_bias_grad(S(), g.N, g.Cout, g.Ho * g.Wo, dy, blobs[1]->diff->mutable_gpu(), acc);
     }
-    if (param_propagate_down[0]) {
-      const float* x = bottom[0]->data->gpu();
-      float* dw = blobs[0]->diff->mutable_gpu();
-      const float* xin = flat_w ? packed_input(bottom[0]) : nullptr;
-      cudaStream_t ws = side_begin();
-      if (flat_w && use_window() && tcw_wgrad_supported(g)) tcw_conv_wgrad(ws, g, xin, dyflat, dw, acc);
-      else if (flat_w) tc_conv_wgrad_flat(ws, g, xin, dyflat, dw, acc);
-      else if (net->precision == PREC_TF32) tc_conv_wgrad(ws, g, x, dy, dw, acc);
-      else ffma_conv_wgrad(ws, g, x, dy, dw, acc);
-      side_end();
-    }
-    if (pd[0]) {
-      const float* w = blobs[0]->data->gpu();
-      float* dx = bottom[0]->diff->mutable_gpu();
-      const float* gate = gate_relu ? bottom[0]->data->gpu() : nullptr;       // y of the in-place ReLU below (y > 0 <=> x > 0)
-      if (flat_d && use_window()) { tcw_conv_dgrad(S(), g, dyflat, packed_filter(true), dx, gate); gate = nullptr; }
-      else if (flat_d) tc_conv_dgrad_flat(S(), g, dyflat, packed_filter(true), dx);
-      else if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
-      else ffma_conv_dgrad(S(), g, dy, w, dx);
-      if (gate) relu_bwd(S(), bottom[0]->count(), dx, gate, dx, 0.f);          // paths without a gating epilogue
-    }
+    // Backward-filter is a leaf (the side stream runs it, side_begin); backward-data is on the critical path of the layers
+    // below.  Large layers, whose kernels each fill the GPU: backward-data first, so that backward-filter then shares the SMs
+    // with the pooling / LRN / pack kernels that follow.  Small layers (LeNet: neither kernel fills the GPU): backward-filter
+    // is released first and runs beside backward-data.  Measured both ways on the four nets.
+    const bool wgrad_first = 2.0 * g.N * g.Ho * g.Wo * (double)g.Cout * g.Cg() * g.kh * g.kw < 4e8;
+    auto run_dgrad = [&] {
+      if (pd[0]) {
+        const float* w = blobs[0]->data->gpu();
+        float* dx = bottom[0]->diff->mutable_gpu();
+        const float* gate = gate_relu ? bottom[0]->data->gpu() : nullptr;       // y of the in-place ReLU below (y > 0 <=> x > 0)
+        if (flat_d && use_window()) { tcw_conv_dgrad(S(), g, dyflat, packed_filter(true), dx, gate); gate = nullptr; }
+        else if (flat_d) tc_conv_dgrad_flat(S(), g, dyflat, packed_filter(true), dx);
+        else if (net->precision == PREC_TF32) tc_conv_dgrad(S(), g, dy, w, dx);
+        else ffma_conv_dgrad(S(), g, dy, w, dx);
+        if (gate) relu_bwd(S(), bottom[0]->count(), dx, gate, dx, 0.f);          // paths without a gating epilogue
+      }
+    };
+    auto run_wgrad = [&] {
+      if (param_propagate_down[0]) {
+        const float* x = bottom[0]->data->gpu();
+        float* dw = blobs[0]->diff->mutable_gpu();
+        const float* xin = flat_w ? packed_input(bottom[0]) : nullptr;
+        cudaStream_t ws = side_begin();
+        if (flat_w && use_window() && tcw_wgrad_supported(g)) tcw_conv_wgrad(ws, g, xin, dyflat, dw, acc);
+        else if (flat_w) tc_conv_wgrad_flat(ws, g, xin, dyflat, dw, acc);
+        else if (net->precision == PREC_TF32) tc_conv_wgrad(ws, g, x, dy, dw, acc);
+        else ffma_conv_wgrad(ws, g, x, dy, dw, acc);
+        side_end();
+      }
+    };
+    if (wgrad_first) { run_wgrad(); run_dgrad(); } else { run_dgrad(); run_wgrad(); }
   }
 };
 
@@ -857,22 +867,28 @@ struct InnerProductLayer : Layer {
         tc_round_to_tf32(S(), (size_t)M * N, dy, dy_r);
       }
     }
-    if (param_propagate_down[0]) {
-      float* dw = blobs[0]->diff->mutable_gpu();
-      const float* xr = tma_w ? rounded_input(bottom[0]) : nullptr;
-      cudaStream_t ws = side_begin();
-      if (tma_w) tcw_matmul_wgrad(ws, M, N, K, dy_r, xr, dw, acc);
-      else if (tf32) tc_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
-      else ffma_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
-      side_end();
-    }
     if (bias_term && param_propagate_down[1] && !bias_done) ip_bias_grad(S(), M, N, dy, blobs[1]->diff->mutable_gpu(), acc);
-    if (pd[0]) {
-      float* dx = bottom[0]->diff->mutable_gpu();
-      if (tma_d) tcw_matmul(S(), M, K, N, dy_r, weights_tf32(), true, nullptr, false, dx);
-      else if (tf32) tc_ip_dgrad(S(), M, N, K, dy, weights_tf32(), dx);
-      else ffma_ip_dgrad(S(), M, N, K, dy, blobs[0]->data->gpu(), dx);
-    }
+    const bool wgrad_first = 2.0 * M * (double)N * K < 4e8;          // see ConvolutionLayer::backward
+    auto run_dgrad = [&] {
+      if (pd[0]) {
+        float* dx = bottom[0]->diff->mutable_gpu();
+        if (tma_d) tcw_matmul(S(), M, K, N, dy_r, weights_tf32(), true, nullptr, false, dx);
+        else if (tf32) tc_ip_dgrad(S(), M, N, K, dy, weights_tf32(), dx);
+        else ffma_ip_dgrad(S(), M, N, K, dy, blobs[0]->data->gpu(), dx);
+      }
+    };
+    auto run_wgrad = [&] {
+      if (param_propagate_down[0]) {
+        float* dw = blobs[0]->diff->mutable_gpu();
+        const float* xr = tma_w ? rounded_input(bottom[0]) : nullptr;
+        cudaStream_t ws = side_begin();
+        if (tma_w) tcw_matmul_wgrad(ws, M, N, K, dy_r, xr, dw, acc);
+        else if (tf32) tc_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
+        else ffma_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
+        side_end();
+      }
+    };
+    if (wgrad_first) { run_wgrad(); run_dgrad(); } else { run_dgrad(); run_wgrad(); }
   }
 };
 
