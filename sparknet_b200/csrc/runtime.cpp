@@ -738,6 +738,7 @@ struct ConvolutionLayer : Layer {
       tcw_conv_wgrad(ws, gs, xin, dyflat, dws, false);
       if (cpad()) tcw_cpad_unpack_wgrad(ws, g, gs.C, dws, dwp, acc);
       else tcw_s2d_unpack_wgrad(ws, g, dws, dwp, acc);
+      if (ws != S() && !pd[0] && net->on_param_grads_ready) net->on_param_grads_ready(this);   // (this path runs backward-data, if any, afterwards)
       side_end();
       if (pd[0]) {
         float* dx = bottom[0]->diff->mutable_gpu();
@@ -780,6 +781,7 @@ struct ConvolutionLayer : Layer {
         else if (flat_w) tc_conv_wgrad_flat(ws, g, xin, dyflat, dw, acc);
         else if (net->precision == PREC_TF32) tc_conv_wgrad(ws, g, x, dy, dw, acc);
         else ffma_conv_wgrad(ws, g, x, dy, dw, acc);
+        if (ws != S() && !wgrad_first && net->on_param_grads_ready) net->on_param_grads_ready(this);
         side_end();
       }
     };
@@ -885,6 +887,7 @@ struct InnerProductLayer : Layer {
         if (tma_w) tcw_matmul_wgrad(ws, M, N, K, dy_r, xr, dw, acc);
         else if (tf32) tc_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
         else ffma_ip_wgrad(ws, M, N, K, x, dy, dw, acc);
+        if (ws != S() && !wgrad_first && net->on_param_grads_ready) net->on_param_grads_ready(this);
         side_end();
       }
     };
@@ -1539,6 +1542,7 @@ Solver::Solver(const cp::SolverParameter& p) : param(p) {
     SN_CUDA(cudaMalloc(&chunk_table, table.size() * sizeof(SgdChunk)));
     SN_CUDA(cudaMemcpy(chunk_table, table.data(), table.size() * sizeof(SgdChunk), cudaMemcpyHostToDevice));
   }
+  for (size_t i = 0; i < net->learnable_params.size(); ++i) param_index[net->learnable_params[i]] = i;
   SN_CUDA(cudaMalloc(&loss_hist, (kLossHist + 1) * sizeof(float)));      // last slot: the loss of a replayed iteration
   SN_CUDA(cudaMemset(loss_hist, 0, (kLossHist + 1) * sizeof(float)));
   SN_CUDA(cudaMalloc(&scalars_dev, sizeof(StepScalars)));
@@ -1611,6 +1615,37 @@ void Solver::drop_graphs() {
   graphs.clear();
   eager_iters = 0;
 }
+void Solver::update_layer_early(Layer* l) {
+  // the layer's blobs sit next to each other in the arena (weights, then bias, each on a 1024-float boundary)
+  size_t lo = ~(size_t)0, hi = 0;
+  for (auto& b : l->blobs) {
+    auto it = param_index.find(b.get());
+    if (it == param_index.end() || sgd_done[it->second]) return;
+    const size_t off = net->param_offsets[it->second], len = (b->count() + 1023) / 1024 * 1024;
+    lo = std::min(lo, off);
+    hi = std::max(hi, off + len);
+  }
+  size_t covered = 0;
+  for (auto& b : l->blobs) covered += (b->count() + 1023) / 1024 * 1024;
+  if (hi <= lo || covered != hi - lo) return;                     // not contiguous: leave it to update_rest
+  sgd_update(ctx().side, hi - lo, net->arena_w + lo, net->arena_g + lo, arena_h + lo, net->arena_s + lo, chunk_table + lo / 1024, 0.f,
+             param.momentum, &scalars_dev->rate);
+  for (auto& b : l->blobs) sgd_done[param_index[b.get()]] = 1;
+}
+void Solver::update_rest(cudaStream_t s) {
+  const size_t n = net->learnable_params.size();
+  size_t i = 0;
+  while (i < n) {
+    if (sgd_done[i]) { ++i; continue; }
+    size_t j = i;
+    while (j < n && !sgd_done[j]) ++j;
+    const size_t lo = net->param_offsets[i], hi = j < n ? net->param_offsets[j] : net->arena_floats;
+    sgd_update(s, hi - lo, net->arena_w + lo, net->arena_g + lo, arena_h + lo, net->arena_s + lo, chunk_table + lo / 1024, 0.f, param.momentum,
+               &scalars_dev->rate);
+    i = j;
+  }
+  std::fill(sgd_done.begin(), sgd_done.end(), 0);
+}
 float Solver::get_learning_rate() {   // sgd_solver.cpp:27-63, same expression types
   const string& pol = param.lr_policy;
   float rate = 0.f;
@@ -1634,6 +1669,11 @@ void Solver::step(int iters) {
   ++step_calls;
   g_in_step = true;
   g_side_allowed = true;
+  {
+    static const bool early = !(getenv("SPARKNET_SGD_EARLY") && atoi(getenv("SPARKNET_SGD_EARLY")) == 0);
+    sgd_done.assign(net->learnable_params.size(), 0);
+    if (early) net->on_param_grads_ready = [this](Layer* l) { update_layer_early(l); };
+  }
   // every learnable blob's device copy must be current before the fused update touches the arena: host-written weights
   // go up in one copy of the pinned arena mirror
   // (a blob whose device copy is already the newest keeps its generation: its tf32 shadow / packed copies stay valid)
@@ -1708,7 +1748,7 @@ void Solver::step(int iters) {
         net->forward_from_to(D, L - 1);
         net->backward_from_to(L - 1, 0);
         side_join();                                           // the backward-filter stream rejoins before the update (and the end of the capture)
-        sgd_update(cs, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum, &scalars_dev->rate);
+        update_rest(cs);
         cudaError_t e = cudaStreamEndCapture(cs, &graph);
         GraphEntry g;
         if (e == cudaSuccess && graph) {
@@ -1746,7 +1786,7 @@ void Solver::step(int iters) {
         const float loss = net->total_loss();
         fprintf(stderr, "Iteration %d, loss = %g, lr = %g\n", iter, loss, rate);
       }
-      if (net->arena_floats) sgd_update(cs, net->arena_floats, net->arena_w, net->arena_g, arena_h, net->arena_s, chunk_table, rate, param.momentum, &scalars_dev->rate);
+      if (net->arena_floats) update_rest(cs);
       // this iteration's loss goes to the pinned host ring too: 4 bytes, asynchronous, read after the caller's next sync
       SN_CUDA(cudaMemcpyAsync(loss_hist_host + (iter % kLossHist), loss_hist + (iter % kLossHist), sizeof(float), cudaMemcpyDeviceToHost, cs));
       ++eager_iters;
@@ -1765,6 +1805,7 @@ void Solver::step(int iters) {
   net->loss_log = nullptr;
   g_in_step = false;
   g_side_allowed = false;
+  net->on_param_grads_ready = nullptr;
   touch_at_exit = g_outside_touch;
 }
 // One training iteration with CUDA events around every layer's forward and backward and around the

@@ -8,6 +8,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <functional>
 #include <map>
 #include <memory>
 #include <set>
@@ -143,6 +144,9 @@ struct Net {
   int phase;
   int precision = PREC_FFMA;
   bool overwrite_param_diffs = false;   // true inside solver_step: weight gradients overwrite (ClearParamDiffs folded away)
+  // set by Solver::step: called by a layer right after it queued its backward-filter on the side stream, when everything
+  // that reads the layer's weights in this iteration has been queued before the fork (Solver::update_layer_early)
+  std::function<void(Layer*)> on_param_grads_ready;
   float* loss_log = nullptr;            // device slot for this iteration's loss (solver-owned), or null
   uint64_t rng_seed = 0;
   std::vector<std::shared_ptr<Layer>> layers;
@@ -217,6 +221,13 @@ struct Solver {
   float get_learning_rate();
   void step(int iters);
   void step_profiled(std::vector<float>* fwd_ms, std::vector<float>* bwd_ms, float* update_ms);
+  // SGD update of ONE layer's parameters on the side stream, behind its backward-filter: the update of the big inner-product
+  // layers (fc6 alone is 62 % of CaffeNet's parameters) then runs under the backward pass of the layers below instead of
+  // after it.  sgd_done marks the parameters already updated in this iteration; update_rest finishes the others.
+  std::map<const Blob*, size_t> param_index;
+  std::vector<char> sgd_done;
+  void update_layer_early(Layer* l);
+  void update_rest(cudaStream_t s);
   std::vector<int> profile_launches_fwd, profile_launches_bwd;   // kernels each layer launched in the last profiled iteration
   void test_and_store(int num_steps, std::vector<float>* score);
 };
