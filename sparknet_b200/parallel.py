@@ -233,7 +233,11 @@ class HostAverager:
                 dist.broadcast(t, src=0)
         self.net.setWeights(w)
 
-    def average(self) -> float:
+    def drain(self) -> float:
+        return 0.0
+
+    def average(self, sync: bool = True) -> float:
+        """Same call shape as PeerAverager.average; the host path is synchronous either way."""
         if self.world == 1:
             return 0.0
         import torch
@@ -253,6 +257,7 @@ def run_rounds(net, averager, tau: int, rounds: int) -> None:
     (broadcast/set weights) -> train(tau) -> average, `rounds` times."""
     for _ in range(rounds):
         net.train(tau)
-        averager.average()
+        averager.average(sync=False)      # enqueue only where the averager can: the next round's first callback runs under it
+    averager.drain()
     if hasattr(averager, "check"):
         averager.check()
